@@ -1,0 +1,173 @@
+/* nmpc_b200.h -- C ABI of the B200-native batched quadruped NMPC solver (libnmpc_b200.so).
+ *
+ * Drop-in boundary for the one hot path of Atarilab/iterative_learning_NMPC:
+ *   QuadrupedAcadosSolver.init()/solve()   (mpc_controller/utils/solver.py:356-429)
+ * which, in the reference, goes through the missing `contact_tamp` class AcadosSolverHelper
+ * (solver.py:7-8,15) -> acados_template.AcadosOcpSolver -> ctypes -> generated C solver
+ * (acados SQP / SQP_RTI + HPIPM + BLASFEO + CasADi-generated model code).
+ *
+ * Every entry point names the reference interface it replaces.  All arrays are fp64, C order,
+ * batch-first; pointers may be HOST or DEVICE (detected with cudaPointerGetAttributes); no torch
+ * types cross this boundary.  A handle is single-caller; distinct handles are independent.
+ * Return value: 0 on success, a negative NMPC_E* code for API misuse, a positive cudaError_t
+ * for CUDA failures.  Per-problem solver outcome is reported in status[B] with acados numbering
+ * (0 success, 1 NaN, 2 max-iter, 3 min-step, 4 QP failure).
+ *
+ * Fixed problem dimensions of this build (Go2 topology):
+ *   nx = 42  x = [q(18) | v(18) | h(6)]                    (solver.py:185-187)
+ *   nu = 30  u = [a(18) | f_FL(3) f_FR(3) f_RL(3) f_RR(3)] (solver.py:311-336,411-421)
+ *   np = 44  per node, per foot: active, plane_point(3), plane_normal(3), p_gain, restrict,
+ *            range_radius, peak                            (solver.py:212-252)
+ *   ny = 76  y   = [base(12) | joint(24) | acc(12) | swing(4) | f_reg(4x3) | pos_cost(4x3)]
+ *   nye= 52  y_e = [base(12) | joint(24) | swing(4) | pos_cost(4x3)]   (solver.py:108-141)
+ *   ng = 42  g   = [friction 4x5 | contact 4x3 | patch 4x1 | centroidal consistency 6]
+ */
+#ifndef NMPC_B200_H
+#define NMPC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NMPC_NX 42
+#define NMPC_NU 30
+#define NMPC_NZ 72
+#define NMPC_NP 44
+#define NMPC_NY 76
+#define NMPC_NYE 52
+#define NMPC_NG 42
+#define NMPC_NP_FOOT 11
+#define NMPC_MAX_NODES 64
+
+/* error codes (negative); positive returns are cudaError_t */
+#define NMPC_OK 0
+#define NMPC_EINVAL (-1)   /* bad argument / null pointer */
+#define NMPC_ENOSYS (-2)   /* option not available in this build */
+#define NMPC_ENODEV (-3)   /* no CUDA device / wrong architecture */
+#define NMPC_ENOMEM (-4)
+
+/* per-problem solver status, acados numbering */
+#define NMPC_STATUS_SUCCESS 0
+#define NMPC_STATUS_NAN 1
+#define NMPC_STATUS_MAXITER 2
+#define NMPC_STATUS_MINSTEP 3
+#define NMPC_STATUS_QP_FAILURE 4
+
+/* HPIPM_MODE as used by MPCOptConfig.hpipm_mode (config/config_abstract.py:5,64) */
+#define NMPC_HPIPM_SPEED_ABS 0
+#define NMPC_HPIPM_SPEED 1
+#define NMPC_HPIPM_BALANCE 2
+#define NMPC_HPIPM_ROBUST 3
+
+typedef struct nmpc_handle nmpc_handle;
+
+/* Solver options.  Replaces AcadosSolverHelper.setup(recompile, use_cython, real_time_it,
+ * max_qp_iter, hpipm_mode) and set_max_iter / set_warm_start_inner_qp / set_warm_start_nlp /
+ * set_qp_tol / set_nlp_tol (solver.py:68-79; also mpc.py:464-473). */
+typedef struct nmpc_opts {
+    int32_t n_nodes;          /* N, shooting intervals (MPCOptConfig.n_nodes = 25)          */
+    int32_t max_iter;         /* SQP iterations (1; 15 on the first tick, mpc.py:465-467)   */
+    int32_t max_qp_iter;      /* IPM iterations per QP (6, mpc_opt.py:27)                   */
+    int32_t real_time_it;     /* 1: SQP_RTI (one linearise + one QP + full step)            */
+    int32_t warm_start_qp;    /* 0 cold, 1 primal (+pi) from previous QP, 2 also lam/t      */
+    int32_t warm_start_nlp;   /* kept for API parity; the iterate always lives in the handle */
+    int32_t hpipm_mode;       /* NMPC_HPIPM_*; this build implements SPEED                  */
+    int32_t enable_time_opt;  /* must be 0 in this build (nu = 30)                          */
+    double dt_nodes;          /* MPCOptConfig.get_dt_nodes()                                */
+    double dt_min, dt_max;    /* MPCOptConfig.get_dt_bounds(); unused unless time-opt       */
+    double nlp_tol;           /* SQP exit: all four residual inf-norms below (1e-1)         */
+    double qp_tol;            /* IPM exit: all four residual inf-norms below (1e-2)         */
+    double reg_eps, reg_eps_e;/* Levenberg-Marquardt terms (MPCCostConfig.reg_eps[_e])      */
+    double mu_contact;        /* friction coefficient (0.8 hard-coded at solver.py:38)      */
+} nmpc_opts;
+
+/* Per-problem statistics of the last nmpc_solve (acados print_stats / get_stats equivalent). */
+typedef struct nmpc_stats {
+    int32_t* sqp_iter;   /* [B]   SQP iterations performed                          */
+    int32_t* qp_iter;    /* [B]   IPM iterations of the last QP                     */
+    int32_t* qp_status;  /* [B]   HPIPM numbering: 0 ok, 1 max-iter, 2 min-step, 3 NaN */
+    double* res;         /* [B,4] NLP residual inf-norms stat, eq, ineq, comp at the last linearisation */
+    double* qp_res;      /* [B,4] QP residual inf-norms at IPM exit                 */
+    double* cost;        /* [B]   NLS cost at the last linearisation point          */
+} nmpc_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------- */
+/* AcadosSolverHelper.__init__ + setup() (solver.py:49-55,68-72).  NULL on failure; *err (may
+ * be NULL) receives the code. */
+nmpc_handle* nmpc_create(const nmpc_opts* opts, int32_t batch, int32_t device, int32_t* err);
+void nmpc_destroy(nmpc_handle* h);
+int nmpc_set_opts(nmpc_handle* h, const nmpc_opts* opts);        /* set_max_iter ... set_nlp_tol */
+int nmpc_get_dims(const nmpc_handle* h, int32_t* batch, int32_t* n_nodes);
+int nmpc_stream(const nmpc_handle* h, void** cuda_stream);        /* the handle's own stream */
+
+/* ---- problem data (QuadrupedAcadosSolver.init, solver.py:356-394) --------------------- */
+/* setup_initial_state + set_initial_state (solver.py:179-192).  qv = [B,36] (q_euler | v);
+ * the centroidal momentum h0 = hg(q,v) (dynamics.py:48-50, pin.computeCentroidalMomentum) is
+ * evaluated on the device.  Also overwrites node 0 of the iterate with x0. */
+int nmpc_set_x0(nmpc_handle* h, const double* qv);
+/* same, but the caller supplies the full state [B,42] including h */
+int nmpc_set_x0_full(nmpc_handle* h, const double* x0);
+/* update_ref + set_ref_terminal (solver.py:352-353): yref [B,N,76], yref_e [B,52] */
+int nmpc_set_yref(nmpc_handle* h, const double* yref, const double* yref_e);
+/* set_cost_weight_constant / set_cost_weight_terminal / update_cost_weights (solver.py:85,
+ * 140-141): diagonal weights; per_problem=0 -> W [76], W_e [52] broadcast; 1 -> [B,76],[B,52] */
+int nmpc_set_weights(nmpc_handle* h, const double* W, const double* W_e, int32_t per_problem);
+/* update_parameters (solver.py:351): p [B,N+1,44] */
+int nmpc_set_params(nmpc_handle* h, const double* p);
+/* setup_initial_feet_pos (solver.py:194-210) done on the device: for every foot whose node-0
+ * `active` is 1 (forced to 1 where i_node[b]==0), plane_point[:, :next_swing] = FK foot position
+ * of the current x0.  i_node [B] int32 (host or device). Call after set_params and set_x0. */
+int nmpc_pin_stance_feet(nmpc_handle* h, const int32_t* i_node);
+/* update_states / update_inputs (solver.py:349-350): overwrite the iterate.  x [B,N+1,42] and/or
+ * u [B,N,30]; either may be NULL. */
+int nmpc_set_guess(nmpc_handle* h, const double* x, const double* u);
+/* warm_start_solver + warm_start_multipliers (solver.py:290-342): shift the stored iterate of
+ * problem b by start_node[b] nodes (states 1.., inputs, duals), zero the force tail (or repeat
+ * the last node when repeat_last). start_node [B] int32. */
+int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, int32_t repeat_last);
+/* forget duals and the stored QP solution (AcadosSolverHelper.reset-like) */
+int nmpc_reset_duals(nmpc_handle* h);
+
+/* ---- solve (AcadosSolverHelper.solve, called at solver.py:402) ------------------------ */
+/* Enqueues the whole SQP / SQP_RTI solve on the handle's stream and, if status != NULL, copies
+ * the per-problem status [B] back and synchronises.  status may be host or device. */
+int nmpc_solve(nmpc_handle* h, int32_t* status);
+int nmpc_synchronize(nmpc_handle* h);
+
+/* ---- results (parse_sol, solver.py:403-429) ------------------------------------------- */
+/* x [B,N+1,42], u [B,N,30], pi [B,N,42] (multiplier of x_{k+1} = phi(x_k,u_k)),
+ * lam [B,N+1,84] (lower | upper multipliers of g).  Any pointer may be NULL. */
+int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* pi, double* lam);
+int nmpc_get_stats(nmpc_handle* h, nmpc_stats* stats);
+/* QP step of the last SQP iteration: dz [B,N+1,72] ([du|dx] per node; du of node N is 0) */
+int nmpc_get_qp_step(nmpc_handle* h, double* dz);
+
+/* ---- kinematics helper (QuadrupedDynamics.update_pin/get_feet_position_w, dynamics.py:48-50,
+ * 101-107; pin.centerOfMass at mpc.py:339) ---------------------------------------------- */
+/* qv [n,36] -> feet [n,4,3], com [n,3], hg [n,6]; outputs may be NULL. */
+int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, double* feet, double* com, double* hg);
+
+/* ---- test / diagnostics hooks (parity tests compare these with the oracle) ------------ */
+/* Linearise at the current iterate without solving and export the dense OCP-QP:
+ * BAbt [B,N,73,42] (rows: B^T(30) | A^T(42) | b^T), RSQrq [B,N+1,73,72] (lower part valid; last
+ * row = gradient), DCt [B,N+1,72,42], lg/ug [B,N+1,42], mask [B,N+1,84].  NULLs skipped. */
+int nmpc_export_qp(nmpc_handle* h, double* BAbt, double* RSQrq, double* DCt,
+                   double* lg, double* ug, double* mask);
+/* Solve externally supplied OCP-QPs (same layouts as nmpc_export_qp) with the device IPM;
+ * dx0 [B,42]; outputs dz [B,N+1,72], pi [B,N,42], lam [B,N+1,84], t [B,N+1,84],
+ * qp_iter/qp_status [B] int32.  Cold start (warm_start 0). */
+int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const double* DCt,
+                  const double* lg, const double* ug, const double* mask, const double* dx0,
+                  double* dz, double* pi, double* lam, double* t,
+                  int32_t* qp_iter, int32_t* qp_status);
+
+/* number of kernels launched by the handle since creation (bench.py's gpu_launches claim) */
+int64_t nmpc_launch_count(const nmpc_handle* h);
+const char* nmpc_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NMPC_B200_H */

@@ -1,0 +1,184 @@
+"""`NmpcSolver`: thin Python object over the C ABI handle (one batch of B OCPs on one GPU)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import _lib as L
+from ._lib import NG, NP, NU, NX, NY, NYE, NZ, NmpcOpts, NmpcStats, check, default_opts, ptr
+
+
+def _f64(a, shape):
+    if hasattr(a, "data_ptr"):           # torch tensor (host or device): must already be fp64
+        import torch
+        assert a.dtype == torch.float64, "fp64 tensors required"
+        return a.contiguous().reshape(shape)
+    return np.ascontiguousarray(a, dtype=np.float64).reshape(shape)
+
+
+def _i32(a, shape):
+    if hasattr(a, "data_ptr"):
+        import torch
+        assert a.dtype == torch.int32
+        return a.contiguous().reshape(shape)
+    return np.ascontiguousarray(np.broadcast_to(np.asarray(a), shape), dtype=np.int32)
+
+
+class NmpcSolver:
+    """Batch of B quadruped OCPs resident on one B200.  Methods mirror include/nmpc_b200.h; array
+    arguments may be numpy arrays (host) or fp64 torch tensors (host or CUDA)."""
+
+    def __init__(self, batch: int, opts: Optional[NmpcOpts] = None, device: int = 0):
+        self.lib = L.load_library()
+        self.opts = (opts or default_opts()).copy()
+        self.B, self.N, self.device = int(batch), int(self.opts.n_nodes), int(device)
+        err = C.c_int32(0)
+        self._h = C.c_void_p(self.lib.nmpc_create(C.byref(self.opts), self.B, self.device, C.byref(err)))
+        if not self._h:
+            check(err.value or -1, "nmpc_create")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.nmpc_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # -- options ------------------------------------------------------------------------
+    def set_opts(self, opts: Optional[NmpcOpts] = None, **kw):
+        o = (opts or self.opts).copy()
+        for k, v in kw.items():
+            if not hasattr(o, k):
+                raise AttributeError(k)
+            setattr(o, k, v)
+        check(self.lib.nmpc_set_opts(self._h, C.byref(o)), "nmpc_set_opts")
+        self.opts = o
+
+    # -- problem data -------------------------------------------------------------------
+    def set_x0(self, qv):
+        a = _f64(qv, (self.B, 36))
+        check(self.lib.nmpc_set_x0(self._h, ptr(a)), "nmpc_set_x0")
+        self.synchronize_if_host(a)
+
+    def set_x0_full(self, x0):
+        a = _f64(x0, (self.B, NX))
+        check(self.lib.nmpc_set_x0_full(self._h, ptr(a)), "nmpc_set_x0_full")
+        self.synchronize_if_host(a)
+
+    def set_yref(self, yref, yref_e):
+        a = _f64(yref, (self.B, self.N, NY))
+        b = _f64(yref_e, (self.B, NYE))
+        check(self.lib.nmpc_set_yref(self._h, ptr(a), ptr(b)), "nmpc_set_yref")
+        self.synchronize_if_host(a)
+
+    def set_weights(self, W, W_e):
+        W = np.asarray(W, dtype=np.float64) if not hasattr(W, "data_ptr") else W
+        per = int(W.ndim == 2)
+        a = _f64(W, (self.B, NY) if per else (NY,))
+        b = _f64(W_e, (self.B, NYE) if per else (NYE,))
+        check(self.lib.nmpc_set_weights(self._h, ptr(a), ptr(b), per), "nmpc_set_weights")
+        self.synchronize_if_host(a)
+
+    def set_params(self, p):
+        a = _f64(p, (self.B, self.N + 1, NP))
+        check(self.lib.nmpc_set_params(self._h, ptr(a)), "nmpc_set_params")
+        self.synchronize_if_host(a)
+
+    def pin_stance_feet(self, i_node):
+        a = _i32(i_node, (self.B,))
+        check(self.lib.nmpc_pin_stance_feet(self._h, ptr(a)), "nmpc_pin_stance_feet")
+        self.synchronize_if_host(a)
+
+    def set_guess(self, x=None, u=None):
+        a = None if x is None else _f64(x, (self.B, self.N + 1, NX))
+        b = None if u is None else _f64(u, (self.B, self.N, NU))
+        check(self.lib.nmpc_set_guess(self._h, ptr(a), ptr(b)), "nmpc_set_guess")
+        self.synchronize_if_host(a if a is not None else b)
+
+    def shift_warm_start(self, start_node, repeat_last: bool = False):
+        a = _i32(start_node, (self.B,))
+        check(self.lib.nmpc_shift_warm_start(self._h, ptr(a), int(repeat_last)), "nmpc_shift_warm_start")
+        self.synchronize_if_host(a)
+
+    def reset_duals(self):
+        check(self.lib.nmpc_reset_duals(self._h), "nmpc_reset_duals")
+
+    def synchronize_if_host(self, a):
+        # host buffers are only borrowed until the async copy has been consumed
+        if isinstance(a, np.ndarray) or (hasattr(a, "is_cuda") and not a.is_cuda):
+            self.synchronize()
+
+    # -- solve --------------------------------------------------------------------------
+    def solve(self, status=None, sync: bool = True):
+        """Enqueue the solve.  With sync=True returns the per-problem status array."""
+        if not sync:
+            check(self.lib.nmpc_solve(self._h, None), "nmpc_solve")
+            return None
+        st = np.zeros(self.B, dtype=np.int32) if status is None else status
+        check(self.lib.nmpc_solve(self._h, ptr(st)), "nmpc_solve")
+        return st
+
+    def synchronize(self):
+        check(self.lib.nmpc_synchronize(self._h), "nmpc_synchronize")
+
+    # -- results ------------------------------------------------------------------------
+    def get_solution(self, duals: bool = True):
+        B, N = self.B, self.N
+        x, u = np.zeros((B, N + 1, NX)), np.zeros((B, N, NU))
+        pi = np.zeros((B, N, NX)) if duals else None
+        lam = np.zeros((B, N + 1, 2 * NG)) if duals else None
+        check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
+        return x, u, pi, lam
+
+    def get_solution_into(self, x=None, u=None, pi=None, lam=None):
+        check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
+
+    def get_stats(self) -> dict:
+        B = self.B
+        out = dict(sqp_iter=np.zeros(B, np.int32), qp_iter=np.zeros(B, np.int32),
+                   qp_status=np.zeros(B, np.int32), res=np.zeros((B, 4)), qp_res=np.zeros((B, 4)),
+                   cost=np.zeros(B))
+        st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost")])
+        check(self.lib.nmpc_get_stats(self._h, C.byref(st)), "nmpc_get_stats")
+        return out
+
+    def get_qp_step(self) -> np.ndarray:
+        dz = np.zeros((self.B, self.N + 1, NZ))
+        check(self.lib.nmpc_get_qp_step(self._h, ptr(dz)), "nmpc_get_qp_step")
+        return dz
+
+    def kinematics(self, qv):
+        a = _f64(qv, (-1, 36))
+        n = a.shape[0]
+        feet, com, hg = np.zeros((n, 4, 3)), np.zeros((n, 3)), np.zeros((n, 6))
+        check(self.lib.nmpc_kinematics(self._h, ptr(a), n, ptr(feet), ptr(com), ptr(hg)), "nmpc_kinematics")
+        return feet, com, hg
+
+    # -- diagnostics --------------------------------------------------------------------
+    def export_qp(self) -> dict:
+        B, N = self.B, self.N
+        out = dict(BAbt=np.zeros((B, N, NZ + 1, NX)), RSQrq=np.zeros((B, N + 1, NZ + 1, NZ)),
+                   DCt=np.zeros((B, N + 1, NZ, NG)), lg=np.zeros((B, N + 1, NG)),
+                   ug=np.zeros((B, N + 1, NG)), mask=np.zeros((B, N + 1, 2 * NG)))
+        check(self.lib.nmpc_export_qp(self._h, *[ptr(out[k]) for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")]),
+              "nmpc_export_qp")
+        return out
+
+    def solve_qp(self, qp: dict, dx0) -> dict:
+        B, N = self.B, self.N
+        arrs = [_f64(qp[k], s) for k, s in (("BAbt", (B, N, NZ + 1, NX)), ("RSQrq", (B, N + 1, NZ + 1, NZ)),
+                                             ("DCt", (B, N + 1, NZ, NG)), ("lg", (B, N + 1, NG)),
+                                             ("ug", (B, N + 1, NG)), ("mask", (B, N + 1, 2 * NG)))]
+        dx0 = _f64(dx0, (B, NX))
+        out = dict(dz=np.zeros((B, N + 1, NZ)), pi=np.zeros((B, N, NX)), lam=np.zeros((B, N + 1, 2 * NG)),
+                   t=np.zeros((B, N + 1, 2 * NG)), qp_iter=np.zeros(B, np.int32), qp_status=np.zeros(B, np.int32))
+        check(self.lib.nmpc_solve_qp(self._h, *[ptr(a) for a in arrs], ptr(dx0),
+                                     *[ptr(out[k]) for k in ("dz", "pi", "lam", "t", "qp_iter", "qp_status")]),
+              "nmpc_solve_qp")
+        return out
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.nmpc_launch_count(self._h))

@@ -1,0 +1,502 @@
+// nmpc_abi.cu -- host side of libnmpc_b200.so: the C ABI declared in include/nmpc_b200.h.
+//
+// Owns the device buffers and one CUDA stream per handle; every entry point only enqueues
+// copies / kernels on that stream (cudaMemcpyDefault lets callers pass host or device pointers).
+// There is NO CPU fallback: creation fails with NMPC_ENODEV when no sm_100 device is present.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "nmpc_common.cuh"
+#include "nmpc_linearize.cuh"
+#include "nmpc_qp_ipm.cuh"
+#include "nmpc_sqp.cuh"
+
+#define CK(call)                                                     \
+    do {                                                             \
+        cudaError_t e_ = (call);                                     \
+        if (e_ != cudaSuccess) return (int)e_;                       \
+    } while (0)
+
+struct nmpc_handle {
+    nmpc_opts o;
+    int B, N, device, Bc;        // Bc: problems per chunk of QP workspace
+    cudaStream_t stream;
+    long long launches;
+    // iterate and problem data [B]
+    double *x, *u, *pi, *lam, *x0, *p, *yref, *yref_e, *W, *We;
+    double *qz, *qpi, *qlam, *qt;
+    double *res, *qp_res, *cost;
+    unsigned long long* res_acc;
+    int32_t *status, *done, *sqp_iter, *qp_iter, *qp_status, *itmp;
+    // QP workspace [Bc]
+    double *G, *M, *C, *D, *L, *vec, *cost_stage;
+    double* scratch;             // staging for kinematics / dx0
+    size_t scratch_bytes;
+};
+
+static int ensure_scratch(nmpc_handle* h, size_t bytes)
+{
+    if (bytes <= h->scratch_bytes) return 0;
+    if (h->scratch) cudaFree(h->scratch);
+    h->scratch = nullptr; h->scratch_bytes = 0;
+    CK(cudaMalloc(&h->scratch, bytes));
+    h->scratch_bytes = bytes;
+    return 0;
+}
+
+template <typename T>
+static cudaError_t dalloc(T** p, size_t n)
+{
+    cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, n * sizeof(T));
+    return e;
+}
+
+extern "C" const char* nmpc_version(void) { return "nmpc_b200 0.1 (sm_100a, fp64, nx=42 nu=30 ng=42)"; }
+
+extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t device, int32_t* err)
+{
+    int32_t dummy;
+    if (!err) err = &dummy;
+    *err = NMPC_EINVAL;
+    if (!o || batch <= 0 || o->n_nodes < 1 || o->n_nodes > NMPC_MAX_NODES) return nullptr;
+    if (o->enable_time_opt) { *err = NMPC_ENOSYS; return nullptr; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device >= ndev) { *err = NMPC_ENODEV; return nullptr; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major < 10) { *err = NMPC_ENODEV; return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { *err = NMPC_ENODEV; return nullptr; }
+
+    nmpc_handle* h = (nmpc_handle*)calloc(1, sizeof(nmpc_handle));
+    h->o = *o; h->B = batch; h->N = o->n_nodes; h->device = device;
+    int cap = 4096;
+    if (const char* s = getenv("NMPC_CHUNK")) { int v = atoi(s); if (v > 0) cap = v; }
+    h->Bc = batch < cap ? batch : cap;
+    const size_t B = batch, N = h->N, Bc = h->Bc;
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+#define A_(ptr, n) if (e == cudaSuccess) e = dalloc(&h->ptr, (n))
+    A_(x, B * (N + 1) * NX); A_(u, B * N * NU); A_(pi, B * N * NX); A_(lam, B * (N + 1) * 2 * NG);
+    A_(x0, B * NX); A_(p, B * (N + 1) * NPAR); A_(yref, B * N * NY); A_(yref_e, B * NYE);
+    A_(W, B * NY); A_(We, B * NYE);
+    A_(qz, B * (N + 1) * NZ); A_(qpi, B * N * NX); A_(qlam, B * (N + 1) * 2 * NG); A_(qt, B * (N + 1) * 2 * NG);
+    A_(res, B * 4); A_(qp_res, B * 4); A_(cost, B); A_(res_acc, B * 4);
+    A_(status, B); A_(done, B); A_(sqp_iter, B); A_(qp_iter, B); A_(qp_status, B); A_(itmp, B);
+    A_(G, Bc * N * G_SZ); A_(M, Bc * (N + 1) * M_SZ); A_(C, Bc * (N + 1) * C_SZ); A_(D, Bc * (N + 1) * D_SZ);
+    A_(L, Bc * (N + 1) * L_SZ); A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
+#undef A_
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(nmpc_qp_ipm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, QP_SMEM_BYTES);
+    if (e != cudaSuccess) {
+        *err = (e == cudaErrorMemoryAllocation) ? NMPC_ENOMEM : (int)e;
+        nmpc_destroy(h);
+        return nullptr;
+    }
+    *err = 0;
+    return h;
+}
+
+extern "C" void nmpc_destroy(nmpc_handle* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
+                    h->qlam, h->qt, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
+                    h->qp_iter, h->qp_status, h->itmp, h->G, h->M, h->C, h->D, h->L, h->vec, h->cost_stage,
+                    h->scratch};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    free(h);
+}
+
+extern "C" int nmpc_set_opts(nmpc_handle* h, const nmpc_opts* o)
+{
+    if (!h || !o || o->n_nodes != h->N) return NMPC_EINVAL;
+    if (o->enable_time_opt) return NMPC_ENOSYS;
+    h->o = *o;
+    return 0;
+}
+
+extern "C" int nmpc_get_dims(const nmpc_handle* h, int32_t* batch, int32_t* n_nodes)
+{
+    if (!h) return NMPC_EINVAL;
+    if (batch) *batch = h->B;
+    if (n_nodes) *n_nodes = h->N;
+    return 0;
+}
+
+extern "C" int nmpc_stream(const nmpc_handle* h, void** s)
+{
+    if (!h || !s) return NMPC_EINVAL;
+    *s = (void*)h->stream;
+    return 0;
+}
+
+extern "C" int64_t nmpc_launch_count(const nmpc_handle* h) { return h ? h->launches : 0; }
+
+static int h2d(nmpc_handle* h, void* dst, const void* src, size_t bytes)
+{
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_set_x0(nmpc_handle* h, const double* qv)
+{
+    if (!h || !qv) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    if (int r = ensure_scratch(h, (size_t)h->B * 36 * 8)) return r;
+    CK(cudaMemcpyAsync(h->scratch, qv, (size_t)h->B * 36 * 8, cudaMemcpyDefault, h->stream));
+    nmpc_set_x0_kernel<<<(h->B + 63) / 64, 64, 0, h->stream>>>(h->scratch, h->B, h->N, h->x0, h->x);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int nmpc_set_x0_full(nmpc_handle* h, const double* x0)
+{
+    if (!h || !x0) return NMPC_EINVAL;
+    if (int r = h2d(h, h->x0, x0, (size_t)h->B * NX * 8)) return r;
+    nmpc_copy_x0_kernel<<<(h->B * NX + 127) / 128, 128, 0, h->stream>>>(h->B, h->N, h->x0, h->x);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int nmpc_set_yref(nmpc_handle* h, const double* yref, const double* yref_e)
+{
+    if (!h) return NMPC_EINVAL;
+    if (yref) if (int r = h2d(h, h->yref, yref, (size_t)h->B * h->N * NY * 8)) return r;
+    if (yref_e) if (int r = h2d(h, h->yref_e, yref_e, (size_t)h->B * NYE * 8)) return r;
+    return 0;
+}
+
+extern "C" int nmpc_set_weights(nmpc_handle* h, const double* W, const double* We, int32_t per_problem)
+{
+    if (!h) return NMPC_EINVAL;
+    if (per_problem) {
+        if (W) if (int r = h2d(h, h->W, W, (size_t)h->B * NY * 8)) return r;
+        if (We) if (int r = h2d(h, h->We, We, (size_t)h->B * NYE * 8)) return r;
+        return 0;
+    }
+    // broadcast: replicate on the host (cost weights change rarely)
+    CK(cudaSetDevice(h->device));
+    if (W) {
+        std::vector<double> w(NY), rep((size_t)h->B * NY);
+        CK(cudaMemcpy(w.data(), W, NY * 8, cudaMemcpyDefault));
+        for (int b = 0; b < h->B; b++) memcpy(&rep[(size_t)b * NY], w.data(), NY * 8);
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemcpy(h->W, rep.data(), rep.size() * 8, cudaMemcpyHostToDevice));
+    }
+    if (We) {
+        std::vector<double> w(NYE), rep((size_t)h->B * NYE);
+        CK(cudaMemcpy(w.data(), We, NYE * 8, cudaMemcpyDefault));
+        for (int b = 0; b < h->B; b++) memcpy(&rep[(size_t)b * NYE], w.data(), NYE * 8);
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemcpy(h->We, rep.data(), rep.size() * 8, cudaMemcpyHostToDevice));
+    }
+    return 0;
+}
+
+extern "C" int nmpc_set_params(nmpc_handle* h, const double* p)
+{
+    if (!h || !p) return NMPC_EINVAL;
+    return h2d(h, h->p, p, (size_t)h->B * (h->N + 1) * NPAR * 8);
+}
+
+extern "C" int nmpc_pin_stance_feet(nmpc_handle* h, const int32_t* i_node)
+{
+    if (!h || !i_node) return NMPC_EINVAL;
+    if (int r = h2d(h, h->itmp, i_node, (size_t)h->B * 4)) return r;
+    nmpc_pin_feet_kernel<<<(h->B + 63) / 64, 64, 0, h->stream>>>(h->B, h->N, h->x0, h->itmp, h->p);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int nmpc_set_guess(nmpc_handle* h, const double* x, const double* u)
+{
+    if (!h) return NMPC_EINVAL;
+    if (x) if (int r = h2d(h, h->x, x, (size_t)h->B * (h->N + 1) * NX * 8)) return r;
+    if (u) if (int r = h2d(h, h->u, u, (size_t)h->B * h->N * NU * 8)) return r;
+    return 0;
+}
+
+extern "C" int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, int32_t repeat_last)
+{
+    if (!h || !start_node) return NMPC_EINVAL;
+    if (int r = h2d(h, h->itmp, start_node, (size_t)h->B * 4)) return r;
+    nmpc_shift_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->itmp, repeat_last, h->x, h->u, h->pi, h->lam);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int nmpc_reset_duals(nmpc_handle* h)
+{
+    if (!h) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B, N = h->N;
+    CK(cudaMemsetAsync(h->pi, 0, B * N * NX * 8, h->stream));
+    CK(cudaMemsetAsync(h->lam, 0, B * (N + 1) * 2 * NG * 8, h->stream));
+    CK(cudaMemsetAsync(h->qz, 0, B * (N + 1) * NZ * 8, h->stream));
+    CK(cudaMemsetAsync(h->qpi, 0, B * N * NX * 8, h->stream));
+    CK(cudaMemsetAsync(h->qlam, 0, B * (N + 1) * 2 * NG * 8, h->stream));
+    CK(cudaMemsetAsync(h->qt, 0, B * (N + 1) * 2 * NG * 8, h->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// solve
+// ---------------------------------------------------------------------------------------------
+static LinArgs lin_args(nmpc_handle* h, int b0)
+{
+    LinArgs a;
+    a.x = h->x; a.u = h->u; a.p = h->p; a.yref = h->yref; a.yref_e = h->yref_e; a.W = h->W; a.We = h->We;
+    a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.cost_stage = h->cost_stage; a.done = h->done;
+    a.N = h->N; a.b0 = b0; a.dt = h->o.dt_nodes; a.reg = h->o.reg_eps; a.reg_e = h->o.reg_eps_e;
+    a.mu_c = h->o.mu_contact;
+    return a;
+}
+
+static QpArgs qp_args(nmpc_handle* h, int b0)
+{
+    QpArgs a;
+    a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.L = h->L; a.vec = h->vec;
+    a.qz = h->qz; a.qpi = h->qpi; a.qlam = h->qlam; a.qt = h->qt;
+    a.dx0_ext = nullptr; a.x0 = h->x0; a.x = h->x; a.u = h->u; a.pi = h->pi; a.lam = h->lam;
+    a.qp_iter = h->qp_iter; a.qp_status = h->qp_status; a.qp_res = h->qp_res;
+    a.done = h->done; a.sqp_iter = h->sqp_iter;
+    a.N = h->N; a.b0 = b0; a.max_iter = h->o.max_qp_iter; a.warm = h->o.warm_start_qp; a.apply = 1;
+    a.tol = h->o.qp_tol;
+    return a;
+}
+
+extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
+{
+    if (!h) return NMPC_EINVAL;
+    if (h->o.hpipm_mode != NMPC_HPIPM_SPEED) return NMPC_ENOSYS;
+    CK(cudaSetDevice(h->device));
+    const int B = h->B, N = h->N;
+    const int rti = h->o.real_time_it != 0;
+    const int max_iter = rti ? 1 : h->o.max_iter;
+    nmpc_sqp_begin_kernel<<<(B + 127) / 128, 128, 0, h->stream>>>(B, rti, h->status, h->done, h->sqp_iter,
+                                                                 h->qp_iter, h->qp_status, h->res_acc);
+    h->launches++;
+    for (int b0 = 0; b0 < B; b0 += h->Bc) {
+        const int Bc = (B - b0 < h->Bc) ? (B - b0) : h->Bc;
+        for (int it = 0; it <= max_iter; it++) {
+            if (rti && it == 1) break;
+            LinArgs la = lin_args(h, b0);
+            nmpc_linearize_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la);
+            h->launches++;
+            if (!rti) {
+                ResArgs ra;
+                ra.G = h->G; ra.M = h->M; ra.C = h->C; ra.D = h->D; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi;
+                ra.lam = h->lam; ra.res_acc = h->res_acc; ra.done = h->done; ra.N = N; ra.b0 = b0;
+                nmpc_residual_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
+                nmpc_sqp_decide_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(
+                    b0, Bc, N, it, max_iter, h->o.nlp_tol, h->res_acc, h->cost_stage, h->res, h->cost,
+                    h->status, h->done);
+                h->launches += 2;
+                if (it == max_iter) break;
+            } else {
+                nmpc_cost_sum_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, N, h->cost_stage, h->cost);
+                h->launches++;
+            }
+            QpArgs qa = qp_args(h, b0);
+            nmpc_qp_ipm_kernel<<<Bc, QP_THREADS, QP_SMEM_BYTES, h->stream>>>(qa);
+            nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
+            h->launches += 2;
+        }
+    }
+    CK(cudaGetLastError());
+    if (status) {
+        CK(cudaMemcpyAsync(status, h->status, (size_t)B * 4, cudaMemcpyDefault, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+extern "C" int nmpc_synchronize(nmpc_handle* h)
+{
+    if (!h) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    return (int)cudaGetLastError();
+}
+
+static int d2h(nmpc_handle* h, void* dst, const void* src, size_t bytes)
+{
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* pi, double* lam)
+{
+    if (!h) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B, N = h->N;
+    if (x) if (int r = d2h(h, x, h->x, B * (N + 1) * NX * 8)) return r;
+    if (u) if (int r = d2h(h, u, h->u, B * N * NU * 8)) return r;
+    if (pi) if (int r = d2h(h, pi, h->pi, B * N * NX * 8)) return r;
+    if (lam) if (int r = d2h(h, lam, h->lam, B * (N + 1) * 2 * NG * 8)) return r;
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_get_stats(nmpc_handle* h, nmpc_stats* s)
+{
+    if (!h || !s) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B;
+    if (s->sqp_iter) if (int r = d2h(h, s->sqp_iter, h->sqp_iter, B * 4)) return r;
+    if (s->qp_iter) if (int r = d2h(h, s->qp_iter, h->qp_iter, B * 4)) return r;
+    if (s->qp_status) if (int r = d2h(h, s->qp_status, h->qp_status, B * 4)) return r;
+    if (s->res) if (int r = d2h(h, s->res, h->res, B * 4 * 8)) return r;
+    if (s->qp_res) if (int r = d2h(h, s->qp_res, h->qp_res, B * 4 * 8)) return r;
+    if (s->cost) if (int r = d2h(h, s->cost, h->cost, B * 8)) return r;
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_get_qp_step(nmpc_handle* h, double* dz)
+{
+    if (!h || !dz) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    if (int r = d2h(h, dz, h->qz, (size_t)h->B * (h->N + 1) * NZ * 8)) return r;
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, double* feet, double* com, double* hg)
+{
+    if (!h || !qv || n <= 0) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t in_b = (size_t)n * 36 * 8, out_d = (size_t)n * (12 + 3 + 6);
+    if (int r = ensure_scratch(h, in_b + out_d * 8)) return r;
+    double* d_in = h->scratch;
+    double* d_feet = h->scratch + (size_t)n * 36;
+    double* d_com = d_feet + (size_t)n * 12;
+    double* d_hg = d_com + (size_t)n * 3;
+    CK(cudaMemcpyAsync(d_in, qv, in_b, cudaMemcpyDefault, h->stream));
+    nmpc_kin0_kernel<<<(n + 63) / 64, 64, 0, h->stream>>>(d_in, n, d_feet, d_com, d_hg);
+    h->launches++;
+    if (feet) CK(cudaMemcpyAsync(feet, d_feet, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
+    if (com) CK(cudaMemcpyAsync(com, d_com, (size_t)n * 3 * 8, cudaMemcpyDefault, h->stream));
+    if (hg) CK(cudaMemcpyAsync(hg, d_hg, (size_t)n * 6 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// diagnostics: export / import dense QPs in the HPIPM-style layouts of the header
+// ---------------------------------------------------------------------------------------------
+extern "C" int nmpc_export_qp(nmpc_handle* h, double* BAbt, double* RSQrq, double* DCt, double* lg, double* ug,
+                              double* mask)
+{
+    if (!h) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const int B = h->B, N = h->N;
+    std::vector<double> hG((size_t)h->Bc * N * G_SZ), hM((size_t)h->Bc * (N + 1) * M_SZ),
+        hC((size_t)h->Bc * (N + 1) * C_SZ), hD((size_t)h->Bc * (N + 1) * D_SZ);
+    CK(cudaMemsetAsync(h->done, 0, (size_t)B * 4, h->stream));
+    for (int b0 = 0; b0 < B; b0 += h->Bc) {
+        const int Bc = (B - b0 < h->Bc) ? (B - b0) : h->Bc;
+        LinArgs la = lin_args(h, b0);
+        nmpc_linearize_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la);
+        h->launches++;
+        CK(cudaMemcpyAsync(hG.data(), h->G, (size_t)Bc * N * G_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(hM.data(), h->M, (size_t)Bc * (N + 1) * M_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(hC.data(), h->C, (size_t)Bc * (N + 1) * C_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(hD.data(), h->D, (size_t)Bc * (N + 1) * D_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        for (int bl = 0; bl < Bc; bl++) {
+            const size_t b = b0 + bl;
+            for (int k = 0; k <= N; k++) {
+                if (BAbt && k < N) {
+                    const double* g = &hG[((size_t)bl * N + k) * G_SZ];
+                    double* o = BAbt + (b * N + k) * (NZ + 1) * NX;
+                    for (int c = 0; c <= NZ; c++)
+                        for (int l = 0; l < NX; l++) o[c * NX + l] = g[l * G_LD + c];
+                }
+                if (RSQrq) {
+                    const double* m = &hM[((size_t)bl * (N + 1) + k) * M_SZ];
+                    double* o = RSQrq + (b * (N + 1) + k) * (NZ + 1) * NZ;
+                    for (int r = 0; r <= NZ; r++)
+                        for (int c = 0; c < NZ; c++)
+                            o[r * NZ + c] = (r < NZ && c > r) ? m[c * M_LD + r] : m[r * M_LD + c];
+                }
+                if (DCt) {
+                    const double* cc = &hC[((size_t)bl * (N + 1) + k) * C_SZ];
+                    double* o = DCt + (b * (N + 1) + k) * NZ * NG;
+                    for (int c = 0; c < NZ; c++)
+                        for (int j = 0; j < NG; j++) o[c * NG + j] = cc[j * C_LD + c];
+                }
+                const double* d = &hD[((size_t)bl * (N + 1) + k) * D_SZ];
+                if (lg) memcpy(lg + (b * (N + 1) + k) * NG, d, NG * 8);
+                if (ug) memcpy(ug + (b * (N + 1) + k) * NG, d + NG, NG * 8);
+                if (mask) memcpy(mask + (b * (N + 1) + k) * 2 * NG, d + 2 * NG, 2 * NG * 8);
+            }
+        }
+    }
+    return 0;
+}
+
+extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const double* DCt,
+                             const double* lg, const double* ug, const double* mask, const double* dx0,
+                             double* dz, double* pi, double* lam, double* t, int32_t* qp_iter, int32_t* qp_status)
+{
+    if (!h || !BAbt || !RSQrq || !DCt || !lg || !ug || !mask || !dx0) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const int B = h->B, N = h->N;
+    if (int r = ensure_scratch(h, (size_t)B * NX * 8)) return r;
+    CK(cudaMemcpyAsync(h->scratch, dx0, (size_t)B * NX * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemsetAsync(h->done, 0, (size_t)B * 4, h->stream));
+    std::vector<double> hG((size_t)h->Bc * N * G_SZ, 0.0), hM((size_t)h->Bc * (N + 1) * M_SZ, 0.0),
+        hC((size_t)h->Bc * (N + 1) * C_SZ, 0.0), hD((size_t)h->Bc * (N + 1) * D_SZ, 0.0);
+    for (int b0 = 0; b0 < B; b0 += h->Bc) {
+        const int Bc = (B - b0 < h->Bc) ? (B - b0) : h->Bc;
+        for (int bl = 0; bl < Bc; bl++) {
+            const size_t b = b0 + bl;
+            for (int k = 0; k <= N; k++) {
+                if (k < N) {
+                    double* g = &hG[((size_t)bl * N + k) * G_SZ];
+                    const double* o = BAbt + (b * N + k) * (NZ + 1) * NX;
+                    for (int c = 0; c <= NZ; c++)
+                        for (int l = 0; l < NX; l++) g[l * G_LD + c] = o[c * NX + l];
+                }
+                double* m = &hM[((size_t)bl * (N + 1) + k) * M_SZ];
+                const double* o = RSQrq + (b * (N + 1) + k) * (NZ + 1) * NZ;
+                for (int r = 0; r <= NZ; r++)
+                    for (int c = 0; c < NZ; c++)
+                        if (r == NZ || c <= r) m[r * M_LD + c] = o[r * NZ + c];
+                double* cc = &hC[((size_t)bl * (N + 1) + k) * C_SZ];
+                const double* oc = DCt + (b * (N + 1) + k) * NZ * NG;
+                for (int c = 0; c < NZ; c++)
+                    for (int j = 0; j < NG; j++) cc[j * C_LD + c] = oc[c * NG + j];
+                double* d = &hD[((size_t)bl * (N + 1) + k) * D_SZ];
+                memcpy(d, lg + (b * (N + 1) + k) * NG, NG * 8);
+                memcpy(d + NG, ug + (b * (N + 1) + k) * NG, NG * 8);
+                memcpy(d + 2 * NG, mask + (b * (N + 1) + k) * 2 * NG, 2 * NG * 8);
+            }
+        }
+        CK(cudaMemcpyAsync(h->G, hG.data(), (size_t)Bc * N * G_SZ * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->M, hM.data(), (size_t)Bc * (N + 1) * M_SZ * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->C, hC.data(), (size_t)Bc * (N + 1) * C_SZ * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->D, hD.data(), (size_t)Bc * (N + 1) * D_SZ * 8, cudaMemcpyHostToDevice, h->stream));
+        QpArgs qa = qp_args(h, b0);
+        qa.dx0_ext = h->scratch; qa.warm = 0; qa.apply = 0; qa.done = nullptr; qa.sqp_iter = nullptr;
+        nmpc_qp_ipm_kernel<<<Bc, QP_THREADS, QP_SMEM_BYTES, h->stream>>>(qa);
+        h->launches++;
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    CK(cudaGetLastError());
+    const size_t Bs = B;
+    if (dz) CK(cudaMemcpyAsync(dz, h->qz, Bs * (N + 1) * NZ * 8, cudaMemcpyDefault, h->stream));
+    if (pi) CK(cudaMemcpyAsync(pi, h->qpi, Bs * N * NX * 8, cudaMemcpyDefault, h->stream));
+    if (lam) CK(cudaMemcpyAsync(lam, h->qlam, Bs * (N + 1) * 2 * NG * 8, cudaMemcpyDefault, h->stream));
+    if (t) CK(cudaMemcpyAsync(t, h->qt, Bs * (N + 1) * 2 * NG * 8, cudaMemcpyDefault, h->stream));
+    if (qp_iter) CK(cudaMemcpyAsync(qp_iter, h->qp_iter, Bs * 4, cudaMemcpyDefault, h->stream));
+    if (qp_status) CK(cudaMemcpyAsync(qp_status, h->qp_status, Bs * 4, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}

@@ -1,0 +1,206 @@
+"""ctypes binding of the CPU oracle (oracle/libnmpc_oracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Importable from tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs, nowhere else.
+Mirrors the product's C ABI (include/nmpc_b200.h) call for call so the parity tests read
+symmetrically.  PARITY UNPINNED: see the header of nmpc_oracle.c.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import Optional
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnmpc_oracle.so")
+
+NX, NU, NZ, NP, NY, NYE, NG = 42, 30, 72, 44, 76, 52, 42
+
+
+class NmpcOpts(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_int32), ("max_iter", C.c_int32), ("max_qp_iter", C.c_int32),
+        ("real_time_it", C.c_int32), ("warm_start_qp", C.c_int32), ("warm_start_nlp", C.c_int32),
+        ("hpipm_mode", C.c_int32), ("enable_time_opt", C.c_int32),
+        ("dt_nodes", C.c_double), ("dt_min", C.c_double), ("dt_max", C.c_double),
+        ("nlp_tol", C.c_double), ("qp_tol", C.c_double),
+        ("reg_eps", C.c_double), ("reg_eps_e", C.c_double), ("mu_contact", C.c_double),
+    ]
+
+
+class NmpcStats(C.Structure):
+    _fields_ = [("sqp_iter", C.c_void_p), ("qp_iter", C.c_void_p), ("qp_status", C.c_void_p),
+                ("res", C.c_void_p), ("qp_res", C.c_void_p), ("cost", C.c_void_p)]
+
+
+def default_opts(**kw) -> NmpcOpts:
+    o = NmpcOpts(n_nodes=25, max_iter=1, max_qp_iter=6, real_time_it=0, warm_start_qp=1,
+                 warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, dt_nodes=0.04, dt_min=0.02,
+                 dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8)
+    for k, v in kw.items():
+        setattr(o, k, v)
+    return o
+
+
+def build(force: bool = False) -> str:
+    """Compile the oracle with its Makefile (gcc)."""
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.check_call(["make", "-C", HERE, "-s"] + (["-B"] if force else []))
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(LIB_PATH)
+        _lib.oracle_create.restype = C.c_void_p
+        _lib.oracle_create.argtypes = [C.POINTER(NmpcOpts), C.c_int32]
+        for name in ("oracle_destroy", "oracle_set_opts", "oracle_set_x0", "oracle_set_x0_full",
+                     "oracle_set_yref", "oracle_set_weights", "oracle_set_params",
+                     "oracle_pin_stance_feet", "oracle_set_guess", "oracle_reset_duals",
+                     "oracle_shift_warm_start", "oracle_solve", "oracle_get_solution",
+                     "oracle_get_stats", "oracle_get_qp_step", "oracle_export_qp", "oracle_solve_qp"):
+            getattr(_lib, name).restype = C.c_int
+    return _lib
+
+
+def _p(a: Optional[np.ndarray]):
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _f64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def kinematics(qv: np.ndarray):
+    qv = _f64(qv).reshape(-1, 36)
+    n = qv.shape[0]
+    feet, com, hg = np.zeros((n, 4, 3)), np.zeros((n, 3)), np.zeros((n, 6))
+    lib().oracle_kinematics(_p(qv), C.c_int32(n), _p(feet), _p(com), _p(hg))
+    return feet, com, hg
+
+
+def model_record(qv: np.ndarray) -> np.ndarray:
+    qv = _f64(qv).reshape(36)
+    dims = np.zeros(8, dtype=np.int32)
+    lib().oracle_dims(_p(dims))
+    rec = np.zeros(int(dims[6]))
+    lib().oracle_model_record(_p(qv), _p(rec))
+    return rec
+
+
+class OracleSolver:
+    """Batch of B OCPs solved on the host; same call sequence as the product's NmpcSolver."""
+
+    def __init__(self, batch: int, opts: Optional[NmpcOpts] = None):
+        self.opts = opts or default_opts()
+        self.B = int(batch)
+        self.N = int(self.opts.n_nodes)
+        self._h = C.c_void_p(lib().oracle_create(C.byref(self.opts), C.c_int32(self.B)))
+        if not self._h:
+            raise RuntimeError("oracle_create failed")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().oracle_destroy(self._h)
+            self._h = None
+
+    def set_opts(self, opts: NmpcOpts):
+        self.opts = opts
+        assert lib().oracle_set_opts(self._h, C.byref(opts)) == 0
+
+    def set_x0(self, qv):
+        qv = _f64(qv).reshape(self.B, 36)
+        lib().oracle_set_x0(self._h, _p(qv))
+
+    def set_x0_full(self, x0):
+        x0 = _f64(x0).reshape(self.B, NX)
+        lib().oracle_set_x0_full(self._h, _p(x0))
+
+    def set_yref(self, yref, yref_e):
+        yref = _f64(yref).reshape(self.B, self.N, NY)
+        yref_e = _f64(yref_e).reshape(self.B, NYE)
+        lib().oracle_set_yref(self._h, _p(yref), _p(yref_e))
+
+    def set_weights(self, W, W_e):
+        W, W_e = _f64(W), _f64(W_e)
+        per = int(W.ndim == 2)
+        lib().oracle_set_weights(self._h, _p(W), _p(W_e), C.c_int32(per))
+
+    def set_params(self, p):
+        p = _f64(p).reshape(self.B, self.N + 1, NP)
+        lib().oracle_set_params(self._h, _p(p))
+
+    def pin_stance_feet(self, i_node):
+        i_node = _i32(np.broadcast_to(i_node, (self.B,)))
+        lib().oracle_pin_stance_feet(self._h, _p(i_node))
+
+    def set_guess(self, x=None, u=None):
+        x = None if x is None else _f64(x).reshape(self.B, self.N + 1, NX)
+        u = None if u is None else _f64(u).reshape(self.B, self.N, NU)
+        lib().oracle_set_guess(self._h, _p(x), _p(u))
+
+    def reset_duals(self):
+        lib().oracle_reset_duals(self._h)
+
+    def shift_warm_start(self, start_node, repeat_last: bool = False):
+        s = _i32(np.broadcast_to(start_node, (self.B,)))
+        lib().oracle_shift_warm_start(self._h, _p(s), C.c_int32(int(repeat_last)))
+
+    def solve(self, n_threads: int = 0) -> np.ndarray:
+        status = np.zeros(self.B, dtype=np.int32)
+        lib().oracle_solve(self._h, _p(status), C.c_int32(n_threads))
+        return status
+
+    def get_solution(self):
+        B, N = self.B, self.N
+        x, u = np.zeros((B, N + 1, NX)), np.zeros((B, N, NU))
+        pi, lam = np.zeros((B, N, NX)), np.zeros((B, N + 1, 2 * NG))
+        lib().oracle_get_solution(self._h, _p(x), _p(u), _p(pi), _p(lam))
+        return x, u, pi, lam
+
+    def get_stats(self) -> dict:
+        B = self.B
+        out = dict(sqp_iter=np.zeros(B, np.int32), qp_iter=np.zeros(B, np.int32),
+                   qp_status=np.zeros(B, np.int32), res=np.zeros((B, 4)), qp_res=np.zeros((B, 4)),
+                   cost=np.zeros(B))
+        st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost")])
+        lib().oracle_get_stats(self._h, C.byref(st))
+        return out
+
+    def get_qp_step(self) -> np.ndarray:
+        dz = np.zeros((self.B, self.N + 1, NZ))
+        lib().oracle_get_qp_step(self._h, _p(dz))
+        return dz
+
+    def export_qp(self) -> dict:
+        B, N = self.B, self.N
+        out = dict(BAbt=np.zeros((B, N, NZ + 1, NX)), RSQrq=np.zeros((B, N + 1, NZ + 1, NZ)),
+                   DCt=np.zeros((B, N + 1, NZ, NG)), lg=np.zeros((B, N + 1, NG)),
+                   ug=np.zeros((B, N + 1, NG)), mask=np.zeros((B, N + 1, 2 * NG)))
+        lib().oracle_export_qp(self._h, *[_p(out[k]) for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")])
+        return out
+
+    def solve_qp(self, qp: dict, dx0: np.ndarray) -> dict:
+        B, N = self.B, self.N
+        dx0 = _f64(dx0).reshape(B, NX)
+        out = dict(dz=np.zeros((B, N + 1, NZ)), pi=np.zeros((B, N, NX)), lam=np.zeros((B, N + 1, 2 * NG)),
+                   t=np.zeros((B, N + 1, 2 * NG)), qp_iter=np.zeros(B, np.int32),
+                   qp_status=np.zeros(B, np.int32), qp_res=np.zeros((B, 4)))
+        args = [_p(_f64(qp[k])) for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")]
+        lib().oracle_solve_qp(self._h, *args, _p(dx0),
+                              *[_p(out[k]) for k in ("dz", "pi", "lam", "t", "qp_iter", "qp_status", "qp_res")])
+        return out
