@@ -163,6 +163,12 @@ int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const
                   double* dz, double* pi, double* lam, double* t,
                   int32_t* qp_iter, int32_t* qp_status);
 
+/* Per-kernel device timing with CUDA events recorded on the handle's stream around each launch
+ * of the three heavy kernels (0 linearise, 1 qp_ipm, 2 residual).  Replaces acados' print_time /
+ * the reference's @time_fn("solve") (solver.py:396) at kernel granularity. */
+int nmpc_set_profiling(nmpc_handle* h, int32_t on);
+int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[3]*/, int64_t* count /*[3]*/);
+
 /* number of kernels launched by the handle since creation (bench.py's gpu_launches claim) */
 int64_t nmpc_launch_count(const nmpc_handle* h);
 const char* nmpc_version(void);

@@ -76,6 +76,8 @@ _SIGS = {
     "nmpc_export_qp": (C.c_int, [C.c_void_p] + [C.c_void_p] * 6),
     "nmpc_solve_qp": (C.c_int, [C.c_void_p] + [C.c_void_p] * 13),
     "nmpc_launch_count": (C.c_int64, [C.c_void_p]),
+    "nmpc_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
+    "nmpc_get_kernel_times": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "nmpc_version": (C.c_char_p, []),
 }
 EXPORTED_SYMBOLS = ["nmpc_create"] + list(_SIGS)

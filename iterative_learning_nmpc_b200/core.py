@@ -179,6 +179,22 @@ class NmpcSolver:
               "nmpc_solve_qp")
         return out
 
+    def set_profiling(self, on: bool = True):
+        check(self.lib.nmpc_set_profiling(self._h, int(on)), "nmpc_set_profiling")
+
+    def kernel_times(self) -> dict:
+        """{kernel: (ms, launches)} accumulated since the last call (CUDA events, handle stream)."""
+        ms = np.zeros(3)
+        cnt = np.zeros(3, dtype=np.int64)
+        check(self.lib.nmpc_get_kernel_times(self._h, ptr(ms), ptr(cnt)), "nmpc_get_kernel_times")
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(("linearize", "qp_ipm", "residual"))}
+
+    @property
+    def stream_ptr(self) -> int:
+        s = C.c_void_p(0)
+        check(self.lib.nmpc_stream(self._h, C.byref(s)), "nmpc_stream")
+        return int(s.value or 0)
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.nmpc_launch_count(self._h))

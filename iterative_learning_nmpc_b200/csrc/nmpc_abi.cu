@@ -34,7 +34,32 @@ struct nmpc_handle {
     double *G, *M, *C, *D, *L, *vec, *cost_stage;
     double* scratch;             // staging for kinematics / dx0
     size_t scratch_bytes;
+    // optional per-kernel timing with CUDA events on the handle's stream (bench.py roofline)
+    int profiling;
+    std::vector<cudaEvent_t>* ev;    // start/stop pairs
+    std::vector<int>* ev_kind;       // 0 linearize, 1 qp_ipm, 2 residual
+    size_t ev_used;
 };
+
+static void prof_begin(nmpc_handle* h, int kind)
+{
+    if (!h->profiling) return;
+    if (h->ev_used + 2 > h->ev->size()) {
+        cudaEvent_t a, b;
+        cudaEventCreate(&a); cudaEventCreate(&b);
+        h->ev->push_back(a); h->ev->push_back(b);
+    }
+    if (h->ev_kind->size() < h->ev_used / 2 + 1) h->ev_kind->push_back(kind);
+    (*h->ev_kind)[h->ev_used / 2] = kind;
+    cudaEventRecord((*h->ev)[h->ev_used], h->stream);
+}
+
+static void prof_end(nmpc_handle* h)
+{
+    if (!h->profiling) return;
+    cudaEventRecord((*h->ev)[h->ev_used + 1], h->stream);
+    h->ev_used += 2;
+}
 
 static int ensure_scratch(nmpc_handle* h, size_t bytes)
 {
@@ -71,6 +96,7 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
 
     nmpc_handle* h = (nmpc_handle*)calloc(1, sizeof(nmpc_handle));
     h->o = *o; h->B = batch; h->N = o->n_nodes; h->device = device;
+    h->ev = new std::vector<cudaEvent_t>(); h->ev_kind = new std::vector<int>();
     int cap = 4096;
     if (const char* s = getenv("NMPC_CHUNK")) { int v = atoi(s); if (v > 0) cap = v; }
     h->Bc = batch < cap ? batch : cap;
@@ -108,6 +134,8 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
                     h->scratch};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->ev) { for (cudaEvent_t e : *h->ev) cudaEventDestroy(e); delete h->ev; }
+    delete h->ev_kind;
     free(h);
 }
 
@@ -286,13 +314,17 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
         for (int it = 0; it <= max_iter; it++) {
             if (rti && it == 1) break;
             LinArgs la = lin_args(h, b0);
+            prof_begin(h, 0);
             nmpc_linearize_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la);
+            prof_end(h);
             h->launches++;
             if (!rti) {
                 ResArgs ra;
                 ra.G = h->G; ra.M = h->M; ra.C = h->C; ra.D = h->D; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi;
                 ra.lam = h->lam; ra.res_acc = h->res_acc; ra.done = h->done; ra.N = N; ra.b0 = b0;
+                prof_begin(h, 2);
                 nmpc_residual_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
+                prof_end(h);
                 nmpc_sqp_decide_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(
                     b0, Bc, N, it, max_iter, h->o.nlp_tol, h->res_acc, h->cost_stage, h->res, h->cost,
                     h->status, h->done);
@@ -303,7 +335,9 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
                 h->launches++;
             }
             QpArgs qa = qp_args(h, b0);
+            prof_begin(h, 1);
             nmpc_qp_ipm_kernel<<<Bc, QP_THREADS, QP_SMEM_BYTES, h->stream>>>(qa);
+            prof_end(h);
             nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
             h->launches += 2;
         }
@@ -313,6 +347,31 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
         CK(cudaMemcpyAsync(status, h->status, (size_t)B * 4, cudaMemcpyDefault, h->stream));
         CK(cudaStreamSynchronize(h->stream));
     }
+    return 0;
+}
+
+extern "C" int nmpc_set_profiling(nmpc_handle* h, int32_t on)
+{
+    if (!h) return NMPC_EINVAL;
+    h->profiling = on ? 1 : 0;
+    h->ev_used = 0;
+    return 0;
+}
+
+// accumulated device time [ms] and launch counts per kernel kind since the last call; resets
+extern "C" int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[3]*/, int64_t* count /*[3]*/)
+{
+    if (!h || !ms || !count) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < 3; i++) { ms[i] = 0.0; count[i] = 0; }
+    for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, (*h->ev)[i], (*h->ev)[i + 1]));
+        const int kind = (*h->ev_kind)[i / 2];
+        ms[kind] += t; count[kind] += 1;
+    }
+    h->ev_used = 0;
     return 0;
 }
 

@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) nmpc_linearize_kernel(LinArgs 
             if (i >= 6 && i < NQ) { w = s_W[36 + i - 6]; e = acc_u[i] - s_yr[36 + i - 6]; }
             else if (i >= NQ) { w = s_W[52 + i - NQ]; e = s_u[i] - s_yr[52 + i - NQ]; }
         }
-        Mp[i * M_LD + i] = term ? 1.0 : (w + reg);
+        Mp[i * M_LD + i] = w + reg;
         Mp[NZ * M_LD + i] = w * e;
         cost += 0.5 * w * e * e;
     }

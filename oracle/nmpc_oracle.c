@@ -921,7 +921,7 @@ static void solve_one(oracle_handle* h, int b, workspace* w)
         if (!o->real_time_it && r[0] < o->nlp_tol && r[1] < o->nlp_tol && r[2] < o->nlp_tol && r[3] < o->nlp_tol) {
             status = NMPC_STATUS_SUCCESS; break;
         }
-        if (it >= max_iter) { status = o->real_time_it ? NMPC_STATUS_SUCCESS : NMPC_STATUS_MAXITER; break; }
+        if (it >= max_iter) { status = NMPC_STATUS_MAXITER; break; }
         double dx0[NX];
         for (int i = 0; i < NX; i++) dx0[i] = x0[i] - x[i];
         qp_info info;
@@ -940,6 +940,8 @@ static void solve_one(oracle_handle* h, int b, workspace* w)
                 lam[k * 2 * NG + j] = w->lin[k].ml[j] > 0.5 ? qlam[k][j] : 0.0;
                 lam[k * 2 * NG + NG + j] = w->lin[k].mu[j] > 0.5 ? qlam[k][NG + j] : 0.0;
             }
+        /* SQP_RTI: one linearisation, one QP, one full step, no convergence test */
+        if (o->real_time_it) { status = NMPC_STATUS_SUCCESS; it++; break; }
     }
     h->status[b] = status;
     h->sqp_iter[b] = it;
