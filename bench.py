@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py -- batched NMPC SQP solves/sec (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--batch B] [--config 2|3]
+
+A "step" is one pass of the hot path (QuadrupedAcadosSolver.init + solve,
+/root/reference/mpc_controller/utils/solver.py:356-429) over one batch of synthetic OCPs:
+BASELINE config 2 -- Go2 trot, 1024 perturbed initial states per GPU, SQP_RTI -- cold-started from
+the same initial guess every step (so every step does identical work).  Weak scaling: every rank
+owns its own 1024 problems; problems are independent, there is no collective on the data path.
+
+  value    whole-job solves/s with the batch resident in HBM (device copies of the guess + solve),
+           CUDA events on the solver's stream, max over ranks.
+  e2e      the same through the C ABI with HOST (pinned) buffers: H2D of every input, solve, D2H
+           of the solution and status inside the timed region.
+  roofline dominant kernel (nmpc_qp_ipm_kernel): algorithmic bytes per launch / mean launch time
+           (CUDA events around each launch, nmpc_set_profiling) over the measured HBM peak.
+  cpu_baseline  the CPU oracle (a port of the algorithm, NOT acados) on the host cores, bounded sample.
+
+`--impl reference` times that CPU oracle alone with all host threads (the reference's own
+acados/HPIPM stack is not installable here: DESIGN.md, "Oracle").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "batched NMPC SQP solves/sec (Go2 trot)"
+UNIT = "solves/s"
+N_NODES = 25
+
+# algorithmic HBM bytes of the QP kernel per OCP per IPM iteration (DESIGN.md "Roofline"): the
+# dense stage blocks are streamed once per sweep that needs them.
+_G, _M, _C, _D, _L, _V = 3108, 5330, 3024, 168, 5330, 606
+
+
+def qp_bytes_per_problem(n_ipm: int, N: int = N_NODES) -> float:
+    """factor sweep: read C, M, G, write L; corrector backward: read C, L, G; two forward sweeps:
+    read L, G, C each; plus the per-stage vector workspace; residual-only exit pass: C, M, G."""
+    st = N + 1
+    fact = (_C + _M + _G + _L + _D) * st
+    corr = (_C + _L + _G) * st
+    fwd = 2 * (_L + _G + _C) * st
+    vec = 6 * _V * st
+    exit_pass = (_C + _M + _G + _D) * st
+    return 8.0 * (n_ipm * (fact + corr + fwd + vec) + exit_pass)
+
+
+def workload_opts(cfg: int):
+    if cfg == 2:
+        return dict(real_time_it=1, max_iter=1, max_qp_iter=6, qp_tol=1e-2, nlp_tol=1e-1, warm_start_qp=0), ("trot",)
+    if cfg == 3:
+        return dict(real_time_it=0, max_iter=15, max_qp_iter=6, qp_tol=1e-2, nlp_tol=1e-1, warm_start_qp=0), \
+            ("trot", "pace", "bound")
+    raise SystemExit("--config must be 2 or 3")
+
+
+def workload_name(cfg: int, B: int) -> str:
+    if cfg == 2:
+        return f"config2: Go2 trot, {B} perturbed initial states per GPU, SQP_RTI, N=25, max_qp_iter=6"
+    return f"config3: Go2 trot/pace/bound mixed, {B} OCPs per GPU, full SQP max_iter=15, N=25, max_qp_iter=6"
+
+
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(self.idx)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self) -> dict:
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+def time_cpu_oracle(batch, opts: dict, n_problems: int, threads: int) -> dict:
+    """Bounded sample of the same workload on the host cores with the CPU oracle."""
+    from oracle import oracle as O
+    O.build()
+    n = min(n_problems, len(batch["qv"]))
+    sub = {k: (v[:n] if isinstance(v, np.ndarray) and v.shape[:1] == (len(batch["qv"]),) else v)
+           for k, v in batch.items()}
+    _, _, hg = O.kinematics(sub["qv"])
+    s = O.OracleSolver(n, O.default_opts(**opts))
+    from iterative_learning_nmpc_b200 import workloads as WL
+    WL.load_into(s, sub, hg)
+    t0 = time.perf_counter()
+    s.solve(threads)
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{n} OCPs of the same batch, one solver per thread (OpenMP dynamic), {dt:.2f} s wall; "
+                      "CPU restatement of the algorithm, not acados/HPIPM"}
+
+
+def run_reference(args) -> None:
+    """`--impl reference`: the reference's CPU path is not installable (acados/HPIPM/CasADi/contact_tamp
+    absent); the CPU oracle port stands in, all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from iterative_learning_nmpc_b200 import workloads as WL
+    opts, gaits = workload_opts(args.config)
+    threads = os.cpu_count() or 1
+    n = max(threads * 4, 32)
+    batch = WL.make_batch(n, seed=args.config - 1, gaits=gaits)
+    vals = []
+    for i in range(args.warmup + args.steps):
+        r = time_cpu_oracle(batch, opts, n, threads)
+        if i >= args.warmup:
+            vals.append(r["value"])
+    v = float(np.mean(vals))
+    cb = dict(r, value=v)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * n / v, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args.config, args.batch), "sample_per_step": n},
+        "cpu_baseline": cb,
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ---------------------------------------------------------------------------------------------
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--batch", type=int, default=1024, help="OCPs per GPU")
+    ap.add_argument("--config", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from iterative_learning_nmpc_b200 import workloads as WL
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    B = args.batch
+    opts, gaits = workload_opts(args.config)
+    batch = WL.make_batch(B, seed=1000 * rank + args.config - 1, gaits=gaits)
+    solver = NmpcSolver(B, default_opts(**opts), device=local)
+    stream = torch.cuda.ExternalStream(solver.stream_ptr, device=local)
+    _, _, hg = solver.kinematics(batch["qv"])
+    xg = batch["x_guess"].copy()
+    xg[:, :, 36:] = hg[:, None, :]
+    keys = ("W", "W_e", "yref", "yref_e", "p", "u_guess", "qv", "i_node")
+    host = {k: torch.from_numpy(np.ascontiguousarray(batch[k])).pin_memory() for k in keys}
+    host["x_guess"] = torch.from_numpy(xg).pin_memory()
+    dev = {k: v.cuda(non_blocking=False) for k, v in host.items()}
+    out_x = torch.empty(B, N_NODES + 1, 42, dtype=torch.float64).pin_memory()
+    out_u = torch.empty(B, N_NODES, 30, dtype=torch.float64).pin_memory()
+    out_st = torch.empty(B, dtype=torch.int32).pin_memory()
+    st_dev = torch.empty(B, dtype=torch.int32, device="cuda")
+
+    def step(src, sync_out: bool):
+        # QuadrupedAcadosSolver.init: weights, references, parameters, guess, x0, stance feet
+        solver.set_weights(src["W"], src["W_e"])
+        solver.set_yref(src["yref"], src["yref_e"])
+        solver.set_params(src["p"])
+        solver.set_guess(src["x_guess"], src["u_guess"])
+        solver.set_x0(src["qv"])
+        solver.pin_stance_feet(src["i_node"])
+        solver.reset_duals()
+        if sync_out:     # QuadrupedAcadosSolver.solve + parse_sol: status and solution back on the host
+            solver.solve(status=out_st)
+            solver.get_solution_into(x=out_x, u=out_u)
+        else:
+            solver.solve(status=None, sync=False)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(src, sync_out: bool, steps: int):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for _ in range(steps):
+            step(src, sync_out)
+        e1.record(stream)
+        solver.synchronize()
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms = e0.elapsed_time(e1)
+        t = torch.tensor([ms, wall], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1])
+
+    # ---- device-resident: value -------------------------------------------------------------
+    for _ in range(args.warmup):
+        step(dev, False)
+    solver.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = solver.launch_count
+    ms_dev, _ = timed(dev, False, args.steps)
+    launches = solver.launch_count - l0
+    # ---- per-kernel timing for the roofline (separate pass so the events do not perturb `value`)
+    solver.set_profiling(True)
+    barrier()
+    for _ in range(args.steps):
+        step(dev, False)
+    kt = solver.kernel_times()
+    solver.set_profiling(False)
+    stats = solver.get_stats()
+    # ---- host buffers through the C ABI: e2e ---------------------------------------------------
+    for _ in range(2):
+        step(host, True)
+    ms_e2e, wall_e2e = timed(host, True, args.steps)
+    clk = clocks.stop()
+    status_counts = {int(k): int(v) for k, v in zip(*np.unique(out_st.numpy(), return_counts=True))}
+
+    h2d = sum(host[k].numel() * host[k].element_size() for k in host)
+    d2h = out_x.numel() * 8 + out_u.numel() * 8 + out_st.numel() * 4
+    total = B * world
+    value = total * args.steps / (ms_dev * 1e-3)
+    e2e = total * args.steps / (max(ms_e2e, wall_e2e) * 1e-3)
+
+    n_ipm = float(np.mean(stats["qp_iter"]))
+    n_sqp = float(np.mean(stats["sqp_iter"]))
+    qp_ms, qp_n = kt["qp_ipm"]
+    lin_ms, lin_n = kt["linearize"]
+    res_ms, res_n = kt["residual"]
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    bytes_launch = qp_bytes_per_problem(round(n_ipm)) * B
+    achieved = bytes_launch / (qp_ms / max(qp_n, 1) * 1e-3) / 1e9 if qp_n else None
+    roofline = {"bound": "hbm", "kernel": "nmpc_qp_ipm_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                "algorithmic_bytes_per_launch": bytes_launch, "launch_ms": qp_ms / max(qp_n, 1),
+                "kernel_share_of_step": {"qp_ipm": qp_ms, "linearize": lin_ms, "residual": res_ms,
+                                         "launches": {"qp_ipm": qp_n, "linearize": lin_n, "residual": res_n}},
+                "mean_ipm_iter": n_ipm, "mean_sqp_iter": n_sqp}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        cpu = time_cpu_oracle(batch, opts, max(threads * 16, 64), threads)
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args.config, B), "batch_per_gpu": B, "global_batch": total,
+                       "parallelism": f"problem-sharded x{world}, no data-path collective",
+                       "l2": "per-step working set (QP stage blocks + factors) is "
+                             f"{B * 26 * (_G + _M + _C + _D + _L + _V) * 8 / 1e9:.2f} GB per GPU, larger than the 126 MB L2"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": max(ms_e2e, wall_e2e) / args.steps},
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "status_counts": status_counts,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -142,10 +142,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 // ---------------------------------------------------------------------------------------------
 // small block-level helpers
 // ---------------------------------------------------------------------------------------------
+// max that keeps a NaN once it has seen one (fmax drops NaNs; the norms must report them)
+__device__ __forceinline__ double nanmax(double a, double b) { return (b > a || b != b) ? b : a; }
 __device__ __forceinline__ double warp_max(double v)
 {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    for (int o = 16; o > 0; o >>= 1) v = nanmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 __device__ __forceinline__ double warp_min(double v)

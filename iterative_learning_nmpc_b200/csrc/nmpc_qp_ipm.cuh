@@ -86,7 +86,7 @@ __device__ __forceinline__ double block_reduce(double v, int op, double* red, in
 #pragma unroll
     for (int w = 1; w < QP_THREADS / 32; w++) {
         const double o = red[w];
-        if (op == 0) r = fmax(r, o); else if (op == 1) r = fmin(r, o); else r += o;
+        if (op == 0) r = nanmax(r, o); else if (op == 1) r = fmin(r, o); else r += o;
     }
     return r;
 }
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(QP_THREADS, 2) nmpc_qp_ipm_kernel(QpArgs a)
                 const double cz = sv[SV_CZ + j];
                 const double slack = e ? (sv[SV_D + NG + j] - cz) : (cz - sv[SV_D + j]);
                 double t, lam;
-                if (it == 0 && a.warm < 2) {
+                if (it == 0 && (a.warm < 2 || !(sv[SV_T + tid] > 0.0) || !(sv[SV_LAM + tid] > 0.0))) {
                     if (msk > 0.5) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; } else { t = 1.0; lam = 0.0; }
                     sv[SV_T + tid] = t; sv[SV_LAM + tid] = lam;
                     qt[(size_t)k * 2 * NG + tid] = t; qlam[(size_t)k * 2 * NG + tid] = lam;
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(QP_THREADS, 2) nmpc_qp_ipm_kernel(QpArgs a)
                 sv[SV_RD + tid] = rd; sv[SV_RM + tid] = rm;
                 vk[V_RD + tid] = rd; vk[V_RM + tid] = rm;
                 acc_mu += rm; acc_nc += (msk > 0.5) ? 1.0 : 0.0;
-                m_d = fmax(m_d, fabs(rd)); m_m = fmax(m_m, fabs(rm));
+                m_d = nanmax(m_d, fabs(rd)); m_m = nanmax(m_m, fabs(rm));
             }
             __syncthreads();
             if (tid < NG) {
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(QP_THREADS, 2) nmpc_qp_ipm_kernel(QpArgs a)
                     if ((tid & 3) == 0 && l < NX) {
                         const double rb = s + sU[l * G_LD + NZ] - sv[SV_ZXN + l];
                         sv[SV_RB + l] = rb; vk[V_RB + l] = rb;
-                        m_b = fmax(m_b, fabs(rb));
+                        m_b = nanmax(m_b, fabs(rb));
                     }
                 }
             }
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(QP_THREADS, 2) nmpc_qp_ipm_kernel(QpArgs a)
                 double s = sv[SV_RG + tid];
                 if ((k == 0 && tid >= NU) || (term && tid < NU)) s = 0.0;
                 sv[SV_RG + tid] = s; vk[V_RG + tid] = s;
-                m_g = fmax(m_g, fabs(s));
+                m_g = nanmax(m_g, fabs(s));
                 sv[SV_QT + tid] += s;                 // q tilde = rg + C^T gamma
             }
             if (last) { __syncthreads(); continue; }   // residual-only pass

@@ -41,15 +41,15 @@ __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_kernel(ResArgs a
     for (int i = tid; i < NX; i += RES_THREADS) {
         s_pik[i] = k > 0 ? a.pi[((size_t)b * N + k - 1) * NX + i] : 0.0;
         s_pin[i] = term ? 0.0 : a.pi[((size_t)b * N + k) * NX + i];
-        if (k == 0) r_e = fmax(r_e, fabs(a.x[(size_t)b * (N + 1) * NX + i] - a.x0[(size_t)b * NX + i]));
-        if (!term) r_e = fmax(r_e, fabs(Gp[i * G_LD + NZ]));
+        if (k == 0) r_e = nanmax(r_e, fabs(a.x[(size_t)b * (N + 1) * NX + i] - a.x0[(size_t)b * NX + i]));
+        if (!term) r_e = nanmax(r_e, fabs(Gp[i * G_LD + NZ]));
     }
     for (int j = tid; j < NG; j += RES_THREADS) {
         const double ml = Dp[2 * NG + j], mu = Dp[3 * NG + j];
         const double c = -Dp[j];
         double dl = 0.0;
-        if (ml > 0.5) { dl += lam[j]; r_i = fmax(r_i, -c); r_c = fmax(r_c, fabs(lam[j] * c)); }
-        if (mu > 0.5) { dl -= lam[NG + j]; r_i = fmax(r_i, c); r_c = fmax(r_c, fabs(lam[NG + j] * c)); }
+        if (ml > 0.5) { dl += lam[j]; r_i = nanmax(r_i, -c); r_c = nanmax(r_c, fabs(lam[j] * c)); }
+        if (mu > 0.5) { dl -= lam[NG + j]; r_i = nanmax(r_i, c); r_c = nanmax(r_c, fabs(lam[NG + j] * c)); }
         s_dl[j] = dl;
     }
     __syncthreads();
@@ -59,15 +59,14 @@ __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_kernel(ResArgs a
         if (!term) for (int l = 0; l < NX; l++) s += Gp[l * G_LD + c] * s_pin[l];
         if (k > 0 && c >= NU) s -= s_pik[c - NU];
         for (int j = 0; j < NG; j++) s -= Cp[j * C_LD + c] * s_dl[j];
-        r_s = fmax(r_s, fabs(s));
-        if (!(s == s)) r_s = __longlong_as_double(0x7ff0000000000000LL);
+        r_s = nanmax(r_s, fabs(s));
     }
     r_s = warp_max(r_s); r_e = warp_max(r_e); r_i = warp_max(r_i); r_c = warp_max(r_c);
     if ((tid & 31) == 0) { s_red[0][tid >> 5] = r_s; s_red[1][tid >> 5] = r_e; s_red[2][tid >> 5] = r_i; s_red[3][tid >> 5] = r_c; }
     __syncthreads();
     if (tid < 4) {
         double v = 0.0;
-        for (int w = 0; w < RES_THREADS / 32; w++) v = fmax(v, s_red[tid][w]);
+        for (int w = 0; w < RES_THREADS / 32; w++) v = nanmax(v, s_red[tid][w]);
         atomic_max_nonneg(a.res_acc + (size_t)b * 4 + tid, v);
     }
 }

@@ -68,6 +68,8 @@
 #define IPM_T_MIN 1e-16
 #define IPM_ALPHA_MIN 1e-12
 static const double GRAV[3] = {0.0, 0.0, -9.81};
+/* running inf-norm that keeps a NaN once it has seen one (plain > comparisons drop NaNs) */
+#define NORM_ACC(r, a) do { const double a_ = fabs(a); if (a_ > (r) || a_ != a_) (r) = a_; } while (0)
 
 typedef struct {
     double A[NX][NX], B[NX][NU], b[NX];
@@ -475,7 +477,8 @@ static int riccati(workspace* w, int N, const double* dx0, int do_fact)
 
 /* QP of the SQP step at the current linearisation held in w->lin.
  * in/out: z [N+1][NZ], pi [N][NX], lam/t [N+1][2NG] (lower | upper).  warm: 0 cold, 1 keep z,pi,
- * 2 keep everything.  dx0 = x0 - xbar_0 is imposed on stage 0. */
+ * 2 keep everything (entries whose stored lam or t is not positive, e.g. after reset_duals, are
+ * initialised as in a cold start).  dx0 = x0 - xbar_0 is imposed on stage 0. */
 static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, int warm,
                    double (*z)[NZ], double (*pi)[NX], double (*lam)[2 * NG], double (*t)[2 * NG],
                    qp_info* info)
@@ -495,11 +498,11 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
             for (int c = 0; c < NZ; c++) cz += s->C[j][c] * z[k][c];
             if (s->ml[j] > 0.5) {
                 nc++;
-                if (warm < 2) { double tl = cz - s->lgq[j]; t[k][j] = tl > IPM_THR0 ? tl : IPM_THR0; lam[k][j] = IPM_MU0 / t[k][j]; }
+                if (warm < 2 || !(t[k][j] > 0.0) || !(lam[k][j] > 0.0)) { double tl = cz - s->lgq[j]; t[k][j] = tl > IPM_THR0 ? tl : IPM_THR0; lam[k][j] = IPM_MU0 / t[k][j]; }
             } else { t[k][j] = 1.0; lam[k][j] = 0.0; }
             if (s->mu[j] > 0.5) {
                 nc++;
-                if (warm < 2) { double tu = s->ugq[j] - cz; t[k][NG + j] = tu > IPM_THR0 ? tu : IPM_THR0; lam[k][NG + j] = IPM_MU0 / t[k][NG + j]; }
+                if (warm < 2 || !(t[k][NG + j] > 0.0) || !(lam[k][NG + j] > 0.0)) { double tu = s->ugq[j] - cz; t[k][NG + j] = tu > IPM_THR0 ? tu : IPM_THR0; lam[k][NG + j] = IPM_MU0 / t[k][NG + j]; }
             } else { t[k][NG + j] = 1.0; lam[k][NG + j] = 0.0; }
         }
     }
@@ -524,9 +527,8 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
                 w->rm[k][NG + j] = s->mu[j] * lam[k][NG + j] * t[k][NG + j];
                 mu += w->rm[k][j] + w->rm[k][NG + j];
                 for (int e = 0; e < 2; e++) {
-                    double a1 = fabs(w->rd[k][e * NG + j]), a2 = fabs(w->rm[k][e * NG + j]);
-                    if (a1 > res_d) res_d = a1;
-                    if (a2 > res_m) res_m = a2;
+                    NORM_ACC(res_d, w->rd[k][e * NG + j]);
+                    NORM_ACC(res_m, w->rm[k][e * NG + j]);
                 }
             }
             for (int c = 0; c < NZ; c++) {
@@ -537,14 +539,14 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
                 for (int j = 0; j < NG; j++) acc -= s->C[j][c] * (lam[k][j] - lam[k][NG + j]);
                 if ((k == 0 && c >= NU) || (k == N && c < NU)) acc = 0.0;   /* fixed x0 / no u_N */
                 w->rg[k][c] = acc;
-                if (fabs(acc) > res_g) res_g = fabs(acc);
+                NORM_ACC(res_g, acc);
             }
             if (k < N) for (int i = 0; i < NX; i++) {
                 double acc = s->b[i] - z[k + 1][NU + i];
                 for (int l = 0; l < NX; l++) acc += s->A[i][l] * z[k][NU + l];
                 for (int l = 0; l < NU; l++) acc += s->B[i][l] * z[k][l];
                 w->rb[k][i] = acc;
-                if (fabs(acc) > res_b) res_b = fabs(acc);
+                NORM_ACC(res_b, acc);
             }
         }
         mu *= inv_nc;
@@ -869,7 +871,7 @@ static void nlp_residuals(const oracle_handle* h, int b, const workspace* w, dou
     const double* x = h->x + (size_t)b * (N + 1) * NX;
     const double* x0 = h->x0 + (size_t)b * NX;
     double rs = 0, re = 0, ri = 0, rc = 0, cst = 0;
-    for (int i = 0; i < NX; i++) { double d = fabs(x[i] - x0[i]); if (d > re) re = d; }
+    for (int i = 0; i < NX; i++) NORM_ACC(re, x[i] - x0[i]);
     for (int k = 0; k <= N; k++) {
         const stage_lin* s = &w->lin[k];
         cst += s->cost;
@@ -879,17 +881,17 @@ static void nlp_residuals(const oracle_handle* h, int b, const workspace* w, dou
             if (k < N) for (int l = 0; l < NX; l++) acc += (c < NU ? s->B[l][c] : s->A[l][c - NU]) * pi[k * NX + l];
             if (k > 0 && c >= NU) acc -= pi[(k - 1) * NX + c - NU];
             for (int j = 0; j < NG; j++) acc -= s->C[j][c] * (s->ml[j] * lam[k * 2 * NG + j] - s->mu[j] * lam[k * 2 * NG + NG + j]);
-            if (fabs(acc) > rs) rs = fabs(acc);
+            NORM_ACC(rs, acc);
         }
-        if (k < N) for (int i = 0; i < NX; i++) if (fabs(s->b[i]) > re) re = fabs(s->b[i]);
+        if (k < N) for (int i = 0; i < NX; i++) NORM_ACC(re, s->b[i]);
         for (int j = 0; j < NG; j++) {
             if (s->ml[j] > 0.5) {
-                if (-s->c[j] > ri) ri = -s->c[j];
-                double cm = fabs(lam[k * 2 * NG + j] * s->c[j]); if (cm > rc) rc = cm;
+                if (-s->c[j] > ri || s->c[j] != s->c[j]) ri = -s->c[j];
+                NORM_ACC(rc, lam[k * 2 * NG + j] * s->c[j]);
             }
             if (s->mu[j] > 0.5) {
-                if (s->c[j] > ri) ri = s->c[j];
-                double cm = fabs(lam[k * 2 * NG + NG + j] * s->c[j]); if (cm > rc) rc = cm;
+                if (s->c[j] > ri || s->c[j] != s->c[j]) ri = s->c[j];
+                NORM_ACC(rc, lam[k * 2 * NG + NG + j] * s->c[j]);
             }
         }
     }

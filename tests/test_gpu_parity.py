@@ -1,0 +1,270 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs.  Tolerance (BASELINE.json north_star): <= 1e-6 relative on the primal/dual iterates
+of each QP; converged NLP solutions within nlp_tol; identical per-problem status."""
+import numpy as np
+import pytest
+
+from iterative_learning_nmpc_b200 import workloads as WL
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-6
+N = 25
+
+
+def _gpu():
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+    return NmpcSolver, default_opts
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1.0))
+
+
+def _pair(O, B, seed, gaits=("trot",), perturb=1.0, **opts):
+    NmpcSolver, default_opts = _gpu()
+    batch = WL.make_batch(B, seed=seed, gaits=gaits, perturb=perturb)
+    _, _, hg = O.kinematics(batch["qv"])
+    so = O.OracleSolver(B, O.default_opts(**opts))
+    sg = NmpcSolver(B, default_opts(**opts))
+    WL.load_into(so, batch, hg)
+    WL.load_into(sg, batch, hg)
+    return so, sg, batch
+
+
+def test_kinematics_parity(oracle_mod):
+    NmpcSolver, default_opts = _gpu()
+    batch = WL.make_batch(257, seed=2)
+    fo, co, ho = oracle_mod.kinematics(batch["qv"])
+    sg = NmpcSolver(1, default_opts())
+    fg, cg, hg = sg.kinematics(batch["qv"])
+    assert rel_err(fg, fo) < 1e-13 and rel_err(cg, co) < 1e-13 and rel_err(hg, ho) < 1e-12
+
+
+def test_linearisation_parity(oracle_mod):
+    """Every block of the exported OCP-QP (dynamics, Gauss-Newton Hessian/gradient, constraint
+    Jacobians, bounds, masks) for three gaits."""
+    so, sg, _ = _pair(oracle_mod, 12, seed=4, gaits=("trot", "pace", "bound"))
+    qo, qg = so.export_qp(), sg.export_qp()
+    np.testing.assert_array_equal(qg["mask"], qo["mask"])
+    for k in ("BAbt", "RSQrq", "DCt", "lg", "ug"):
+        assert rel_err(qg[k], qo[k]) < 1e-11, k
+
+
+@pytest.mark.parametrize("cap", [0, 1, 2, 3, 6, 10])
+def test_qp_iterates_parity(oracle_mod, cap):
+    """Primal/dual iterate of the IPM after `cap` iterations, on identical QP data."""
+    O = oracle_mod
+    B = 6
+    so, sg, _ = _pair(O, B, seed=5, max_qp_iter=cap, qp_tol=1e-9, warm_start_qp=0)
+    qp = so.export_qp()
+    dx0 = np.random.default_rng(1).normal(0, 1e-2, (B, 42))
+    ro = so.solve_qp(qp, dx0)
+    rg = sg.solve_qp(qp, dx0)
+    np.testing.assert_array_equal(rg["qp_iter"], ro["qp_iter"])
+    np.testing.assert_array_equal(rg["qp_status"], ro["qp_status"])
+    m = qp["mask"] > 0.5
+    for k in ("dz", "pi"):
+        assert rel_err(rg[k], ro[k]) < REL, (k, rel_err(rg[k], ro[k]))
+    for k in ("lam", "t"):
+        assert rel_err(rg[k][m], ro[k][m]) < REL, (k, rel_err(rg[k][m], ro[k][m]))
+
+
+def test_qp_without_inequalities_is_one_riccati_solve(oracle_mod):
+    O = oracle_mod
+    B = 4
+    so, sg, _ = _pair(O, B, seed=6, max_qp_iter=1, qp_tol=1e-300, warm_start_qp=0)
+    qp = so.export_qp()
+    qp["mask"][:] = 0
+    dx0 = np.random.default_rng(2).normal(0, 1e-2, (B, 42))
+    ro, rg = so.solve_qp(qp, dx0), sg.solve_qp(qp, dx0)
+    assert rel_err(rg["dz"], ro["dz"]) < 1e-9 and rel_err(rg["pi"], ro["pi"]) < 1e-9
+
+
+def test_rti_solve_parity(oracle_mod):
+    so, sg, batch = _pair(oracle_mod, 33, seed=7, real_time_it=1, warm_start_qp=0)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    xo, uo, pio, lamo = so.get_solution()
+    xg, ug, pig, lamg = sg.get_solution()
+    assert rel_err(xg, xo) < REL and rel_err(ug, uo) < REL
+    assert rel_err(pig, pio) < REL and rel_err(lamg, lamo) < REL
+    so_s, sg_s = so.get_stats(), sg.get_stats()
+    for k in ("sqp_iter", "qp_iter", "qp_status"):
+        np.testing.assert_array_equal(sg_s[k], so_s[k])
+    assert rel_err(sg_s["cost"], so_s["cost"]) < 1e-10
+    np.testing.assert_array_equal(xg[:, 0, :36], batch["qv"])
+
+
+def test_full_sqp_parity_and_convergence(oracle_mod):
+    opts = dict(max_iter=40, max_qp_iter=20, qp_tol=1e-3, nlp_tol=1e-1, warm_start_qp=0)
+    so, sg, _ = _pair(oracle_mod, 8, seed=3, perturb=0.5, **opts)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    assert (st_g == 0).all()
+    so_s, sg_s = so.get_stats(), sg.get_stats()
+    np.testing.assert_array_equal(sg_s["sqp_iter"], so_s["sqp_iter"])
+    assert (sg_s["res"] < 1e-1).all()                       # converged within nlp_tol
+    xo, uo, _, _ = so.get_solution()
+    xg, ug, _, _ = sg.get_solution()
+    # many SQP iterations compound rounding differences: NLP solutions agree well inside nlp_tol
+    assert rel_err(xg, xo) < 1e-5 and rel_err(ug, uo) < 1e-5
+
+
+def test_sqp_few_iterations_iterate_parity(oracle_mod):
+    """Three SQP iterations with the default 6-iteration IPM cap and QP warm start 1 (the
+    reference's first-tick setting is 15 iterations, mpc.py:464-473)."""
+    opts = dict(max_iter=3, max_qp_iter=6, qp_tol=1e-2, nlp_tol=1e-2, warm_start_qp=1)
+    so, sg, _ = _pair(oracle_mod, 10, seed=8, gaits=("trot", "pace"), **opts)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    xo, uo, pio, lamo = so.get_solution()
+    xg, ug, pig, lamg = sg.get_solution()
+    assert rel_err(xg, xo) < REL and rel_err(ug, uo) < REL and rel_err(pig, pio) < REL and rel_err(lamg, lamo) < REL
+    assert rel_err(sg.get_stats()["res"], so.get_stats()["res"]) < 1e-5
+
+
+def test_status_codes_parity(oracle_mod):
+    """MAXITER when the tolerance is unreachable, NaN confined to the poisoned problem."""
+    O = oracle_mod
+    B = 5
+    so, sg, batch = _pair(O, B, seed=9, max_iter=2, nlp_tol=1e-12, warm_start_qp=0)
+    _, _, hg = O.kinematics(batch["qv"])
+    xg = batch["x_guess"].copy()
+    xg[:, :, 36:] = hg[:, None, :]
+    xg[3, 4, 9] = np.nan
+    so.set_guess(xg, None)
+    sg.set_guess(xg, None)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    assert st_g[3] == 1 and (np.delete(st_g, 3) == 2).all()
+    x, u, _, _ = sg.get_solution()
+    keep = [0, 1, 2, 4]
+    assert np.isfinite(x[keep]).all() and np.isfinite(u[keep]).all()
+
+
+@pytest.mark.parametrize("repeat_last", [False, True])
+def test_shift_warm_start_parity(oracle_mod, repeat_last):
+    O = oracle_mod
+    NmpcSolver, default_opts = _gpu()
+    B = 6
+    rng = np.random.default_rng(0)
+    x, u = rng.normal(size=(B, N + 1, 42)), rng.normal(size=(B, N, 30))
+    so, sg = O.OracleSolver(B, O.default_opts()), NmpcSolver(B, default_opts())
+    start = np.array([0, 1, 2, 5, 24, 25], dtype=np.int32)
+    for s in (so, sg):
+        s.set_guess(x, u)
+        s.shift_warm_start(start, repeat_last)
+    for a, b in zip(sg.get_solution(), so.get_solution()):
+        np.testing.assert_array_equal(a, b)
+
+
+def test_receding_horizon_ticks_parity(oracle_mod):
+    """Three consecutive replanning ticks: solve, shift by one node, new x0 from the plan
+    (LocomotionMPC.open_loop semantics, mpc.py:416-462), with QP and NLP warm starts."""
+    O = oracle_mod
+    B = 4
+    so, sg, batch = _pair(O, B, seed=12, real_time_it=1, warm_start_qp=1)
+    for tick in range(3):
+        st_o, st_g = so.solve(0), sg.solve()
+        np.testing.assert_array_equal(st_g, st_o)
+        xo, uo, _, _ = so.get_solution()
+        xg, ug, _, _ = sg.get_solution()
+        assert rel_err(xg, xo) < REL * (tick + 1) and rel_err(ug, uo) < REL * (tick + 1), tick
+        nxt = xo[:, 1, :].copy()
+        for s in (so, sg):
+            s.shift_warm_start(np.ones(B, np.int32), False)
+            s.set_x0_full(nxt)
+
+
+def test_batch_is_independent_and_chunking_invariant(oracle_mod, monkeypatch):
+    """Size-independent property used at full size: a problem's solution does not depend on its
+    position in the batch nor on the workspace chunking."""
+    NmpcSolver, default_opts = _gpu()
+    B = 96
+    batch = WL.make_batch(B, seed=13)
+    _, _, hg = oracle_mod.kinematics(batch["qv"])
+
+    def run(bt, hg_, chunk=None):
+        if chunk:
+            monkeypatch.setenv("NMPC_CHUNK", str(chunk))
+        else:
+            monkeypatch.delenv("NMPC_CHUNK", raising=False)
+        s = NmpcSolver(len(bt["qv"]), default_opts(real_time_it=1, warm_start_qp=0))
+        WL.load_into(s, bt, hg_)
+        st = s.solve()
+        x, u, _, _ = s.get_solution()
+        return st, x, u
+
+    st0, x0, u0 = run(batch, hg)
+    st1, x1, u1 = run(batch, hg, chunk=40)           # 40 + 40 + 16
+    np.testing.assert_array_equal(st0, st1)
+    np.testing.assert_array_equal(x0, x1)
+    np.testing.assert_array_equal(u0, u1)
+    perm = np.random.default_rng(0).permutation(B)
+    pb = {k: (v[perm] if isinstance(v, np.ndarray) and v.shape[:1] == (B,) else v) for k, v in batch.items()}
+    st2, x2, u2 = run(pb, hg[perm])
+    np.testing.assert_array_equal(st0[perm], st2)
+    np.testing.assert_array_equal(x0[perm], x2)
+    np.testing.assert_array_equal(u0[perm], u2)
+
+
+def test_full_size_batch_properties(oracle_mod):
+    """BASELINE config 2 at full size (1024 OCPs, SQP_RTI): every problem succeeds, the measured
+    state is imposed exactly, the QP residuals the device reports are finite, and a sample of the
+    batch matches the oracle."""
+    NmpcSolver, default_opts = _gpu()
+    O = oracle_mod
+    B = 1024
+    batch = WL.make_batch(B, seed=1)
+    sg = NmpcSolver(B, default_opts(real_time_it=1, warm_start_qp=0))
+    _, _, hg = sg.kinematics(batch["qv"])
+    WL.load_into(sg, batch, hg)
+    st = sg.solve()
+    assert (st == 0).all()
+    x, u, _, _ = sg.get_solution()
+    np.testing.assert_array_equal(x[:, 0, :36], batch["qv"])
+    stats = sg.get_stats()
+    assert np.isfinite(stats["qp_res"]).all() and (stats["qp_iter"] <= 6).all()
+    idx = np.arange(0, B, 64)
+    sub = {k: (v[idx] if isinstance(v, np.ndarray) and v.shape[:1] == (B,) else v) for k, v in batch.items()}
+    so = O.OracleSolver(len(idx), O.default_opts(real_time_it=1, warm_start_qp=0))
+    WL.load_into(so, sub, hg[idx])
+    so.solve(0)
+    xo, uo, _, _ = so.get_solution()
+    assert rel_err(x[idx], xo) < REL and rel_err(u[idx], uo) < REL
+
+
+def test_device_pointers_are_accepted(oracle_mod):
+    """The C ABI takes host or device pointers (torch tensors only provide the memory)."""
+    import torch
+    NmpcSolver, default_opts = _gpu()
+    B = 8
+    batch = WL.make_batch(B, seed=14)
+    _, _, hg = oracle_mod.kinematics(batch["qv"])
+    s_h = NmpcSolver(B, default_opts(real_time_it=1, warm_start_qp=0))
+    s_d = NmpcSolver(B, default_opts(real_time_it=1, warm_start_qp=0))
+    WL.load_into(s_h, batch, hg)
+    dev = {k: (torch.from_numpy(np.ascontiguousarray(v)).cuda() if isinstance(v, np.ndarray) else v)
+           for k, v in batch.items()}
+    xg = batch["x_guess"].copy()
+    xg[:, :, 36:] = hg[:, None, :]
+    s_d.set_weights(dev["W"], dev["W_e"])
+    s_d.set_yref(dev["yref"], dev["yref_e"])
+    s_d.set_params(dev["p"])
+    s_d.set_guess(torch.from_numpy(xg).cuda(), dev["u_guess"])
+    s_d.set_x0(dev["qv"])
+    s_d.pin_stance_feet(dev["i_node"])
+    s_d.reset_duals()
+    st_d = torch.zeros(B, dtype=torch.int32, device="cuda")
+    s_d.solve(status=st_d)
+    st_h = s_h.solve()
+    np.testing.assert_array_equal(st_d.cpu().numpy(), st_h)
+    xd = torch.zeros(B, N + 1, 42, dtype=torch.float64, device="cuda")
+    ud = torch.zeros(B, N, 30, dtype=torch.float64, device="cuda")
+    s_d.get_solution_into(x=xd, u=ud)
+    xh, uh, _, _ = s_h.get_solution()
+    np.testing.assert_array_equal(xd.cpu().numpy(), xh)
+    np.testing.assert_array_equal(ud.cpu().numpy(), uh)
