@@ -13,7 +13,7 @@ owns its own 1024 problems; problems are independent, there is no collective on 
            CUDA events on the solver's stream, max over ranks.
   e2e      the same through the C ABI with HOST (pinned) buffers: H2D of every input, solve, D2H
            of the solution and status inside the timed region.
-  roofline dominant kernel (nmpc_qp_ipm_kernel): algorithmic bytes per launch / mean launch time
+  roofline dominant kernel (by summed device time): algorithmic bytes per launch / mean launch time
            (CUDA events around each launch, nmpc_set_profiling) over the measured HBM peak.
   cpu_baseline  the CPU oracle (a port of the algorithm, NOT acados) on the host cores, bounded sample.
 
@@ -40,21 +40,23 @@ METRIC = "batched NMPC SQP solves/sec (Go2 trot)"
 UNIT = "solves/s"
 N_NODES = 25
 
-# algorithmic HBM bytes of the QP kernel per OCP per IPM iteration (DESIGN.md "Roofline"): the
-# dense stage blocks are streamed once per sweep that needs them.
-_G, _M, _C, _D, _L, _V = 3108, 5330, 3024, 168, 5330, 606
+# Algorithmic HBM traffic per OCP per launch of the heavy kernels, in doubles per stage (DESIGN.md
+# "Roofline"): every dense stage block a kernel needs is counted once per sweep that needs it.
+_G, _M, _C, _D, _LP, _LPU = 3108, 5330, 3024, 168, 2880, 1830
+ALGO_DOUBLES_PER_STAGE = {
+    # K1: read C, M (H + gradient), G, bounds/masks, iterate vectors; write Ht and residual vectors
+    "qp_stage": _C + _M + _G + _D + 500 + _LP + 400,
+    # K3: backward: read Ht, G, (qt, rb), write L; forward: read the u panels of L, G, rb, write dz
+    "qp_factor": (_LP + _G + 114 + _LP) + (_LPU + _G + 42 + 72),
+    # K7: backward: read L, G, (qt, rb), write l, p; forward: read L, G, (rb, p, l), write dz, dpi
+    "qp_corr": (_LP + _G + 114 + 114) + (_LP + _G + 156 + 114),
+    # model evaluation + assembly: read x, u, p, yref; write G, M, C, D (record written + read once)
+    "linearize": _G + _M + _C + _D + 2 * 735 + 250,
+}
 
 
-def qp_bytes_per_problem(n_ipm: int, N: int = N_NODES) -> float:
-    """factor sweep: read C, M, G, write L; corrector backward: read C, L, G; two forward sweeps:
-    read L, G, C each; plus the per-stage vector workspace; residual-only exit pass: C, M, G."""
-    st = N + 1
-    fact = (_C + _M + _G + _L + _D) * st
-    corr = (_C + _L + _G) * st
-    fwd = 2 * (_L + _G + _C) * st
-    vec = 6 * _V * st
-    exit_pass = (_C + _M + _G + _D) * st
-    return 8.0 * (n_ipm * (fact + corr + fwd + vec) + exit_pass)
+def algo_bytes_per_launch(kind: str, B: int, N: int = N_NODES) -> float:
+    return 8.0 * ALGO_DOUBLES_PER_STAGE[kind] * (N + 1) * B
 
 
 def workload_opts(cfg: int):
@@ -287,23 +289,28 @@ def main() -> None:
 
     n_ipm = float(np.mean(stats["qp_iter"]))
     n_sqp = float(np.mean(stats["sqp_iter"]))
-    qp_ms, qp_n = kt["qp_ipm"]
-    lin_ms, lin_n = kt["linearize"]
-    res_ms, res_n = kt["residual"]
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    bytes_launch = qp_bytes_per_problem(round(n_ipm)) * B
-    achieved = bytes_launch / (qp_ms / max(qp_n, 1) * 1e-3) / 1e9 if qp_n else None
-    roofline = {"bound": "hbm", "kernel": "nmpc_qp_ipm_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                "algorithmic_bytes_per_launch": bytes_launch, "launch_ms": qp_ms / max(qp_n, 1),
-                "kernel_share_of_step": {"qp_ipm": qp_ms, "linearize": lin_ms, "residual": res_ms,
-                                         "launches": {"qp_ipm": qp_n, "linearize": lin_n, "residual": res_n}},
+    kinds = {k: {"ms_total": v[0], "launches": v[1]} for k, v in kt.items()}
+    heavy = [k for k in ALGO_DOUBLES_PER_STAGE if kinds[k]["launches"]]
+    for k in heavy:
+        ms_l = kinds[k]["ms_total"] / kinds[k]["launches"]
+        kinds[k]["launch_ms"] = ms_l
+        kinds[k]["achieved_gbs"] = algo_bytes_per_launch(k, B) / (ms_l * 1e-3) / 1e9
+        kinds[k]["frac_of_hbm_peak"] = kinds[k]["achieved_gbs"] / peak
+    dom = max(heavy, key=lambda k: kinds[k]["ms_total"])
+    roofline = {"bound": "hbm", "kernel": {"qp_stage": "nmpc_qp_stage_kernel", "qp_factor": "nmpc_qp_factor_kernel",
+                                           "qp_corr": "nmpc_qp_corr_solve_kernel",
+                                           "linearize": "nmpc_model_kernel+nmpc_linearize_kernel"}[dom],
+                "achieved": kinds[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                "frac": kinds[dom]["frac_of_hbm_peak"], "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                "algorithmic_bytes_per_launch": algo_bytes_per_launch(dom, B), "launch_ms": kinds[dom]["launch_ms"],
+                "per_kind": kinds, "profiled_steps": args.steps,
                 "mean_ipm_iter": n_ipm, "mean_sqp_iter": n_sqp}
 
     cpu = None
@@ -319,7 +326,7 @@ def main() -> None:
             "config": {"workload": workload_name(args.config, B), "batch_per_gpu": B, "global_batch": total,
                        "parallelism": f"problem-sharded x{world}, no data-path collective",
                        "l2": "per-step working set (QP stage blocks + factors) is "
-                             f"{B * 26 * (_G + _M + _C + _D + _L + _V) * 8 / 1e9:.2f} GB per GPU, larger than the 126 MB L2"},
+                             f"{B * 26 * (_G + _M + _C + _D + 2 * _LP + 752) * 8 / 1e9:.2f} GB per GPU, larger than the 126 MB L2"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": max(ms_e2e, wall_e2e) / args.steps},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,

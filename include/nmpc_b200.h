@@ -163,11 +163,18 @@ int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const
                   double* dz, double* pi, double* lam, double* t,
                   int32_t* qp_iter, int32_t* qp_status);
 
-/* Per-kernel device timing with CUDA events recorded on the handle's stream around each launch
- * of the three heavy kernels (0 linearise, 1 qp_ipm, 2 residual).  Replaces acados' print_time /
- * the reference's @time_fn("solve") (solver.py:396) at kernel granularity. */
+/* Per-kernel device timing with CUDA events recorded on the handle's stream around the launches,
+ * grouped by kind.  Replaces acados' print_time / the reference's @time_fn("solve")
+ * (solver.py:396) at kernel granularity.  ms / count have NMPC_PROF_KINDS entries. */
+#define NMPC_PROF_LINEARIZE 0   /* model evaluation + stage assembly                    */
+#define NMPC_PROF_QP_STAGE 1    /* stage-parallel residuals / Gamma / barrier Hessian   */
+#define NMPC_PROF_RESIDUAL 2    /* NLP residual norms (full SQP only)                   */
+#define NMPC_PROF_QP_FACTOR 3   /* Riccati factorisation + affine forward sweep         */
+#define NMPC_PROF_QP_CORR 4     /* corrector solve on the stored factorisation          */
+#define NMPC_PROF_QP_OTHER 5    /* init / decide / step lengths / sigma / rhs / update  */
+#define NMPC_PROF_KINDS 6
 int nmpc_set_profiling(nmpc_handle* h, int32_t on);
-int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[3]*/, int64_t* count /*[3]*/);
+int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[NMPC_PROF_KINDS]*/, int64_t* count /*[NMPC_PROF_KINDS]*/);
 
 /* number of kernels launched by the handle since creation (bench.py's gpu_launches claim) */
 int64_t nmpc_launch_count(const nmpc_handle* h);

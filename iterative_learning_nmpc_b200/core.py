@@ -184,10 +184,11 @@ class NmpcSolver:
 
     def kernel_times(self) -> dict:
         """{kernel: (ms, launches)} accumulated since the last call (CUDA events, handle stream)."""
-        ms = np.zeros(3)
-        cnt = np.zeros(3, dtype=np.int64)
+        kinds = ("linearize", "qp_stage", "residual", "qp_factor", "qp_corr", "qp_other")
+        ms = np.zeros(len(kinds))
+        cnt = np.zeros(len(kinds), dtype=np.int64)
         check(self.lib.nmpc_get_kernel_times(self._h, ptr(ms), ptr(cnt)), "nmpc_get_kernel_times")
-        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(("linearize", "qp_ipm", "residual"))}
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(kinds)}
 
     @property
     def stream_ptr(self) -> int:

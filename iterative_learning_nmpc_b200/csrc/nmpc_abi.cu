@@ -28,16 +28,17 @@ struct nmpc_handle {
     double *x, *u, *pi, *lam, *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;
     double *res, *qp_res, *cost;
-    unsigned long long* res_acc;
-    int32_t *status, *done, *sqp_iter, *qp_iter, *qp_status, *itmp;
+    unsigned long long *res_acc, *qp_res_acc, *qp_alpha;
+    int32_t *status, *done, *sqp_iter, *qp_iter, *qp_status, *itmp, *qp_done, *qp_nc;
+    double *qp_mu_part, *qp_mu, *qp_sigma_mu;
     // QP workspace [Bc]
-    double *G, *M, *C, *D, *L, *vec, *cost_stage;
+    double *G, *M, *C, *D, *Ht, *L, *vec, *cost_stage, *rec;
     double* scratch;             // staging for kinematics / dx0
     size_t scratch_bytes;
     // optional per-kernel timing with CUDA events on the handle's stream (bench.py roofline)
     int profiling;
     std::vector<cudaEvent_t>* ev;    // start/stop pairs
-    std::vector<int>* ev_kind;       // 0 linearize, 1 qp_ipm, 2 residual
+    std::vector<int>* ev_kind;       // NMPC_PROF_* kinds
     size_t ev_used;
 };
 
@@ -110,10 +111,18 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     A_(res, B * 4); A_(qp_res, B * 4); A_(cost, B); A_(res_acc, B * 4);
     A_(status, B); A_(done, B); A_(sqp_iter, B); A_(qp_iter, B); A_(qp_status, B); A_(itmp, B);
     A_(G, Bc * N * G_SZ); A_(M, Bc * (N + 1) * M_SZ); A_(C, Bc * (N + 1) * C_SZ); A_(D, Bc * (N + 1) * D_SZ);
-    A_(L, Bc * (N + 1) * L_SZ); A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
+    A_(qp_res_acc, B * 4); A_(qp_alpha, B * 2); A_(qp_done, B); A_(qp_nc, B);
+    A_(qp_mu_part, B * (N + 1)); A_(qp_mu, B); A_(qp_sigma_mu, B);
+    A_(Ht, Bc * (N + 1) * LP_SZ);
+    A_(L, Bc * (N + 1) * LP_SZ); A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
+    A_(rec, ((Bc * (N + 1) + REC_BLK - 1) / REC_BLK) * NMPC_REC_SIZE * REC_BLK);
 #undef A_
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_ipm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, QP_SMEM_BYTES);
+        e = cudaFuncSetAttribute(nmpc_qp_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(nmpc_qp_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K3_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(nmpc_qp_corr_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM_BYTES);
     if (e != cudaSuccess) {
         *err = (e == cudaErrorMemoryAllocation) ? NMPC_ENOMEM : (int)e;
         nmpc_destroy(h);
@@ -130,8 +139,9 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
                     h->qlam, h->qt, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
-                    h->qp_iter, h->qp_status, h->itmp, h->G, h->M, h->C, h->D, h->L, h->vec, h->cost_stage,
-                    h->scratch};
+                    h->qp_iter, h->qp_status, h->itmp, h->G, h->M, h->C, h->D, h->Ht, h->L, h->vec, h->cost_stage,
+                    h->rec, h->scratch, h->qp_res_acc, h->qp_alpha, h->qp_done, h->qp_nc, h->qp_mu_part,
+                    h->qp_mu, h->qp_sigma_mu};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->ev) { for (cudaEvent_t e : *h->ev) cudaEventDestroy(e); delete h->ev; }
@@ -280,22 +290,90 @@ static LinArgs lin_args(nmpc_handle* h, int b0)
     LinArgs a;
     a.x = h->x; a.u = h->u; a.p = h->p; a.yref = h->yref; a.yref_e = h->yref_e; a.W = h->W; a.We = h->We;
     a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.cost_stage = h->cost_stage; a.done = h->done;
-    a.N = h->N; a.b0 = b0; a.dt = h->o.dt_nodes; a.reg = h->o.reg_eps; a.reg_e = h->o.reg_eps_e;
+    a.rec = h->rec; a.N = h->N; a.b0 = b0; a.dt = h->o.dt_nodes; a.reg = h->o.reg_eps; a.reg_e = h->o.reg_eps_e;
     a.mu_c = h->o.mu_contact;
     return a;
+}
+
+// model evaluation (thread per instance x part) followed by the per-stage assembly
+static void launch_linearize(nmpc_handle* h, int b0, int Bc)
+{
+    const int N = h->N, n_inst = Bc * (N + 1);
+    ModelArgs ma;
+    ma.x = h->x; ma.rec = h->rec; ma.done = h->done; ma.n_inst = n_inst; ma.N = N; ma.b0 = b0;
+    nmpc_model_kernel<<<dim3((n_inst + MODEL_THREADS - 1) / MODEL_THREADS, NMPC_MODEL_PARTS), MODEL_THREADS, 0,
+                        h->stream>>>(ma);
+    LinArgs la = lin_args(h, b0);
+    nmpc_linearize_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la);
+    h->launches += 2;
 }
 
 static QpArgs qp_args(nmpc_handle* h, int b0)
 {
     QpArgs a;
-    a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.L = h->L; a.vec = h->vec;
+    a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.Ht = h->Ht; a.L = h->L; a.vec = h->vec;
     a.qz = h->qz; a.qpi = h->qpi; a.qlam = h->qlam; a.qt = h->qt;
-    a.dx0_ext = nullptr; a.x0 = h->x0; a.x = h->x; a.u = h->u; a.pi = h->pi; a.lam = h->lam;
+    a.res_acc = h->qp_res_acc; a.alpha = h->qp_alpha; a.nc = h->qp_nc; a.mu_part = h->qp_mu_part;
+    a.mu = h->qp_mu; a.sigma_mu = h->qp_sigma_mu; a.qp_done = h->qp_done;
     a.qp_iter = h->qp_iter; a.qp_status = h->qp_status; a.qp_res = h->qp_res;
-    a.done = h->done; a.sqp_iter = h->sqp_iter;
-    a.N = h->N; a.b0 = b0; a.max_iter = h->o.max_qp_iter; a.warm = h->o.warm_start_qp; a.apply = 1;
+    a.dx0_ext = nullptr; a.x0 = h->x0; a.x = h->x; a.u = h->u; a.pi = h->pi; a.lam = h->lam;
+    a.sqp_done = h->done; a.sqp_iter = h->sqp_iter;
+    a.N = h->N; a.b0 = b0; a.max_iter = h->o.max_qp_iter; a.warm = h->o.warm_start_qp; a.it = 0; a.last = 0;
     a.tol = h->o.qp_tol;
     return a;
+}
+
+// One OCP-QP solve for the problems [b0, b0+Bc): the interior-point iteration as a sequence of
+// stage-parallel and per-problem kernels on the handle's stream (no host synchronisation; problems
+// that have finished are skipped through qp_done).
+static void run_qp(nmpc_handle* h, QpArgs a, int Bc, bool apply)
+{
+    const int N = h->N;
+    cudaStream_t s = h->stream;
+    const dim3 gs(N + 1, Bc);
+    const int tb = (Bc + 127) / 128;
+    prof_begin(h, NMPC_PROF_QP_OTHER);
+    nmpc_qp_init_kernel<<<Bc, 128, 0, s>>>(a);
+    prof_end(h);
+    h->launches++;
+    for (int it = 0; it <= a.max_iter; it++) {
+        a.it = it; a.last = (it >= a.max_iter);
+        if (it > 0) {
+            prof_begin(h, NMPC_PROF_QP_OTHER);
+            nmpc_qp_update_kernel<<<gs, 128, 0, s>>>(a);
+            prof_end(h);
+            h->launches++;
+        }
+        prof_begin(h, NMPC_PROF_QP_STAGE);
+        nmpc_qp_stage_kernel<<<gs, QP_THREADS, K1_SMEM_BYTES, s>>>(a);
+        prof_end(h);
+        prof_begin(h, NMPC_PROF_QP_OTHER);
+        nmpc_qp_decide_kernel<<<tb, 128, 0, s>>>(a, Bc);
+        prof_end(h);
+        h->launches += 2;
+        if (a.last) break;
+        prof_begin(h, NMPC_PROF_QP_FACTOR);
+        nmpc_qp_factor_kernel<<<Bc, QP_THREADS, K3_SMEM_BYTES, s>>>(a);
+        prof_end(h);
+        prof_begin(h, NMPC_PROF_QP_OTHER);
+        nmpc_qp_step_kernel<<<gs, 128, 0, s>>>(a);
+        nmpc_qp_sigma_kernel<<<Bc, QP_THREADS, 0, s>>>(a);
+        nmpc_qp_corr_rhs_kernel<<<gs, 96, 0, s>>>(a);
+        prof_end(h);
+        prof_begin(h, NMPC_PROF_QP_CORR);
+        nmpc_qp_corr_solve_kernel<<<Bc, QP_THREADS, K7_SMEM_BYTES, s>>>(a);
+        prof_end(h);
+        prof_begin(h, NMPC_PROF_QP_OTHER);
+        nmpc_qp_step_kernel<<<gs, 128, 0, s>>>(a);
+        prof_end(h);
+        h->launches += 6;
+    }
+    if (apply) {
+        prof_begin(h, NMPC_PROF_QP_OTHER);
+        nmpc_qp_apply_kernel<<<Bc, 128, 0, s>>>(a);
+        prof_end(h);
+        h->launches++;
+    }
 }
 
 extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
@@ -313,16 +391,14 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
         const int Bc = (B - b0 < h->Bc) ? (B - b0) : h->Bc;
         for (int it = 0; it <= max_iter; it++) {
             if (rti && it == 1) break;
-            LinArgs la = lin_args(h, b0);
-            prof_begin(h, 0);
-            nmpc_linearize_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la);
+            prof_begin(h, NMPC_PROF_LINEARIZE);
+            launch_linearize(h, b0, Bc);
             prof_end(h);
-            h->launches++;
             if (!rti) {
                 ResArgs ra;
                 ra.G = h->G; ra.M = h->M; ra.C = h->C; ra.D = h->D; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi;
                 ra.lam = h->lam; ra.res_acc = h->res_acc; ra.done = h->done; ra.N = N; ra.b0 = b0;
-                prof_begin(h, 2);
+                prof_begin(h, NMPC_PROF_RESIDUAL);
                 nmpc_residual_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
                 prof_end(h);
                 nmpc_sqp_decide_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(
@@ -334,12 +410,9 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
                 nmpc_cost_sum_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, N, h->cost_stage, h->cost);
                 h->launches++;
             }
-            QpArgs qa = qp_args(h, b0);
-            prof_begin(h, 1);
-            nmpc_qp_ipm_kernel<<<Bc, QP_THREADS, QP_SMEM_BYTES, h->stream>>>(qa);
-            prof_end(h);
+            run_qp(h, qp_args(h, b0), Bc, true);
             nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
-            h->launches += 2;
+            h->launches++;
         }
     }
     CK(cudaGetLastError());
@@ -359,12 +432,12 @@ extern "C" int nmpc_set_profiling(nmpc_handle* h, int32_t on)
 }
 
 // accumulated device time [ms] and launch counts per kernel kind since the last call; resets
-extern "C" int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[3]*/, int64_t* count /*[3]*/)
+extern "C" int nmpc_get_kernel_times(nmpc_handle* h, double* ms, int64_t* count)
 {
     if (!h || !ms || !count) return NMPC_EINVAL;
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
-    for (int i = 0; i < 3; i++) { ms[i] = 0.0; count[i] = 0; }
+    for (int i = 0; i < NMPC_PROF_KINDS; i++) { ms[i] = 0.0; count[i] = 0; }
     for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
         float t = 0.f;
         CK(cudaEventElapsedTime(&t, (*h->ev)[i], (*h->ev)[i + 1]));
@@ -460,9 +533,7 @@ extern "C" int nmpc_export_qp(nmpc_handle* h, double* BAbt, double* RSQrq, doubl
     CK(cudaMemsetAsync(h->done, 0, (size_t)B * 4, h->stream));
     for (int b0 = 0; b0 < B; b0 += h->Bc) {
         const int Bc = (B - b0 < h->Bc) ? (B - b0) : h->Bc;
-        LinArgs la = lin_args(h, b0);
-        nmpc_linearize_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la);
-        h->launches++;
+        launch_linearize(h, b0, Bc);
         CK(cudaMemcpyAsync(hG.data(), h->G, (size_t)Bc * N * G_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
         CK(cudaMemcpyAsync(hM.data(), h->M, (size_t)Bc * (N + 1) * M_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
         CK(cudaMemcpyAsync(hC.data(), h->C, (size_t)Bc * (N + 1) * C_SZ * 8, cudaMemcpyDeviceToHost, h->stream));
@@ -525,9 +596,9 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
                 }
                 double* m = &hM[((size_t)bl * (N + 1) + k) * M_SZ];
                 const double* o = RSQrq + (b * (N + 1) + k) * (NZ + 1) * NZ;
-                for (int r = 0; r <= NZ; r++)
+                for (int r = 0; r <= NZ; r++)              // HPIPM convention: lower triangle is the data
                     for (int c = 0; c < NZ; c++)
-                        if (r == NZ || c <= r) m[r * M_LD + c] = o[r * NZ + c];
+                        m[r * M_LD + c] = (r < NZ && c > r) ? o[c * NZ + r] : o[r * NZ + c];
                 double* cc = &hC[((size_t)bl * (N + 1) + k) * C_SZ];
                 const double* oc = DCt + (b * (N + 1) + k) * NZ * NG;
                 for (int c = 0; c < NZ; c++)
@@ -543,9 +614,8 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
         CK(cudaMemcpyAsync(h->C, hC.data(), (size_t)Bc * (N + 1) * C_SZ * 8, cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemcpyAsync(h->D, hD.data(), (size_t)Bc * (N + 1) * D_SZ * 8, cudaMemcpyHostToDevice, h->stream));
         QpArgs qa = qp_args(h, b0);
-        qa.dx0_ext = h->scratch; qa.warm = 0; qa.apply = 0; qa.done = nullptr; qa.sqp_iter = nullptr;
-        nmpc_qp_ipm_kernel<<<Bc, QP_THREADS, QP_SMEM_BYTES, h->stream>>>(qa);
-        h->launches++;
+        qa.dx0_ext = h->scratch; qa.warm = 0; qa.sqp_done = nullptr; qa.sqp_iter = nullptr;
+        run_qp(h, qa, Bc, false);
         CK(cudaStreamSynchronize(h->stream));
     }
     CK(cudaGetLastError());

@@ -5,10 +5,11 @@
 //   problem data x0 [B][42]  p [B][(N+1)*44]  yref [B][N*76]  yref_e [B][52]  W [B][76]  We [B][52]
 //   QP stage block (per problem, per node; "k-major" so rank-k updates read contiguous rows):
 //     G  [42][74]   row l = [B(l,0:30) | A(l,0:42) | b(l) | pad]        (BAbt^T, ld 74)
-//     M  [73][73]+1 lower part = Hessian, row 72 = gradient              (RSQrq,  ld 73)
+//     M  [73][73]+1 full symmetric Hessian, row 72 = gradient             (RSQrq,  ld 73)
 //     C  [42][72]   row j = constraint j over z = [u;x]                  (DCt^T,  ld 72)
 //     lg [42] ug [42] mask [84]
-//   factor block  L [73][73]+1: Cholesky factor of M_k, row 72 = L^-1 m (ld 73)
+//   factor block  L [2880] panel-packed lower Cholesky factor of M_k + row 72 = L^-1 m
+//                 (twelve 6-column panels, nmpc_qp_ipm.cuh); Ht uses the same packing
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -63,7 +64,6 @@
 #define IPM_T_MIN 1e-16
 #define IPM_ALPHA_MIN 1e-12
 
-#define QP_THREADS 256
 
 // ---------------------------------------------------------------------------------------------
 // mbarrier + bulk async copy (TMA 1-D form; SASS: UBLKCP / SYNCS)

@@ -1,33 +1,64 @@
-// nmpc_linearize.cuh -- stage linearisation kernel: generated model code + QP stage assembly.
+// nmpc_linearize.cuh -- stage linearisation: generated model code + QP stage assembly.
 //
 // Replaces, for every node of every problem, what acados does per SQP iteration with the
 // CasADi-generated functions of the reference's model (SURVEY.md 3.2c "linearise all N+1
 // stages"; model declared at mpc_controller/utils/dynamics.py:109-134 and in the missing
 // contact_tamp FloatingBaseDynamics/PointContact): multiple-shooting defect and its Jacobians,
 // Gauss-Newton Hessian/gradient of the least-squares cost, constraint values and Jacobians.
-// One CTA per (node, problem).  The generated straight-line kinematics come in 8 independent
-// parts (<= 5k flops each); lane 0 of warps 0..7 runs one part each into shared memory while
-// warps 8..11 zero the stage block in HBM; then all threads scatter the structured non-zeros.  Formulation: spec/FORMULATION.md.
+//
+// Two kernels:
+//  1. nmpc_model_kernel: ONE THREAD per (stage instance, model part) runs the generated
+//     straight-line kinematics (feet, CoM, centroidal momentum and their Jacobians; 21k flops per
+//     instance in 8 independent parts).  A block is 128 consecutive instances of one part, so
+//     control flow is uniform and the record is written structure-of-arrays, blocked by 128
+//     instances: rec[(inst/128)][slot][inst%128] -- every store of a warp is one 256-byte line.
+//  2. nmpc_linearize_kernel: one CTA per stage instance gathers its record and scatters the
+//     structured non-zeros of the dense stage blocks G, M, C, D the Riccati kernel streams.
+// Formulation: DESIGN.md "The OCP".
 #pragma once
 #include "nmpc_common.cuh"
 
+#define REC_BLK 128                                   // instances per SoA block of the record
 #define NMPC_HD __device__ __noinline__
-#define NMPC_REC(i) rec[(i)]
+#define NMPC_REC(i) rec[(size_t)(i) * REC_BLK]
 #include "nmpc_gen_model.h"
 
-#define LIN_THREADS 384   // 8 warps run one model part each on lane 0, 4 warps clear the block
+#define LIN_THREADS 256
+#define MODEL_THREADS REC_BLK
+
+struct ModelArgs {
+    const double* x;          // [B][(N+1)*42]
+    double* rec;              // [ceil(n_inst/128)][NMPC_REC_SIZE][128]
+    const int32_t* done;      // [B] or null
+    int n_inst, N, b0;
+};
+
+__global__ void __launch_bounds__(MODEL_THREADS) nmpc_model_kernel(ModelArgs a)
+{
+    const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
+    if (i >= a.n_inst) return;
+    const int bl = i / (a.N + 1);
+    if (a.done && a.done[a.b0 + bl]) return;
+    const double* xp = a.x + ((size_t)a.b0 * (a.N + 1) + i) * NX;
+    double q[NQ], v[NQ];
+#pragma unroll
+    for (int j = 0; j < NQ; j++) { q[j] = xp[j]; v[j] = xp[NQ + j]; }
+    double* rec = a.rec + (size_t)blockIdx.x * NMPC_REC_SIZE * REC_BLK + threadIdx.x;
+    nmpc_model_part(blockIdx.y, q, v, rec);
+}
 
 struct LinArgs {
     const double* x; const double* u; const double* p;
     const double* yref; const double* yref_e; const double* W; const double* We;
     double* G; double* M; double* C; double* D;
     double* cost_stage;      // [Bc][N+1]
+    const double* rec;       // model record, blocked SoA (nmpc_model_kernel)
     const int32_t* done;     // [B] or null
     int N; int b0;
     double dt, reg, reg_e, mu_c;
 };
 
-__global__ void __launch_bounds__(LIN_THREADS, 1) nmpc_linearize_kernel(LinArgs a)
+__global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_kernel(LinArgs a)
 {
     const int k = blockIdx.x, bl = blockIdx.y, b = a.b0 + bl;
     const int tid = threadIdx.x;
@@ -59,20 +90,16 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) nmpc_linearize_kernel(LinArgs 
     double* Dp = a.D + ((size_t)bl * (N + 1) + k) * D_SZ;
 
     {
-        const int warp = tid >> 5, lane = tid & 31;
-        if (warp < NMPC_MODEL_PARTS) {
-            if (lane == 0) nmpc_model_part(warp, s_x, s_x + NQ, rec);
-            else if (warp == 0 && lane <= NF) {
-                const int ft = lane - 1;
-                tangent_basis(&s_p[ft * NMPC_NP_FOOT + P_NORMAL], s_n[ft], s_t1[ft], s_t2[ft]);
-            }
-        } else {
-            const int t = tid - 32 * NMPC_MODEL_PARTS, nt = LIN_THREADS - 32 * NMPC_MODEL_PARTS;
-            if (Gp) for (int i = t; i < G_SZ; i += nt) Gp[i] = 0.0;
-            for (int i = t; i < M_SZ; i += nt) Mp[i] = 0.0;
-            for (int i = t; i < C_SZ; i += nt) Cp[i] = 0.0;
-            for (int i = t; i < D_SZ; i += nt) Dp[i] = 0.0;
-        }
+        const int inst = bl * (N + 1) + k;
+        const double* rp = a.rec + (size_t)(inst / REC_BLK) * NMPC_REC_SIZE * REC_BLK + (inst % REC_BLK);
+        for (int i = tid; i < NMPC_REC_SIZE; i += LIN_THREADS) rec[i] = rp[(size_t)i * REC_BLK];
+        if (tid < NF) tangent_basis(&s_p[tid * NMPC_NP_FOOT + P_NORMAL], s_n[tid], s_t1[tid], s_t2[tid]);
+        // dense blocks: zero-fill with 16-byte stores, then scatter the structured non-zeros
+        double2 z2 = make_double2(0.0, 0.0);
+        if (Gp) for (int i = tid; i < G_SZ / 2; i += LIN_THREADS) reinterpret_cast<double2*>(Gp)[i] = z2;
+        for (int i = tid; i < M_SZ / 2; i += LIN_THREADS) reinterpret_cast<double2*>(Mp)[i] = z2;
+        for (int i = tid; i < C_SZ / 2; i += LIN_THREADS) reinterpret_cast<double2*>(Cp)[i] = z2;
+        for (int i = tid; i < D_SZ / 2; i += LIN_THREADS) reinterpret_cast<double2*>(Dp)[i] = z2;
     }
     __syncthreads();
 
@@ -186,10 +213,9 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) nmpc_linearize_kernel(LinArgs 
             Mp[(IH + i6) * M_LD + IH + i6] = reg;
         }
     }
-    // q block (dense lower 18x18) and q gradient
+    // q block (dense symmetric 18x18) and q gradient
     for (int e = tid; e < NQ * NQ; e += LIN_THREADS) {
-        const int i = e / NQ, j = e % NQ;
-        if (j > i) continue;
+        const int i = e / NQ, j = e % NQ;      // both triangles: the stage kernel multiplies by rows
         double s = 0.0;
         for (int ft = 0; ft < NF; ft++) {
             const double pk = s_p[ft * NMPC_NP_FOOT + P_PEAK];
