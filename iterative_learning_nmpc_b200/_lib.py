@@ -9,7 +9,7 @@ from typing import Optional
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libnmpc_b200.so")
+LIB_PATH = os.environ.get("NMPC_LIB") or os.path.join(PKG, "libnmpc_b200.so")   # NMPC_LIB: debug builds
 
 NX, NU, NZ, NP, NY, NYE, NG = 42, 30, 72, 44, 76, 52, 42
 STATUS_NAMES = {0: "SUCCESS", 1: "NAN", 2: "MAXITER", 3: "MINSTEP", 4: "QP_FAILURE"}

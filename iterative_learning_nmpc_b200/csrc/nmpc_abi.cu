@@ -629,3 +629,17 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
     CK(cudaStreamSynchronize(h->stream));
     return 0;
 }
+
+// debug builds (-DNMPC_TIMING): per-phase cycle counts of CTA 0 of nmpc_qp_factor_kernel
+extern "C" int nmpc_debug_phase_cycles(unsigned long long* out16, int reset)
+{
+#ifdef NMPC_TIMING
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpyFromSymbol(out16, g_phase_cycles, sizeof(unsigned long long) * 16));
+    if (reset) { unsigned long long z[16] = {0}; CK(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z))); }
+    return 0;
+#else
+    (void)out16; (void)reset;
+    return NMPC_ENOSYS;
+#endif
+}

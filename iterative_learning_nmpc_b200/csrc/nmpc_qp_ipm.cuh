@@ -111,13 +111,15 @@ __device__ __forceinline__ double block_sum(double v, double* red, int tid)
     return r;
 }
 
-// tile (3 rows x 6 columns) owned by thread t < N_TILES: row block rb in 0..23, column block cb <= rb/2
+// tile (3 rows x 6 columns) owned by thread t < N_TILES: column block cb in 0..11, row block rb in
+// 2*cb..23.  Tiles are numbered column block by column block, so that in the right-looking
+// factorisation whole warps run out of trailing work together (warp 0 after panel 1, ...).
 __device__ __forceinline__ void tile_of(int t, int& rb, int& cb)
 {
-    int m = 0;
-    while ((m + 1) * (m + 2) <= t) m++;
-    const int rem = t - m * (m + 1);
-    if (rem < m + 1) { rb = 2 * m; cb = rem; } else { rb = 2 * m + 1; cb = rem - (m + 1); }
+    int c = 0;
+    while ((c + 1) * (24 - c) <= t) c++;          // first tile of column block c is c * (25 - c)
+    cb = c;
+    rb = 2 * c + (t - c * (25 - c));
 }
 
 __device__ __forceinline__ void load6(const double* p, double* v)
@@ -448,18 +450,42 @@ __device__ __forceinline__ void forward_stage(const double* sLp, double* sv, con
     if (tid >= 32 && tid < 32 + NX) sv[SV_Z + NU + tid - 32] = sv[SV_DX + tid - 32];
     __syncthreads();
     for (int i = tid; i < NZ; i += QP_THREADS) vk[V_DZ + i] = sv[SV_Z + i];
-    if (!term) {                    // dx+ = G [du; dx] + rb   (G streamed from L2/HBM, one row per warp pass)
-        for (int l = warp; l < NX; l += QP_WARPS) {
-            double s = 0.0;
-            for (int c = lane; c < NZ; c += 32) s += Gp[l * G_LD + c] * sv[SV_Z + c];
-            s = warp_sum(s);
-            if (lane == 0) sv[SV_DXN + l] = s + sv[SV_RB + l];
+    if (!term) {                    // dx+ = G [du; dx] + rb : G streamed from L2/HBM; all loads of a warp's
+                                    // nine rows are issued before the first reduction (memory-level parallelism)
+        const double z0 = sv[SV_Z + lane], z1 = sv[SV_Z + 32 + lane];
+        const double z2 = lane < NZ - 64 ? sv[SV_Z + 64 + lane] : 0.0;
+        double s[9];
+#pragma unroll
+        for (int i = 0; i < 9; i++) {
+            const int l = warp + QP_WARPS * i;
+            s[i] = 0.0;
+            if (l < NX) {
+                const double* row = Gp + l * G_LD;
+                s[i] = row[lane] * z0 + row[32 + lane] * z1;
+                if (lane < NZ - 64) s[i] += row[64 + lane] * z2;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 9; i++) {
+            const int l = warp + QP_WARPS * i;
+            const double r = warp_sum(s[i]);
+            if (lane == 0 && l < NX) sv[SV_DXN + l] = r + sv[SV_RB + l];
         }
     }
     __syncthreads();
     if (!term && tid < NX) sv[SV_DX + tid] = sv[SV_DXN + tid];
     __syncthreads();
 }
+
+// Phase-cycle instrumentation of K3 (debug builds with -DNMPC_TIMING only): CTA 0, thread 0
+// accumulates clock64() deltas per phase into g_phase_cycles.
+#ifdef NMPC_TIMING
+__device__ unsigned long long g_phase_cycles[16];
+// register accumulators (static indices), flushed once at the end of the kernel
+#define TMARK(ph) do { const long long t_ = clock64(); t_acc[ph] += (unsigned long long)(t_ - t_prev); t_prev = t_; } while (0)
+#else
+#define TMARK(ph) do { } while (0)
+#endif
 
 // =============================================================================================
 // K3: backward square-root Riccati factorisation + forward sweep (affine direction).
@@ -469,6 +495,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
 {
     extern __shared__ __align__(16) double smem[];
     __shared__ __align__(8) uint64_t bar;
+    __shared__ unsigned s_gmask[24];
     const int tid = threadIdx.x;
     const int bl = blockIdx.x, b = a.b0 + bl, N = a.N;
     if (a.qp_done[b]) return;
@@ -482,14 +509,18 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
     double* vb = a.vec + (size_t)bl * (N + 1) * V_STAGE;
 
     uint32_t phase = 0;
+#ifdef NMPC_TIMING
+    unsigned long long t_acc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    long long t_prev = clock64();
+#endif
     if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
     for (int i = tid; i < LP_SZ; i += QP_THREADS) sLp[i] = 0.0;
 
-    // this thread's tile of the stage Hessian (tile threads) or its three 1x6 pieces of row 72
+    // this thread's 3x6 tile of the stage Hessian
     const bool is_tile = tid < N_TILES;
     int rb = 0, cb = 0;
     if (is_tile) tile_of(tid, rb, cb);
-    const int rcb0 = 3 * (tid - N_TILES);          // first column block of a row-72 thread
+    const int rcb0 = 3 * (tid - N_TILES);          // threads 156..159: column blocks of the short AL tiles
     const int r0 = 3 * rb, c0 = 6 * cb;
     const int doff = r0 - c0;                      // diagonal tiles: column of the diagonal in row 0 (0 or 3)
     const bool diag_tile = is_tile && (rb / 2 == cb);
@@ -505,17 +536,35 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
         for (int i = tid; i < NZ; i += QP_THREADS) sv[SV_QT + i] = vk[V_QT + i];
         if (!term) for (int i = tid; i < NX; i += QP_THREADS) sv[SV_RB + i] = vk[V_RB + i];
         __syncthreads();
+        TMARK(0);
 
         if (!term) {
             // w = L+ (L+' rb) + p+ ; L+ = Lxx of stage k+1, still in the x panels of sLp
             value_fn_times_rb([&](int l, int i) { return sLp[lp_idx(NU + l, NU + i)]; }, sv, tid);
+            TMARK(1);
             mbar_wait(&bar, phase); phase ^= 1;          // G_k has landed in sU
+            TMARK(2);
             // m = q tilde + G' w
             if (tid < NZ) {
                 double s = sv[SV_QT + tid];
                 for (int l = 0; l < NX; l++) s += sU[l * G_LD + tid] * sv[SV_W + l];
                 sv[SV_QT + tid] = s;
             }
+            // rows of G that are non-zero inside each 6-column block (the dynamics are sparse: double
+            // integrator rows + six momentum rows); generic in the data, dense G just sets every bit
+            if (tid < 12 * 2) {
+                const int cc = tid >> 1, half = tid & 1;
+                unsigned mbits = 0u;
+                for (int l = 21 * half; l < 21 * half + 21; l++) {
+                    double gv[6];
+                    load6(sU + l * G_LD + 6 * cc, gv);
+                    const bool nz = (gv[0] != 0.0) | (gv[1] != 0.0) | (gv[2] != 0.0) | (gv[3] != 0.0) | (gv[4] != 0.0) | (gv[5] != 0.0);
+                    if (nz) mbits |= 1u << (l - 21 * half);
+                }
+                s_gmask[tid] = mbits;
+            }
+            __syncthreads();
+            TMARK(3);
             // AL = L+' G (42 x 72): 3 x 6 register tiles, rows 3*ib.., cols 6*cc..; the 156 tiles of
             // ib < 13 go to the tile threads, the 12 short tiles of ib = 13 to the last four threads
             {
@@ -531,7 +580,11 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                         for (int c = 0; c < 6; c++) al[r][c] = 0.0;
                     const int jbi = (NU + i0) / PB, ci = (NU + i0) % PB;     // panel / column of L+(:, i0)
                     const double* lcol = sLp + P_OFF(jbi) + ci;
-                    for (int l = i0; l < NX; l++) {
+                    unsigned long long rows = ((unsigned long long)s_gmask[2 * cc + 1] << 21) | s_gmask[2 * cc];
+                    rows &= ~((1ULL << i0) - 1ULL);
+                    while (rows) {
+                        const int l = __ffsll((long long)rows) - 1;
+                        rows &= rows - 1ULL;
                         // L+(l, i0..i0+2): entries above the diagonal are stored as zeros
                         const double* lp = lcol + (NU + l - PB * jbi) * PB;
                         const double l0 = lp[0], l1 = lp[1], l2 = lp[2];
@@ -548,6 +601,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                     }
                 }
                 __syncthreads();          // every read of G is done: write AL in place
+                TMARK(4);
                 if (is_tile) {
                     const int i0 = 3 * (tid / 12), cc0 = 6 * (tid % 12);
 #pragma unroll
@@ -560,6 +614,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                 }
             }
             __syncthreads();
+            TMARK(5);
         }
         // stage Hessian tile from HBM straight into registers (18 contiguous doubles), + AL' AL
         if (is_tile) {
@@ -582,14 +637,9 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                         for (int c = 0; c < 6; c++) if (c == doff + r) acc[r][c] += IPM_REG_PRIM;
                 }
             }
-        } else {
-            // row 72 (the linear term m) is owned by the last four threads, three 1x6 pieces each
-#pragma unroll
-            for (int r = 0; r < 3; r++)
-#pragma unroll
-                for (int c = 0; c < 6; c++) acc[r][c] = sv[SV_QT + 6 * (rcb0 + r) + c];
         }
         __syncthreads();            // all reads of AL (sU) and of L+ (sLp) are done
+        TMARK(6);
         if (tid == 0) {
             bulk_store_wait_read();               // the previous factor has left sLp
             if (k > 0) {                          // sU is free: prefetch G of the next stage
@@ -598,6 +648,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
             }
         }
         __syncthreads();
+        TMARK(7);
 
         // ---- fused right-looking Cholesky on the register tiles; panels go through sLp ----
         for (int jb = jb0; jb < NPANEL; jb++) {
@@ -610,14 +661,12 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
 #pragma unroll
                         for (int c = 0; c < 6; c++) pan[(r0 + r - j0) * PB + c] = acc[r][c];
                 }
-            } else if (jb >= rcb0 && jb < rcb0 + 3) {
-#pragma unroll
-                for (int c = 0; c < 6; c++) {
-                    const double v = (jb == rcb0) ? acc[0][c] : (jb == rcb0 + 1 ? acc[1][c] : acc[2][c]);
-                    pan[(NZ - j0) * PB + c] = v;
-                }
             }
+            // row 72 of the panel: the linear term m (kept in shared memory, updated below by the
+            // same threads 0..5 that copy it here)
+            if (tid < PB) pan[(NZ - j0) * PB + tid] = sv[SV_QT + j0 + tid];
             __syncthreads();
+            TMARK(8);
             // panel factorisation: thread t handles row j0 + t; the 6x6 diagonal block is factored
             // redundantly in registers by every row thread (no extra barrier).  Non-positive pivots
             // zero the column (BLASFEO potrf rule).  The diagonal-block rows are written back after
@@ -634,8 +683,9 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
 #pragma unroll
                         for (int e = 0; e < c; e++) v -= Dm[aa][e] * Dm[c][e];
                         if (c == aa) {
+                            // one rsqrt per pivot (the serial chain of the factorisation): 1/L_aa, L_aa = v/L_aa
                             double d = 0.0, inv = 0.0;
-                            if (v > 0.0) { d = sqrt(v); inv = 1.0 / d; }
+                            if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
                             Dm[aa][aa] = inv;
                             if (tid == aa) drow[c] = d;
                         } else {
@@ -649,6 +699,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                         for (int c = aa + 1; c < PB; c++) drow[c] = 0.0;
                     }
                 }
+                TMARK(14);
                 if (tid >= PB) {
                     double rowv[PB];
                     load6(pan + tid * PB, rowv);
@@ -663,7 +714,9 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                     for (int jj = 0; jj < PB; jj++) pan[tid * PB + jj] = rowv[jj];
                 }
             }
+            TMARK(9);
             __syncthreads();
+            TMARK(10);
             if (tid < PB) {
 #pragma unroll
                 for (int c = 0; c < PB; c++) pan[tid * PB + c] = drow[c];
@@ -683,22 +736,20 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
                         }
                     }
                 }
-            } else {
-                const double* pa = pan + (NZ - j0) * PB;
-#pragma unroll
-                for (int r = 0; r < 3; r++) {
-                    const int cbr = rcb0 + r;
-                    if (cbr > jb) {
-                        const double* pb = pan + (6 * cbr - j0) * PB;
-#pragma unroll
-                        for (int kk = 0; kk < PB; kk++) {
-                            const double av = pa[kk];
-#pragma unroll
-                            for (int c = 0; c < 6; c++) acc[r][c] -= av * pb[c * PB + kk];
-                        }
-                    }
-                }
             }
+            // trailing update of row 72: m_c -= l . L(c, j0..j0+5), thread t owns column j0 + 6 + t
+            if (tid < NZ - j0 - PB) {
+                const double* pa = pan + (NZ - j0) * PB;
+                const double* pb = pan + (PB + tid) * PB;
+                double av[6], bv[6];
+                load6(pa, av);
+                load6(pb, bv);
+                double sm_ = sv[SV_QT + j0 + PB + tid];
+#pragma unroll
+                for (int kk = 0; kk < PB; kk++) sm_ -= av[kk] * bv[kk];
+                sv[SV_QT + j0 + PB + tid] = sm_;
+            }
+            TMARK(11);
         }
         // ---- factor -> HBM (one bulk store); p_k = Lxx lx stays in shared memory for stage k-1 ----
         fence_proxy_async();
@@ -710,6 +761,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
             sv[SV_PN + tid] = s;
         }
         __syncthreads();
+        TMARK(12);
     }
 
     // ================= forward sweep (affine direction; multipliers dpi not needed) =================
@@ -730,6 +782,13 @@ __global__ void __launch_bounds__(QP_THREADS, 4) nmpc_qp_factor_kernel(QpArgs a)
         }
         forward_stage<false>(sLp, sv, term ? nullptr : Gb + (size_t)k * G_SZ, vk, nullptr, term, tid);
     }
+    TMARK(13);
+#ifdef NMPC_TIMING
+    if (bl == 0 && tid == 0) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) g_phase_cycles[i] += t_acc[i];
+    }
+#endif
 }
 
 // =============================================================================================
