@@ -149,6 +149,10 @@ int nmpc_get_qp_step(nmpc_handle* h, double* dz);
 /* qv [n,36] -> feet [n,4,3], com [n,3], hg [n,6]; outputs may be NULL. */
 int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, double* feet, double* com, double* hg);
 
+/* QuadrupedDynamics.id_torques (dynamics.py:136-163): tau [n,12] = rnea(q, v, a)[joints] -
+ * sum_feet J_foot(q)^T f.  qva [n,54] = (q_euler | v | a), f [n,12] world-frame contact forces. */
+int nmpc_inverse_dynamics(nmpc_handle* h, const double* qva, const double* f, int32_t n, double* tau);
+
 /* ---- test / diagnostics hooks (parity tests compare these with the oracle) ------------ */
 /* Linearise at the current iterate without solving and export the dense OCP-QP:
  * BAbt [B,N,73,42] (rows: B^T(30) | A^T(42) | b^T), RSQrq [B,N+1,73,72] (lower part valid; last
@@ -179,6 +183,8 @@ int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[NMPC_PROF_KINDS]*/, int6
 /* number of kernels launched by the handle since creation (bench.py's gpu_launches claim) */
 int64_t nmpc_launch_count(const nmpc_handle* h);
 const char* nmpc_version(void);
+/* total mass of the compiled robot model (kg): pin_model mass, used for force guesses */
+double nmpc_model_mass(void);
 
 #ifdef __cplusplus
 }

@@ -73,12 +73,14 @@ _SIGS = {
     "nmpc_get_stats": (C.c_int, [C.c_void_p, C.POINTER(NmpcStats)]),
     "nmpc_get_qp_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 3),
+    "nmpc_inverse_dynamics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "nmpc_export_qp": (C.c_int, [C.c_void_p] + [C.c_void_p] * 6),
     "nmpc_solve_qp": (C.c_int, [C.c_void_p] + [C.c_void_p] * 13),
     "nmpc_launch_count": (C.c_int64, [C.c_void_p]),
     "nmpc_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "nmpc_get_kernel_times": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "nmpc_version": (C.c_char_p, []),
+    "nmpc_model_mass": (C.c_double, []),
 }
 EXPORTED_SYMBOLS = ["nmpc_create"] + list(_SIGS)
 

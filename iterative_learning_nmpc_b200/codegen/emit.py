@@ -47,7 +47,7 @@ def record_layout(nq: int, nfeet: int):
 def generate(urdf: str = DEFAULT_URDF, feet: List[str] = None) -> Tuple[str, dict]:
     feet = feet or DEFAULT_FEET
     model = load_urdf(urdf)
-    sk = build_symbolic(model, feet)
+    sk = build_symbolic(model, feet, with_dynamics=True)
     g = sk.g
     nq = model.nq
     nf = len(feet)
@@ -105,6 +105,20 @@ def generate(urdf: str = DEFAULT_URDF, feet: List[str] = None) -> Tuple[str, dic
         outs0.append((f"h[{i}]", sk.h[i]))
     body0, stats0 = g.emit_body(outs0, sym_expr)
 
+    # feed-forward joint torques: inverse dynamics minus the contact forces mapped through the foot
+    # Jacobians (dynamics.py:136-163: pin.rnea(q, v, a)[-nu:] - sum_feet f_ee @ J_ee[:3, -nu:])
+    sym_expr.update({f"a{i}": f"a[{i}]" for i in range(nq)})
+    fsym = [g.sym(f"f{i}") for i in range(3 * nf)]
+    sym_expr.update({f"f{i}": f"f[{i}]" for i in range(3 * nf)})
+    outs_tau: List[Tuple[str, int]] = []
+    for j in range(6, nq):
+        t = sk.tau[j]
+        for ft in range(nf):
+            for i in range(3):
+                t = g.sub(t, g.mul(sk.foot_J[ft][i][j], fsym[3 * ft + i]))
+        outs_tau.append((f"tau[{j - 6}]", t))
+    body_tau, stats_tau = g.emit_body(outs_tau, sym_expr)
+
     with open(urdf, "rb") as fh:
         digest = hashlib.sha256(fh.read()).hexdigest()[:16]
 
@@ -150,9 +164,15 @@ def generate(urdf: str = DEFAULT_URDF, feet: List[str] = None) -> Tuple[str, dic
     hdr.append("NMPC_HD void nmpc_model_kin0(const double* __restrict__ q, const double* __restrict__ v,"
                " double* __restrict__ feet, double* __restrict__ com, double* __restrict__ h)\n{\n")
     hdr.append(body0)
-    hdr.append("}\n#endif /* NMPC_GEN_MODEL_H */\n")
+    hdr.append("}\n")
+    hdr.append(f"\n/* joint torques tau[{model.nj}] = rnea(q, v, a)[joints] - sum_feet J_foot^T f: {stats_tau['flops']} flops */\n")
+    hdr.append("#ifdef NMPC_WITH_RNEA\n")
+    hdr.append("NMPC_HD void nmpc_model_rnea(const double* __restrict__ q, const double* __restrict__ v,"
+               " const double* __restrict__ a, const double* __restrict__ f, double* __restrict__ tau)\n{\n")
+    hdr.append(body_tau)
+    hdr.append("}\n#endif\n#endif /* NMPC_GEN_MODEL_H */\n")
     meta = {"nq": nq, "nfeet": nf, "mass": sk.mass, "layout": off,
-            "stats_full": stats_full, "stats0": stats0, "model": model, "sk": sk}
+            "stats_full": stats_full, "stats0": stats0, "stats_tau": stats_tau, "model": model, "sk": sk}
     return "".join(hdr), meta
 
 

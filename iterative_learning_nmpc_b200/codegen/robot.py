@@ -198,9 +198,14 @@ class SymbolicKinematics:
     h_q: List[List[int]]             # [6][nq]
     h_v: List[List[int]]             # [6][nq]
     mass: float
+    a: List[int] = field(default_factory=list)     # acceleration symbols (Euler-rate derivatives + joints)
+    tau: List[int] = field(default_factory=list)   # [nq] generalised forces of inverse dynamics M a + C v + g
 
 
-def build_symbolic(model: RobotModel, feet_frames: Sequence[str]) -> SymbolicKinematics:
+GRAVITY = 9.81
+
+
+def build_symbolic(model: RobotModel, feet_frames: Sequence[str], with_dynamics: bool = False) -> SymbolicKinematics:
     g = Graph()
     nq = model.nq
     q = [g.sym(f"q{i}") for i in range(nq)]
@@ -279,6 +284,8 @@ def build_symbolic(model: RobotModel, feet_frames: Sequence[str]) -> SymbolicKin
 
     h_lin = [E(g, g.zero)] * 3
     h_ang = [E(g, g.zero)] * 3
+    kinetic = E(g, g.zero)
+    potential = E(g, g.zero)
     for name, link in model.links.items():
         if link.mass <= 0.0:
             continue
@@ -289,6 +296,10 @@ def build_symbolic(model: RobotModel, feet_frames: Sequence[str]) -> SymbolicKin
         w = link_w[name]
         # R I R^T w
         Iw = _matvec(R, _matvec(_const_mat(g, link.inertia), _matvec(_transpose(R), w)))
+        if with_dynamics:
+            kinetic = kinetic + (0.5 * link.mass) * (cd[0] * cd[0] + cd[1] * cd[1] + cd[2] * cd[2]) \
+                + 0.5 * (w[0] * Iw[0] + w[1] * Iw[1] + w[2] * Iw[2])
+            potential = potential + (link.mass * GRAVITY) * c[2]
         r = [a - b for a, b in zip(c, com_e)]
         mv = [link.mass * x for x in cd]
         orb = _cross(r, mv)
@@ -296,4 +307,17 @@ def build_symbolic(model: RobotModel, feet_frames: Sequence[str]) -> SymbolicKin
     h = nodes(h_lin) + nodes(h_ang)
     h_q = g.jacobian(h, q)
     h_v = g.jacobian(h, v)
-    return SymbolicKinematics(g, q, v, foot_p, foot_J, foot_v, foot_vq, com, com_J, h, h_q, h_v, mass)
+    sk = SymbolicKinematics(g, q, v, foot_p, foot_J, foot_v, foot_vq, com, com_J, h, h_q, h_v, mass)
+    if with_dynamics:
+        # Inverse dynamics from the Lagrangian L = T - V in the generalised coordinates (q, v = q_dot):
+        #   tau = d/dt (dT/dv) - dT/dq + dV/dq,   d/dt (dT/dv) = (d2T/dv dq) v + (d2T/dv2) a
+        # which equals Pinocchio's rnea(q, v, a) on the joint rows (dynamics.py:156); the base rows are
+        # the generalised forces conjugate to the Euler coordinates.
+        acc = [g.sym(f"a{i}") for i in range(nq)]
+        mom = g.grad(kinetic.n, v)
+        mom_dot = [g.add(x, y) for x, y in zip(g.jvp(mom, q, v), g.jvp(mom, v, acc))]
+        dT_dq = g.grad(kinetic.n, q)
+        dV_dq = g.grad(potential.n, q)
+        sk.a = acc
+        sk.tau = [g.add(g.sub(md, tq), vq) for md, tq, vq in zip(mom_dot, dT_dq, dV_dq)]
+    return sk

@@ -156,6 +156,19 @@ class NmpcSolver:
         check(self.lib.nmpc_kinematics(self._h, ptr(a), n, ptr(feet), ptr(com), ptr(hg)), "nmpc_kinematics")
         return feet, com, hg
 
+    @property
+    def total_mass(self) -> float:
+        return float(self.lib.nmpc_model_mass())
+
+    def inverse_dynamics(self, qva, f):
+        """tau [n,12] = rnea(q, v, a)[joints] - sum_feet J^T f  (dynamics.py:136-163)."""
+        a = _f64(qva, (-1, 54))
+        n = a.shape[0]
+        b = _f64(f, (n, 12))
+        tau = np.zeros((n, 12))
+        check(self.lib.nmpc_inverse_dynamics(self._h, ptr(a), ptr(b), n, ptr(tau)), "nmpc_inverse_dynamics")
+        return tau
+
     # -- diagnostics --------------------------------------------------------------------
     def export_qp(self) -> dict:
         B, N = self.B, self.N

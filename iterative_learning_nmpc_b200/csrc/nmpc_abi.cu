@@ -519,6 +519,26 @@ extern "C" int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, doub
     return (int)cudaGetLastError();
 }
 
+extern "C" double nmpc_model_mass(void) { return NMPC_MASS; }
+
+extern "C" int nmpc_inverse_dynamics(nmpc_handle* h, const double* qva, const double* f, int32_t n, double* tau)
+{
+    if (!h || !qva || !f || !tau || n <= 0) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t nd = (size_t)n * (54 + 12 + 12);
+    if (int r = ensure_scratch(h, nd * 8)) return r;
+    double* d_qva = h->scratch;
+    double* d_f = d_qva + (size_t)n * 54;
+    double* d_tau = d_f + (size_t)n * 12;
+    CK(cudaMemcpyAsync(d_qva, qva, (size_t)n * 54 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_f, f, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
+    nmpc_rnea_kernel<<<(n + 63) / 64, 64, 0, h->stream>>>(d_qva, d_f, n, d_tau);
+    h->launches++;
+    CK(cudaMemcpyAsync(tau, d_tau, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return (int)cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------------
 // diagnostics: export / import dense QPs in the HPIPM-style layouts of the header
 // ---------------------------------------------------------------------------------------------

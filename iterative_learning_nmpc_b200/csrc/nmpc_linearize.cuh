@@ -21,6 +21,7 @@
 #define REC_BLK 128                                   // instances per SoA block of the record
 #define NMPC_HD __device__ __noinline__
 #define NMPC_REC(i) rec[(size_t)(i) * REC_BLK]
+#define NMPC_WITH_RNEA 1
 #include "nmpc_gen_model.h"
 
 #define LIN_THREADS 256
@@ -381,6 +382,20 @@ __global__ void nmpc_kin0_kernel(const double* qv, int n, double* feet, double* 
     if (feet) for (int j = 0; j < 12; j++) feet[(size_t)i * 12 + j] = f[j];
     if (com) for (int j = 0; j < 3; j++) com[(size_t)i * 3 + j] = c[j];
     if (hg) for (int j = 0; j < 6; j++) hg[(size_t)i * 6 + j] = h[j];
+}
+
+// feed-forward joint torques (QuadrupedDynamics.id_torques, dynamics.py:136-163): thread per instance
+__global__ void nmpc_rnea_kernel(const double* qva, const double* f, int n, double* tau)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double q[NQ], v[NQ], a[NQ], ff[12], t[NQ - 6];
+    for (int j = 0; j < NQ; j++) {
+        q[j] = qva[(size_t)i * 54 + j]; v[j] = qva[(size_t)i * 54 + NQ + j]; a[j] = qva[(size_t)i * 54 + 2 * NQ + j];
+    }
+    for (int j = 0; j < 12; j++) ff[j] = f[(size_t)i * 12 + j];
+    nmpc_model_rnea(q, v, a, ff, t);
+    for (int j = 0; j < NQ - 6; j++) tau[(size_t)i * (NQ - 6) + j] = t[j];
 }
 
 // x0 = [q, v, hg(q, v)]; also overwrites node 0 of the iterate (solver.py:179-192)

@@ -38,6 +38,7 @@
 
 #define NMPC_HD static
 #define NMPC_REC(i) rec[(i)]
+#define NMPC_WITH_RNEA 1
 #include "nmpc_gen_model.h"
 
 /* z = [u; x] index helpers */
@@ -722,6 +723,13 @@ int oracle_kinematics(const double* qv, int32_t n, double* feet, double* com, do
         if (com) memcpy(com + 3 * i, c, sizeof(c));
         if (hg) memcpy(hg + 6 * i, hh, sizeof(hh));
     }
+    return 0;
+}
+
+int oracle_inverse_dynamics(const double* qva, const double* f, int32_t n, double* tau)
+{
+    for (int i = 0; i < n; i++)
+        nmpc_model_rnea(qva + 54 * i, qva + 54 * i + 18, qva + 54 * i + 36, f + 12 * i, tau + 12 * i);
     return 0;
 }
 

@@ -65,7 +65,8 @@ def lib():
                      "oracle_set_yref", "oracle_set_weights", "oracle_set_params",
                      "oracle_pin_stance_feet", "oracle_set_guess", "oracle_reset_duals",
                      "oracle_shift_warm_start", "oracle_solve", "oracle_get_solution",
-                     "oracle_get_stats", "oracle_get_qp_step", "oracle_export_qp", "oracle_solve_qp"):
+                     "oracle_get_stats", "oracle_get_qp_step", "oracle_export_qp", "oracle_solve_qp",
+                     "oracle_inverse_dynamics"):
             getattr(_lib, name).restype = C.c_int
     return _lib
 
@@ -91,6 +92,15 @@ def kinematics(qv: np.ndarray):
     feet, com, hg = np.zeros((n, 4, 3)), np.zeros((n, 3)), np.zeros((n, 6))
     lib().oracle_kinematics(_p(qv), C.c_int32(n), _p(feet), _p(com), _p(hg))
     return feet, com, hg
+
+
+def inverse_dynamics(qva: np.ndarray, f: np.ndarray) -> np.ndarray:
+    qva = _f64(qva).reshape(-1, 54)
+    n = qva.shape[0]
+    f = _f64(f).reshape(n, 12)
+    tau = np.zeros((n, 12))
+    lib().oracle_inverse_dynamics(_p(qva), _p(f), C.c_int32(n), _p(tau))
+    return tau
 
 
 def model_record(qv: np.ndarray) -> np.ndarray:

@@ -1,0 +1,68 @@
+"""TEST INFRASTRUCTURE: an adapter that lets the reference-facing front-end
+(`QuadrupedAcadosSolver` / `LocomotionMPC`) run on the CPU oracle, so that the host logic can be
+tested without a GPU and so that GPU runs of the front-end have a checker.  Never imported by the
+package; the product front-end only opens the CUDA library."""
+import ctypes as C
+
+import numpy as np
+
+from oracle import oracle as O
+
+
+def _to_oracle_opts(opts) -> "O.NmpcOpts":
+    o = O.NmpcOpts()
+    assert C.sizeof(o) == C.sizeof(opts)
+    C.memmove(C.byref(o), C.byref(opts), C.sizeof(o))
+    return o
+
+
+class OracleHandle:
+    """Method-for-method stand-in for `core.NmpcSolver` on top of `oracle.OracleSolver`."""
+
+    total_mass = None
+
+    def __init__(self, batch, opts, device=0):
+        self.B = int(batch)
+        self.opts = opts.copy()
+        self.N = int(opts.n_nodes)
+        self._s = O.OracleSolver(self.B, _to_oracle_opts(opts))
+        dims = np.zeros(8, dtype=np.int32)
+        self.total_mass = 15.017 if OracleHandle.total_mass is None else OracleHandle.total_mass
+        self.launch_count = 0
+
+    def set_opts(self, opts=None, **kw):
+        o = (opts or self.opts).copy()
+        for k, v in kw.items():
+            setattr(o, k, v)
+        self.opts = o
+        self._s.set_opts(_to_oracle_opts(o))
+
+    def solve(self, status=None, sync=True):
+        return self._s.solve(1)
+
+    def get_solution(self, duals=True):
+        return self._s.get_solution()
+
+    def kinematics(self, qv):
+        return O.kinematics(qv)
+
+    def inverse_dynamics(self, qva, f):
+        return O.inverse_dynamics(qva, f)
+
+    def set_profiling(self, on=True):
+        pass
+
+    def kernel_times(self):
+        return {}
+
+    def synchronize(self):
+        pass
+
+    def __getattr__(self, name):          # set_x0, set_yref, set_weights, set_params, set_guess, ...
+        return getattr(self._s, name)
+
+
+def use_oracle_backend(monkeypatch):
+    from iterative_learning_nmpc_b200.mpc_controller.utils import acados_helper as H
+    monkeypatch.setattr(H.AcadosSolverHelper, "_make_handle",
+                        lambda self: OracleHandle(self.batch, self._opts, self.device))

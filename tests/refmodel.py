@@ -81,3 +81,52 @@ class NumericModel:
             hl += link.mass * cd
             ha += R @ link.inertia @ R.T @ w + np.cross(c - com, link.mass * cd)
         return np.concatenate([hl, ha])
+
+    # -- Newton-Euler joint torques with finite-difference link accelerations (independent of the
+    #    Lagrangian derivation the code generator uses) -------------------------------------------
+    def _omega(self, q, v, name, h=1e-6):
+        Rp, Rm, R0 = self.poses(q + h * v)[name][0], self.poses(q - h * v)[name][0], self.poses(q)[name][0]
+        Wx = ((Rp - Rm) / (2 * h)) @ R0.T
+        return np.array([Wx[2, 1], Wx[0, 2], Wx[1, 0]])
+
+    def joint_torques(self, q, v, a, f_feet, e=1e-4, g=9.81):
+        """tau[12] = inverse dynamics of the joints minus the contact forces f_feet [4,3] (world)."""
+        q, v, a = (np.asarray(x, float) for x in (q, v, a))
+        traj = lambda t: (q + t * v + 0.5 * t * t * a, v + t * a)
+        P0 = self.poses(q)
+        Pp, Pm = self.poses(traj(e)[0]), self.poses(traj(-e)[0])
+        wrench = {}                       # link -> (force, moment about the link's CoM), world axes
+        for name, link in self.m.links.items():
+            if link.mass <= 0:
+                continue
+            R, p = P0[name]
+            c = lambda P: P[name][1] + P[name][0] @ link.com
+            cdd = (c(Pp) - 2 * c(P0) + c(Pm)) / (e * e)
+            w0 = self._omega(q, v, name)
+            wd = (self._omega(*traj(e), name) - self._omega(*traj(-e), name)) / (2 * e)
+            Iw = R @ link.inertia @ R.T
+            wrench[name] = (link.mass * (cdd + np.array([0, 0, g])), Iw @ wd + np.cross(w0, Iw @ w0), c(P0))
+        children = {}
+        for j in self.m.joints:
+            children.setdefault(j.parent, []).append(j)
+
+        def subtree(link):
+            out = [link]
+            for j in children.get(link, []):
+                out += subtree(j.child)
+            return out
+
+        tau = np.zeros(12)
+        for j in self.m.act_joints:
+            Rp, pp = P0[j.parent]
+            pj = pp + Rp @ j.xyz
+            axis_w = Rp @ rpy_matrix(j.rpy) @ j.axis
+            m = np.zeros(3)
+            for name in subtree(j.child):
+                if name in wrench:
+                    F, Nn, c = wrench[name]
+                    m += Nn + np.cross(c - pj, F)
+                if name in FEET:
+                    m -= np.cross(P0[name][1] - pj, np.asarray(f_feet, float)[FEET.index(name)])
+            tau[self.idx[j.name] - 6] = axis_w @ m
+        return tau

@@ -1,0 +1,95 @@
+"""The reference-facing front-end on the CUDA library vs the same front-end on the CPU oracle
+(tests/oracle_backend.py): one tick, a warm-started second tick, a batched tick, a short
+LocomotionMPC open-loop run (BASELINE config 1 in miniature) and the feed-forward torques."""
+import numpy as np
+import pytest
+
+from iterative_learning_nmpc_b200 import problem as P
+from iterative_learning_nmpc_b200 import workloads as WL
+from oracle_backend import OracleHandle
+from test_front_end import FEET, _front_end, _scenario
+
+pytestmark = pytest.mark.gpu
+REL = 1e-6
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1.0))
+
+
+def _on_oracle(obj):
+    """Swap the handle of an already-built front-end for the oracle (same options)."""
+    obj._handle = OracleHandle(obj.batch, obj._opts, 0)
+    obj.dyn.bind_device(obj._handle.kinematics, obj._handle.inverse_dynamics)
+    obj.update_cost_weights()
+    return obj
+
+
+def test_model_mass_and_inverse_dynamics(oracle_mod):
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+    s = NmpcSolver(1, default_opts())
+    assert abs(s.total_mass - WL.MASS) < 1e-3
+    rng = np.random.default_rng(5)
+    n = 300
+    qva = np.tile(np.concatenate((P.nominal_state(0.3), np.zeros(18))), (n, 1))
+    qva[:, :18] += rng.uniform(-0.3, 0.3, (n, 18))
+    qva[:, 18:] = rng.uniform(-3, 3, (n, 36))
+    f = rng.uniform(-40, 80, (n, 12))
+    tg = s.inverse_dynamics(qva, f)
+    to = oracle_mod.inverse_dynamics(qva, f)
+    assert rel_err(tg, to) < 1e-11
+
+
+def test_two_ticks_match_oracle(oracle_mod):
+    sc = _scenario(31, 0)
+    g, o = _front_end(sc), _on_oracle(_front_end(sc))
+    outs = []
+    for s in (g, o):
+        s.dyn.update_pin(sc["q"], sc["v"])
+        s.set_max_iter(15)
+        s.init(0, sc["q"], sc["v"], sc["base_ref"], sc["base_ref_e"], P.GO2_JOINT_HOME, 0.05, sc["cnt"], None, sc["peak"])
+        first = [a.copy() for a in s.solve()] + [s.status.copy()]
+        sc2 = _scenario(31, 1)
+        s.set_max_iter(1)
+        q1, v1 = first[0][1].copy(), first[1][1].copy()
+        s.dyn.update_pin(q1, v1)
+        s.init(1, q1, v1, sc["base_ref"], sc["base_ref_e"], P.GO2_JOINT_HOME, 0.05, sc2["cnt"], None, sc2["peak"])
+        second = [a.copy() for a in s.solve()] + [s.status.copy()]
+        outs.append((first, second))
+    for tick in (0, 1):
+        a, b = outs[0][tick], outs[1][tick]
+        assert np.array_equal(a[5], b[5])
+        for k in range(4):
+            assert rel_err(a[k], b[k]) < REL, (tick, k)
+
+
+def test_batched_tick_matches_oracle(oracle_mod):
+    scs = [_scenario(40 + b, i) for b, i in enumerate((0, 2, 5, 7, 11))]
+    stack = lambda k: np.stack([sc[k] for sc in scs])
+    res = []
+    for mk in (lambda s: s, _on_oracle):
+        sb = mk(_front_end(scs[0], batch=len(scs)))
+        sb.init(np.array([sc["i_node"] for sc in scs]), stack("q"), stack("v"), stack("base_ref"), stack("base_ref_e"),
+                P.GO2_JOINT_HOME, 0.05, stack("cnt"), None, stack("peak"))
+        res.append([a.copy() for a in sb.solve()] + [sb.status.copy()])
+    assert np.array_equal(res[0][5], res[1][5])
+    for k in range(4):
+        assert rel_err(res[0][k], res[1][k]) < REL, k
+
+
+def test_locomotion_mpc_open_loop_matches_oracle(oracle_mod):
+    """Config 1 in miniature: three replanning ticks of the sim-free loop (first one with 15 SQP
+    iterations), GPU vs oracle front-end, compared on the visited configurations."""
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import LocomotionMPC
+    trajs = []
+    for use_oracle in (False, True):
+        mpc = LocomotionMPC(None, FEET, "go2", gait_name="trot", print_info=False, solve_async=False)
+        if use_oracle:
+            _on_oracle(mpc.solver)
+        mpc.set_command(np.array([0.15, 0.0, 0.0]), 0.0)
+        q_mj = np.zeros(19); q_mj[2] = WL.STAND_HEIGHT; q_mj[3] = 1.0; q_mj[7:] = P.GO2_JOINT_HOME
+        trajs.append(mpc.open_loop(q_mj, np.zeros(18), 0.0855))
+    assert trajs[0].shape == trajs[1].shape == (86, 19)
+    assert rel_err(trajs[0], trajs[1]) < 1e-5      # three chained solves: tolerance compounds

@@ -93,3 +93,30 @@ def test_total_mass_and_stand_height(oracle_mod, num):
     feet, _, hg = oracle_mod.kinematics(qv)
     np.testing.assert_allclose(feet[0, :, 2], 0.0, atol=1e-9)     # feet on the ground
     np.testing.assert_allclose(hg, 0.0, atol=1e-14)
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_inverse_dynamics_matches_newton_euler(oracle_mod, num, seed):
+    """Generated Lagrangian inverse dynamics (stand-in for pin.rnea - J^T f, dynamics.py:136-163)
+    vs a numeric Newton-Euler pass with finite-difference link accelerations."""
+    rng = np.random.default_rng(100 + seed)
+    q, v = _rand_qv(rng)
+    a = rng.uniform(-5, 5, NQ)
+    f = rng.uniform(-30, 60, (4, 3))
+    tau = oracle_mod.inverse_dynamics(np.concatenate([q, v, a]), f.reshape(-1))[0]
+    ref = num.joint_torques(q, v, a, f)
+    assert np.abs(tau - ref).max() < 2e-4 * max(1.0, np.abs(ref).max()), (tau, ref)
+
+
+def test_inverse_dynamics_static_is_gravity_minus_contacts(oracle_mod, num):
+    """At rest with zero forces the torques are pure gravity terms; adding the forces that carry the
+    weight changes them by -J^T f exactly."""
+    q = np.zeros(NQ); q[2] = 0.3; q[6:] = np.tile([0.0, 0.9, -1.8], 4)
+    z = np.zeros(NQ)
+    rec = oracle_mod.model_record(np.concatenate([q, z]))
+    J = rec[REC["FOOT_J"]:REC["FOOT_J"] + 12 * NQ].reshape(4, 3, NQ)
+    f = np.tile([0.0, 0.0, num.mass * 9.81 / 4], (4, 1))
+    t0 = oracle_mod.inverse_dynamics(np.concatenate([q, z, z]), np.zeros(12))[0]
+    t1 = oracle_mod.inverse_dynamics(np.concatenate([q, z, z]), f.reshape(-1))[0]
+    expect = -np.einsum("fij,fi->j", J, f)[6:]
+    assert np.allclose(t1 - t0, expect, atol=1e-12)
