@@ -1,0 +1,60 @@
+"""Golden regression vectors (tests/golden/*.npz, written by tests/golden/make_golden.py with the
+CPU oracle -- the reference holds none).  CPU: the oracle still reproduces them.
+GPU: the CUDA path reproduces them through the C ABI within the north-star tolerance."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+from iterative_learning_nmpc_b200 import workloads as WL
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_spec = importlib.util.spec_from_file_location("make_golden", os.path.join(HERE, "golden", "make_golden.py"))
+MG = importlib.util.module_from_spec(_spec)
+_spec.loader.exec_module(MG)
+
+
+def _load(name):
+    return dict(np.load(os.path.join(HERE, "golden", name + ".npz")))
+
+
+def rel_err(a, b):
+    return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1.0))
+
+
+@pytest.mark.parametrize("name", sorted(MG.CASES))
+def test_oracle_reproduces_golden(oracle_mod, name):
+    gold = _load(name)
+    batch, out = MG.run_case(name)
+    assert str(out["inputs_sha256"]) == str(gold["inputs_sha256"]), "workload generator changed: regenerate goldens"
+    np.testing.assert_array_equal(out["status"], gold["status"])
+    np.testing.assert_array_equal(out["sqp_iter"], gold["sqp_iter"])
+    np.testing.assert_array_equal(out["qp_iter"], gold["qp_iter"])
+    for k in ("feet", "com", "hg"):
+        assert rel_err(out[k], gold[k]) < 1e-13, k
+    for k in ("x", "u", "pi", "lam"):         # same binary, same machine class: tight but not bitwise (-march)
+        assert rel_err(out[k], gold[k]) < 1e-8, k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(MG.CASES))
+def test_gpu_reproduces_golden(name):
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+    gold = _load(name)
+    B, seed, gaits, opts = MG.CASES[name]
+    batch = WL.make_batch(B, seed=seed, gaits=gaits)
+    assert MG.digest(batch) == str(gold["inputs_sha256"])
+    s = NmpcSolver(B, default_opts(**opts))
+    feet, com, hg = s.kinematics(batch["qv"])
+    assert rel_err(feet, gold["feet"]) < 1e-12 and rel_err(hg, gold["hg"]) < 1e-12
+    WL.load_into(s, batch, hg)
+    status = s.solve()
+    x, u, pi, lam = s.get_solution()
+    np.testing.assert_array_equal(status, gold["status"])
+    st = s.get_stats()
+    np.testing.assert_array_equal(st["qp_iter"], gold["qp_iter"])
+    tol = 1e-6 if opts["max_iter"] == 1 else 1e-5          # 15 chained QPs compound the per-QP 1e-6
+    for k, a in (("x", x), ("u", u), ("pi", pi), ("lam", lam)):
+        assert rel_err(a, gold[k]) < tol, (k, rel_err(a, gold[k]))
