@@ -308,6 +308,8 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
                     self.last_node = np.broadcast_to(np.asarray(i_node, dtype=np.int64), self._lead).copy()
             elif i_node > 0:
                 self.warm_start_solver(i_node, repeat_last=False)
+            elif not self._has_solution:
+                self._fill_cold_guess(q, v)          # no-op with the reference's "zero" first guess
         self.update_solver()
         if self.print_info:
             self.print_contact_constraints()
