@@ -167,6 +167,10 @@ int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const
                   double* dz, double* pi, double* lam, double* t,
                   int32_t* qp_iter, int32_t* qp_status);
 
+/* which solver nmpc_solve_qp used for the last call: 1 = the fused structured kernel (the product
+ * path; taken whenever the supplied QP has the structure of this OCP family), 0 = generic dense */
+int nmpc_last_qp_path(const nmpc_handle* h);
+
 /* Per-kernel device timing with CUDA events recorded on the handle's stream around the launches,
  * grouped by kind.  Replaces acados' print_time / the reference's @time_fn("solve")
  * (solver.py:396) at kernel granularity.  ms / count have NMPC_PROF_KINDS entries. */
@@ -176,7 +180,8 @@ int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const
 #define NMPC_PROF_QP_FACTOR 3   /* Riccati factorisation + affine forward sweep         */
 #define NMPC_PROF_QP_CORR 4     /* corrector solve on the stored factorisation          */
 #define NMPC_PROF_QP_OTHER 5    /* init / decide / step lengths / sigma / rhs / update  */
-#define NMPC_PROF_KINDS 6
+#define NMPC_PROF_QP_FUSED 6    /* the fused per-OCP interior-point kernel (product path) */
+#define NMPC_PROF_KINDS 7
 int nmpc_set_profiling(nmpc_handle* h, int32_t on);
 int nmpc_get_kernel_times(nmpc_handle* h, double* ms /*[NMPC_PROF_KINDS]*/, int64_t* count /*[NMPC_PROF_KINDS]*/);
 

@@ -79,6 +79,7 @@ _SIGS = {
     "nmpc_launch_count": (C.c_int64, [C.c_void_p]),
     "nmpc_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "nmpc_get_kernel_times": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nmpc_last_qp_path": (C.c_int, [C.c_void_p]),
     "nmpc_version": (C.c_char_p, []),
     "nmpc_model_mass": (C.c_double, []),
 }

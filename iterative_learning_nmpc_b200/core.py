@@ -192,12 +192,16 @@ class NmpcSolver:
               "nmpc_solve_qp")
         return out
 
+    @property
+    def last_qp_path(self) -> str:
+        return {1: "fused", 0: "dense"}.get(int(self.lib.nmpc_last_qp_path(self._h)), "?")
+
     def set_profiling(self, on: bool = True):
         check(self.lib.nmpc_set_profiling(self._h, int(on)), "nmpc_set_profiling")
 
     def kernel_times(self) -> dict:
         """{kernel: (ms, launches)} accumulated since the last call (CUDA events, handle stream)."""
-        kinds = ("linearize", "qp_stage", "residual", "qp_factor", "qp_corr", "qp_other")
+        kinds = ("linearize", "qp_stage", "residual", "qp_factor", "qp_corr", "qp_other", "qp_fused")
         ms = np.zeros(len(kinds))
         cnt = np.zeros(len(kinds), dtype=np.int64)
         check(self.lib.nmpc_get_kernel_times(self._h, ptr(ms), ptr(cnt)), "nmpc_get_kernel_times")

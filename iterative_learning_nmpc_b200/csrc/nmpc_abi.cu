@@ -11,6 +11,7 @@
 #include "nmpc_common.cuh"
 #include "nmpc_linearize.cuh"
 #include "nmpc_qp_ipm.cuh"
+#include "nmpc_qp_fused.cuh"
 #include "nmpc_sqp.cuh"
 
 #define CK(call)                                                     \
@@ -33,6 +34,10 @@ struct nmpc_handle {
     double *qp_mu_part, *qp_mu, *qp_sigma_mu;
     // QP workspace [Bc]
     double *G, *M, *C, *D, *Ht, *L, *vec, *cost_stage, *rec;
+    double *SR, *FR;             // structured stage / factor records of the fused QP path
+    int32_t* sr_flag;
+    int last_qp_path;            // nmpc_solve_qp: 1 fused, 0 generic dense
+    int dense_qp;                // NMPC_DENSE_QP=1: generic dense kernels (nmpc_qp_ipm.cuh) instead of the fused path
     double* scratch;             // staging for kinematics / dx0
     size_t scratch_bytes;
     // optional per-kernel timing with CUDA events on the handle's stream (bench.py roofline)
@@ -116,6 +121,7 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     A_(Ht, Bc * (N + 1) * LP_SZ);
     A_(L, Bc * (N + 1) * LP_SZ); A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
     A_(rec, ((Bc * (N + 1) + REC_BLK - 1) / REC_BLK) * NMPC_REC_SIZE * REC_BLK);
+    A_(SR, Bc * (N + 1) * SR_SZ); A_(FR, Bc * (N + 1) * FR_SZ); A_(sr_flag, 1);
 #undef A_
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(nmpc_qp_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM_BYTES);
@@ -123,6 +129,9 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
         e = cudaFuncSetAttribute(nmpc_qp_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K3_SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(nmpc_qp_corr_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
+    if (const char* s = getenv("NMPC_DENSE_QP")) h->dense_qp = atoi(s) != 0;
     if (e != cudaSuccess) {
         *err = (e == cudaErrorMemoryAllocation) ? NMPC_ENOMEM : (int)e;
         nmpc_destroy(h);
@@ -140,7 +149,7 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
                     h->qlam, h->qt, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
                     h->qp_iter, h->qp_status, h->itmp, h->G, h->M, h->C, h->D, h->Ht, h->L, h->vec, h->cost_stage,
-                    h->rec, h->scratch, h->qp_res_acc, h->qp_alpha, h->qp_done, h->qp_nc, h->qp_mu_part,
+                    h->rec, h->scratch, h->SR, h->FR, h->sr_flag, h->qp_res_acc, h->qp_alpha, h->qp_done, h->qp_nc, h->qp_mu_part,
                     h->qp_mu, h->qp_sigma_mu};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -376,6 +385,34 @@ static void run_qp(nmpc_handle* h, QpArgs a, int Bc, bool apply)
     }
 }
 
+// The product path: dense stage blocks -> stage records, then ONE fused kernel per QP (nmpc_qp_fused.cuh).
+static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, int check)
+{
+    const int N = h->N;
+    cudaStream_t s = h->stream;
+    SrArgs sa;
+    sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
+    sa.done = a.sqp_done; sa.N = N; sa.b0 = a.b0; sa.check = check; sa.dt = h->o.dt_nodes;
+    prof_begin(h, NMPC_PROF_QP_OTHER);
+    nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, s>>>(sa);
+    prof_end(h);
+    FqArgs f;
+    f.SR = h->SR; f.FR = h->FR; f.vec = h->vec; f.qz = a.qz; f.qpi = a.qpi; f.qlam = a.qlam; f.qt = a.qt;
+    f.qp_iter = a.qp_iter; f.qp_status = a.qp_status; f.qp_res = a.qp_res; f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
+    f.x = a.x; f.sqp_done = a.sqp_done; f.N = N; f.b0 = a.b0; f.max_iter = a.max_iter; f.warm = a.warm;
+    f.tol = a.tol; f.dt = h->o.dt_nodes;
+    prof_begin(h, NMPC_PROF_QP_FUSED);
+    nmpc_qp_fused_kernel<<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
+    prof_end(h);
+    h->launches += 2;
+    if (apply) {
+        prof_begin(h, NMPC_PROF_QP_OTHER);
+        nmpc_qp_apply_kernel<<<Bc, 128, 0, s>>>(a);
+        prof_end(h);
+        h->launches++;
+    }
+}
+
 extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
 {
     if (!h) return NMPC_EINVAL;
@@ -410,7 +447,8 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
                 nmpc_cost_sum_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, N, h->cost_stage, h->cost);
                 h->launches++;
             }
-            run_qp(h, qp_args(h, b0), Bc, true);
+            if (h->dense_qp) run_qp(h, qp_args(h, b0), Bc, true);
+            else run_qp_fused(h, qp_args(h, b0), Bc, true, 0);
             nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
             h->launches++;
         }
@@ -635,7 +673,21 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
         CK(cudaMemcpyAsync(h->D, hD.data(), (size_t)Bc * (N + 1) * D_SZ * 8, cudaMemcpyHostToDevice, h->stream));
         QpArgs qa = qp_args(h, b0);
         qa.dx0_ext = h->scratch; qa.warm = 0; qa.sqp_done = nullptr; qa.sqp_iter = nullptr;
-        run_qp(h, qa, Bc, false);
+        // QPs with the structure of this OCP family (every QP the solver itself builds) take the fused
+        // product path; anything else is solved by the generic dense kernels
+        int32_t generic = h->dense_qp;
+        if (!generic) {
+            CK(cudaMemsetAsync(h->sr_flag, 0, 4, h->stream));
+            SrArgs sa;
+            sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
+            sa.done = nullptr; sa.N = N; sa.b0 = b0; sa.check = 1; sa.dt = h->o.dt_nodes;
+            nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, h->stream>>>(sa);
+            CK(cudaMemcpyAsync(&generic, h->sr_flag, 4, cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+        }
+        h->last_qp_path = generic ? 0 : 1;
+        if (generic) run_qp(h, qa, Bc, false);
+        else run_qp_fused(h, qa, Bc, false, 0);
         CK(cudaStreamSynchronize(h->stream));
     }
     CK(cudaGetLastError());
@@ -649,6 +701,8 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
     CK(cudaStreamSynchronize(h->stream));
     return 0;
 }
+
+extern "C" int nmpc_last_qp_path(const nmpc_handle* h) { return h ? h->last_qp_path : -1; }
 
 // debug builds (-DNMPC_TIMING): per-phase cycle counts of CTA 0 of nmpc_qp_factor_kernel
 extern "C" int nmpc_debug_phase_cycles(unsigned long long* out16, int reset)

@@ -1,0 +1,977 @@
+// nmpc_qp_fused.cuh -- the product's OCP-QP interior point: ONE persistent CTA per OCP runs the
+// whole Mehrotra predictor-corrector IPM (all iterations, all stages) with a Riccati recursion
+// specialised to the structure of this OCP family.
+//
+// Same algorithm as nmpc_qp_ipm.cuh (HPIPM `speed` semantics; oracle:
+// oracle/nmpc_oracle.c::qp_ipm) -- the Newton directions are identical in exact arithmetic -- but
+// the arithmetic is organised around what the stage matrices of THIS problem look like:
+//
+//   dynamics   q+ = q + dt v + c a,  v+ = v + dt a,  h+ = h + Hq q + Hf f        (c = dt^2/2)
+//              -> G = [B A] is never formed: G'PG is O(n^2) combinations of blocks of P plus
+//                 rank-6 corrections through Hq (6x18), Hf (6x12)
+//   cost       diagonal in (a, f, v, h), dense only in the 18x18 q block
+//   constraints friction rows touch one foot's 3 force columns; contact / patch / centroidal rows
+//              touch (q, v) (+ an identity column in h)
+//              -> H + C' Gamma C = diag(18) + four 3x3 blocks in u, dense 42x42 in x, zero u-x block
+//
+// so a stage is described by a 1692-double "stage record" (SR) instead of 11.6k doubles of dense
+// blocks, and the Riccati step is the CLASSICAL recursion on P (42x42): Cholesky of the 30x30
+// input block only (30 sequential pivots instead of 72), Lxu = Mxu Luu^-T, P = Mxx - Lxu Lxu'.
+//
+// Fusion: the stage-parallel work of an IPM iteration (residuals, Gamma, barrier Hessian) is done
+// by the same CTA right before it factorises the stage, all reductions over stages (norms, mu,
+// step lengths, sigma) are CTA-local, and nothing but the per-stage vectors and the factors
+// (needed again by the forward / corrector sweeps) goes back to HBM.  One kernel launch per QP.
+#pragma once
+#include "nmpc_qp_ipm.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// stage record (doubles)
+// ---------------------------------------------------------------------------------------------
+#define SR_HQ 0                      // [6][18]  d h+ / d q
+#define SR_HF (SR_HQ + 6 * NQ)       // [6][12]  d h+ / d f
+#define SR_B (SR_HF + 6 * 12)        // [42]     dynamics defect f(x,u) - x+
+#define SR_RD (SR_B + NX)            // [30]     Hessian diagonal, u block
+#define SR_QV (SR_RD + NU)           // [18]     Hessian diagonal, v block
+#define SR_QH (SR_QV + NQ)           // [6]      Hessian diagonal, h block
+#define SR_QQ (SR_QH + 6)            // [18][18] Hessian, q block (full symmetric)
+#define SR_GR (SR_QQ + NQ * NQ)      // [72]     gradient
+#define SR_CF (SR_GR + NZ)           // [20][3]  friction rows over their foot's force
+#define SR_CX (SR_CF + 20 * 3)       // [22][36] contact / patch / centroidal rows over (q, v)
+#define SR_D (SR_CX + 22 * 36)       // lg[42] ug[42] mask_l[42] mask_u[42]
+#define SR_SZ (SR_D + 4 * NG)        // 1692
+#define NGX 22                       // constraint rows on the state
+#define NGF 20                       // friction rows
+
+// factor record (doubles): u panels of the stage factor (Luu, Lxu, row 72 = lu) | P | p
+#define FR_MU 0
+#define P_LD 43
+#define FR_P (FR_MU + LP_UPANELS)            // 1830
+#define FR_PV (FR_P + NX * P_LD)             // 3636
+#define FR_SZ (FR_PV + NX + 2)               // 3680
+
+static_assert(SR_SZ % 2 == 0 && FR_P % 2 == 0 && FR_PV % 2 == 0 && FR_SZ % 2 == 0, "16-byte alignment of bulk copies");
+
+// ---------------------------------------------------------------------------------------------
+// dense stage blocks -> stage record (used for externally supplied QPs and, for now, after the
+// dense linearisation).  One CTA per (stage, problem).  With `check` set, every dense entry is
+// compared with the value the record implies; a mismatch raises *flag (the caller then falls back
+// to the generic dense path, nmpc_qp_ipm.cuh).
+// ---------------------------------------------------------------------------------------------
+struct SrArgs {
+    const double* G; const double* M; const double* C; const double* D;
+    double* SR;
+    int32_t* flag;
+    const int32_t* done;
+    int N, b0, check;
+    double dt;
+};
+
+__device__ __forceinline__ bool sr_differs(double a, double b) { return !(a == b) && !(a != a && b != b); }
+
+__global__ void __launch_bounds__(128) nmpc_dense2sr_kernel(SrArgs a)
+{
+    const int k = blockIdx.x, bl = blockIdx.y, tid = threadIdx.x, N = a.N;
+    if (a.done && a.done[a.b0 + bl]) return;
+    const bool term = (k == N);
+    const double* Gp = term ? nullptr : a.G + ((size_t)bl * N + k) * G_SZ;
+    const double* Mp = a.M + ((size_t)bl * (N + 1) + k) * M_SZ;
+    const double* Cp = a.C + ((size_t)bl * (N + 1) + k) * C_SZ;
+    const double* Dp = a.D + ((size_t)bl * (N + 1) + k) * D_SZ;
+    double* S = a.SR + ((size_t)bl * (N + 1) + k) * SR_SZ;
+    for (int e = tid; e < 6 * NQ; e += 128) S[SR_HQ + e] = term ? 0.0 : Gp[(2 * NQ + e / NQ) * G_LD + IQ + e % NQ];
+    for (int e = tid; e < 6 * 12; e += 128) S[SR_HF + e] = term ? 0.0 : Gp[(2 * NQ + e / 12) * G_LD + IFRC + e % 12];
+    for (int e = tid; e < NX; e += 128) S[SR_B + e] = term ? 0.0 : Gp[e * G_LD + NZ];
+    for (int e = tid; e < NU; e += 128) S[SR_RD + e] = Mp[e * M_LD + e];
+    for (int e = tid; e < NQ; e += 128) S[SR_QV + e] = Mp[(IV + e) * M_LD + IV + e];
+    for (int e = tid; e < 6; e += 128) S[SR_QH + e] = Mp[(IH + e) * M_LD + IH + e];
+    for (int e = tid; e < NQ * NQ; e += 128) S[SR_QQ + e] = Mp[(IQ + e / NQ) * M_LD + IQ + e % NQ];
+    for (int e = tid; e < NZ; e += 128) S[SR_GR + e] = Mp[NZ * M_LD + e];
+    for (int e = tid; e < NGF * 3; e += 128) { const int j = e / 3; S[SR_CF + e] = Cp[j * C_LD + IFRC + 3 * (j / 5) + e % 3]; }
+    for (int e = tid; e < NGX * 36; e += 128) S[SR_CX + e] = Cp[(NGF + e / 36) * C_LD + IQ + e % 36];
+    for (int e = tid; e < 4 * NG; e += 128) S[SR_D + e] = Dp[e];
+    if (!a.check) return;
+    // ---- structure check: the dense blocks must be exactly what the record expands to ----
+    bool bad = false;
+    const double dt = a.dt, c2 = 0.5 * dt * dt;
+    if (!term) {
+        for (int e = tid; e < NX * NZ; e += 128) {
+            const int l = e / NZ, c = e % NZ;
+            double ex = 0.0;
+            if (l < NQ) { if (c == IA + l) ex = c2; else if (c == IQ + l) ex = 1.0; else if (c == IV + l) ex = dt; }
+            else if (l < 2 * NQ) { const int i = l - NQ; if (c == IA + i) ex = dt; else if (c == IV + i) ex = 1.0; }
+            else {
+                const int i = l - 2 * NQ;
+                if (c >= IFRC && c < IQ) ex = Gp[l * G_LD + c];
+                else if (c >= IQ && c < IV) ex = Gp[l * G_LD + c];
+                else if (c == IH + i) ex = 1.0;
+            }
+            bad |= sr_differs(Gp[l * G_LD + c], ex);
+        }
+    }
+    for (int e = tid; e < NZ * NZ; e += 128) {
+        const int i = e / NZ, j = e % NZ;
+        const bool in_q = (i >= IQ && i < IV && j >= IQ && j < IV);
+        if (i != j && !in_q) bad |= sr_differs(Mp[i * M_LD + j], 0.0);
+        if (in_q) bad |= sr_differs(Mp[i * M_LD + j], Mp[j * M_LD + i]);
+    }
+    for (int e = tid; e < NG * NZ; e += 128) {
+        const int j = e / NZ, c = e % NZ;
+        bool allowed;
+        double fixed = 0.0;
+        bool has_fixed = false;
+        if (j < NGF) allowed = (c >= IFRC + 3 * (j / 5) && c < IFRC + 3 * (j / 5) + 3);
+        else {
+            allowed = (c >= IQ && c < IH);
+            if (j >= GR_CONS && c >= IH) { has_fixed = true; fixed = (c == IH + (j - GR_CONS)) ? 1.0 : 0.0; }
+        }
+        const double v = Cp[j * C_LD + c];
+        // a row with both sides masked out contributes nothing (Gamma = gamma = 0): anything goes
+        if (!(Dp[2 * NG + j] > 0.5 || Dp[3 * NG + j] > 0.5)) continue;
+        if (has_fixed) bad |= sr_differs(v, fixed);
+        else if (!allowed) bad |= sr_differs(v, 0.0);
+    }
+    if (bad) atomicOr(a.flag, 1);
+}
+
+// ---------------------------------------------------------------------------------------------
+// fused IPM kernel
+// ---------------------------------------------------------------------------------------------
+#define FQ_THREADS 128
+#define FQ_WARPS (FQ_THREADS / 32)
+#define N_UTILES 100                 // 3x6 tiles of rows 0..71 x columns 0..29 at or below the diagonal
+#define N_XTILES 105                 // 3x3 tiles of the lower triangle of the 42x42 state block
+
+struct FqArgs {
+    const double* SR;               // [Bc][N+1][SR_SZ]
+    double* FR;                     // [Bc][N+1][FR_SZ]
+    double* vec;                    // [Bc][(N+1)*V_STAGE]
+    double* qz; double* qpi; double* qlam; double* qt;       // QP iterate, global problem index
+    int32_t* qp_iter; int32_t* qp_status; double* qp_res;
+    const double* dx0_ext; const double* x0; const double* x;
+    const int32_t* sqp_done;
+    int N, b0, max_iter, warm;
+    double tol, dt;
+};
+
+// shared memory carve-up (doubles)
+#define FS_P 0                               // P_{k+1}, full symmetric, ld 43
+#define FS_M (FS_P + NX * P_LD)              // u panels of the stage matrix (LP_UPANELS); before the
+                                             // factorisation the same space holds U and PGh
+#define FS_SR (FS_M + LP_UPANELS)            // stage record
+#define FS_V (FS_SR + SR_SZ)                 // vectors
+#define FS_U FS_M                            // U[42][30] = P[:,h] [Hf | Hq]   (ld 30)
+#define FS_PGH (FS_U + NX * NU)              // PGh[6][72] = (P G)[h rows]     (1260 + 432 <= 1830)
+// vectors
+#define FV_Z 0
+#define FV_ZXN (FV_Z + NZ)
+#define FV_PIK (FV_ZXN + NX)
+#define FV_PIN (FV_PIK + NX)
+#define FV_LAM (FV_PIN + NX)
+#define FV_T (FV_LAM + 2 * NG)
+#define FV_CZ (FV_T + 2 * NG)
+#define FV_RD (FV_CZ + NG)
+#define FV_RM (FV_RD + 2 * NG)
+#define FV_GAM (FV_RM + 2 * NG)
+#define FV_GAMV (FV_GAM + NG)
+#define FV_DL (FV_GAMV + NG)
+#define FV_RG (FV_DL + NG)
+#define FV_QT (FV_RG + NZ)                   // m: linear term, row 72 of the stage matrix (NZ)
+#define FV_RB (FV_QT + NZ)
+#define FV_W (FV_RB + NX)
+#define FV_PN (FV_W + NX)                    // p_{k+1}
+#define FV_DX (FV_PN + NX)
+#define FV_DXN (FV_DX + NX)
+#define FV_DZ (FV_DXN + NX)
+#define FV_RED (FV_DZ + NZ)                  // 16 reduction slots
+#define FV_END (FV_RED + 16)
+#define FQ_SMEM_BYTES ((FS_V + FV_END) * 8)
+
+// C z for the current stage: sv[FV_CZ + j] = sum_c C(j, c) zz[c], zz over [u; x]
+__device__ __forceinline__ void fq_cz(const double* S, const double* zz, double* out, int tid)
+{
+    if (tid < NG) {
+        const int j = tid;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        if (j < NGF) {
+            const double* cf = S + SR_CF + 3 * j;
+            const double* f = zz + IFRC + 3 * (j / 5);
+            s0 = cf[0] * f[0] + cf[1] * f[1] + cf[2] * f[2];
+        } else {
+            const double* cx = S + SR_CX + 36 * (j - NGF);
+            const double* xx = zz + IQ;
+#pragma unroll
+            for (int c = 0; c < 36; c += 4) {
+                s0 += cx[c] * xx[c]; s1 += cx[c + 1] * xx[c + 1]; s2 += cx[c + 2] * xx[c + 2]; s3 += cx[c + 3] * xx[c + 3];
+            }
+            if (j >= GR_CONS) s0 += zz[IH + j - GR_CONS];
+        }
+        out[j] = (s0 + s1) + (s2 + s3);
+    }
+}
+
+// (C' g)[c] for a multiplier-like vector g over the 42 constraint rows
+__device__ __forceinline__ double fq_ct(const double* S, const double* g, int c)
+{
+    double s = 0.0;
+    if (c < IFRC) return 0.0;
+    if (c < IQ) {
+        const int ft = (c - IFRC) / 3, i = (c - IFRC) % 3;
+#pragma unroll
+        for (int r = 0; r < 5; r++) s += S[SR_CF + 3 * (5 * ft + r) + i] * g[5 * ft + r];
+        return s;
+    }
+    if (c < IH) {
+        const double* cx = S + SR_CX + (c - IQ);
+        double s1 = 0.0;
+#pragma unroll
+        for (int jj = 0; jj < NGX; jj += 2) { s += cx[36 * jj] * g[NGF + jj]; s1 += cx[36 * (jj + 1)] * g[NGF + jj + 1]; }
+        return s + s1;
+    }
+    return g[GR_CONS + c - IH];
+}
+
+// (G' w)[c] for w over the next state (structured dynamics)
+__device__ __forceinline__ double fq_gt(const double* S, const double* w, int c, double dt, double c2)
+{
+    if (c < IFRC) return c2 * w[c] + dt * w[NQ + c];
+    if (c < IQ) {
+        const int j = c - IFRC;
+        double s = 0.0;
+#pragma unroll
+        for (int h = 0; h < 6; h++) s += S[SR_HF + 12 * h + j] * w[2 * NQ + h];
+        return s;
+    }
+    if (c < IV) {
+        const int i = c - IQ;
+        double s = w[i];
+#pragma unroll
+        for (int h = 0; h < 6; h++) s += S[SR_HQ + NQ * h + i] * w[2 * NQ + h];
+        return s;
+    }
+    if (c < IH) { const int i = c - IV; return dt * w[i] + w[NQ + i]; }
+    return w[2 * NQ + c - IH];
+}
+
+// (G zz)[l] for zz over [u; x] (no affine term)
+__device__ __forceinline__ double fq_g(const double* S, const double* zz, int l, double dt, double c2)
+{
+    if (l < NQ) return zz[IQ + l] + dt * zz[IV + l] + c2 * zz[IA + l];
+    if (l < 2 * NQ) { const int i = l - NQ; return zz[IV + i] + dt * zz[IA + i]; }
+    const int i = l - 2 * NQ;
+    double s = zz[IH + i], s1 = 0.0;
+    const double* hq = S + SR_HQ + NQ * i;
+    const double* hf = S + SR_HF + 12 * i;
+#pragma unroll
+    for (int j = 0; j < NQ; j += 2) { s += hq[j] * zz[IQ + j]; s1 += hq[j + 1] * zz[IQ + j + 1]; }
+#pragma unroll
+    for (int j = 0; j < 12; j += 2) { s += hf[j] * zz[IFRC + j]; s1 += hf[j + 1] * zz[IFRC + j + 1]; }
+    return s + s1;
+}
+
+// (H zz)[c]: Gauss-Newton Hessian times a vector over [u; x]
+__device__ __forceinline__ double fq_h(const double* S, const double* zz, int c)
+{
+    if (c < IQ) return S[SR_RD + c] * zz[c];
+    if (c < IV) {
+        const double* row = S + SR_QQ + NQ * (c - IQ);
+        double s = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int j = 0; j < NQ; j += 2) { s += row[j] * zz[IQ + j]; s1 += row[j + 1] * zz[IQ + j + 1]; }
+        return s + s1;
+    }
+    if (c < IH) return S[SR_QV + c - IV] * zz[c];
+    return S[SR_QH + c - IH] * zz[c];
+}
+
+__device__ __forceinline__ double fq_block_max(double v, double* red, int tid)
+{
+    v = warp_max(v);
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    return nanmax(nanmax(red[0], red[1]), nanmax(red[2], red[3]));
+}
+__device__ __forceinline__ double fq_block_min(double v, double* red, int tid)
+{
+    v = warp_min(v);
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    return fmin(fmin(red[0], red[1]), fmin(red[2], red[3]));
+}
+__device__ __forceinline__ double fq_block_sum(double v, double* red, int tid)
+{
+    v = warp_sum(v);
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    return ((red[0] + red[1]) + red[2]) + red[3];
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward sweep, one stage.  In: sM = u panels of stage k (Luu, Lxu, row 72 = lu), S = SR_k,
+// sv[FV_DX] = dx_k, sv[FV_RB] = rb_k; CORR: sP = P_k, sv[FV_PN] = p_k.
+// Out: dz_k, dt_k, dlam_k (and CORR: dpi_{k-1}) to the stage vectors, step-length candidates
+// folded into a_p / a_d, sv[FV_DX] = dx_{k+1}.
+// ---------------------------------------------------------------------------------------------
+template <bool CORR>
+__device__ __forceinline__ void fq_forward_stage(const double* sM, const double* sP, const double* S, double* sv,
+                                                 double* vk, double* dpi_prev, const double* qlam, const double* qt,
+                                                 bool term, int tid, double dt, double c2, double& a_p, double& a_d)
+{
+    const int lane = tid & 31;
+    if (CORR && dpi_prev && tid >= 64 && tid < 64 + NX) {           // dpi_{k-1} = P_k dx_k + p_k
+        const int i = tid - 64;
+        const double* row = sP + i * P_LD;
+        double s0 = sv[FV_PN + i], s1 = 0.0;
+#pragma unroll
+        for (int j = 0; j < NX; j += 2) { s0 += row[j] * sv[FV_DX + j]; s1 += row[j + 1] * sv[FV_DX + j + 1]; }
+        dpi_prev[i] = s0 + s1;
+    }
+    if (!term) {
+        if (tid < 32) {             // du = -Luu^-T (lu + Lxu' dx)
+            double rhs = 0.0;
+            if (lane < NU) {
+                double r1 = 0.0;
+                rhs = sM[lp_idx(NZ, lane)];
+                for (int l = 0; l < NX; l += 2) {
+                    rhs += sM[lp_idx(NU + l, lane)] * sv[FV_DX + l];
+                    r1 += sM[lp_idx(NU + l + 1, lane)] * sv[FV_DX + l + 1];
+                }
+                rhs += r1;
+            }
+            double du = 0.0;
+            for (int i = NU - 1; i >= 0; i--) {
+                const double d = sM[lp_idx(i, i)];
+                const double inv = d != 0.0 ? 1.0 / d : 0.0;
+                const double dui = -__shfl_sync(0xffffffffu, rhs, i) * inv;
+                if (lane == i) du = dui;
+                if (lane < i) rhs += sM[lp_idx(i, lane)] * dui;
+            }
+            if (lane < NU) sv[FV_DZ + lane] = du;
+        }
+    } else if (tid < NU) sv[FV_DZ + tid] = 0.0;
+    if (tid >= 32 && tid < 32 + NX) sv[FV_DZ + NU + tid - 32] = sv[FV_DX + tid - 32];
+    __syncthreads();
+    if (tid < NZ) vk[V_DZ + tid] = sv[FV_DZ + tid];
+    fq_cz(S, sv + FV_DZ, sv + FV_CZ, tid);                           // threads 0..41
+    if (!term && tid >= 64 && tid < 64 + NX) {                      // dx+ = G dz + rb
+        const int l = tid - 64;
+        sv[FV_DXN + l] = fq_g(S, sv + FV_DZ, l, dt, c2) + sv[FV_RB + l];
+    }
+    __syncthreads();
+    if (tid < 2 * NG) {
+        const int e = tid / NG, j = tid % NG;
+        double dtv = 0.0, dl = 0.0;
+        if (S[SR_D + 2 * NG + tid] > 0.5) {
+            const double lam = qlam[tid], t = qt[tid];
+            const double cdz = sv[FV_CZ + j];
+            dtv = (e ? -cdz : cdz) + vk[V_RD + tid];
+            dl = -(vk[V_RM + tid] + lam * dtv) / t;
+            if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
+            if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
+        }
+        vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
+    }
+    if (!term && tid < NX) sv[FV_DX + tid] = sv[FV_DXN + tid];
+    __syncthreads();
+}
+
+// x tile t (t < N_XTILES) -> row block xr in 0..13, column block xc <= xr of the 42x42 state block
+__device__ __forceinline__ void xtile_of(int t, int& xr, int& xc)
+{
+    int r = 0;
+    while ((r + 1) * (r + 2) / 2 <= t) r++;
+    xr = r;
+    xc = t - r * (r + 1) / 2;
+}
+
+// (P G)[r][J]: row r of P_{k+1} (state index) against column J of G = [B A] (z index)
+__device__ __forceinline__ double fq_pg(const double* sP, const double* sU, int r, int J, double dt, double c2)
+{
+    const double* row = sP + r * P_LD;
+    if (J < IFRC) return c2 * row[J] + dt * row[NQ + J];
+    if (J < IQ) return sU[r * NU + (J - IFRC)];
+    if (J < IV) return row[J - IQ] + sU[r * NU + 12 + (J - IQ)];
+    if (J < IH) return dt * row[J - IV] + row[NQ + J - IV];
+    return row[2 * NQ + J - IH];
+}
+
+// (G' P G)[I][J] with the h rows of P G precomputed in sG (PGh[6][72])
+__device__ __forceinline__ double fq_gtpg(const double* sP, const double* sU, const double* sG, const double* S,
+                                          int I, int J, double dt, double c2)
+{
+    if (I < IFRC) return c2 * fq_pg(sP, sU, I, J, dt, c2) + dt * fq_pg(sP, sU, NQ + I, J, dt, c2);
+    if (I < IQ) {
+        const int i = I - IFRC;
+        double s = 0.0;
+#pragma unroll
+        for (int h = 0; h < 6; h++) s += S[SR_HF + 12 * h + i] * sG[h * NZ + J];
+        return s;
+    }
+    if (I < IV) {
+        const int i = I - IQ;
+        double s = fq_pg(sP, sU, i, J, dt, c2);
+#pragma unroll
+        for (int h = 0; h < 6; h++) s += S[SR_HQ + NQ * h + i] * sG[h * NZ + J];
+        return s;
+    }
+    if (I < IH) { const int i = I - IV; return dt * fq_pg(sP, sU, i, J, dt, c2) + fq_pg(sP, sU, NQ + i, J, dt, c2); }
+    return sG[(I - IH) * NZ + J];
+}
+
+__global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
+{
+    extern __shared__ __align__(16) double smem[];
+    __shared__ __align__(8) uint64_t bar;
+    const int tid = threadIdx.x;
+    const int bl = blockIdx.x, b = a.b0 + bl, N = a.N;
+    if (a.sqp_done && a.sqp_done[b]) return;             // finished problems keep their statistics
+    double* sP = smem + FS_P;
+    double* sM = smem + FS_M;
+    double* S = smem + FS_SR;
+    double* sv = smem + FS_V;
+    double* sU = smem + FS_U;
+    double* sG = smem + FS_PGH;
+    double* red = sv + FV_RED;
+    const double dt = a.dt, c2 = 0.5 * a.dt * a.dt;
+
+    const double* SRb = a.SR + (size_t)bl * (N + 1) * SR_SZ;
+    double* FRb = a.FR + (size_t)bl * (N + 1) * FR_SZ;
+    double* vb = a.vec + (size_t)bl * (N + 1) * V_STAGE;
+    double* qz = a.qz + (size_t)b * (N + 1) * NZ;
+    double* qpi = a.qpi + (size_t)b * N * NX;
+    double* qlamb = a.qlam + (size_t)b * (N + 1) * 2 * NG;
+    double* qtb = a.qt + (size_t)b * (N + 1) * 2 * NG;
+
+    uint32_t phase = 0;
+    if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+
+    // ---- start of the QP (nmpc_qp_init_kernel) ----
+    if (a.warm == 0) {
+        for (int i = tid; i < (N + 1) * NZ; i += FQ_THREADS) qz[i] = 0.0;
+        for (int i = tid; i < N * NX; i += FQ_THREADS) qpi[i] = 0.0;
+    }
+    __syncthreads();
+    if (tid < NX)
+        qz[NU + tid] = a.dx0_ext ? a.dx0_ext[(size_t)b * NX + tid]
+                                 : a.x0[(size_t)b * NX + tid] - a.x[(size_t)b * (N + 1) * NX + tid];
+    if (tid < NU) qz[(size_t)N * NZ + tid] = 0.0;
+    __syncthreads();
+
+    // tile ownership
+    const bool has_ut = tid < N_UTILES, has_xt = tid < N_XTILES;
+    int urb = 0, ucb = 0, xr = 0, xc = 0;
+    if (has_ut) tile_of(tid, urb, ucb);
+    if (has_xt) xtile_of(tid, xr, xc);
+    const int ur0 = 3 * urb, uc0 = 6 * ucb;
+
+    int status = 1, iters = 0, nc_total = 0;
+    double alpha_p = 1.0, alpha_d = 1.0, mu = 0.0;
+    double res4[4] = {0.0, 0.0, 0.0, 0.0};
+
+    for (int it = 0; it <= a.max_iter; it++) {
+        const bool last = (it >= a.max_iter);
+        // ================= update with the step of the previous iteration (nmpc_qp_update_kernel) =====
+        if (it > 0) {
+            alpha_p *= (1.0 - alpha_p) * 0.99 + alpha_p * 0.9999999;
+            alpha_d *= (1.0 - alpha_d) * 0.99 + alpha_d * 0.9999999;
+            if (alpha_p < IPM_ALPHA_MIN && alpha_d < IPM_ALPHA_MIN) { status = 2; break; }
+            for (int k = 0; k <= N; k++) {
+                const double* vk = vb + (size_t)k * V_STAGE;
+                const double* Dm = SRb + (size_t)k * SR_SZ + SR_D + 2 * NG;
+                if (tid < NZ) qz[(size_t)k * NZ + tid] += alpha_p * vk[V_DZ + tid];
+                if (k < N && tid >= 80 && tid < 80 + NX) qpi[(size_t)k * NX + tid - 80] += alpha_d * vk[V_DPI + tid - 80];
+                if (tid < 2 * NG && Dm[tid] > 0.5) {
+                    double* qt = qtb + (size_t)k * 2 * NG;
+                    double* ql = qlamb + (size_t)k * 2 * NG;
+                    qt[tid] = fmax(qt[tid] + alpha_p * vk[V_DT + tid], IPM_T_MIN);
+                    ql[tid] = fmax(ql[tid] + alpha_d * vk[V_DLAM + tid], IPM_LAM_MIN);
+                }
+            }
+            __syncthreads();
+        }
+        iters = it;
+
+        // ================= backward pass: residuals of every stage (+ factorisation unless last) =====
+        double n_g = 0.0, n_b = 0.0, n_d = 0.0, n_m = 0.0, acc_mu = 0.0;
+        int cnt = 0;
+        if (tid == 0) {
+            bulk_store_wait_read();
+            mbar_arrive_expect_tx(&bar, SR_SZ * 8);
+            bulk_g2s(S, SRb + (size_t)N * SR_SZ, SR_SZ * 8, &bar);
+        }
+        for (int k = N; k >= 0; k--) {
+            const bool term = (k == N);
+            double* vk = vb + (size_t)k * V_STAGE;
+            double* qlam = qlamb + (size_t)k * 2 * NG;
+            double* qt = qtb + (size_t)k * 2 * NG;
+            if (tid < NZ) sv[FV_Z + tid] = qz[(size_t)k * NZ + tid];
+            if (tid >= 80 && tid < 80 + NX) {
+                const int i = tid - 80;
+                sv[FV_ZXN + i] = term ? 0.0 : qz[(size_t)(k + 1) * NZ + NU + i];
+                sv[FV_PIK + i] = (k > 0) ? qpi[(size_t)(k - 1) * NX + i] : 0.0;
+                sv[FV_PIN + i] = term ? 0.0 : qpi[(size_t)k * NX + i];
+            }
+            if (tid < 2 * NG) { sv[FV_LAM + tid] = qlam[tid]; sv[FV_T + tid] = qt[tid]; }
+            __syncthreads();
+            mbar_wait(&bar, phase); phase ^= 1;                      // SR_k has landed
+
+            fq_cz(S, sv + FV_Z, sv + FV_CZ, tid);
+            __syncthreads();
+            if (tid < 2 * NG) {
+                const int e = tid / NG, j = tid % NG;
+                const double msk = S[SR_D + 2 * NG + tid];
+                const double cz = sv[FV_CZ + j];
+                const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
+                double t = sv[FV_T + tid], lam = sv[FV_LAM + tid];
+                if (it == 0 && (a.warm < 2 || !(t > 0.0) || !(lam > 0.0))) {
+                    if (msk > 0.5) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; } else { t = 1.0; lam = 0.0; }
+                    sv[FV_T + tid] = t; sv[FV_LAM + tid] = lam;
+                    qt[tid] = t; qlam[tid] = lam;
+                }
+                const double rd = msk > 0.5 ? (slack - t) : 0.0;
+                const double rm = msk > 0.5 ? lam * t : 0.0;
+                sv[FV_RD + tid] = rd; sv[FV_RM + tid] = rm;
+                vk[V_RD + tid] = rd; vk[V_RM + tid] = rm;
+                acc_mu += rm; cnt += (msk > 0.5) ? 1 : 0;
+                n_d = nanmax(n_d, fabs(rd)); n_m = nanmax(n_m, fabs(rm));
+            }
+            __syncthreads();
+            if (tid < NG) {
+                const int j = tid;
+                const double ml = S[SR_D + 2 * NG + j], mu_ = S[SR_D + 3 * NG + j];
+                const double ll = sv[FV_LAM + j], lu = sv[FV_LAM + NG + j];
+                const double tl = sv[FV_T + j], tu = sv[FV_T + NG + j];
+                double Gam = 0.0, gam = 0.0, dl = 0.0;
+                if (ml > 0.5) { Gam += ll / tl; gam += (sv[FV_RM + j] + ll * sv[FV_RD + j]) / tl; dl += ll; }
+                if (mu_ > 0.5) { Gam += lu / tu; gam -= (sv[FV_RM + NG + j] + lu * sv[FV_RD + NG + j]) / tu; dl -= lu; }
+                sv[FV_GAM + j] = Gam; sv[FV_GAMV + j] = gam; sv[FV_DL + j] = dl;
+            }
+            __syncthreads();
+            if (tid < NZ) {
+                const int c = tid;
+                double s = S[SR_GR + c] + fq_h(S, sv + FV_Z, c);
+                if (c >= NU && k > 0) s -= sv[FV_PIK + c - NU];
+                s -= fq_ct(S, sv + FV_DL, c);
+                const double qp = fq_ct(S, sv + FV_GAMV, c);
+                if (!term) s += fq_gt(S, sv + FV_PIN, c, dt, c2);
+                if ((k == 0 && c >= NU) || (term && c < NU)) s = 0.0;
+                vk[V_RG + c] = s; sv[FV_QT + c] = qp + s;
+                n_g = nanmax(n_g, fabs(s));
+            } else if (!term && tid >= 80 && tid < 80 + NX) {
+                const int l = tid - 80;
+                const double rb = fq_g(S, sv + FV_Z, l, dt, c2) + S[SR_B + l] - sv[FV_ZXN + l];
+                sv[FV_RB + l] = rb; vk[V_RB + l] = rb;
+                n_b = nanmax(n_b, fabs(rb));
+            }
+            __syncthreads();
+            if (last) {
+                if (k > 0 && tid == 0) {
+                    mbar_arrive_expect_tx(&bar, SR_SZ * 8);
+                    bulk_g2s(S, SRb + (size_t)(k - 1) * SR_SZ, SR_SZ * 8, &bar);
+                }
+                continue;
+            }
+
+            // ---------------- Riccati step of stage k (classical recursion on P) ----------------
+            double xa[3][3], ua[3][6];
+            if (tid == 0) bulk_store_wait_read();                    // the previous factor record has left sM / sP
+            if (!term) {
+                if (tid < NX) {                                      // w = P+ rb + p+
+                    const double* row = sP + tid * P_LD;
+                    double s0 = sv[FV_PN + tid], s1 = 0.0;
+#pragma unroll
+                    for (int j = 0; j < NX; j += 2) { s0 += row[j] * sv[FV_RB + j]; s1 += row[j + 1] * sv[FV_RB + j + 1]; }
+                    sv[FV_W + tid] = s0 + s1;
+                }
+                __syncthreads();                                     // also orders wait_read before the writes to sU
+                for (int e = tid; e < NX * NU; e += FQ_THREADS) {    // U = P+[:, h] [Hf | Hq]
+                    const int r = e / NU, j = e % NU;
+                    const double* ph = sP + r * P_LD + 2 * NQ;
+                    const double* hc = (j < 12) ? (S + SR_HF + j) : (S + SR_HQ + (j - 12));
+                    const int ld = (j < 12) ? 12 : NQ;
+                    double s = 0.0;
+#pragma unroll
+                    for (int h = 0; h < 6; h++) s += ph[h] * hc[ld * h];
+                    sU[e] = s;
+                }
+                if (tid < NZ) sv[FV_QT + tid] += fq_gt(S, sv + FV_W, tid, dt, c2);       // m = q tilde + G' w
+                __syncthreads();
+                for (int e = tid; e < 6 * NZ; e += FQ_THREADS)       // PGh = (P+ G)[h rows]
+                    sG[e] = fq_pg(sP, sU, 2 * NQ + e / NZ, e % NZ, dt, c2);
+                __syncthreads();
+                // ---- u tile: rows ur0..+2 (z index), columns uc0..+5 (u index) ----
+                if (has_ut) {
+#pragma unroll
+                    for (int r = 0; r < 3; r++) {
+                        const int I = ur0 + r;
+#pragma unroll
+                        for (int c = 0; c < 6; c++) {
+                            const int J = uc0 + c;
+                            double v = fq_gtpg(sP, sU, sG, S, I, J, dt, c2);
+                            if (I == J) v += S[SR_RD + I] + IPM_REG_PRIM;
+                            ua[r][c] = v;
+                        }
+                    }
+                    if (ur0 >= IFRC && ur0 < IQ && uc0 >= IFRC) {    // friction rows: 3x3 block of the foot
+                        const int ft = (ur0 - IFRC) / 3;
+                        const int cofs = IFRC + 3 * ft - uc0;        // first column of the foot inside this tile
+                        if (cofs >= 0 && cofs < 6) {
+                            for (int r5 = 0; r5 < 5; r5++) {
+                                const double g = sv[FV_GAM + 5 * ft + r5];
+                                const double* cf = S + SR_CF + 3 * (5 * ft + r5);
+#pragma unroll
+                                for (int r = 0; r < 3; r++)
+#pragma unroll
+                                    for (int c = 0; c < 3; c++) {
+                                        const double add = g * cf[r] * cf[c];
+                                        if (cofs == 0) ua[r][c] += add; else ua[r][3 + c] += add;
+                                    }
+                            }
+                        }
+                    }
+                }
+            }
+            // ---- x tile: rows 3xr..+2, columns 3xc..+2 of the state block ----
+            if (has_xt) {
+                const int i0 = 3 * xr, j0x = 3 * xc;
+#pragma unroll
+                for (int r = 0; r < 3; r++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int ii = i0 + r, jj = j0x + c;
+                        double v = term ? 0.0 : fq_gtpg(sP, sU, sG, S, IQ + ii, IQ + jj, dt, c2);
+                        if (ii < NQ && jj < NQ) v += S[SR_QQ + NQ * ii + jj];
+                        else if (ii == jj) v += (ii < 2 * NQ) ? S[SR_QV + ii - NQ] : S[SR_QH + ii - 2 * NQ];
+                        if (!term && ii == jj) v += IPM_REG_PRIM;
+                        xa[r][c] = v;
+                    }
+                if (i0 < 2 * NQ) {                                   // (q,v) x (q,v): all 22 state rows
+                    for (int g = 0; g < NGX; g++) {
+                        const double gm = sv[FV_GAM + NGF + g];
+                        if (gm == 0.0) continue;
+                        const double* row = S + SR_CX + 36 * g;
+                        const double a0 = row[i0] * gm, a1 = row[i0 + 1] * gm, a2 = row[i0 + 2] * gm;
+                        const double b0 = row[j0x], b1 = row[j0x + 1], b2 = row[j0x + 2];
+                        xa[0][0] += a0 * b0; xa[0][1] += a0 * b1; xa[0][2] += a0 * b2;
+                        xa[1][0] += a1 * b0; xa[1][1] += a1 * b1; xa[1][2] += a1 * b2;
+                        xa[2][0] += a2 * b0; xa[2][1] += a2 * b1; xa[2][2] += a2 * b2;
+                    }
+                } else {                                             // h rows: only the centroidal rows reach them
+#pragma unroll
+                    for (int r = 0; r < 3; r++) {
+                        const int hi = i0 + r - 2 * NQ;
+                        const double gm = sv[FV_GAM + GR_CONS + hi];
+#pragma unroll
+                        for (int c = 0; c < 3; c++) {
+                            const int jj = j0x + c;
+                            if (jj < 2 * NQ) xa[r][c] += gm * S[SR_CX + 36 * (16 + hi) + jj];
+                            else if (jj == i0 + r) xa[r][c] += gm;
+                        }
+                    }
+                }
+            }
+            __syncthreads();                 // every read of SR_k, P+, U, PGh is done
+            if (k > 0 && tid == 0) {         // prefetch the next stage record under the factorisation
+                mbar_arrive_expect_tx(&bar, SR_SZ * 8);
+                bulk_g2s(S, SRb + (size_t)(k - 1) * SR_SZ, SR_SZ * 8, &bar);
+            }
+            if (!term) {
+                // ---- right-looking Cholesky of the 30 input columns; x tiles take the same rank-6 updates ----
+                for (int jb = 0; jb < 5; jb++) {
+                    const int j0 = PB * jb;
+                    double* pan = sM + P_OFF(jb);                    // rows j0..72 of columns j0..j0+5
+                    if (has_ut && ucb == jb) {
+#pragma unroll
+                        for (int r = 0; r < 3; r++)
+#pragma unroll
+                            for (int c = 0; c < 6; c++) pan[(ur0 + r - j0) * PB + c] = ua[r][c];
+                    }
+                    if (tid < PB) pan[(NZ - j0) * PB + tid] = sv[FV_QT + j0 + tid];
+                    __syncthreads();
+                    const int nrow = NZ + 1 - j0;
+                    double drow[PB] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                    if (tid < nrow) {
+                        double Dm[PB][PB];
+#pragma unroll
+                        for (int aa = 0; aa < PB; aa++) {
+#pragma unroll
+                            for (int c = 0; c <= aa; c++) {
+                                double v = pan[aa * PB + c];
+#pragma unroll
+                                for (int e = 0; e < c; e++) v -= Dm[aa][e] * Dm[c][e];
+                                if (c == aa) {
+                                    double d = 0.0, inv = 0.0;
+                                    if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
+                                    Dm[aa][aa] = inv;
+                                    if (tid == aa) drow[c] = d;
+                                } else {
+                                    const double lv = v * Dm[c][c];
+                                    Dm[aa][c] = lv;
+                                    if (tid == aa) drow[c] = lv;
+                                }
+                            }
+                        }
+                        if (tid >= PB) {
+                            double rowv[PB];
+                            load6(pan + tid * PB, rowv);
+#pragma unroll
+                            for (int jj = 0; jj < PB; jj++) {
+                                double v = rowv[jj];
+#pragma unroll
+                                for (int e = 0; e < jj; e++) v -= rowv[e] * Dm[jj][e];
+                                rowv[jj] = v * Dm[jj][jj];
+                            }
+#pragma unroll
+                            for (int jj = 0; jj < PB; jj++) pan[tid * PB + jj] = rowv[jj];
+                        }
+                    }
+                    __syncthreads();
+                    if (tid < PB) {
+#pragma unroll
+                        for (int c = 0; c < PB; c++) pan[tid * PB + c] = drow[c];
+                    }
+                    if (has_ut && ucb > jb) {
+                        const double* pa = pan + (ur0 - j0) * PB;
+                        const double* pb = pan + (uc0 - j0) * PB;
+#pragma unroll
+                        for (int kk = 0; kk < PB; kk++) {
+                            const double a0 = pa[kk], a1 = pa[PB + kk], a2 = pa[2 * PB + kk];
+#pragma unroll
+                            for (int c = 0; c < 6; c++) {
+                                const double bv = pb[c * PB + kk];
+                                ua[0][c] -= a0 * bv; ua[1][c] -= a1 * bv; ua[2][c] -= a2 * bv;
+                            }
+                        }
+                    }
+                    if (has_xt) {
+                        const double* pa = pan + (NU + 3 * xr - j0) * PB;
+                        const double* pb = pan + (NU + 3 * xc - j0) * PB;
+                        double av[3][PB], bv[3][PB];
+#pragma unroll
+                        for (int r = 0; r < 3; r++) { load6(pa + r * PB, av[r]); load6(pb + r * PB, bv[r]); }
+#pragma unroll
+                        for (int r = 0; r < 3; r++)
+#pragma unroll
+                            for (int c = 0; c < 3; c++)
+#pragma unroll
+                                for (int kk = 0; kk < PB; kk++) xa[r][c] -= av[r][kk] * bv[c][kk];
+                    }
+                    if (tid < NZ - j0 - PB) {                        // row 72: m_c -= lu . L(c, j0..j0+5)
+                        const double* pa = pan + (NZ - j0) * PB;
+                        const double* pb = pan + (PB + tid) * PB;
+                        double av[6], bv[6];
+                        load6(pa, av);
+                        load6(pb, bv);
+                        double sm_ = sv[FV_QT + j0 + PB + tid];
+#pragma unroll
+                        for (int kk = 0; kk < PB; kk++) sm_ -= av[kk] * bv[kk];
+                        sv[FV_QT + j0 + PB + tid] = sm_;
+                    }
+                    // the next panel's owners write a different panel; the m row is ordered by the next barrier
+                }
+            }
+            __syncthreads();
+            // ---- P_k (both triangles) -> sP, p_k -> sv; factor record -> HBM ----
+            if (has_xt) {
+#pragma unroll
+                for (int r = 0; r < 3; r++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int ii = 3 * xr + r, jj = 3 * xc + c;
+                        if (ii >= jj) { sP[ii * P_LD + jj] = xa[r][c]; sP[jj * P_LD + ii] = xa[r][c]; }
+                    }
+            }
+            if (tid < NX) { const double pv = sv[FV_QT + NU + tid]; sv[FV_PN + tid] = pv; vk[V_P + tid] = pv; }
+            fence_proxy_async();
+            __syncthreads();
+            if (tid == 0) {
+                double* fr = FRb + (size_t)k * FR_SZ;
+                if (!term) bulk_s2g(fr + FR_MU, sM, LP_UPANELS * 8);
+                bulk_s2g(fr + FR_P, sP, NX * P_LD * 8);
+            }
+        }
+
+        // ================= norms, mu, exit tests (nmpc_qp_decide_kernel) =================
+        res4[0] = fq_block_max(n_g, red, tid);
+        res4[1] = fq_block_max(n_b, red, tid);
+        res4[2] = fq_block_max(n_d, red, tid);
+        res4[3] = fq_block_max(n_m, red, tid);
+        const double mu_sum = fq_block_sum(acc_mu, red, tid);
+        if (it == 0) nc_total = (int)(fq_block_sum((double)cnt, red, tid) + 0.5);
+        mu = nc_total > 0 ? mu_sum / nc_total : 0.0;
+        {
+            bool bad = false, conv = true;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if (isinf(res4[i]) || !(res4[i] == res4[i])) bad = true;
+                if (!(res4[i] < a.tol)) conv = false;
+            }
+            if (bad) { status = 3; break; }
+            if (conv) { status = 0; break; }
+            if (last) { status = 1; break; }
+        }
+
+        // ================= forward sweep: affine direction, step lengths =================
+        double a_p = 1.0, a_d = 1.0;
+        if (tid < NX) sv[FV_DX + tid] = 0.0;
+        if (tid == 0) bulk_store_wait_all();                         // the factor records are in global memory
+        __syncthreads();
+        for (int k = 0; k <= N; k++) {
+            const bool term = (k == N);
+            double* vk = vb + (size_t)k * V_STAGE;
+            if (tid == 0) {
+                const uint32_t bytes = (SR_SZ + (term ? 0 : LP_UPANELS)) * 8;
+                mbar_arrive_expect_tx(&bar, bytes);
+                bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
+                if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
+            }
+            if (!term && tid < NX) sv[FV_RB + tid] = vk[V_RB + tid];
+            __syncthreads();
+            mbar_wait(&bar, phase); phase ^= 1;
+            fq_forward_stage<false>(sM, sP, S, sv, vk, nullptr, qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG,
+                                    term, tid, dt, c2, a_p, a_d);
+        }
+        a_p = fq_block_min(a_p, red, tid);
+        a_d = fq_block_min(a_d, red, tid);
+        const double alpha_aff = fmin(a_p, a_d);
+
+        // ================= centring parameter (nmpc_qp_sigma_kernel) =================
+        double sigma_mu;
+        {
+            double s = 0.0;
+            for (int k = 0; k <= N; k++) {
+                if (tid < 2 * NG && SRb[(size_t)k * SR_SZ + SR_D + 2 * NG + tid] > 0.5) {
+                    const double* vk = vb + (size_t)k * V_STAGE;
+                    s += (qlamb[(size_t)k * 2 * NG + tid] + alpha_aff * vk[V_DLAM + tid]) *
+                         (qtb[(size_t)k * 2 * NG + tid] + alpha_aff * vk[V_DT + tid]);
+                }
+            }
+            s = fq_block_sum(s, red, tid);
+            const double mu_aff = nc_total > 0 ? s / nc_total : 0.0;
+            double sg = mu > 0.0 ? mu_aff / mu : 0.0;
+            sg = sg * sg * sg;
+            sigma_mu = sg * mu;
+        }
+
+        // ================= corrector: backward vector sweep on the stored factorisation =================
+        for (int k = N; k >= 0; k--) {
+            const bool term = (k == N);
+            double* vk = vb + (size_t)k * V_STAGE;
+            if (tid == 0) {
+                // SR_k, the u panels of stage k, and (once, for the terminal stage) nothing else: P_{k+1} is
+                // already in sP from the previous step of this sweep
+                const uint32_t bytes = (SR_SZ + (term ? 0 : LP_UPANELS)) * 8;
+                mbar_arrive_expect_tx(&bar, bytes);
+                bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
+                if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
+            }
+            if (!term && tid < NX) sv[FV_RB + tid] = vk[V_RB + tid];
+            if (tid < NZ) sv[FV_RG + tid] = vk[V_RG + tid];
+            __syncthreads();
+            mbar_wait(&bar, phase); phase ^= 1;
+            // corrector complementarity residual, gamma
+            if (tid < 2 * NG) {
+                double v = 0.0;
+                if (S[SR_D + 2 * NG + tid] > 0.5) {
+                    const double lam = qlamb[(size_t)k * 2 * NG + tid], t = qtb[(size_t)k * 2 * NG + tid];
+                    const double rmc = lam * t + vk[V_DT + tid] * vk[V_DLAM + tid] - sigma_mu;
+                    vk[V_RM + tid] = rmc;
+                    v = (rmc + lam * vk[V_RD + tid]) / t;
+                }
+                sv[FV_RD + tid] = v;                                 // scratch: per-side gamma
+            }
+            __syncthreads();
+            if (tid < NG) sv[FV_GAMV + tid] = sv[FV_RD + tid] - sv[FV_RD + NG + tid];
+            if (!term && tid >= 64 && tid < 64 + NX) {               // w = P+ rb + p+
+                const int i = tid - 64;
+                const double* row = sP + i * P_LD;
+                double s0 = sv[FV_PN + i], s1 = 0.0;
+#pragma unroll
+                for (int j = 0; j < NX; j += 2) { s0 += row[j] * sv[FV_RB + j]; s1 += row[j + 1] * sv[FV_RB + j + 1]; }
+                sv[FV_W + i] = s0 + s1;
+            }
+            __syncthreads();
+            if (tid < NZ) {                                          // m = rg + C' gamma + G' w
+                double s = sv[FV_RG + tid] + fq_ct(S, sv + FV_GAMV, tid);
+                if (!term) s += fq_gt(S, sv + FV_W, tid, dt, c2);
+                sv[FV_QT + tid] = s;
+            }
+            __syncthreads();
+            if (tid == 0) {                                          // sP is free: fetch P_k for the next step
+                mbar_arrive_expect_tx(&bar, NX * P_LD * 8);
+                bulk_g2s(sP, FRb + (size_t)k * FR_SZ + FR_P, NX * P_LD * 8, &bar);
+            }
+            if (!term) {
+                if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
+                    double m0 = tid < NU ? sv[FV_QT + tid] : 0.0;
+                    for (int j = 0; j < NU; j++) {
+                        const double d = sM[lp_idx(j, j)];
+                        const double inv = d != 0.0 ? 1.0 / d : 0.0;
+                        const double xj = __shfl_sync(0xffffffffu, m0, j) * inv;
+                        if (tid == j) m0 = xj;
+                        if (tid > j && tid < NU) m0 -= sM[lp_idx(tid, j)] * xj;
+                    }
+                    if (tid < NU) { sv[FV_DZ + tid] = m0; vk[V_LROW + tid] = m0; }
+                }
+                __syncthreads();
+                if (tid < NX) {                                      // p = m_x - Lxu lu
+                    double s0 = sv[FV_QT + NU + tid], s1 = 0.0;
+                    const double* row = sM;                          // panel-packed: gather per panel
+#pragma unroll
+                    for (int jb = 0; jb < 5; jb++) {
+                        double lv[6];
+                        load6(row + P_OFF(jb) + (NU + tid - PB * jb) * PB, lv);
+#pragma unroll
+                        for (int c = 0; c < 6; c += 2) { s0 -= lv[c] * sv[FV_DZ + PB * jb + c]; s1 -= lv[c + 1] * sv[FV_DZ + PB * jb + c + 1]; }
+                    }
+                    const double pv = s0 + s1;
+                    sv[FV_PN + tid] = pv; vk[V_P + tid] = pv;
+                }
+            } else if (tid < NX) {
+                const double pv = sv[FV_QT + NU + tid];
+                sv[FV_PN + tid] = pv; vk[V_P + tid] = pv;
+            }
+            __syncthreads();
+            mbar_wait(&bar, phase); phase ^= 1;                      // P_k is in sP
+        }
+
+        // ================= corrector: forward sweep with multiplier directions =================
+        a_p = 1.0; a_d = 1.0;
+        if (tid < NX) sv[FV_DX + tid] = 0.0;
+        __syncthreads();
+        for (int k = 0; k <= N; k++) {
+            const bool term = (k == N);
+            double* vk = vb + (size_t)k * V_STAGE;
+            if (tid == 0) {
+                const uint32_t bytes = (SR_SZ + (term ? 0 : LP_UPANELS) + (k > 0 ? NX * P_LD : 0)) * 8;
+                mbar_arrive_expect_tx(&bar, bytes);
+                bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
+                if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
+                if (k > 0) bulk_g2s(sP, FRb + (size_t)k * FR_SZ + FR_P, NX * P_LD * 8, &bar);
+            }
+            if (tid < NX) {
+                sv[FV_RB + tid] = term ? 0.0 : vk[V_RB + tid];
+                sv[FV_PN + tid] = vk[V_P + tid];
+            }
+            __syncthreads();
+            mbar_wait(&bar, phase); phase ^= 1;
+            if (!term && tid < NU) sM[lp_idx(NZ, tid)] = vk[V_LROW + tid];      // the corrector's lu replaces the affine one
+            __syncthreads();
+            fq_forward_stage<true>(sM, sP, S, sv, vk, k > 0 ? vb + (size_t)(k - 1) * V_STAGE + V_DPI : nullptr,
+                                   qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG, term, tid, dt, c2, a_p, a_d);
+        }
+        alpha_p = fq_block_min(a_p, red, tid);
+        alpha_d = fq_block_min(a_d, red, tid);
+    }
+
+    // ---- statistics of this QP ----
+    if (tid == 0) {
+        bulk_store_wait_all();
+        a.qp_iter[b] = iters;
+        a.qp_status[b] = status;
+        for (int i = 0; i < 4; i++) a.qp_res[(size_t)b * 4 + i] = res4[i];
+    }
+}

@@ -63,6 +63,7 @@ def test_qp_iterates_parity(oracle_mod, cap):
     dx0 = np.random.default_rng(1).normal(0, 1e-2, (B, 42))
     ro = so.solve_qp(qp, dx0)
     rg = sg.solve_qp(qp, dx0)
+    assert sg.last_qp_path == "fused"          # the product's kernel, not the generic dense fallback
     np.testing.assert_array_equal(rg["qp_iter"], ro["qp_iter"])
     np.testing.assert_array_equal(rg["qp_status"], ro["qp_status"])
     m = qp["mask"] > 0.5
