@@ -16,8 +16,8 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libnmpc_b200.so")
 SOURCES = ["nmpc_abi.cu"]
-DEPS = ["nmpc_abi.cu", "nmpc_common.cuh", "nmpc_linearize.cuh", "nmpc_qp_ipm.cuh", "nmpc_sqp.cuh",
-        "nmpc_gen_model.h", os.path.join("..", "..", "include", "nmpc_b200.h")]
+DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))) + \
+    [os.path.join("..", "..", "include", "nmpc_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "--shared", "-Xcompiler", "-fPIC"]
 

@@ -13,6 +13,7 @@
 #include "nmpc_qp_ipm.cuh"
 #include "nmpc_qp_fused.cuh"
 #include "nmpc_sqp.cuh"
+#include "nmpc_linearize_sr.cuh"
 
 #define CK(call)                                                     \
     do {                                                             \
@@ -317,6 +318,19 @@ static void launch_linearize(nmpc_handle* h, int b0, int Bc)
     h->launches += 2;
 }
 
+// product path: model evaluation followed by the assembly of the structured stage records
+static void launch_linearize_sr(nmpc_handle* h, int b0, int Bc)
+{
+    const int N = h->N, n_inst = Bc * (N + 1);
+    ModelArgs ma;
+    ma.x = h->x; ma.rec = h->rec; ma.done = h->done; ma.n_inst = n_inst; ma.N = N; ma.b0 = b0;
+    nmpc_model_kernel<<<dim3((n_inst + MODEL_THREADS - 1) / MODEL_THREADS, NMPC_MODEL_PARTS), MODEL_THREADS, 0,
+                        h->stream>>>(ma);
+    LinArgs la = lin_args(h, b0);
+    nmpc_linearize_sr_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la, h->SR);
+    h->launches += 2;
+}
+
 static QpArgs qp_args(nmpc_handle* h, int b0)
 {
     QpArgs a;
@@ -386,16 +400,19 @@ static void run_qp(nmpc_handle* h, QpArgs a, int Bc, bool apply)
 }
 
 // The product path: dense stage blocks -> stage records, then ONE fused kernel per QP (nmpc_qp_fused.cuh).
-static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, int check)
+static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, bool from_dense)
 {
     const int N = h->N;
     cudaStream_t s = h->stream;
-    SrArgs sa;
-    sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
-    sa.done = a.sqp_done; sa.N = N; sa.b0 = a.b0; sa.check = check; sa.dt = h->o.dt_nodes;
-    prof_begin(h, NMPC_PROF_QP_OTHER);
-    nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, s>>>(sa);
-    prof_end(h);
+    if (from_dense) {              // externally supplied dense QP: extract the stage records first
+        SrArgs sa;
+        sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
+        sa.done = a.sqp_done; sa.N = N; sa.b0 = a.b0; sa.check = 0; sa.dt = h->o.dt_nodes;
+        prof_begin(h, NMPC_PROF_QP_OTHER);
+        nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, s>>>(sa);
+        prof_end(h);
+        h->launches++;
+    }
     FqArgs f;
     f.SR = h->SR; f.FR = h->FR; f.vec = h->vec; f.qz = a.qz; f.qpi = a.qpi; f.qlam = a.qlam; f.qt = a.qt;
     f.qp_iter = a.qp_iter; f.qp_status = a.qp_status; f.qp_res = a.qp_res; f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
@@ -404,10 +421,10 @@ static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, int check
     prof_begin(h, NMPC_PROF_QP_FUSED);
     nmpc_qp_fused_kernel<<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
     prof_end(h);
-    h->launches += 2;
+    h->launches++;
     if (apply) {
         prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_apply_kernel<<<Bc, 128, 0, s>>>(a);
+        nmpc_qp_apply_sr_kernel<<<Bc, 128, 0, s>>>(a, h->SR);
         prof_end(h);
         h->launches++;
     }
@@ -429,14 +446,22 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
         for (int it = 0; it <= max_iter; it++) {
             if (rti && it == 1) break;
             prof_begin(h, NMPC_PROF_LINEARIZE);
-            launch_linearize(h, b0, Bc);
+            if (h->dense_qp) launch_linearize(h, b0, Bc);
+            else launch_linearize_sr(h, b0, Bc);
             prof_end(h);
             if (!rti) {
-                ResArgs ra;
-                ra.G = h->G; ra.M = h->M; ra.C = h->C; ra.D = h->D; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi;
-                ra.lam = h->lam; ra.res_acc = h->res_acc; ra.done = h->done; ra.N = N; ra.b0 = b0;
                 prof_begin(h, NMPC_PROF_RESIDUAL);
-                nmpc_residual_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
+                if (h->dense_qp) {
+                    ResArgs ra;
+                    ra.G = h->G; ra.M = h->M; ra.C = h->C; ra.D = h->D; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi;
+                    ra.lam = h->lam; ra.res_acc = h->res_acc; ra.done = h->done; ra.N = N; ra.b0 = b0;
+                    nmpc_residual_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
+                } else {
+                    ResSrArgs ra;
+                    ra.SR = h->SR; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi; ra.lam = h->lam; ra.res_acc = h->res_acc;
+                    ra.done = h->done; ra.N = N; ra.b0 = b0; ra.dt = h->o.dt_nodes;
+                    nmpc_residual_sr_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
+                }
                 prof_end(h);
                 nmpc_sqp_decide_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(
                     b0, Bc, N, it, max_iter, h->o.nlp_tol, h->res_acc, h->cost_stage, h->res, h->cost,
@@ -448,7 +473,7 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
                 h->launches++;
             }
             if (h->dense_qp) run_qp(h, qp_args(h, b0), Bc, true);
-            else run_qp_fused(h, qp_args(h, b0), Bc, true, 0);
+            else run_qp_fused(h, qp_args(h, b0), Bc, true, false);
             nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
             h->launches++;
         }
@@ -687,7 +712,7 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
         }
         h->last_qp_path = generic ? 0 : 1;
         if (generic) run_qp(h, qa, Bc, false);
-        else run_qp_fused(h, qa, Bc, false, 0);
+        else run_qp_fused(h, qa, Bc, false, false);   // the check pass above already wrote the records
         CK(cudaStreamSynchronize(h->stream));
     }
     CK(cudaGetLastError());
@@ -709,6 +734,11 @@ extern "C" int nmpc_debug_phase_cycles(unsigned long long* out16, int reset)
 {
 #ifdef NMPC_TIMING
     CK(cudaDeviceSynchronize());
+    if (reset >= 2) {            // fused kernel: 24 counters (out16 must hold 24 entries)
+        CK(cudaMemcpyFromSymbol(out16, g_fq_cycles, sizeof(unsigned long long) * 24));
+        if (reset == 3) { unsigned long long z[24] = {0}; CK(cudaMemcpyToSymbol(g_fq_cycles, z, sizeof(z))); }
+        return 0;
+    }
     CK(cudaMemcpyFromSymbol(out16, g_phase_cycles, sizeof(unsigned long long) * 16));
     if (reset) { unsigned long long z[16] = {0}; CK(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z))); }
     return 0;

@@ -341,13 +341,17 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
                 }
                 rhs += r1;
             }
-            double du = 0.0;
+            // back substitution with Luu': branch-free, one shuffle + multiply + fused multiply-add per step;
+            // lane l keeps rhs_l * (1 / L_ll) ready so the broadcast value is already the solution component
+            double du = 0.0, myinv = 0.0;
+            const int ll = lane < NU ? lane : NU - 1;
+            { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? 1.0 / d : 0.0; }
+#pragma unroll
             for (int i = NU - 1; i >= 0; i--) {
-                const double d = sM[lp_idx(i, i)];
-                const double inv = d != 0.0 ? 1.0 / d : 0.0;
-                const double dui = -__shfl_sync(0xffffffffu, rhs, i) * inv;
-                if (lane == i) du = dui;
-                if (lane < i) rhs += sM[lp_idx(i, lane)] * dui;
+                const double dui = -__shfl_sync(0xffffffffu, rhs * myinv, i);
+                const double lv = sM[lp_idx(i, ll < i ? ll : i)];
+                du = (lane == i) ? dui : du;
+                rhs = (lane < i) ? fma(lv, dui, rhs) : rhs;
             }
             if (lane < NU) sv[FV_DZ + lane] = du;
         }
@@ -378,51 +382,102 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
     __syncthreads();
 }
 
-// x tile t (t < N_XTILES) -> row block xr in 0..13, column block xc <= xr of the 42x42 state block
-__device__ __forceinline__ void xtile_of(int t, int& xr, int& xc)
+// ---------------------------------------------------------------------------------------------
+// register tiles of the stage matrix, sorted by block type so that a warp meets at most three or
+// four different assembly formulas: {row type, column type, row block, column block}
+//   u tiles (3 x 6): rows of z = [a f q v h] (types 0..4) x columns a / f (types 0 / 1)
+//   x tiles (3 x 3): rows q / v / h (types 0..2) x columns q / v / h of the 42 x 42 state block
+// ---------------------------------------------------------------------------------------------
+__constant__ unsigned char c_utile[100][4] = {{0,0,0,0}, {0,0,1,0}, {0,0,2,0}, {0,0,3,0}, {0,0,4,0}, {0,0,5,0}, {0,0,2,1}, {0,0,3,1}, {0,0,4,1}, {0,0,5,1}, {0,0,4,2}, {0,0,5,2}, {1,0,6,0}, {1,0,7,0}, {1,0,8,0}, {1,0,9,0}, {1,0,6,1}, {1,0,7,1}, {1,0,8,1}, {1,0,9,1}, {1,0,6,2}, {1,0,7,2}, {1,0,8,2}, {1,0,9,2}, {2,0,10,0}, {2,0,11,0}, {2,0,12,0}, {2,0,13,0}, {2,0,14,0}, {2,0,15,0}, {2,0,10,1}, {2,0,11,1}, {2,0,12,1}, {2,0,13,1}, {2,0,14,1}, {2,0,15,1}, {2,0,10,2}, {2,0,11,2}, {2,0,12,2}, {2,0,13,2}, {2,0,14,2}, {2,0,15,2}, {3,0,16,0}, {3,0,17,0}, {3,0,18,0}, {3,0,19,0}, {3,0,20,0}, {3,0,21,0}, {3,0,16,1}, {3,0,17,1}, {3,0,18,1}, {3,0,19,1}, {3,0,20,1}, {3,0,21,1}, {3,0,16,2}, {3,0,17,2}, {3,0,18,2}, {3,0,19,2}, {3,0,20,2}, {3,0,21,2}, {4,0,22,0}, {4,0,23,0}, {4,0,22,1}, {4,0,23,1}, {4,0,22,2}, {4,0,23,2}, {1,1,6,3}, {1,1,7,3}, {1,1,8,3}, {1,1,9,3}, {1,1,8,4}, {1,1,9,4}, {2,1,10,3}, {2,1,11,3}, {2,1,12,3}, {2,1,13,3}, {2,1,14,3}, {2,1,15,3}, {2,1,10,4}, {2,1,11,4}, {2,1,12,4}, {2,1,13,4}, {2,1,14,4}, {2,1,15,4}, {3,1,16,3}, {3,1,17,3}, {3,1,18,3}, {3,1,19,3}, {3,1,20,3}, {3,1,21,3}, {3,1,16,4}, {3,1,17,4}, {3,1,18,4}, {3,1,19,4}, {3,1,20,4}, {3,1,21,4}, {4,1,22,3}, {4,1,23,3}, {4,1,22,4}, {4,1,23,4}};
+__constant__ unsigned char c_xtile[105][4] = {{0,0,0,0}, {0,0,1,0}, {0,0,1,1}, {0,0,2,0}, {0,0,2,1}, {0,0,2,2}, {0,0,3,0}, {0,0,3,1}, {0,0,3,2}, {0,0,3,3}, {0,0,4,0}, {0,0,4,1}, {0,0,4,2}, {0,0,4,3}, {0,0,4,4}, {0,0,5,0}, {0,0,5,1}, {0,0,5,2}, {0,0,5,3}, {0,0,5,4}, {0,0,5,5}, {1,0,6,0}, {1,0,6,1}, {1,0,6,2}, {1,0,6,3}, {1,0,6,4}, {1,0,6,5}, {1,0,7,0}, {1,0,7,1}, {1,0,7,2}, {1,0,7,3}, {1,0,7,4}, {1,0,7,5}, {1,0,8,0}, {1,0,8,1}, {1,0,8,2}, {1,0,8,3}, {1,0,8,4}, {1,0,8,5}, {1,0,9,0}, {1,0,9,1}, {1,0,9,2}, {1,0,9,3}, {1,0,9,4}, {1,0,9,5}, {1,0,10,0}, {1,0,10,1}, {1,0,10,2}, {1,0,10,3}, {1,0,10,4}, {1,0,10,5}, {1,0,11,0}, {1,0,11,1}, {1,0,11,2}, {1,0,11,3}, {1,0,11,4}, {1,0,11,5}, {1,1,6,6}, {1,1,7,6}, {1,1,7,7}, {1,1,8,6}, {1,1,8,7}, {1,1,8,8}, {1,1,9,6}, {1,1,9,7}, {1,1,9,8}, {1,1,9,9}, {1,1,10,6}, {1,1,10,7}, {1,1,10,8}, {1,1,10,9}, {1,1,10,10}, {1,1,11,6}, {1,1,11,7}, {1,1,11,8}, {1,1,11,9}, {1,1,11,10}, {1,1,11,11}, {2,0,12,0}, {2,0,12,1}, {2,0,12,2}, {2,0,12,3}, {2,0,12,4}, {2,0,12,5}, {2,0,13,0}, {2,0,13,1}, {2,0,13,2}, {2,0,13,3}, {2,0,13,4}, {2,0,13,5}, {2,1,12,6}, {2,1,12,7}, {2,1,12,8}, {2,1,12,9}, {2,1,12,10}, {2,1,12,11}, {2,1,13,6}, {2,1,13,7}, {2,1,13,8}, {2,1,13,9}, {2,1,13,10}, {2,1,13,11}, {2,2,12,12}, {2,2,13,12}, {2,2,13,13}};
+
+// blocks of P_{k+1} (sP, ld 43; state order q 0..17, v 18..35, h 36..41) and of U = P[:,h] [Hf | Hq] (sU, ld 30)
+#define PQQ(i, j) sP[(i) * P_LD + (j)]
+#define PQV(i, j) sP[(i) * P_LD + NQ + (j)]
+#define PVQ(i, j) sP[(NQ + (i)) * P_LD + (j)]
+#define PVV(i, j) sP[(NQ + (i)) * P_LD + NQ + (j)]
+#define PHQ(h, j) sP[(2 * NQ + (h)) * P_LD + (j)]
+#define PHV(h, j) sP[(2 * NQ + (h)) * P_LD + NQ + (j)]
+#define PHH(h, g) sP[(2 * NQ + (h)) * P_LD + 2 * NQ + (g)]
+#define UF(r, j) sU[(r) * NU + (j)]
+#define UQ(r, j) sU[(r) * NU + 12 + (j)]
+
+// (G' P G) on a 3 x 6 tile: rows i0.. of block type RT (a f q v h), columns j0.. of block type CT (a f)
+template <int RT, int CT>
+__device__ __forceinline__ void fq_asm_u(const double* sP, const double* sU, const double* S, int i0, int j0,
+                                         double dt, double c2, double (&t)[3][6])
 {
-    int r = 0;
-    while ((r + 1) * (r + 2) / 2 <= t) r++;
-    xr = r;
-    xc = t - r * (r + 1) / 2;
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const int i = i0 + r;
+#pragma unroll
+        for (int c = 0; c < 6; c++) {
+            const int j = j0 + c;
+            double v;
+            if (CT == 0) {
+                if (RT == 0) v = c2 * c2 * PQQ(i, j) + c2 * dt * (PQV(i, j) + PVQ(i, j)) + dt * dt * PVV(i, j);
+                else if (RT == 1) v = c2 * UF(j, i) + dt * UF(NQ + j, i);
+                else if (RT == 2) v = c2 * (PQQ(i, j) + UQ(j, i)) + dt * (PQV(i, j) + UQ(NQ + j, i));
+                else if (RT == 3) v = c2 * dt * PQQ(i, j) + c2 * PVQ(i, j) + dt * dt * PQV(i, j) + dt * PVV(i, j);
+                else v = c2 * PHQ(i, j) + dt * PHV(i, j);
+            } else {
+                if (RT == 1) {
+                    v = 0.0;
+#pragma unroll
+                    for (int h = 0; h < 6; h++) v += S[SR_HF + 12 * h + i] * UF(2 * NQ + h, j);
+                } else if (RT == 2) {
+                    v = UF(i, j);
+#pragma unroll
+                    for (int h = 0; h < 6; h++) v += S[SR_HQ + NQ * h + i] * UF(2 * NQ + h, j);
+                } else if (RT == 3) v = dt * UF(i, j) + UF(NQ + i, j);
+                else v = UF(2 * NQ + i, j);
+            }
+            t[r][c] = v;
+        }
+    }
 }
 
-// (P G)[r][J]: row r of P_{k+1} (state index) against column J of G = [B A] (z index)
-__device__ __forceinline__ double fq_pg(const double* sP, const double* sU, int r, int J, double dt, double c2)
+// (G' P G) on a 3 x 3 tile of the state block: row type RT, column type CT in (q v h)
+template <int RT, int CT>
+__device__ __forceinline__ void fq_asm_x(const double* sP, const double* sU, const double* S, int i0, int j0,
+                                         double dt, double (&t)[3][3])
 {
-    const double* row = sP + r * P_LD;
-    if (J < IFRC) return c2 * row[J] + dt * row[NQ + J];
-    if (J < IQ) return sU[r * NU + (J - IFRC)];
-    if (J < IV) return row[J - IQ] + sU[r * NU + 12 + (J - IQ)];
-    if (J < IH) return dt * row[J - IV] + row[NQ + J - IV];
-    return row[2 * NQ + J - IH];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const int i = i0 + r;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const int j = j0 + c;
+            double v;
+            if (RT == 0) {
+                v = PQQ(i, j) + UQ(i, j) + UQ(j, i);
+#pragma unroll
+                for (int h = 0; h < 6; h++) v += S[SR_HQ + NQ * h + i] * UQ(2 * NQ + h, j);
+            } else if (RT == 1 && CT == 0) v = dt * PQQ(i, j) + PVQ(i, j) + dt * UQ(i, j) + UQ(NQ + i, j);
+            else if (RT == 1) v = dt * dt * PQQ(i, j) + dt * (PQV(i, j) + PVQ(i, j)) + PVV(i, j);
+            else if (CT == 0) v = PHQ(i, j) + UQ(2 * NQ + i, j);
+            else if (CT == 1) v = dt * PHQ(i, j) + PHV(i, j);
+            else v = PHH(i, j);
+            t[r][c] = v;
+        }
+    }
 }
 
-// (G' P G)[I][J] with the h rows of P G precomputed in sG (PGh[6][72])
-__device__ __forceinline__ double fq_gtpg(const double* sP, const double* sU, const double* sG, const double* S,
-                                          int I, int J, double dt, double c2)
-{
-    if (I < IFRC) return c2 * fq_pg(sP, sU, I, J, dt, c2) + dt * fq_pg(sP, sU, NQ + I, J, dt, c2);
-    if (I < IQ) {
-        const int i = I - IFRC;
-        double s = 0.0;
-#pragma unroll
-        for (int h = 0; h < 6; h++) s += S[SR_HF + 12 * h + i] * sG[h * NZ + J];
-        return s;
-    }
-    if (I < IV) {
-        const int i = I - IQ;
-        double s = fq_pg(sP, sU, i, J, dt, c2);
-#pragma unroll
-        for (int h = 0; h < 6; h++) s += S[SR_HQ + NQ * h + i] * sG[h * NZ + J];
-        return s;
-    }
-    if (I < IH) { const int i = I - IV; return dt * fq_pg(sP, sU, i, J, dt, c2) + fq_pg(sP, sU, NQ + i, J, dt, c2); }
-    return sG[(I - IH) * NZ + J];
-}
+#ifdef NMPC_TIMING
+__device__ unsigned long long g_fq_cycles[24];
+#define FMARK(ph) do { const long long t_ = clock64(); f_acc[ph] += (unsigned long long)(t_ - f_prev); f_prev = t_; } while (0)
+#else
+#define FMARK(ph) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 {
+#ifdef NMPC_TIMING
+    unsigned long long f_acc[24];
+#pragma unroll
+    for (int i = 0; i < 24; i++) f_acc[i] = 0ULL;
+    long long f_prev = clock64();
+#endif
     extern __shared__ __align__(16) double smem[];
     __shared__ __align__(8) uint64_t bar;
     const int tid = threadIdx.x;
@@ -433,7 +488,6 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     double* S = smem + FS_SR;
     double* sv = smem + FS_V;
     double* sU = smem + FS_U;
-    double* sG = smem + FS_PGH;
     double* red = sv + FV_RED;
     const double dt = a.dt, c2 = 0.5 * a.dt * a.dt;
 
@@ -462,10 +516,15 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 
     // tile ownership
     const bool has_ut = tid < N_UTILES, has_xt = tid < N_XTILES;
-    int urb = 0, ucb = 0, xr = 0, xc = 0;
-    if (has_ut) tile_of(tid, urb, ucb);
-    if (has_xt) xtile_of(tid, xr, xc);
+    int urt = 0, uct = 0, urb = 0, ucb = 0, xrt = 0, xct = 0, xr = 0, xc = 0;
+    if (has_ut) { urt = c_utile[tid][0]; uct = c_utile[tid][1]; urb = c_utile[tid][2]; ucb = c_utile[tid][3]; }
+    if (has_xt) { xrt = c_xtile[tid][0]; xct = c_xtile[tid][1]; xr = c_xtile[tid][2]; xc = c_xtile[tid][3]; }
     const int ur0 = 3 * urb, uc0 = 6 * ucb;
+    // first row / column of the tiles inside their block types
+    const int uti = ur0 - (urt == 0 ? IA : urt == 1 ? IFRC : urt == 2 ? IQ : urt == 3 ? IV : IH);
+    const int utj = uc0 - (uct == 0 ? IA : IFRC);
+    const int xti = 3 * xr - (xrt == 0 ? 0 : xrt == 1 ? NQ : 2 * NQ);
+    const int xtj = 3 * xc - (xct == 0 ? 0 : xct == 1 ? NQ : 2 * NQ);
 
     int status = 1, iters = 0, nc_total = 0;
     double alpha_p = 1.0, alpha_d = 1.0, mu = 0.0;
@@ -493,6 +552,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             __syncthreads();
         }
         iters = it;
+        FMARK(0);
 
         // ================= backward pass: residuals of every stage (+ factorisation unless last) =====
         double n_g = 0.0, n_b = 0.0, n_d = 0.0, n_m = 0.0, acc_mu = 0.0;
@@ -516,7 +576,9 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             }
             if (tid < 2 * NG) { sv[FV_LAM + tid] = qlam[tid]; sv[FV_T + tid] = qt[tid]; }
             __syncthreads();
+            FMARK(1);
             mbar_wait(&bar, phase); phase ^= 1;                      // SR_k has landed
+            FMARK(2);
 
             fq_cz(S, sv + FV_Z, sv + FV_CZ, tid);
             __syncthreads();
@@ -575,6 +637,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 continue;
             }
 
+            FMARK(3);
             // ---------------- Riccati step of stage k (classical recursion on P) ----------------
             double xa[3][3], ua[3][6];
             if (tid == 0) bulk_store_wait_read();                    // the previous factor record has left sM / sP
@@ -599,21 +662,26 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 }
                 if (tid < NZ) sv[FV_QT + tid] += fq_gt(S, sv + FV_W, tid, dt, c2);       // m = q tilde + G' w
                 __syncthreads();
-                for (int e = tid; e < 6 * NZ; e += FQ_THREADS)       // PGh = (P+ G)[h rows]
-                    sG[e] = fq_pg(sP, sU, 2 * NQ + e / NZ, e % NZ, dt, c2);
-                __syncthreads();
+                FMARK(4);
                 // ---- u tile: rows ur0..+2 (z index), columns uc0..+5 (u index) ----
                 if (has_ut) {
+                    switch (uct * 5 + urt) {
+                    case 0: fq_asm_u<0, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 1: fq_asm_u<1, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 2: fq_asm_u<2, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 3: fq_asm_u<3, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 4: fq_asm_u<4, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 6: fq_asm_u<1, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 7: fq_asm_u<2, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    case 8: fq_asm_u<3, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    default: fq_asm_u<4, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                    }
+                    if (urb / 2 == ucb) {                            // diagonal tile: Hessian diagonal + regularisation
 #pragma unroll
-                    for (int r = 0; r < 3; r++) {
-                        const int I = ur0 + r;
+                        for (int r = 0; r < 3; r++)
 #pragma unroll
-                        for (int c = 0; c < 6; c++) {
-                            const int J = uc0 + c;
-                            double v = fq_gtpg(sP, sU, sG, S, I, J, dt, c2);
-                            if (I == J) v += S[SR_RD + I] + IPM_REG_PRIM;
-                            ua[r][c] = v;
-                        }
+                            for (int c = 0; c < 6; c++)
+                                if (ur0 + r == uc0 + c) ua[r][c] += S[SR_RD + ur0 + r] + IPM_REG_PRIM;
                     }
                     if (ur0 >= IFRC && ur0 < IQ && uc0 >= IFRC) {    // friction rows: 3x3 block of the foot
                         const int ft = (ur0 - IFRC) / 3;
@@ -637,16 +705,31 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             // ---- x tile: rows 3xr..+2, columns 3xc..+2 of the state block ----
             if (has_xt) {
                 const int i0 = 3 * xr, j0x = 3 * xc;
+                if (term) {
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+#pragma unroll
+                        for (int c = 0; c < 3; c++) xa[r][c] = 0.0;
+                } else {
+                    switch (xrt * 3 + xct) {
+                    case 0: fq_asm_x<0, 0>(sP, sU, S, xti, xtj, dt, xa); break;
+                    case 3: fq_asm_x<1, 0>(sP, sU, S, xti, xtj, dt, xa); break;
+                    case 4: fq_asm_x<1, 1>(sP, sU, S, xti, xtj, dt, xa); break;
+                    case 6: fq_asm_x<2, 0>(sP, sU, S, xti, xtj, dt, xa); break;
+                    case 7: fq_asm_x<2, 1>(sP, sU, S, xti, xtj, dt, xa); break;
+                    default: fq_asm_x<2, 2>(sP, sU, S, xti, xtj, dt, xa); break;
+                    }
+                }
 #pragma unroll
                 for (int r = 0; r < 3; r++)
 #pragma unroll
                     for (int c = 0; c < 3; c++) {
                         const int ii = i0 + r, jj = j0x + c;
-                        double v = term ? 0.0 : fq_gtpg(sP, sU, sG, S, IQ + ii, IQ + jj, dt, c2);
-                        if (ii < NQ && jj < NQ) v += S[SR_QQ + NQ * ii + jj];
-                        else if (ii == jj) v += (ii < 2 * NQ) ? S[SR_QV + ii - NQ] : S[SR_QH + ii - 2 * NQ];
+                        double v = 0.0;
+                        if (xrt == 0) v = S[SR_QQ + NQ * ii + jj];
+                        else if (ii == jj) v = (xrt == 1) ? S[SR_QV + ii - NQ] : S[SR_QH + ii - 2 * NQ];
                         if (!term && ii == jj) v += IPM_REG_PRIM;
-                        xa[r][c] = v;
+                        xa[r][c] += v;
                     }
                 if (i0 < 2 * NQ) {                                   // (q,v) x (q,v): all 22 state rows
                     for (int g = 0; g < NGX; g++) {
@@ -674,6 +757,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 }
             }
             __syncthreads();                 // every read of SR_k, P+, U, PGh is done
+            FMARK(5);
             if (k > 0 && tid == 0) {         // prefetch the next stage record under the factorisation
                 mbar_arrive_expect_tx(&bar, SR_SZ * 8);
                 bulk_g2s(S, SRb + (size_t)(k - 1) * SR_SZ, SR_SZ * 8, &bar);
@@ -691,41 +775,43 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                     }
                     if (tid < PB) pan[(NZ - j0) * PB + tid] = sv[FV_QT + j0 + tid];
                     __syncthreads();
+                    // Panel factorisation, right-looking in registers: every row thread factors the 6x6 diagonal
+                    // block redundantly and carries its own row along as a seventh row, so the dependent chain per
+                    // pivot is one rsqrt, one multiply and one fused multiply-add.  Non-positive pivots zero their
+                    // column (BLASFEO potrf rule).
                     const int nrow = NZ + 1 - j0;
                     double drow[PB] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
                     if (tid < nrow) {
-                        double Dm[PB][PB];
+                        double A[PB][PB], rv[PB];
 #pragma unroll
-                        for (int aa = 0; aa < PB; aa++) {
+                        for (int aa = 0; aa < PB; aa++)
 #pragma unroll
-                            for (int c = 0; c <= aa; c++) {
-                                double v = pan[aa * PB + c];
+                            for (int c = 0; c <= aa; c++) A[aa][c] = pan[aa * PB + c];
+                        load6(pan + tid * PB, rv);
 #pragma unroll
-                                for (int e = 0; e < c; e++) v -= Dm[aa][e] * Dm[c][e];
-                                if (c == aa) {
-                                    double d = 0.0, inv = 0.0;
-                                    if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
-                                    Dm[aa][aa] = inv;
-                                    if (tid == aa) drow[c] = d;
-                                } else {
-                                    const double lv = v * Dm[c][c];
-                                    Dm[aa][c] = lv;
-                                    if (tid == aa) drow[c] = lv;
-                                }
+                        for (int j = 0; j < PB; j++) {
+                            const double v = A[j][j];
+                            double d = 0.0, inv = 0.0;
+                            if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
+                            A[j][j] = d;
+#pragma unroll
+                            for (int i = j + 1; i < PB; i++) A[i][j] *= inv;
+                            rv[j] *= inv;
+#pragma unroll
+                            for (int c = j + 1; c < PB; c++) {
+#pragma unroll
+                                for (int i = c; i < PB; i++) A[i][c] -= A[i][j] * A[c][j];
+                                rv[c] -= rv[j] * A[c][j];
                             }
                         }
                         if (tid >= PB) {
-                            double rowv[PB];
-                            load6(pan + tid * PB, rowv);
 #pragma unroll
-                            for (int jj = 0; jj < PB; jj++) {
-                                double v = rowv[jj];
+                            for (int jj = 0; jj < PB; jj++) pan[tid * PB + jj] = rv[jj];
+                        } else {
 #pragma unroll
-                                for (int e = 0; e < jj; e++) v -= rowv[e] * Dm[jj][e];
-                                rowv[jj] = v * Dm[jj][jj];
-                            }
+                            for (int aa = 0; aa < PB; aa++)
 #pragma unroll
-                            for (int jj = 0; jj < PB; jj++) pan[tid * PB + jj] = rowv[jj];
+                                for (int c = 0; c <= aa; c++) if (tid == aa) drow[c] = A[aa][c];
                         }
                     }
                     __syncthreads();
@@ -774,6 +860,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 }
             }
             __syncthreads();
+            FMARK(6);
             // ---- P_k (both triangles) -> sP, p_k -> sv; factor record -> HBM ----
             if (has_xt) {
 #pragma unroll
@@ -794,6 +881,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             }
         }
 
+        FMARK(7);
         // ================= norms, mu, exit tests (nmpc_qp_decide_kernel) =================
         res4[0] = fq_block_max(n_g, red, tid);
         res4[1] = fq_block_max(n_b, red, tid);
@@ -814,6 +902,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             if (last) { status = 1; break; }
         }
 
+        FMARK(8);
         // ================= forward sweep: affine direction, step lengths =================
         double a_p = 1.0, a_d = 1.0;
         if (tid < NX) sv[FV_DX + tid] = 0.0;
@@ -838,6 +927,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         a_d = fq_block_min(a_d, red, tid);
         const double alpha_aff = fmin(a_p, a_d);
 
+        FMARK(9);
         // ================= centring parameter (nmpc_qp_sigma_kernel) =================
         double sigma_mu;
         {
@@ -856,6 +946,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             sigma_mu = sg * mu;
         }
 
+        FMARK(10);
         // ================= corrector: backward vector sweep on the stored factorisation =================
         for (int k = N; k >= 0; k--) {
             const bool term = (k == N);
@@ -871,7 +962,9 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             if (!term && tid < NX) sv[FV_RB + tid] = vk[V_RB + tid];
             if (tid < NZ) sv[FV_RG + tid] = vk[V_RG + tid];
             __syncthreads();
+            FMARK(13);
             mbar_wait(&bar, phase); phase ^= 1;
+            FMARK(14);
             // corrector complementarity residual, gamma
             if (tid < 2 * NG) {
                 double v = 0.0;
@@ -894,29 +987,34 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 sv[FV_W + i] = s0 + s1;
             }
             __syncthreads();
+            FMARK(15);
             if (tid < NZ) {                                          // m = rg + C' gamma + G' w
                 double s = sv[FV_RG + tid] + fq_ct(S, sv + FV_GAMV, tid);
                 if (!term) s += fq_gt(S, sv + FV_W, tid, dt, c2);
                 sv[FV_QT + tid] = s;
             }
             __syncthreads();
+            FMARK(16);
             if (tid == 0) {                                          // sP is free: fetch P_k for the next step
                 mbar_arrive_expect_tx(&bar, NX * P_LD * 8);
                 bulk_g2s(sP, FRb + (size_t)k * FR_SZ + FR_P, NX * P_LD * 8, &bar);
             }
+            __syncwarp();         // reconverge warp 0 before its shuffles: a split warp takes the slow shuffle path
             if (!term) {
                 if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
-                    double m0 = tid < NU ? sv[FV_QT + tid] : 0.0;
+                    double m0 = tid < NU ? sv[FV_QT + tid] : 0.0, myinv = 0.0;
+                    const int ll = tid < NU ? tid : NU - 1;
+                    { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? 1.0 / d : 0.0; }
+#pragma unroll
                     for (int j = 0; j < NU; j++) {
-                        const double d = sM[lp_idx(j, j)];
-                        const double inv = d != 0.0 ? 1.0 / d : 0.0;
-                        const double xj = __shfl_sync(0xffffffffu, m0, j) * inv;
-                        if (tid == j) m0 = xj;
-                        if (tid > j && tid < NU) m0 -= sM[lp_idx(tid, j)] * xj;
+                        const double xj = __shfl_sync(0xffffffffu, m0 * myinv, j);
+                        const double lv = sM[lp_idx(ll > j ? ll : j, j)];
+                        m0 = (tid == j) ? xj : ((tid > j && tid < NU) ? fma(-lv, xj, m0) : m0);
                     }
                     if (tid < NU) { sv[FV_DZ + tid] = m0; vk[V_LROW + tid] = m0; }
                 }
                 __syncthreads();
+                FMARK(17);
                 if (tid < NX) {                                      // p = m_x - Lxu lu
                     double s0 = sv[FV_QT + NU + tid], s1 = 0.0;
                     const double* row = sM;                          // panel-packed: gather per panel
@@ -935,9 +1033,13 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 sv[FV_PN + tid] = pv; vk[V_P + tid] = pv;
             }
             __syncthreads();
+            FMARK(18);
             mbar_wait(&bar, phase); phase ^= 1;                      // P_k is in sP
+            __syncthreads();      // nobody may still be polling this phase when thread 0 re-arms the barrier
+            FMARK(19);
         }
 
+        FMARK(11);
         // ================= corrector: forward sweep with multiplier directions =================
         a_p = 1.0; a_d = 1.0;
         if (tid < NX) sv[FV_DX + tid] = 0.0;
@@ -965,8 +1067,15 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         }
         alpha_p = fq_block_min(a_p, red, tid);
         alpha_d = fq_block_min(a_d, red, tid);
+        FMARK(12);
     }
 
+#ifdef NMPC_TIMING
+    if (bl == 0 && tid == 0) {
+#pragma unroll
+        for (int i = 0; i < 24; i++) g_fq_cycles[i] += f_acc[i];
+    }
+#endif
     // ---- statistics of this QP ----
     if (tid == 0) {
         bulk_store_wait_all();
