@@ -53,9 +53,17 @@ ALGO_DOUBLES_PER_STAGE = {
     # model evaluation + assembly: read x, u, p, yref; write G, M, C, D (record written + read once)
     "linearize": _G + _M + _C + _D + 2 * 735 + 250,
 }
+# The fused kernel (nmpc_qp_fused.cuh) runs a whole QP: max_qp_iter x (stage + factor + corrector) plus the final
+# residual pass.  Its ALGORITHMIC bytes are those of the dense algorithm above (the invariant SURVEY.md 8d
+# prescribes: structure exploitation must not shrink the numerator); the bytes it really moves are `traffic`.
+ALGO_DOUBLES_PER_STAGE_PER_ITER = (ALGO_DOUBLES_PER_STAGE["qp_stage"] + ALGO_DOUBLES_PER_STAGE["qp_factor"]
+                                   + ALGO_DOUBLES_PER_STAGE["qp_corr"])
 
 
-def algo_bytes_per_launch(kind: str, B: int, N: int = N_NODES) -> float:
+def algo_bytes_per_launch(kind: str, B: int, N: int = N_NODES, n_ipm: float = 6.0) -> float:
+    if kind == "qp_fused":
+        per_stage = n_ipm * ALGO_DOUBLES_PER_STAGE_PER_ITER + ALGO_DOUBLES_PER_STAGE["qp_stage"]
+        return 8.0 * per_stage * (N + 1) * B
     return 8.0 * ALGO_DOUBLES_PER_STAGE[kind] * (N + 1) * B
 
 
@@ -122,7 +130,7 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------
-def time_cpu_oracle(batch, opts: dict, n_problems: int, threads: int) -> dict:
+def time_cpu_oracle(batch, opts: dict, n_problems: int, threads: int, repeats: int = 1) -> dict:
     """Bounded sample of the same workload on the host cores with the CPU oracle."""
     from oracle import oracle as O
     O.build()
@@ -132,12 +140,14 @@ def time_cpu_oracle(batch, opts: dict, n_problems: int, threads: int) -> dict:
     _, _, hg = O.kinematics(sub["qv"])
     s = O.OracleSolver(n, O.default_opts(**opts))
     from iterative_learning_nmpc_b200 import workloads as WL
-    WL.load_into(s, sub, hg)
-    t0 = time.perf_counter()
-    s.solve(threads)
-    dt = time.perf_counter() - t0
-    return {"value": n / dt, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{n} OCPs of the same batch, one solver per thread (OpenMP dynamic), {dt:.2f} s wall; "
+    dt = 0.0
+    for _ in range(repeats):                   # identical cold-started work every repeat, like the GPU steps
+        WL.load_into(s, sub, hg)
+        t0 = time.perf_counter()
+        s.solve(threads)
+        dt += time.perf_counter() - t0
+    return {"value": n * repeats / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{repeats} x {n} OCPs of the same batch, one solver per thread (OpenMP dynamic), {dt:.2f} s wall; "
                       "CPU restatement of the algorithm, not acados/HPIPM"}
 
 
@@ -150,7 +160,7 @@ def run_reference(args) -> None:
     from iterative_learning_nmpc_b200 import workloads as WL
     opts, gaits = workload_opts(args.config)
     threads = os.cpu_count() or 1
-    n = max(threads * 4, 32)
+    n = max(threads * 64, 512)                # ~1 s of CPU work per step on 16 cores
     batch = WL.make_batch(n, seed=args.config - 1, gaits=gaits)
     vals = []
     for i in range(args.warmup + args.steps):
@@ -296,27 +306,37 @@ def main() -> None:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     kinds = {k: {"ms_total": v[0], "launches": v[1]} for k, v in kt.items()}
-    heavy = [k for k in ALGO_DOUBLES_PER_STAGE if kinds[k]["launches"]]
+    heavy = [k for k in list(ALGO_DOUBLES_PER_STAGE) + ["qp_fused"] if kinds.get(k, {}).get("launches")]
     for k in heavy:
         ms_l = kinds[k]["ms_total"] / kinds[k]["launches"]
         kinds[k]["launch_ms"] = ms_l
-        kinds[k]["achieved_gbs"] = algo_bytes_per_launch(k, B) / (ms_l * 1e-3) / 1e9
+        kinds[k]["achieved_gbs"] = algo_bytes_per_launch(k, B, n_ipm=n_ipm) / (ms_l * 1e-3) / 1e9
         kinds[k]["frac_of_hbm_peak"] = kinds[k]["achieved_gbs"] / peak
     dom = max(heavy, key=lambda k: kinds[k]["ms_total"])
+    traffic = None
+    try:                                   # DRAM bytes per launch from the committed ncu capture, scaled to this batch
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if dom in tr and args.config == int(tr.get("config", 2)):
+            traffic = float(tr[dom]) * B / float(tr["batch"])
+    except (OSError, ValueError):
+        pass
     roofline = {"bound": "hbm", "kernel": {"qp_stage": "nmpc_qp_stage_kernel", "qp_factor": "nmpc_qp_factor_kernel",
-                                           "qp_corr": "nmpc_qp_corr_solve_kernel",
-                                           "linearize": "nmpc_model_kernel+nmpc_linearize_kernel"}[dom],
+                                           "qp_corr": "nmpc_qp_corr_solve_kernel", "qp_fused": "nmpc_qp_fused_kernel",
+                                           "linearize": "nmpc_model_kernel+nmpc_linearize_sr_kernel"}[dom],
                 "achieved": kinds[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                "frac": kinds[dom]["frac_of_hbm_peak"], "traffic": None,
+                "frac": kinds[dom]["frac_of_hbm_peak"], "traffic": traffic,
+                "algorithmic_bytes": "dense-algorithm bytes (SURVEY.md 8d invariant); `traffic` = measured DRAM bytes "
+                                     "of the structured implementation (ncu, profiles/traffic.json)",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
-                "algorithmic_bytes_per_launch": algo_bytes_per_launch(dom, B), "launch_ms": kinds[dom]["launch_ms"],
+                "algorithmic_bytes_per_launch": algo_bytes_per_launch(dom, B, n_ipm=n_ipm), "launch_ms": kinds[dom]["launch_ms"],
                 "per_kind": kinds, "profiled_steps": args.steps,
                 "mean_ipm_iter": n_ipm, "mean_sqp_iter": n_sqp}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        cpu = time_cpu_oracle(batch, opts, max(threads * 16, 64), threads)
+        # ~0.85k solves/s on 16 cores: 8192 OCP solves (the 1024-OCP batch, eight times) is about 10 s of CPU work
+        cpu = time_cpu_oracle(batch, opts, B, threads, repeats=8 if args.config == 2 else 1)
 
     if rank == 0:
         print(json.dumps({
