@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- batched NMPC SQP solves/sec (BASELINE.json metric) on N B200s of one node.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--batch B] [--config 2|3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--batch B] [--config 2|3|4|5]
 
 A "step" is one pass of the hot path (QuadrupedAcadosSolver.init + solve,
 /root/reference/mpc_controller/utils/solver.py:356-429) over one batch of synthetic OCPs:
@@ -60,7 +60,14 @@ ALGO_DOUBLES_PER_STAGE_PER_ITER = (ALGO_DOUBLES_PER_STAGE["qp_stage"] + ALGO_DOU
                                    + ALGO_DOUBLES_PER_STAGE["qp_corr"])
 
 
+def ocps_per_launch(B: int) -> float:
+    """The QP workspace is chunked (NMPC_CHUNK, default 4096 OCPs): a launch covers one chunk."""
+    chunk = int(os.environ.get("NMPC_CHUNK", "4096"))
+    return B / max(1, -(-B // chunk))
+
+
 def algo_bytes_per_launch(kind: str, B: int, N: int = N_NODES, n_ipm: float = 6.0) -> float:
+    B = ocps_per_launch(B)
     if kind == "qp_fused":
         per_stage = n_ipm * ALGO_DOUBLES_PER_STAGE_PER_ITER + ALGO_DOUBLES_PER_STAGE["qp_stage"]
         return 8.0 * per_stage * (N + 1) * B
@@ -73,13 +80,28 @@ def workload_opts(cfg: int):
     if cfg == 3:
         return dict(real_time_it=0, max_iter=15, max_qp_iter=6, qp_tol=1e-2, nlp_tol=1e-1, warm_start_qp=0), \
             ("trot", "pace", "bound")
-    raise SystemExit("--config must be 2 or 3")
+    if cfg in (4, 5):     # default mpc_opt.py: SQP (not RTI), max_iter = 1 per replanning tick (mpc_opt.py:26-38)
+        return dict(real_time_it=0, max_iter=1, max_qp_iter=6, qp_tol=1e-2, nlp_tol=1e-1, warm_start_qp=0), ("trot",)
+    raise SystemExit("--config must be 2, 3, 4 or 5")
+
+
+def workload_kwargs(cfg: int, kin) -> dict:
+    if cfg == 4:
+        return dict(restrict_cnt=True, kin=kin)
+    if cfg == 5:
+        return dict(push=True)
+    return {}
 
 
 def workload_name(cfg: int, B: int) -> str:
     if cfg == 2:
         return f"config2: Go2 trot, {B} perturbed initial states per GPU, SQP_RTI, N=25, max_qp_iter=6"
-    return f"config3: Go2 trot/pace/bound mixed, {B} OCPs per GPU, full SQP max_iter=15, N=25, max_qp_iter=6"
+    if cfg == 3:
+        return f"config3: Go2 trot/pace/bound mixed, {B} OCPs per GPU, full SQP max_iter=15, N=25, max_qp_iter=6"
+    if cfg == 4:
+        return (f"config4 (without enable_time_opt, which is not built): Go2 trot, {B} OCPs per GPU, cnt_patch_restriction "
+                "with Raibert footholds + opt_peak, SQP max_iter=1, N=25, max_qp_iter=6")
+    return f"config5: DAgger sweep tick, Go2 trot, {B} push-perturbed OCPs per GPU, SQP max_iter=1, N=25, max_qp_iter=6"
 
 
 # ---------------------------------------------------------------------------------------------
@@ -161,7 +183,9 @@ def run_reference(args) -> None:
     opts, gaits = workload_opts(args.config)
     threads = os.cpu_count() or 1
     n = max(threads * 64, 512)                # ~1 s of CPU work per step on 16 cores
-    batch = WL.make_batch(n, seed=args.config - 1, gaits=gaits)
+    from oracle import oracle as O
+    O.build()
+    batch = WL.make_batch(n, seed=args.config - 1, gaits=gaits, **workload_kwargs(args.config, O.kinematics))
     vals = []
     for i in range(args.warmup + args.steps):
         r = time_cpu_oracle(batch, opts, n, threads)
@@ -214,8 +238,8 @@ def main() -> None:
 
     B = args.batch
     opts, gaits = workload_opts(args.config)
-    batch = WL.make_batch(B, seed=1000 * rank + args.config - 1, gaits=gaits)
     solver = NmpcSolver(B, default_opts(**opts), device=local)
+    batch = WL.make_batch(B, seed=1000 * rank + args.config - 1, gaits=gaits, **workload_kwargs(args.config, solver.kinematics))
     stream = torch.cuda.ExternalStream(solver.stream_ptr, device=local)
     _, _, hg = solver.kinematics(batch["qv"])
     xg = batch["x_guess"].copy()
@@ -317,7 +341,7 @@ def main() -> None:
     try:                                   # DRAM bytes per launch from the committed ncu capture, scaled to this batch
         tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         if dom in tr and args.config == int(tr.get("config", 2)):
-            traffic = float(tr[dom]) * B / float(tr["batch"])
+            traffic = float(tr[dom]) * ocps_per_launch(B) / float(tr["batch"])
     except (OSError, ValueError):
         pass
     roofline = {"bound": "hbm", "kernel": {"qp_stage": "nmpc_qp_stage_kernel", "qp_factor": "nmpc_qp_factor_kernel",
@@ -345,8 +369,8 @@ def main() -> None:
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args.config, B), "batch_per_gpu": B, "global_batch": total,
                        "parallelism": f"problem-sharded x{world}, no data-path collective",
-                       "l2": "per-step working set (QP stage blocks + factors) is "
-                             f"{B * 26 * (_G + _M + _C + _D + 2 * _LP + 752) * 8 / 1e9:.2f} GB per GPU, larger than the 126 MB L2"},
+                       "l2": "per-step working set (stage records 1692 + factor records 3680 + stage vectors 752 doubles per "
+                             f"stage) is {ocps_per_launch(B) * 26 * (1692 + 3680 + 752) * 8 / 1e9:.2f} GB per launch, larger than the 126 MB L2"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": max(ms_e2e, wall_e2e) / args.steps},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,

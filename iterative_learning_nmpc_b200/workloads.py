@@ -14,16 +14,42 @@ import numpy as np
 
 from . import problem as P
 from .mpc_controller.config.quadruped.utils import get_quadruped_config
-from .mpc_controller.utils.contact_planner import ContactPlanner
+from .mpc_controller.utils.contact_planner import ContactPlanner, RaiberContactPlanner
 
 FEET = ["FL_foot", "FR_foot", "RL_foot", "RR_foot"]
 STAND_HEIGHT = 0.2648058464833031     # base height at which the home pose has its feet at z = 0
 MASS = 15.017
 
 
+def _restricted_base_ref(loc: np.ndarray, nom_height: float):
+    """`LocomotionMPC.compute_base_ref_cnt_restricted` (mpc.py:274-315) for one problem, loc [4, N+1, 3]."""
+    u = np.unique(loc, axis=1)
+    nz = np.argwhere(np.all(u != np.zeros(3), axis=-1))
+    count = np.bincount(nz[:, 1]) if len(nz) else np.zeros(0, dtype=int)
+    if len(count) > 0:
+        first = int(np.argmax(count))
+        last = len(count) - int(np.argmax(count[::-1])) - 1
+        c_first, c_last = u[:, first, :].mean(axis=0), u[:, last, :].mean(axis=0)
+    else:
+        c_first, c_last = loc[:, 0, :].mean(axis=0), loc[:, -1, :].mean(axis=0)
+    ref, ref_e = np.zeros(12), np.zeros(12)
+    ref[:2] = 0.35 * c_first[:2] + 0.65 * c_last[:2]
+    ref_e[:2] = c_last[:2]
+    ref[2] = ref_e[2] = nom_height
+    return ref, ref_e
+
+
 def make_batch(B: int, seed: int = 0, gaits: Sequence[str] = ("trot",), n_nodes: int = 25,
-               dt_nodes: float = 0.04, perturb: float = 1.0, robot: str = "go2") -> Dict[str, np.ndarray]:
+               dt_nodes: float = 0.04, perturb: float = 1.0, robot: str = "go2",
+               restrict_cnt: bool = False, push: bool = False, kin=None) -> Dict[str, np.ndarray]:
     """B independent OCPs: perturbed x0, random gait phase, random velocity goal.
+
+    restrict_cnt (BASELINE config 4, without time optimisation): Raibert footholds per problem
+    (`contact_planner.py:265-322`), contact-patch restriction rows and foot-target costs switched on,
+    references centred on the planned contacts; needs `kin(qv) -> (feet, com, hg)` (the solver's
+    kinematics) for the hip offsets and the CoM.
+    push (config 5): the base velocity carries the impulse of a 50-70 N push held for 0.2-0.4 s in a
+    random horizontal direction (`Behavior_Cloning/examples/cfgs/bc_experimental.yaml:32-35`).
 
     Returns qv [B,36], W [B,76], W_e [B,52], yref [B,N,76], yref_e [B,52], p [B,N+1,44],
     i_node [B] int32, x_guess [B,N+1,42] (q,v repeated, h filled by the caller or zero),
@@ -40,6 +66,11 @@ def make_batch(B: int, seed: int = 0, gaits: Sequence[str] = ("trot",), n_nodes:
     qv[:, 6:18] += rng.uniform(-0.3, 0.3, (B, 12)) * s
     qv[:, 18:24] += rng.uniform(-0.5, 0.5, (B, 6)) * s     # base twist
     qv[:, 24:36] += rng.uniform(-2.0, 2.0, (B, 12)) * s    # joint velocities
+    if push:
+        dv = rng.uniform(50.0, 70.0, B) * rng.uniform(0.2, 0.4, B) / MASS
+        ang = rng.uniform(-np.pi, np.pi, B)
+        qv[:, 18] += dv * np.cos(ang)
+        qv[:, 19] += dv * np.sin(ang)
     v_des = np.zeros((B, 3))
     v_des[:, 0] = rng.uniform(0.0, 0.3, B)
     v_des[:, 1] = rng.uniform(-0.1, 0.1, B)
@@ -50,22 +81,40 @@ def make_batch(B: int, seed: int = 0, gaits: Sequence[str] = ("trot",), n_nodes:
     p = np.zeros((B, N + 1, P.NP))
     yref = np.zeros((B, N, P.NY)); yref_e = np.zeros((B, P.NYE))
     u_guess = np.zeros((B, N, P.NU))
+    if restrict_cnt:
+        if kin is None:
+            raise ValueError("restrict_cnt needs the solver's kinematics (kin=solver.kinematics)")
+        feet0, _, _ = kin(P.nominal_state(0.0)[None])
+        hip = np.array(feet0[0], dtype=float)
+        hip[:, 2] = 0.0
+        _, com, _ = kin(qv)
     for g, name in enumerate(gaits):
         idx = np.nonzero(gait_id == g)[0]
         if idx.size == 0:
             continue
         gait, opt, cost = get_quadruped_config(name, robot, fallback_to_trot_cost=True, fix_swapped_heights=True)
         planner = ContactPlanner(FEET, dt_nodes, gait)
-        Wg, Weg = P.pack_weights(cost)
+        Wg, Weg = P.pack_weights(cost, restrict_cnt)
         W[idx], We[idx] = Wg, Weg
         cnt = np.stack([planner.get_contacts(int(i), N + 1) for i in i_node[idx]])
         peak = np.stack([planner.get_peaks(int(i), N + 1) for i in i_node[idx]])
-        p[idx] = P.pack_params(cnt, cost, 0.0, peak)
-        tracking = np.zeros((idx.size, 12))
-        tracking[:, :2] = qv[idx, :2]
-        tracking[:, 3] = qv[idx, 3]
-        ref, ref_e = P.base_ref_vel_tracking(qv[idx, :18], v_des[idx], 0.0, tracking, gait.nom_height)
-        yr, yre = P.pack_reference(ref, ref_e, P.GO2_JOINT_HOME, gait.step_height, N)
+        loc = None
+        if restrict_cnt:       # LocomotionMPC.__init__ / optimize with contact_planner="raibert" (mpc.py:76-84, 332-341)
+            rp = RaiberContactPlanner(FEET, dt_nodes, gait, hip.copy(), y_offset=0.02, x_offset=0.04,
+                                      foot_size=0.0085, cache_cnt=False)
+            loc = np.zeros((idx.size, 4, N + 1, 3))
+            ref, ref_e = np.zeros((idx.size, 12)), np.zeros((idx.size, 12))
+            for n, b in enumerate(idx):
+                rp.set_state(qv[b, :3], qv[b, 18:21], qv[b, 3:6][::-1], com[b], v_des[b], 0.0)
+                loc[n] = rp.get_locations(int(i_node[b]), N + 1)
+                ref[n], ref_e[n] = _restricted_base_ref(loc[n], gait.nom_height)
+        else:
+            tracking = np.zeros((idx.size, 12))
+            tracking[:, :2] = qv[idx, :2]
+            tracking[:, 3] = qv[idx, 3]
+            ref, ref_e = P.base_ref_vel_tracking(qv[idx, :18], v_des[idx], 0.0, tracking, gait.nom_height)
+        p[idx] = P.pack_params(cnt, cost, 0.0, peak, restrict_cnt, loc)
+        yr, yre = P.pack_reference(ref, ref_e, P.GO2_JOINT_HOME, gait.step_height, N, loc)
         yref[idx], yref_e[idx] = yr, yre
         act = cnt[:, :, :N].transpose(0, 2, 1).astype(float)          # [b, k, foot]
         n_act = np.maximum(act.sum(-1, keepdims=True), 1.0)

@@ -23,9 +23,9 @@ def rel_err(a, b):
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1.0))
 
 
-def _pair(O, B, seed, gaits=("trot",), perturb=1.0, **opts):
+def _pair(O, B, seed, gaits=("trot",), perturb=1.0, workload=None, **opts):
     NmpcSolver, default_opts = _gpu()
-    batch = WL.make_batch(B, seed=seed, gaits=gaits, perturb=perturb)
+    batch = WL.make_batch(B, seed=seed, gaits=gaits, perturb=perturb, **(workload or {}))
     _, _, hg = O.kinematics(batch["qv"])
     so = O.OracleSolver(B, O.default_opts(**opts))
     sg = NmpcSolver(B, default_opts(**opts))
@@ -269,3 +269,28 @@ def test_device_pointers_are_accepted(oracle_mod):
     xh, uh, _, _ = s_h.get_solution()
     np.testing.assert_array_equal(xd.cpu().numpy(), xh)
     np.testing.assert_array_equal(ud.cpu().numpy(), uh)
+
+
+@pytest.mark.parametrize("cfg", ["config4_restricted_contacts", "config5_push"])
+def test_config4_and_5_workloads_parity(oracle_mod, cfg):
+    """BASELINE configs 4 (contact-patch restriction with Raibert footholds + opt_peak; without time
+    optimisation) and 5 (push-perturbed DAgger tick): default mpc_opt.py options, SQP with max_iter = 1."""
+    O = oracle_mod
+    wl = dict(restrict_cnt=True, kin=O.kinematics) if cfg.startswith("config4") else dict(push=True)
+    so, sg, batch = _pair(O, 48, seed=11, workload=wl, real_time_it=0, max_iter=1, warm_start_qp=0)
+    if cfg.startswith("config4"):
+        assert (batch["p"].reshape(48, N + 1, 4, 11)[..., 8] > 0.5).any()        # some touch-downs are restricted
+        qo, qg = so.export_qp(), sg.export_qp()
+        np.testing.assert_array_equal(qg["mask"], qo["mask"])
+        assert (qo["mask"].reshape(48, N + 1, 2, 42)[:, :, 1, 32:36] > 0.5).any()  # patch rows are in the QP
+        for k in ("BAbt", "RSQrq", "DCt", "lg", "ug"):
+            assert rel_err(qg[k], qo[k]) < 1e-11, k
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    xo, uo, pio, lamo = so.get_solution()
+    xg, ug, pig, lamg = sg.get_solution()
+    assert rel_err(xg, xo) < REL and rel_err(ug, uo) < REL
+    assert rel_err(pig, pio) < REL and rel_err(lamg, lamo) < REL
+    so_s, sg_s = so.get_stats(), sg.get_stats()
+    for k in ("sqp_iter", "qp_iter", "qp_status"):
+        np.testing.assert_array_equal(sg_s[k], so_s[k])
