@@ -153,6 +153,19 @@ int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, double* feet, d
  * sum_feet J_foot(q)^T f.  qva [n,54] = (q_euler | v | a), f [n,12] world-frame contact forces. */
 int nmpc_inverse_dynamics(nmpc_handle* h, const double* qva, const double* f, int32_t n, double* tau);
 
+/* ---- plan -> torque, batched.  Replaces, for every problem of the batch at once:
+ * LocomotionMPC.interpolate_state_trajectory (mpc.py:371-414: cubic Hermite of (q,v) and (v,a) on the node
+ * grid, sampled at linspace(0, T, n_interp+1)[1:]), the zero-order hold a_plan/f_plan = sol[id_repeat]
+ * (mpc.py:110,544-545), QuadrupedDynamics.id_torques (dynamics.py:136-163), _compute_pd_torques
+ * (mpc.py:592-599) and the DAgger label action = (tau + kd v)/kp + q (Behavior_Cloning/utils/Rollout_MPC.py:298).
+ * Works on the solution resident in the handle (after nmpc_solve).  Plan steps step0 .. step0+n_steps-1 of the
+ * n_interp-sample plan.  qv_meas [B,n_steps,36] = measured (q_euler | v) at each step, or NULL to evaluate on
+ * the plan itself (open-loop labels).  Outputs (host or device, any may be NULL): q_plan, v_plan
+ * [B,n_steps,18]; tau_ff, tau, action [B,n_steps,12]. */
+int nmpc_plan_torques(nmpc_handle* h, const double* qv_meas, int32_t n_interp, int32_t step0, int32_t n_steps,
+                      double kp, double kd, double* q_plan, double* v_plan, double* tau_ff, double* tau,
+                      double* action);
+
 /* ---- test / diagnostics hooks (parity tests compare these with the oracle) ------------ */
 /* Linearise at the current iterate without solving and export the dense OCP-QP:
  * BAbt [B,N,73,42] (rows: B^T(30) | A^T(42) | b^T), RSQrq [B,N+1,73,72] (lower part valid; last

@@ -169,6 +169,21 @@ class NmpcSolver:
         check(self.lib.nmpc_inverse_dynamics(self._h, ptr(a), ptr(b), n, ptr(tau)), "nmpc_inverse_dynamics")
         return tau
 
+    def plan_torques(self, n_interp: int, step0: int = 0, n_steps: Optional[int] = None, kp: float = 20.0,
+                     kd: float = 1.75, qv_meas=None) -> dict:
+        """Batched plan -> torque from the resident solution (include/nmpc_b200.h::nmpc_plan_torques;
+        reference mpc.py:371-414, 544-545, 592-599, dynamics.py:136-163, Rollout_MPC.py:298).
+        Returns q_plan, v_plan [B,n_steps,18] and tau_ff, tau, action [B,n_steps,12]."""
+        n_steps = n_interp - step0 if n_steps is None else int(n_steps)
+        B = self.B
+        out = {k: np.zeros((B, n_steps, w)) for k, w in
+               (("q_plan", 18), ("v_plan", 18), ("tau_ff", 12), ("tau", 12), ("action", 12))}
+        m = None if qv_meas is None else _f64(qv_meas, (B, n_steps, 36))
+        check(self.lib.nmpc_plan_torques(self._h, None if m is None else ptr(m), int(n_interp), int(step0), n_steps,
+                                         float(kp), float(kd), ptr(out["q_plan"]), ptr(out["v_plan"]),
+                                         ptr(out["tau_ff"]), ptr(out["tau"]), ptr(out["action"])), "nmpc_plan_torques")
+        return out
+
     # -- diagnostics --------------------------------------------------------------------
     def export_qp(self) -> dict:
         B, N = self.B, self.N

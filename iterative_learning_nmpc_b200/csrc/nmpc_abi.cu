@@ -14,6 +14,7 @@
 #include "nmpc_qp_fused.cuh"
 #include "nmpc_sqp.cuh"
 #include "nmpc_linearize_sr.cuh"
+#include "nmpc_plan.cuh"
 
 #define CK(call)                                                     \
     do {                                                             \
@@ -598,6 +599,40 @@ extern "C" int nmpc_inverse_dynamics(nmpc_handle* h, const double* qva, const do
     nmpc_rnea_kernel<<<(n + 63) / 64, 64, 0, h->stream>>>(d_qva, d_f, n, d_tau);
     h->launches++;
     CK(cudaMemcpyAsync(tau, d_tau, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return (int)cudaGetLastError();
+}
+
+// plan -> torque for every problem of the batch, from the solution resident on the device (nmpc_plan.cuh)
+extern "C" int nmpc_plan_torques(nmpc_handle* h, const double* qv_meas, int32_t n_interp, int32_t step0, int32_t n_steps,
+                                 double kp, double kd, double* q_plan, double* v_plan, double* tau_ff, double* tau,
+                                 double* action)
+{
+    if (!h || n_interp < 2 || n_steps <= 0 || step0 < 0 || step0 + n_steps > n_interp || !(kp != 0.0)) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t n = (size_t)h->B * n_steps;
+    // scratch: [meas 36 | q 18 | v 18 | tau_ff 12 | tau 12 | action 12] per (problem, step)
+    if (int r = ensure_scratch(h, n * 108 * 8)) return r;
+    double* d_meas = h->scratch;
+    double* d_q = d_meas + n * 36;
+    double* d_v = d_q + n * 18;
+    double* d_tff = d_v + n * 18;
+    double* d_tau = d_tff + n * 12;
+    double* d_act = d_tau + n * 12;
+    if (qv_meas) CK(cudaMemcpyAsync(d_meas, qv_meas, n * 36 * 8, cudaMemcpyDefault, h->stream));
+    PlanArgs a;
+    a.x = h->x; a.u = h->u; a.qv_meas = qv_meas ? d_meas : nullptr;
+    a.q_plan = q_plan ? d_q : nullptr; a.v_plan = v_plan ? d_v : nullptr; a.tau_ff = tau_ff ? d_tff : nullptr;
+    a.tau = tau ? d_tau : nullptr; a.action = action ? d_act : nullptr;
+    a.B = h->B; a.N = h->N; a.n_interp = n_interp; a.step0 = step0; a.n_steps = n_steps;
+    a.dt = h->o.dt_nodes; a.kp = kp; a.kd = kd;
+    nmpc_plan_torque_kernel<<<(unsigned)((n + 63) / 64), 64, 0, h->stream>>>(a);
+    h->launches++;
+    if (q_plan) CK(cudaMemcpyAsync(q_plan, d_q, n * 18 * 8, cudaMemcpyDefault, h->stream));
+    if (v_plan) CK(cudaMemcpyAsync(v_plan, d_v, n * 18 * 8, cudaMemcpyDefault, h->stream));
+    if (tau_ff) CK(cudaMemcpyAsync(tau_ff, d_tff, n * 12 * 8, cudaMemcpyDefault, h->stream));
+    if (tau) CK(cudaMemcpyAsync(tau, d_tau, n * 12 * 8, cudaMemcpyDefault, h->stream));
+    if (action) CK(cudaMemcpyAsync(action, d_act, n * 12 * 8, cudaMemcpyDefault, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return (int)cudaGetLastError();
 }

@@ -349,3 +349,15 @@ class BatchedQuadrupedSolver(QuadrupedAcadosSolver):
                  compute_timings: bool = True, device: int = 0):
         super().__init__(path_urdf, feet_frame_names, config_opt, config_cost, height_offset, print_info,
                          compute_timings, batch=int(batch), device=device)
+
+    def plan_torques(self, sim_dt: float = 1.0e-3, step0: int = 0, n_steps: Optional[int] = None, Kp: float = 20.,
+                     Kd: float = 1.75, qv_meas: Optional[np.ndarray] = None) -> dict:
+        """"Get torques" for the whole batch, on the device, from the solution of the last `solve`:
+        what `LocomotionMPC._adopt_plan` + `_compute_torques_ff` + `_compute_pd_torques` do per sim step on
+        the host (mpc.py:371-414, 535-599) and the DAgger label `action = (tau + Kd v)/Kp + q`
+        (Behavior_Cloning/utils/Rollout_MPC.py:298).  Plan steps `step0 .. step0+n_steps-1` of the
+        `round(time_horizon / sim_dt)`-sample plan; `qv_meas [B,n_steps,36]` are measured Euler states
+        (None: evaluate on the plan itself).  Returns q_plan, v_plan [B,n,18], tau_ff, tau, action [B,n,12]."""
+        n_interp = round(self.config_opt.time_horizon / sim_dt)
+        return self.handle.plan_torques(n_interp, step0, n_steps, Kp, Kd, qv_meas)
+

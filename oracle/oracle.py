@@ -103,6 +103,38 @@ def inverse_dynamics(qva: np.ndarray, f: np.ndarray) -> np.ndarray:
     return tau
 
 
+def plan_torques(x: np.ndarray, u: np.ndarray, dt_nodes: float, n_interp: int, step0: int = 0,
+                 n_steps: Optional[int] = None, kp: float = 20.0, kd: float = 1.75, qv_meas=None) -> dict:
+    """Checker for nmpc_plan_torques: the reference's own host pipeline, one problem at a time --
+    scipy CubicHermiteSpline exactly as `LocomotionMPC.interpolate_trajectory_with_derivatives`
+    (/root/reference/mpc_controller/mpc.py:388-414) calls it, `id_repeat` hold (mpc.py:110,544-545),
+    id_torques (dynamics.py:136-163, through the C oracle), PD (mpc.py:592-599) and the DAgger label
+    (Behavior_Cloning/utils/Rollout_MPC.py:298).  x [B,N+1,42], u [B,N,30]."""
+    from scipy.interpolate import CubicHermiteSpline
+    x, u = np.asarray(x, float), np.asarray(u, float)
+    B, N = u.shape[0], u.shape[1]
+    n_steps = n_interp - step0 if n_steps is None else int(n_steps)
+    sl = slice(step0, step0 + n_steps)
+    id_repeat = np.int32(np.linspace(0, 1, n_interp) * (N - 1))
+    out = {k: np.zeros((B, n_steps, w)) for k, w in
+           (("q_plan", 18), ("v_plan", 18), ("tau_ff", 12), ("tau", 12), ("action", 12))}
+    for b in range(B):
+        q_sol, v_sol, a_sol, f_sol = x[b, :, :18], x[b, :, 18:36], u[b, :, :18], u[b, :, 18:30]
+        time_traj = np.concatenate(([0.], np.cumsum(np.full(N, dt_nodes))))
+        t = np.linspace(time_traj[0], time_traj[-1], n_interp + 1)
+        pos = CubicHermiteSpline(time_traj, q_sol, v_sol)(t)[1:]
+        acc = np.concatenate((a_sol[:1], a_sol))
+        vel = CubicHermiteSpline(time_traj, v_sol, acc)(t)[1:]
+        qp, vp = pos[sl], vel[sl]
+        qm, vm = (qp, vp) if qv_meas is None else (np.asarray(qv_meas)[b, :, :18], np.asarray(qv_meas)[b, :, 18:])
+        ap, fp = a_sol[id_repeat][sl], f_sol[id_repeat][sl]
+        tff = inverse_dynamics(np.concatenate([qm, vm, ap], axis=1), fp)
+        tau = tff + kp * (qp[:, 6:] - qm[:, 6:]) + kd * (vp[:, 6:] - vm[:, 6:])
+        out["q_plan"][b], out["v_plan"][b], out["tau_ff"][b], out["tau"][b] = qp, vp, tff, tau
+        out["action"][b] = (tau + kd * vm[:, 6:]) / kp + qm[:, 6:]
+    return out
+
+
 def model_record(qv: np.ndarray) -> np.ndarray:
     qv = _f64(qv).reshape(36)
     dims = np.zeros(8, dtype=np.int32)

@@ -294,3 +294,28 @@ def test_config4_and_5_workloads_parity(oracle_mod, cfg):
     so_s, sg_s = so.get_stats(), sg.get_stats()
     for k in ("sqp_iter", "qp_iter", "qp_status"):
         np.testing.assert_array_equal(sg_s[k], so_s[k])
+
+
+@pytest.mark.parametrize("measured", [False, True])
+def test_plan_torques_parity(oracle_mod, measured):
+    """Batched plan -> torque on the device against the reference's host pipeline (scipy Hermite splines,
+    id_repeat hold, inverse dynamics, PD, DAgger action).  Floating point: 1e-10 relative."""
+    O = oracle_mod
+    so, sg, batch = _pair(O, 9, seed=13, real_time_it=1, warm_start_qp=0)
+    sg.solve()
+    xg, ug, _, _ = sg.get_solution()
+    n_interp, step0, n_steps = 1000, 17, 60
+    meas = None
+    if measured:
+        rng = np.random.default_rng(3)
+        ref = O.plan_torques(xg, ug, 0.04, n_interp, step0, n_steps)
+        meas = np.concatenate([ref["q_plan"], ref["v_plan"]], axis=2) + rng.normal(0, 1e-2, (9, n_steps, 36))
+    want = O.plan_torques(xg, ug, 0.04, n_interp, step0, n_steps, kp=20.0, kd=1.75, qv_meas=meas)
+    got = sg.plan_torques(n_interp, step0, n_steps, kp=20.0, kd=1.75, qv_meas=meas)
+    for k in ("q_plan", "v_plan", "tau_ff", "tau", "action"):
+        assert rel_err(got[k], want[k]) < 1e-10, (k, rel_err(got[k], want[k]))
+    # whole plan, including the last sample (t = T) and the first one
+    want = O.plan_torques(xg[:2], ug[:2], 0.04, 250)
+    got = sg.plan_torques(250)
+    for k in ("q_plan", "v_plan", "tau"):
+        assert rel_err(got[k][:2], want[k]) < 1e-10, k

@@ -120,3 +120,26 @@ def test_inverse_dynamics_static_is_gravity_minus_contacts(oracle_mod, num):
     t1 = oracle_mod.inverse_dynamics(np.concatenate([q, z, z]), f.reshape(-1))[0]
     expect = -np.einsum("fij,fi->j", J, f)[6:]
     assert np.allclose(t1 - t0, expect, atol=1e-12)
+
+
+def test_plan_torques_restatement_properties(oracle_mod):
+    """oracle.plan_torques (checker of nmpc_plan_torques): Hermite interpolation reproduces the node values
+    at the node times, the inputs are held per `id_repeat`, and on the plan itself the PD term vanishes."""
+    O = oracle_mod
+    rng = np.random.default_rng(0)
+    B, N = 3, 25
+    x = rng.normal(0, 0.3, (B, N + 1, 42))
+    u = rng.normal(0, 1.0, (B, N, 30))
+    n_interp = 10 * N
+    r = O.plan_torques(x, u, 0.04, n_interp, kp=20.0, kd=1.75)
+    for k in range(1, N + 1):                     # sample 10k-1 of the plan is t = t_k
+        np.testing.assert_allclose(r["q_plan"][:, 10 * k - 1], x[:, k, :18], atol=1e-12)
+        np.testing.assert_allclose(r["v_plan"][:, 10 * k - 1], x[:, k, 18:36], atol=1e-12)
+    np.testing.assert_allclose(r["tau"], r["tau_ff"], atol=1e-12)
+    np.testing.assert_allclose(r["action"], (r["tau_ff"] + 1.75 * r["v_plan"][:, :, 6:]) / 20.0 + r["q_plan"][:, :, 6:],
+                               atol=1e-12)
+    idr = np.int32(np.linspace(0, 1, n_interp) * (N - 1))
+    qva = np.concatenate([r["q_plan"][0], r["v_plan"][0], u[0, idr, :18]], axis=1)
+    np.testing.assert_allclose(r["tau_ff"][0], O.inverse_dynamics(qva, u[0, idr, 18:]), atol=1e-12)
+    sub = O.plan_torques(x, u, 0.04, n_interp, step0=40, n_steps=7)
+    np.testing.assert_array_equal(sub["q_plan"], r["q_plan"][:, 40:47])
