@@ -11,8 +11,9 @@ owns its own 1024 problems; problems are independent, there is no collective on 
 
   value    whole-job solves/s with the batch resident in HBM (device copies of the guess + solve),
            CUDA events on the solver's stream, max over ranks.
-  e2e      the same through the C ABI with HOST (pinned) buffers: H2D of every input, solve, D2H
-           of the solution and status inside the timed region.
+  e2e      the same through the C ABI with HOST (pinned) buffers: H2D of every input of
+           `QuadrupedAcadosSolver.init` (weights, base references, contact masks / peaks / locations, x0,
+           node index), solve, D2H of the solution and status inside the timed region.
   roofline dominant kernel (by summed device time): algorithmic bytes per launch / mean launch time
            (CUDA events around each launch, nmpc_set_profiling) over the measured HBM peak.
   cpu_baseline  the CPU oracle (a port of the algorithm, NOT acados) on the host cores, bounded sample.
@@ -241,25 +242,33 @@ def main() -> None:
     solver = NmpcSolver(B, default_opts(**opts), device=local)
     batch = WL.make_batch(B, seed=1000 * rank + args.config - 1, gaits=gaits, **workload_kwargs(args.config, solver.kinematics))
     stream = torch.cuda.ExternalStream(solver.stream_ptr, device=local)
-    _, _, hg = solver.kinematics(batch["qv"])
-    xg = batch["x_guess"].copy()
-    xg[:, :, 36:] = hg[:, None, :]
-    keys = ("W", "W_e", "yref", "yref_e", "p", "u_guess", "qv", "i_node")
-    host = {k: torch.from_numpy(np.ascontiguousarray(batch[k])).pin_memory() for k in keys}
-    host["x_guess"] = torch.from_numpy(xg).pin_memory()
+    # compact planner outputs, as `QuadrupedAcadosSolver.init` receives them (the expansion into per-node
+    # parameters / references, h0, stance-foot pinning and the first guess are device kernels)
+    cp = batch["compact"]
+    tensors = {"W": batch["W"], "W_e": batch["W_e"], "qv": batch["qv"], "i_node": batch["i_node"],
+               "base_ref": cp["base_ref"], "base_ref_e": cp["base_ref_e"], "step_height": cp["step_height"],
+               "cnt_sequence": cp["cnt_sequence"], "swing_peak": cp["swing_peak"]}
+    if cp["cnt_locations"] is not None:
+        tensors["cnt_locations"] = cp["cnt_locations"]
+    host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in tensors.items()}
     dev = {k: v.cuda(non_blocking=False) for k, v in host.items()}
     out_x = torch.empty(B, N_NODES + 1, 42, dtype=torch.float64).pin_memory()
     out_u = torch.empty(B, N_NODES, 30, dtype=torch.float64).pin_memory()
     out_st = torch.empty(B, dtype=torch.int32).pin_memory()
-    st_dev = torch.empty(B, dtype=torch.int32, device="cuda")
+    lib, hnd = solver.lib, solver._h
+    from iterative_learning_nmpc_b200._lib import check, ptr
+    joint_ref = np.ascontiguousarray(cp["joint_ref"], dtype=np.float64)
+    p_gain = np.ascontiguousarray(cp["p_gain"], dtype=np.float64)
 
     def step(src, sync_out: bool):
-        # QuadrupedAcadosSolver.init: weights, references, parameters, guess, x0, stance feet
+        # QuadrupedAcadosSolver.init: weights, references + contact plan (expanded on the device), x0, stance feet, guess
         solver.set_weights(src["W"], src["W_e"])
-        solver.set_yref(src["yref"], src["yref_e"])
-        solver.set_params(src["p"])
-        solver.set_guess(src["x_guess"], src["u_guess"])
+        check(lib.nmpc_init_tick(hnd, ptr(src["base_ref"]), ptr(src["base_ref_e"]), ptr(joint_ref), 0,
+                                 ptr(src["step_height"]), 1, ptr(src["cnt_sequence"]), ptr(src["swing_peak"]),
+                                 ptr(src.get("cnt_locations")), ptr(p_gain), float(cp["cnt_radius"]),
+                                 float(cp["height_offset"]), int(cp["restrict_cnt"])), "nmpc_init_tick")
         solver.set_x0(src["qv"])
+        solver.cold_guess()
         solver.pin_stance_feet(src["i_node"])
         solver.reset_duals()
         if sync_out:     # QuadrupedAcadosSolver.solve + parse_sol: status and solution back on the host

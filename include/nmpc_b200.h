@@ -116,6 +116,22 @@ int nmpc_set_yref(nmpc_handle* h, const double* yref, const double* yref_e);
 int nmpc_set_weights(nmpc_handle* h, const double* W, const double* W_e, int32_t per_problem);
 /* update_parameters (solver.py:351): p [B,N+1,44] */
 int nmpc_set_params(nmpc_handle* h, const double* p);
+/* QuadrupedAcadosSolver.init with the expansion done on the device (replaces the host loops of
+ * setup_reference solver.py:153-177, init_contacts_parameters :212-225, setup_cnt_status :227-252,
+ * setup_contact_loc :254-275 and the node-by-node update_solver :344-353).  Compact planner outputs:
+ * base_ref, base_ref_e [B,12] (base_ref_e NULL = base_ref); joint_ref [B,12] or [12]; step_height [B] or
+ * [1]; cnt_sequence int8 [B,4,N+1]; swing_peak int8 [B,4,N+1] or NULL (opt_peak off); cnt_locations
+ * [B,4,N+1,3] or NULL; p_gain [4] = W_foot_pos_constr_stab; cnt_radius, height_offset; restrict_cnt as
+ * set_contact_restriction (NMPC_EINVAL if set without locations).  Writes p, yref, yref_e of the handle. */
+int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const double* base_ref_e, const double* joint_ref,
+                   int32_t joint_per_problem, const double* step_height, int32_t height_per_problem,
+                   const int8_t* cnt_sequence, const int8_t* swing_peak, const double* cnt_locations,
+                   const double* p_gain, double cnt_radius, double height_offset, int32_t restrict_cnt);
+/* cold first guess of the batched front-end: x0 held over the horizon, zero accelerations, the robot's
+ * weight shared by the stance feet of every node (from x0 and p on the device) */
+int nmpc_cold_guess(nmpc_handle* h);
+/* problem data as held on the device: p [B,N+1,44], yref [B,N,76], yref_e [B,52], x0 [B,42]; NULLs skipped */
+int nmpc_get_problem_data(nmpc_handle* h, double* p, double* yref, double* yref_e, double* x0);
 /* setup_initial_feet_pos (solver.py:194-210) done on the device: for every foot whose node-0
  * `active` is 1 (forced to 1 where i_node[b]==0), plane_point[:, :next_swing] = FK foot position
  * of the current x0.  i_node [B] int32 (host or device). Call after set_params and set_x0. */

@@ -86,6 +86,41 @@ class NmpcSolver:
         check(self.lib.nmpc_set_params(self._h, ptr(a)), "nmpc_set_params")
         self.synchronize_if_host(a)
 
+    def init_tick(self, base_ref, base_ref_e=None, joint_ref=None, step_height=0.0, cnt_sequence=None,
+                  swing_peak=None, cnt_locations=None, p_gain=None, cnt_radius: float = 0.0,
+                  height_offset: float = 0.0, restrict_cnt: bool = False):
+        """`QuadrupedAcadosSolver.init` with the expansion on the device (nmpc_init_tick): base_ref(_e) [B,12],
+        joint_ref [B,12] or [12], step_height [B] or scalar, cnt_sequence / swing_peak int8 [B,4,N+1],
+        cnt_locations [B,4,N+1,3] or None, p_gain [4]."""
+        B, N1 = self.B, self.N + 1
+        ref = _f64(base_ref, (B, 12))
+        ref_e = None if base_ref_e is None else _f64(base_ref_e, (B, 12))
+        jr = np.ascontiguousarray(joint_ref, dtype=np.float64)
+        jpp = int(jr.size == B * 12 and B > 1 or jr.ndim == 2)
+        jr = jr.reshape((B, 12) if jpp else (12,))
+        sh = np.ascontiguousarray(np.atleast_1d(step_height), dtype=np.float64)
+        hpp = int(sh.size == B and (B > 1 or np.ndim(step_height) > 0))
+        sh = sh.reshape((B,) if hpp else (1,))
+        if restrict_cnt and cnt_locations is None:
+            raise ValueError("Contact plan not provided")
+        cnt = np.ascontiguousarray(cnt_sequence, dtype=np.int8).reshape(B, 4, N1)
+        peak = None if swing_peak is None else np.ascontiguousarray(swing_peak, dtype=np.int8).reshape(B, 4, N1)
+        loc = None if cnt_locations is None else _f64(cnt_locations, (B, 4, N1, 3))
+        gain = np.ascontiguousarray(p_gain, dtype=np.float64).reshape(4)
+        check(self.lib.nmpc_init_tick(self._h, ptr(ref), ptr(ref_e), ptr(jr), jpp, ptr(sh), hpp, ptr(cnt), ptr(peak),
+                                      ptr(loc), ptr(gain), float(cnt_radius), float(height_offset), int(bool(restrict_cnt))),
+              "nmpc_init_tick")
+
+    def cold_guess(self):
+        check(self.lib.nmpc_cold_guess(self._h), "nmpc_cold_guess")
+
+    def get_problem_data(self) -> dict:
+        B, N = self.B, self.N
+        out = dict(p=np.zeros((B, N + 1, NP)), yref=np.zeros((B, N, NY)), yref_e=np.zeros((B, NYE)), x0=np.zeros((B, NX)))
+        check(self.lib.nmpc_get_problem_data(self._h, ptr(out["p"]), ptr(out["yref"]), ptr(out["yref_e"]), ptr(out["x0"])),
+              "nmpc_get_problem_data")
+        return out
+
     def pin_stance_feet(self, i_node):
         a = _i32(i_node, (self.B,))
         check(self.lib.nmpc_pin_stance_feet(self._h, ptr(a)), "nmpc_pin_stance_feet")

@@ -15,6 +15,7 @@
 #include "nmpc_sqp.cuh"
 #include "nmpc_linearize_sr.cuh"
 #include "nmpc_plan.cuh"
+#include "nmpc_init.cuh"
 
 #define CK(call)                                                     \
     do {                                                             \
@@ -185,6 +186,7 @@ extern "C" int nmpc_stream(const nmpc_handle* h, void** s)
 
 extern "C" int64_t nmpc_launch_count(const nmpc_handle* h) { return h ? h->launches : 0; }
 
+static int d2h(nmpc_handle* h, void* dst, const void* src, size_t bytes);
 static int h2d(nmpc_handle* h, void* dst, const void* src, size_t bytes)
 {
     CK(cudaSetDevice(h->device));
@@ -251,6 +253,71 @@ extern "C" int nmpc_set_params(nmpc_handle* h, const double* p)
 {
     if (!h || !p) return NMPC_EINVAL;
     return h2d(h, h->p, p, (size_t)h->B * (h->N + 1) * NPAR * 8);
+}
+
+// QuadrupedAcadosSolver.init on the device: compact planner outputs in, node-major records out (nmpc_init.cuh)
+extern "C" int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const double* base_ref_e, const double* joint_ref,
+                              int32_t joint_per_problem, const double* step_height, int32_t height_per_problem,
+                              const int8_t* cnt_sequence, const int8_t* swing_peak, const double* cnt_locations,
+                              const double* p_gain, double cnt_radius, double height_offset, int32_t restrict_cnt)
+{
+    if (!h || !base_ref || !joint_ref || !step_height || !cnt_sequence || !p_gain) return NMPC_EINVAL;
+    if (restrict_cnt && !cnt_locations) return NMPC_EINVAL;           // "Contact plan not provided" (solver.py:377)
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B, N1 = h->N + 1;
+    const size_t n_ref = B * 12, n_jr = joint_per_problem ? B * 12 : 12, n_sh = height_per_problem ? B : 1;
+    const size_t n_cnt = B * NF * N1, n_loc = cnt_locations ? B * NF * N1 * 3 : 0;
+    const size_t cnt_pad = (n_cnt + 7) & ~(size_t)7;
+    const size_t bytes = (2 * n_ref + n_jr + n_sh + n_loc) * 8 + 2 * cnt_pad;
+    if (int r = ensure_scratch(h, bytes)) return r;
+    double* d_ref = h->scratch;
+    double* d_ref_e = d_ref + n_ref;
+    double* d_jr = d_ref_e + n_ref;
+    double* d_sh = d_jr + n_jr;
+    double* d_loc = d_sh + n_sh;
+    signed char* d_cnt = reinterpret_cast<signed char*>(d_loc + n_loc);
+    signed char* d_peak = d_cnt + cnt_pad;
+    CK(cudaMemcpyAsync(d_ref, base_ref, n_ref * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_ref_e, base_ref_e ? base_ref_e : base_ref, n_ref * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_jr, joint_ref, n_jr * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_sh, step_height, n_sh * 8, cudaMemcpyDefault, h->stream));
+    if (n_loc) CK(cudaMemcpyAsync(d_loc, cnt_locations, n_loc * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_cnt, cnt_sequence, n_cnt, cudaMemcpyDefault, h->stream));
+    if (swing_peak) CK(cudaMemcpyAsync(d_peak, swing_peak, n_cnt, cudaMemcpyDefault, h->stream));
+    TickArgs a;
+    a.base_ref = d_ref; a.base_ref_e = d_ref_e; a.joint_ref = d_jr; a.step_height = d_sh;
+    a.cnt = d_cnt; a.peak = swing_peak ? d_peak : nullptr; a.loc = n_loc ? d_loc : nullptr;
+    for (int f = 0; f < NF; f++) a.p_gain[f] = p_gain[f];
+    a.radius = cnt_radius; a.height_offset = height_offset; a.restrict_cnt = restrict_cnt;
+    a.joint_per_problem = joint_per_problem; a.height_per_problem = height_per_problem;
+    a.p = h->p; a.yref = h->yref; a.yref_e = h->yref_e; a.B = h->B; a.N = h->N;
+    nmpc_init_tick_kernel<<<h->B, 128, 0, h->stream>>>(a);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+// cold first guess from x0 and the contact mask already on the device (call after nmpc_set_x0 and nmpc_init_tick / nmpc_set_params)
+extern "C" int nmpc_cold_guess(nmpc_handle* h)
+{
+    if (!h) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    nmpc_cold_guess_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->x0, h->p, h->x, h->u);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+// problem data as the solver holds it (tests: device-side expansion vs the host packing)
+extern "C" int nmpc_get_problem_data(nmpc_handle* h, double* p, double* yref, double* yref_e, double* x0)
+{
+    if (!h) return NMPC_EINVAL;
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B, N = h->N;
+    if (p) if (int r = d2h(h, p, h->p, B * (N + 1) * NPAR * 8)) return r;
+    if (yref) if (int r = d2h(h, yref, h->yref, B * N * NY * 8)) return r;
+    if (yref_e) if (int r = d2h(h, yref_e, h->yref_e, B * NYE * 8)) return r;
+    if (x0) if (int r = d2h(h, x0, h->x0, B * NX * 8)) return r;
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
 }
 
 extern "C" int nmpc_pin_stance_feet(nmpc_handle* h, const int32_t* i_node)

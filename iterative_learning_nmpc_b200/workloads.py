@@ -81,6 +81,12 @@ def make_batch(B: int, seed: int = 0, gaits: Sequence[str] = ("trot",), n_nodes:
     p = np.zeros((B, N + 1, P.NP))
     yref = np.zeros((B, N, P.NY)); yref_e = np.zeros((B, P.NYE))
     u_guess = np.zeros((B, N, P.NU))
+    # compact planner outputs (what QuadrupedAcadosSolver.init receives; nmpc_init_tick expands them on the device)
+    c_ref, c_ref_e = np.zeros((B, 12)), np.zeros((B, 12))
+    c_cnt, c_peak = np.zeros((B, 4, N + 1), dtype=np.int8), np.zeros((B, 4, N + 1), dtype=np.int8)
+    c_loc = np.zeros((B, 4, N + 1, 3)) if restrict_cnt else None
+    c_step = np.zeros(B)
+    p_gain, cnt_radius = None, 0.0
     if restrict_cnt:
         if kin is None:
             raise ValueError("restrict_cnt needs the solver's kinematics (kin=solver.kinematics)")
@@ -116,6 +122,12 @@ def make_batch(B: int, seed: int = 0, gaits: Sequence[str] = ("trot",), n_nodes:
         p[idx] = P.pack_params(cnt, cost, 0.0, peak, restrict_cnt, loc)
         yr, yre = P.pack_reference(ref, ref_e, P.GO2_JOINT_HOME, gait.step_height, N, loc)
         yref[idx], yref_e[idx] = yr, yre
+        c_ref[idx], c_ref_e[idx], c_cnt[idx], c_peak[idx], c_step[idx] = ref, ref_e, cnt, peak, gait.step_height
+        if restrict_cnt:
+            c_loc[idx] = loc
+        g_gain = np.asarray(cost.W_foot_pos_constr_stab, dtype=float)
+        assert p_gain is None or np.array_equal(p_gain, g_gain), "per-gait contact gains differ"
+        p_gain, cnt_radius = g_gain, float(cost.cnt_radius)
         act = cnt[:, :, :N].transpose(0, 2, 1).astype(float)          # [b, k, foot]
         n_act = np.maximum(act.sum(-1, keepdims=True), 1.0)
         fz = act * (MASS * 9.81) / n_act
@@ -123,7 +135,21 @@ def make_batch(B: int, seed: int = 0, gaits: Sequence[str] = ("trot",), n_nodes:
     x_guess = np.zeros((B, N + 1, P.NX))
     x_guess[:, :, :36] = qv[:, None, :]
     return dict(qv=qv, W=W, W_e=We, yref=yref, yref_e=yref_e, p=p, i_node=i_node, x_guess=x_guess,
-                u_guess=u_guess, gait_id=gait_id.astype(np.int32), v_des=v_des)
+                u_guess=u_guess, gait_id=gait_id.astype(np.int32), v_des=v_des,
+                compact=dict(base_ref=c_ref, base_ref_e=c_ref_e, joint_ref=np.array(P.GO2_JOINT_HOME, dtype=float),
+                             step_height=c_step, cnt_sequence=c_cnt, swing_peak=c_peak, cnt_locations=c_loc,
+                             p_gain=p_gain, cnt_radius=cnt_radius, height_offset=0.0, restrict_cnt=bool(restrict_cnt)))
+
+
+def load_compact(solver, batch: Dict[str, np.ndarray]) -> None:
+    """The same problem through the device-side `init` (product NmpcSolver only): compact planner outputs in,
+    expansion into p / yref, x0 with h0, stance-foot pinning and the cold first guess all on the GPU."""
+    solver.set_weights(batch["W"], batch["W_e"])
+    solver.init_tick(**batch["compact"])
+    solver.set_x0(batch["qv"])
+    solver.cold_guess()                      # from the planner's mask, before node 0 is forced to stance for i_node = 0
+    solver.pin_stance_feet(batch["i_node"])
+    solver.reset_duals()
 
 
 def load_into(solver, batch: Dict[str, np.ndarray], hg: Optional[np.ndarray] = None) -> None:

@@ -33,7 +33,8 @@ CASES = {
 def digest(batch) -> str:
     h = hashlib.sha256()
     for k in sorted(batch):
-        h.update(np.ascontiguousarray(batch[k]).tobytes())
+        if isinstance(batch[k], np.ndarray):     # the expanded problem data; `compact` restates the same inputs
+            h.update(np.ascontiguousarray(batch[k]).tobytes())
     return h.hexdigest()
 
 

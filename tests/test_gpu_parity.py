@@ -319,3 +319,38 @@ def test_plan_torques_parity(oracle_mod, measured):
     got = sg.plan_torques(250)
     for k in ("q_plan", "v_plan", "tau"):
         assert rel_err(got[k][:2], want[k]) < 1e-10, k
+
+
+@pytest.mark.parametrize("restrict", [False, True])
+def test_device_init_matches_host_packing(oracle_mod, restrict):
+    """nmpc_init_tick / nmpc_cold_guess (QuadrupedAcadosSolver.init expanded on the device from the compact
+    planner outputs) against the host packing of problem.py that the oracle consumes: p, yref, yref_e
+    bit-exact, and the RTI solve from the device-built problem equal to the oracle's."""
+    O = oracle_mod
+    wl = dict(restrict_cnt=True, kin=O.kinematics) if restrict else {}
+    so, sg, batch = _pair(O, 37, seed=21, gaits=("trot", "pace", "bound"), workload=wl, real_time_it=1, warm_start_qp=0)
+    host = sg.get_problem_data()                 # after load_into + pin_stance_feet
+    NmpcSolver, default_opts = _gpu()
+    sd = NmpcSolver(37, default_opts(real_time_it=1, warm_start_qp=0))
+    WL.load_compact(sd, batch)
+    dev = sd.get_problem_data()
+    for k in ("p", "yref", "yref_e", "x0"):
+        np.testing.assert_array_equal(dev[k], host[k], err_msg=k)
+    xd0, ud0, _, _ = sd.get_solution(duals=False)
+    xh0, uh0, _, _ = sg.get_solution(duals=False)
+    np.testing.assert_array_equal(xd0[:, :, :36], xh0[:, :, :36])
+    assert rel_err(xd0, xh0) < 1e-14             # h0: device kinematics vs the oracle's (the host path was fed the latter)
+    assert rel_err(ud0, uh0) < 1e-15             # weight / n_stance: same expression, host vs device rounding
+    st_o, st_d = so.solve(0), sd.solve()
+    np.testing.assert_array_equal(st_d, st_o)
+    xo, uo, _, _ = so.get_solution()
+    xd, ud, _, _ = sd.get_solution()
+    assert rel_err(xd, xo) < REL and rel_err(ud, uo) < REL
+
+
+def test_device_init_argument_errors():
+    NmpcSolver, default_opts = _gpu()
+    s = NmpcSolver(2, default_opts())
+    with pytest.raises(ValueError):              # restriction without a contact plan (solver.py:377)
+        s.init_tick(np.zeros((2, 12)), joint_ref=np.zeros(12), cnt_sequence=np.ones((2, 4, N + 1)),
+                    p_gain=np.zeros(4), restrict_cnt=True)
