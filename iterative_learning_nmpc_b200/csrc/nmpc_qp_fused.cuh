@@ -650,15 +650,22 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                     sv[FV_W + tid] = s0 + s1;
                 }
                 __syncthreads();                                     // also orders wait_read before the writes to sU
-                for (int e = tid; e < NX * NU; e += FQ_THREADS) {    // U = P+[:, h] [Hf | Hq]
-                    const int r = e / NU, j = e % NU;
-                    const double* ph = sP + r * P_LD + 2 * NQ;
+                if (tid < 4 * NU) {                                  // U = P+[:, h] [Hf | Hq]
+                    // thread = (column j, row group g): the column of [Hf | Hq] stays in registers, the six P entries
+                    // of a row are one broadcast per warp (12 loads per entry before, 6 per row now)
+                    const int j = tid % NU, g = tid / NU;
                     const double* hc = (j < 12) ? (S + SR_HF + j) : (S + SR_HQ + (j - 12));
                     const int ld = (j < 12) ? 12 : NQ;
-                    double s = 0.0;
+                    double hcv[6];
 #pragma unroll
-                    for (int h = 0; h < 6; h++) s += ph[h] * hc[ld * h];
-                    sU[e] = s;
+                    for (int h = 0; h < 6; h++) hcv[h] = hc[ld * h];
+                    for (int r = g; r < NX; r += 4) {
+                        const double* ph = sP + r * P_LD + 2 * NQ;
+                        double s = 0.0;
+#pragma unroll
+                        for (int h = 0; h < 6; h++) s += ph[h] * hcv[h];
+                        sU[r * NU + j] = s;
+                    }
                 }
                 if (tid < NZ) sv[FV_QT + tid] += fq_gt(S, sv + FV_W, tid, dt, c2);       // m = q tilde + G' w
                 __syncthreads();
