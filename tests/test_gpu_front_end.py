@@ -103,3 +103,26 @@ def test_locomotion_mpc_open_loop_matches_oracle(oracle_mod, guess, tol):
         trajs.append(mpc.open_loop(q_mj, np.zeros(18), 0.0855))
     assert trajs[0].shape == trajs[1].shape == (86, 19)
     assert rel_err(trajs[0], trajs[1]) < tol, rel_err(trajs[0], trajs[1])
+
+
+def test_batch_to_rollouts_writes_reference_npz(tmp_path):
+    """Solved batch -> device plan/torque -> per-rollout records in the reference's .npz layout."""
+    from iterative_learning_nmpc_b200 import dataset as DS
+    from iterative_learning_nmpc_b200 import workloads as WL
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+    B = 5
+    batch = WL.make_batch(B, seed=31)
+    s = NmpcSolver(B, default_opts(real_time_it=1, warm_start_qp=0))
+    WL.load_compact(s, batch)
+    s.solve()
+    recs = DS.batch_to_rollouts(s, batch, sim_dt=1e-3, n_steps=20, kp=20.0, kd=1.5)
+    assert len(recs) == B
+    out = s.plan_torques(1000, 0, 20, kp=20.0, kd=1.5)
+    for b, r in enumerate(recs):
+        assert r["state"].shape == (20, 44) and r["action"].shape == (20, 12)
+        np.testing.assert_allclose(r["q"][:, 7:], out["q_plan"][b][:, 6:], atol=0)          # joints pass through
+        np.testing.assert_allclose(r["action"], (out["tau"][b] + 1.5 * r["v"][:, 6:]) / 20.0 + r["q"][:, 7:], atol=1e-14)
+        np.testing.assert_array_equal(r["contact_vec"][0], batch["compact"]["cnt_sequence"][b][:, 0])
+        path = DS.save_rollout(r, str(tmp_path), nominal=False, replanning_point=b, nth_traj=0)
+        assert sorted(np.load(path).files) == sorted(DS.KEYS)
