@@ -332,3 +332,113 @@ class LocomotionMPC(PinController):
         ex = getattr(self, "executor", None)
         if ex is not None:
             ex.shutdown(wait=False, cancel_futures=True)
+
+
+class BatchedLocomotionMPC:
+    """B sim-free MPC rollouts in lockstep: `LocomotionMPC.open_loop` (mpc.py:416-462) with a leading batch
+    dimension, which is what the data-collection loops (`Behavior_Cloning/utils/Rollout_MPC.py`,
+    `DAgger/utils/data_collection_locosafedagger.py`) need from the controller when thousands of rollouts are
+    run at once.  Every rollout has its own start state, gait phase offset and velocity command; all share the
+    gait, the options and the sim clock.  Per replanning tick: one batched `init` + `solve`
+    (`BatchedQuadrupedSolver`), one batched plan -> torque call on the device (`nmpc_plan_torques`) for the
+    sim steps until the next tick; between ticks the state follows the plan, exactly as in `open_loop`.
+
+    Cyclic contact plans only (the default `ContactPlanner`); states are Euler vectors `[B,18]` (use
+    `dataset.euler_to_mujoco` / `QuadrupedDynamics.convert_from_mujoco` at the boundary).
+    """
+
+    def __init__(self, batch: int, path_urdf: Optional[str], feet_frame_names: List[str], robot_name: str,
+                 gait_name: str = "trot", joint_ref: Optional[np.ndarray] = None, sim_dt: float = 1.0e-3,
+                 height_offset: float = 0., print_info: bool = False, device: int = 0):
+        from .utils.solver import BatchedQuadrupedSolver
+        self.B = int(batch)
+        self.config_gait, self.config_opt, self.config_cost = get_quadruped_config(gait_name, robot_name)
+        self.solver = BatchedQuadrupedSolver(self.B, path_urdf, feet_frame_names, self.config_opt, self.config_cost,
+                                             height_offset, print_info, device=device)
+        self.height_offset, self.sim_dt = height_offset, sim_dt
+        self.dt_nodes = self.solver.dt_nodes
+        self.replanning_steps = int(1 / (self.config_opt.replanning_freq * sim_dt))
+        self.n_interp_plan = round(self.config_opt.time_horizon / sim_dt)
+        self.contact_planner = ContactPlanner(feet_frame_names, self.dt_nodes, self.config_gait)
+        nu = 12
+        self.joint_ref = np.zeros(nu) if joint_ref is None else np.asarray(joint_ref, dtype=float)[-nu:]
+        self.Kp, self.Kd = self.config_opt.Kp, self.config_opt.Kd
+        self.reset(reset_solver=False)
+
+    def reset(self, reset_solver: bool = True, i_node0=0) -> None:
+        if reset_solver:
+            self.solver.reset()
+        self.first_solve, self.sim_step, self.current_opt_node = True, 0, 0
+        self.i_node0 = np.broadcast_to(np.asarray(i_node0, dtype=np.int64), (self.B,)).copy()
+        self.v_des, self.w_yaw = np.zeros((self.B, 3)), np.zeros(self.B)
+        self.base_ref_vel_tracking = np.zeros((self.B, 12))
+        self.status_log: List[np.ndarray] = []
+
+    def set_command(self, v_des=np.zeros(3), w_yaw=0.) -> None:
+        self.v_des = np.broadcast_to(np.asarray(v_des, dtype=float), (self.B, 3)).copy()
+        self.w_yaw = np.broadcast_to(np.asarray(w_yaw, dtype=float), (self.B,)).copy()
+
+    def _advance_reference(self, n_steps: int) -> None:
+        """`increment_base_ref_position` (mpc.py:204-208), one sim step at a time, for every rollout."""
+        for _ in range(n_steps):
+            for b in range(self.B):
+                R_WB = rpy_to_matrix(self.base_ref_vel_tracking[b, 3:6][::-1])
+                v = np.round(R_WB @ self.v_des[b], 1)
+                self.base_ref_vel_tracking[b, :2] += v[:2] * self.sim_dt
+                self.base_ref_vel_tracking[b, 3] += self.w_yaw[b] * self.sim_dt
+
+    def set_convergence_on_first_iter(self) -> None:
+        o = self.config_opt
+        if self.first_solve:
+            self.solver.set_max_iter(N_SQP_FIRST)
+            self.solver.set_nlp_tol(o.nlp_tol / 10.)
+            self.solver.set_qp_tol(o.qp_tol / 10.)
+        elif self.sim_step <= self.replanning_steps:
+            self.solver.set_max_iter(o.max_iter)
+            self.solver.set_nlp_tol(o.nlp_tol)
+            self.solver.set_qp_tol(o.qp_tol)
+
+    def optimize(self, q: np.ndarray, v: np.ndarray):
+        """One replanning tick for all rollouts (mpc.py:317-369): contact plan and references at each rollout's
+        own node, batched `init` and `solve`."""
+        from ..problem import base_ref_vel_tracking
+        N1 = self.config_opt.n_nodes + 1
+        node = self.i_node0 + self.current_opt_node
+        cnt = np.stack([self.contact_planner.get_contacts(int(i), N1) for i in node])
+        peak = np.stack([self.contact_planner.get_peaks(int(i), N1) for i in node]) if self.config_opt.opt_peak else None
+        ref, ref_e = base_ref_vel_tracking(q, self.v_des, self.w_yaw, self.base_ref_vel_tracking,
+                                           self.config_gait.nom_height, self.height_offset, self.config_opt.time_horizon)
+        self.solver.init(node, q, v, ref, ref_e, self.joint_ref, self.config_gait.step_height, cnt, None, peak)
+        sol = self.solver.solve()
+        self.status_log.append(np.array(self.solver.status).copy())
+        return sol
+
+    def open_loop(self, q: np.ndarray, v: np.ndarray, trajectory_time: float, record_torques: bool = False):
+        """Roll all B rollouts forward on their own plans from Euler states q, v [B,18].
+        Returns q_traj, v_traj [n_steps,B,18] (and tau [n_steps,B,12] with `record_torques`)."""
+        q, v = np.array(q, dtype=float).reshape(self.B, 18), np.array(v, dtype=float).reshape(self.B, 18)
+        R = self.replanning_steps
+        qs, vs, taus = [], [], []
+        sim_time = 0.0
+        n_total = 0
+        while sim_time <= trajectory_time:
+            if sim_time >= (self.current_opt_node + 1) * self.dt_nodes:
+                self.current_opt_node += 1
+            if self.sim_step % R == 0:
+                self.set_convergence_on_first_iter()
+                self.optimize(q, v)
+                self.first_solve = False
+                # the samples up to the next tick, on the device: Hermite interpolation (+ inverse dynamics, PD)
+                out = self.solver.handle.plan_torques(self.n_interp_plan, 0, R, self.Kp, self.Kd)
+                plan_q, plan_v, plan_tau, k = out["q_plan"], out["v_plan"], out["tau"], 0
+            q, v = plan_q[:, k].copy(), plan_v[:, k].copy()
+            qs.append(q); vs.append(v)
+            if record_torques:
+                taus.append(plan_tau[:, k].copy())
+            k += 1
+            self._advance_reference(1)
+            self.sim_step += 1
+            n_total += 1
+            sim_time += self.sim_dt
+        res = (np.array(qs), np.array(vs))
+        return res + (np.array(taus),) if record_torques else res

@@ -49,6 +49,10 @@ class OracleHandle:
     def inverse_dynamics(self, qva, f):
         return O.inverse_dynamics(qva, f)
 
+    def plan_torques(self, n_interp, step0=0, n_steps=None, kp=20.0, kd=1.75, qv_meas=None):
+        x, u, _, _ = self._s.get_solution()
+        return O.plan_torques(x, u, float(self.opts.dt_nodes), n_interp, step0, n_steps, kp, kd, qv_meas)
+
     def set_profiling(self, on=True):
         pass
 

@@ -199,3 +199,33 @@ def test_compute_torques_dof_sync(backend):
     assert np.isfinite(tau).all() and np.abs(tau).max() < 60.0
     # standing still on four... two stance feet of a trot: knees carry weight => non-trivial feed-forward
     assert np.abs(tau).max() > 0.5
+
+
+def test_batched_locomotion_mpc_matches_unbatched_rollouts(backend):
+    """`BatchedLocomotionMPC.open_loop` (B rollouts in lockstep) against B runs of `LocomotionMPC.open_loop`,
+    both on the oracle backend: same visited configurations, different start states and commands."""
+    from iterative_learning_nmpc_b200 import dataset as DS
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import BatchedLocomotionMPC, LocomotionMPC
+    from iterative_learning_nmpc_b200.mpc_controller.utils.dynamics import QuadrupedDynamics
+    B, T = 2, 0.0415
+    rng = np.random.default_rng(8)
+    q0 = np.tile(P.nominal_state(WL.STAND_HEIGHT)[:18], (B, 1)); q0[:, 6:] += rng.uniform(-0.05, 0.05, (B, 12))
+    v0 = np.zeros((B, 18))
+    cmds = np.array([[0.15, 0.0, 0.0], [0.1, 0.05, 0.0]])
+    single = []
+    for b in range(B):
+        mpc = LocomotionMPC(None, FEET, "go2", gait_name="trot", print_info=False, solve_async=False,
+                            joint_ref=P.GO2_JOINT_HOME)
+        mpc.solver.cold_guess = "hold"
+        mpc.set_command(cmds[b], 0.0)
+        q_mj, v_mj = QuadrupedDynamics.convert_to_mujoco(q0[b], v0[b])
+        single.append(mpc.open_loop(q_mj, v_mj, T))
+    bm = BatchedLocomotionMPC(B, None, FEET, "go2", gait_name="trot", joint_ref=P.GO2_JOINT_HOME)
+    bm.set_command(cmds, 0.0)
+    qs, vs, taus = bm.open_loop(q0, v0, T, record_torques=True)
+    assert qs.shape == (len(single[0]), B, 18) and taus.shape == (len(single[0]), B, 12)
+    assert len(bm.status_log) == -(-len(single[0]) // bm.replanning_steps)    # one solve per replanning tick
+    for b in range(B):
+        q_mj, _ = DS.euler_to_mujoco(qs[:, b], vs[:, b])
+        err = np.abs(q_mj - single[b]).max()
+        assert err < 1e-6, (b, err)

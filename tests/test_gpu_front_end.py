@@ -126,3 +126,26 @@ def test_batch_to_rollouts_writes_reference_npz(tmp_path):
         np.testing.assert_array_equal(r["contact_vec"][0], batch["compact"]["cnt_sequence"][b][:, 0])
         path = DS.save_rollout(r, str(tmp_path), nominal=False, replanning_point=b, nth_traj=0)
         assert sorted(np.load(path).files) == sorted(DS.KEYS)
+
+
+def test_batched_locomotion_mpc_gpu_matches_oracle(oracle_mod):
+    """B lockstep rollouts (own start state, phase offset and command each) through the batched front-end:
+    CUDA path vs the same front-end on the oracle; three replanning ticks, first one with 15 SQP iterations."""
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import BatchedLocomotionMPC
+    B, T = 4, 0.0855
+    rng = np.random.default_rng(9)
+    q0 = np.tile(P.nominal_state(WL.STAND_HEIGHT)[:18], (B, 1)); q0[:, 6:] += rng.uniform(-0.05, 0.05, (B, 12))
+    v0 = rng.uniform(-0.1, 0.1, (B, 18))
+    cmds = np.stack([rng.uniform(0.0, 0.3, B), rng.uniform(-0.1, 0.1, B), np.zeros(B)], axis=1)
+    res = []
+    for use_oracle in (False, True):
+        bm = BatchedLocomotionMPC(B, None, FEET, "go2", gait_name="trot", joint_ref=P.GO2_JOINT_HOME)
+        if use_oracle:
+            _on_oracle(bm.solver)
+        bm.reset(reset_solver=False, i_node0=np.array([0, 3, 6, 9]))
+        bm.set_command(cmds, 0.0)
+        res.append(bm.open_loop(q0, v0, T, record_torques=True) + (np.array(bm.status_log),))
+    assert res[0][0].shape == (86, B, 18)
+    np.testing.assert_array_equal(res[0][3], res[1][3])
+    assert rel_err(res[0][0], res[1][0]) < 1e-5 and rel_err(res[0][1], res[1][1]) < 1e-5
+    assert rel_err(res[0][2], res[1][2]) < 1e-4          # torques: inverse dynamics amplifies the plan's 1e-6
