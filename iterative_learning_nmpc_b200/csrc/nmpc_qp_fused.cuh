@@ -514,17 +514,26 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     if (tid < NU) qz[(size_t)N * NZ + tid] = 0.0;
     __syncthreads();
 
-    // tile ownership
-    const bool has_ut = tid < N_UTILES, has_xt = tid < N_XTILES;
-    int urt = 0, uct = 0, urb = 0, ucb = 0, xrt = 0, xct = 0, xr = 0, xc = 0;
-    if (has_ut) { urt = c_utile[tid][0]; uct = c_utile[tid][1]; urb = c_utile[tid][2]; ucb = c_utile[tid][3]; }
-    if (has_xt) { xrt = c_xtile[tid][0]; xct = c_xtile[tid][1]; xr = c_xtile[tid][2]; xc = c_xtile[tid][3]; }
-    const int ur0 = 3 * urb, uc0 = 6 * ucb;
-    // first row / column of the tiles inside their block types
-    const int uti = ur0 - (urt == 0 ? IA : urt == 1 ? IFRC : urt == 2 ? IQ : urt == 3 ? IV : IH);
-    const int utj = uc0 - (uct == 0 ? IA : IFRC);
-    const int xti = 3 * xr - (xrt == 0 ? 0 : xrt == 1 ? NQ : 2 * NQ);
-    const int xtj = 3 * xc - (xct == 0 ? 0 : xct == 1 ? NQ : 2 * NQ);
+    // tile ownership, packed into one register.  The unpacked fields (and everything derived from them) used to be
+    // kernel-lifetime values that the register peak of the panel factorisation pushed into local memory; with four
+    // CTAs per SM those reloads miss the L1 left over next to 211 KB of shared memory.  Each use site below unpacks
+    // what it needs behind an opaque move, so nothing but `tcode` stays live across the stage.
+    unsigned tcode = 0;
+    if (tid < N_UTILES)
+        tcode |= c_utile[tid][0] | (c_utile[tid][1] << 3) | (c_utile[tid][2] << 4) | (c_utile[tid][3] << 9) | (1u << 24);
+    if (tid < N_XTILES)
+        tcode |= (c_xtile[tid][0] << 12) | (c_xtile[tid][1] << 14) | (c_xtile[tid][2] << 16) | (c_xtile[tid][3] << 20) | (1u << 25);
+#define FQ_UNPACK_U                                                                                              \
+    unsigned tc_ = tcode; asm volatile("" : "+r"(tc_));                                                          \
+    const bool has_ut = (tc_ >> 24) & 1u;                                                                        \
+    const int urt = tc_ & 7u, uct = (tc_ >> 3) & 1u, urb = (tc_ >> 4) & 31u, ucb = (tc_ >> 9) & 7u;              \
+    const int ur0 = 3 * urb, uc0 = 6 * ucb;                                                                      \
+    (void)urt; (void)uct; (void)ur0; (void)uc0; (void)has_ut
+#define FQ_UNPACK_X                                                                                              \
+    unsigned tx_ = tcode; asm volatile("" : "+r"(tx_));                                                          \
+    const bool has_xt = (tx_ >> 25) & 1u;                                                                        \
+    const int xrt = (tx_ >> 12) & 3u, xct = (tx_ >> 14) & 3u, xr = (tx_ >> 16) & 15u, xc = (tx_ >> 20) & 15u;    \
+    (void)xrt; (void)xct; (void)xr; (void)xc; (void)has_xt
 
     int status = 1, iters = 0, nc_total = 0;
     double alpha_p = 1.0, alpha_d = 1.0, mu = 0.0;
@@ -671,6 +680,10 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 __syncthreads();
                 FMARK(4);
                 // ---- u tile: rows ur0..+2 (z index), columns uc0..+5 (u index) ----
+                FQ_UNPACK_U;
+                // first row / column of the tile inside its block types
+                const int uti = ur0 - (urt == 0 ? IA : urt == 1 ? IFRC : urt == 2 ? IQ : urt == 3 ? IV : IH);
+                const int utj = uc0 - (uct == 0 ? IA : IFRC);
                 if (has_ut) {
                     switch (uct * 5 + urt) {
                     case 0: fq_asm_u<0, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
@@ -710,6 +723,10 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 }
             }
             // ---- x tile: rows 3xr..+2, columns 3xc..+2 of the state block ----
+            {
+            FQ_UNPACK_X;
+            const int xti = 3 * xr - (xrt == 0 ? 0 : xrt == 1 ? NQ : 2 * NQ);
+            const int xtj = 3 * xc - (xct == 0 ? 0 : xct == 1 ? NQ : 2 * NQ);
             if (has_xt) {
                 const int i0 = 3 * xr, j0x = 3 * xc;
                 if (term) {
@@ -763,6 +780,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                     }
                 }
             }
+            }
             __syncthreads();                 // every read of SR_k, P+, U, PGh is done
             FMARK(5);
             if (k > 0 && tid == 0) {         // prefetch the next stage record under the factorisation
@@ -774,11 +792,14 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 for (int jb = 0; jb < 5; jb++) {
                     const int j0 = PB * jb;
                     double* pan = sM + P_OFF(jb);                    // rows j0..72 of columns j0..j0+5
+                    {
+                    FQ_UNPACK_U;
                     if (has_ut && ucb == jb) {
 #pragma unroll
                         for (int r = 0; r < 3; r++)
 #pragma unroll
                             for (int c = 0; c < 6; c++) pan[(ur0 + r - j0) * PB + c] = ua[r][c];
+                    }
                     }
                     if (tid < PB) pan[(NZ - j0) * PB + tid] = sv[FV_QT + j0 + tid];
                     __syncthreads();
@@ -826,6 +847,8 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 #pragma unroll
                         for (int c = 0; c < PB; c++) pan[tid * PB + c] = drow[c];
                     }
+                    FQ_UNPACK_U;
+                    FQ_UNPACK_X;
                     if (has_ut && ucb > jb) {
                         const double* pa = pan + (ur0 - j0) * PB;
                         const double* pb = pan + (uc0 - j0) * PB;
@@ -869,6 +892,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             __syncthreads();
             FMARK(6);
             // ---- P_k (both triangles) -> sP, p_k -> sv; factor record -> HBM ----
+            FQ_UNPACK_X;
             if (has_xt) {
 #pragma unroll
                 for (int r = 0; r < 3; r++)
