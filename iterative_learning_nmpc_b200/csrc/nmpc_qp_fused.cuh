@@ -185,7 +185,10 @@ struct FqArgs {
 #define FV_DZ (FV_DXN + NX)
 #define FV_RED (FV_DZ + NZ)                  // 16 reduction slots
 #define FV_END (FV_RED + 16)
-#define FQ_SMEM_BYTES ((FS_V + FV_END) * 8)
+// per-thread running norms / complementarity sum of the backward pass (5 x 128): in shared memory rather than in
+// registers that would be spilled across the panel factorisation of every stage
+#define FS_ACC (FS_V + FV_END)
+#define FQ_SMEM_BYTES ((FS_ACC + 5 * FQ_THREADS) * 8)
 
 // C z for the current stage: sv[FV_CZ + j] = sum_c C(j, c) zz[c], zz over [u; x]
 __device__ __forceinline__ void fq_cz(const double* S, const double* zz, double* out, int tid)
@@ -345,11 +348,14 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
             // lane l keeps rhs_l * (1 / L_ll) ready so the broadcast value is already the solution component
             double du = 0.0, myinv = 0.0;
             const int ll = lane < NU ? lane : NU - 1;
-            { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? 1.0 / d : 0.0; }
+            { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
+            // L(i, ll) for i >= ll sits at colb + 6 i (panel-packed, 6 doubles per row): one register instead of a
+            // table of 30 per-lane addresses, which the compiler hoisted out of the stage loop and kept in local memory
+            const double* colb = sM + P_OFF(ll / PB) - PB * PB * (ll / PB) + ll % PB;
 #pragma unroll
             for (int i = NU - 1; i >= 0; i--) {
                 const double dui = -__shfl_sync(0xffffffffu, rhs * myinv, i);
-                const double lv = sM[lp_idx(i, ll < i ? ll : i)];
+                const double lv = (lane < i) ? colb[PB * i] : 0.0;
                 du = (lane == i) ? dui : du;
                 rhs = (lane < i) ? fma(lv, dui, rhs) : rhs;
             }
@@ -470,6 +476,8 @@ __device__ unsigned long long g_fq_cycles[24];
 #define FMARK(ph) do { } while (0)
 #endif
 
+__device__ __forceinline__ int fq_opaque(int v) { asm volatile("" : "+r"(v)); return v; }
+
 __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 {
 #ifdef NMPC_TIMING
@@ -491,13 +499,16 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     double* red = sv + FV_RED;
     const double dt = a.dt, c2 = 0.5 * a.dt * a.dt;
 
-    const double* SRb = a.SR + (size_t)bl * (N + 1) * SR_SZ;
-    double* FRb = a.FR + (size_t)bl * (N + 1) * FR_SZ;
-    double* vb = a.vec + (size_t)bl * (N + 1) * V_STAGE;
-    double* qz = a.qz + (size_t)b * (N + 1) * NZ;
-    double* qpi = a.qpi + (size_t)b * N * NX;
-    double* qlamb = a.qlam + (size_t)b * (N + 1) * 2 * NG;
-    double* qtb = a.qt + (size_t)b * (N + 1) * 2 * NG;
+    // Base pointers of this OCP are NOT kept in registers for the lifetime of the kernel (seven 64-bit values that the
+    // register peak of the panel factorisation would push into local memory): every use recomputes them from the
+    // kernel parameters (constant bank) and the block index, behind an opaque move so that they are not hoisted.
+#define SRb (a.SR + (size_t)fq_opaque(bl) * (N + 1) * SR_SZ)
+#define FRb (a.FR + (size_t)fq_opaque(bl) * (N + 1) * FR_SZ)
+#define vb (a.vec + (size_t)fq_opaque(bl) * (N + 1) * V_STAGE)
+#define qz (a.qz + (size_t)fq_opaque(b) * (N + 1) * NZ)
+#define qpi (a.qpi + (size_t)fq_opaque(b) * N * NX)
+#define qlamb (a.qlam + (size_t)fq_opaque(b) * (N + 1) * 2 * NG)
+#define qtb (a.qt + (size_t)fq_opaque(b) * (N + 1) * 2 * NG)
 
     uint32_t phase = 0;
     if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
@@ -564,7 +575,9 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         FMARK(0);
 
         // ================= backward pass: residuals of every stage (+ factorisation unless last) =====
-        double n_g = 0.0, n_b = 0.0, n_d = 0.0, n_m = 0.0, acc_mu = 0.0;
+        double* acc = smem + FS_ACC + tid;       // [0] n_g  [1] n_b  [2] n_d  [3] n_m  [4] sum lam t   (stride FQ_THREADS)
+#pragma unroll
+        for (int i = 0; i < 5; i++) acc[i * FQ_THREADS] = 0.0;
         int cnt = 0;
         if (tid == 0) {
             bulk_store_wait_read();
@@ -606,8 +619,9 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 const double rm = msk > 0.5 ? lam * t : 0.0;
                 sv[FV_RD + tid] = rd; sv[FV_RM + tid] = rm;
                 vk[V_RD + tid] = rd; vk[V_RM + tid] = rm;
-                acc_mu += rm; cnt += (msk > 0.5) ? 1 : 0;
-                n_d = nanmax(n_d, fabs(rd)); n_m = nanmax(n_m, fabs(rm));
+                acc[4 * FQ_THREADS] += rm; cnt += (msk > 0.5) ? 1 : 0;
+                acc[2 * FQ_THREADS] = nanmax(acc[2 * FQ_THREADS], fabs(rd));
+                acc[3 * FQ_THREADS] = nanmax(acc[3 * FQ_THREADS], fabs(rm));
             }
             __syncthreads();
             if (tid < NG) {
@@ -630,12 +644,12 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 if (!term) s += fq_gt(S, sv + FV_PIN, c, dt, c2);
                 if ((k == 0 && c >= NU) || (term && c < NU)) s = 0.0;
                 vk[V_RG + c] = s; sv[FV_QT + c] = qp + s;
-                n_g = nanmax(n_g, fabs(s));
+                acc[0] = nanmax(acc[0], fabs(s));
             } else if (!term && tid >= 80 && tid < 80 + NX) {
                 const int l = tid - 80;
                 const double rb = fq_g(S, sv + FV_Z, l, dt, c2) + S[SR_B + l] - sv[FV_ZXN + l];
                 sv[FV_RB + l] = rb; vk[V_RB + l] = rb;
-                n_b = nanmax(n_b, fabs(rb));
+                acc[FQ_THREADS] = nanmax(acc[FQ_THREADS], fabs(rb));
             }
             __syncthreads();
             if (last) {
@@ -914,11 +928,11 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 
         FMARK(7);
         // ================= norms, mu, exit tests (nmpc_qp_decide_kernel) =================
-        res4[0] = fq_block_max(n_g, red, tid);
-        res4[1] = fq_block_max(n_b, red, tid);
-        res4[2] = fq_block_max(n_d, red, tid);
-        res4[3] = fq_block_max(n_m, red, tid);
-        const double mu_sum = fq_block_sum(acc_mu, red, tid);
+        res4[0] = fq_block_max(acc[0], red, tid);
+        res4[1] = fq_block_max(acc[FQ_THREADS], red, tid);
+        res4[2] = fq_block_max(acc[2 * FQ_THREADS], red, tid);
+        res4[3] = fq_block_max(acc[3 * FQ_THREADS], red, tid);
+        const double mu_sum = fq_block_sum(acc[4 * FQ_THREADS], red, tid);
         if (it == 0) nc_total = (int)(fq_block_sum((double)cnt, red, tid) + 0.5);
         mu = nc_total > 0 ? mu_sum / nc_total : 0.0;
         {
@@ -1035,11 +1049,12 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
                     double m0 = tid < NU ? sv[FV_QT + tid] : 0.0, myinv = 0.0;
                     const int ll = tid < NU ? tid : NU - 1;
-                    { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? 1.0 / d : 0.0; }
+                    { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
 #pragma unroll
                     for (int j = 0; j < NU; j++) {
                         const double xj = __shfl_sync(0xffffffffu, m0 * myinv, j);
-                        const double lv = sM[lp_idx(ll > j ? ll : j, j)];
+                        // L(ll, j), ll > j: compile-time panel offset + 6 ll
+                        const double lv = (tid > j && tid < NU) ? sM[P_OFF(j / PB) - PB * PB * (j / PB) + j % PB + PB * ll] : 0.0;
                         m0 = (tid == j) ? xj : ((tid > j && tid < NU) ? fma(-lv, xj, m0) : m0);
                     }
                     if (tid < NU) { sv[FV_DZ + tid] = m0; vk[V_LROW + tid] = m0; }
@@ -1114,4 +1129,11 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         a.qp_status[b] = status;
         for (int i = 0; i < 4; i++) a.qp_res[(size_t)b * 4 + i] = res4[i];
     }
+#undef SRb
+#undef FRb
+#undef vb
+#undef qz
+#undef qpi
+#undef qlamb
+#undef qtb
 }
