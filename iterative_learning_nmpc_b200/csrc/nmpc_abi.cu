@@ -485,7 +485,7 @@ static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, bool from
     f.SR = h->SR; f.FR = h->FR; f.vec = h->vec; f.qz = a.qz; f.qpi = a.qpi; f.qlam = a.qlam; f.qt = a.qt;
     f.qp_iter = a.qp_iter; f.qp_status = a.qp_status; f.qp_res = a.qp_res; f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
     f.x = a.x; f.sqp_done = a.sqp_done; f.N = N; f.b0 = a.b0; f.max_iter = a.max_iter; f.warm = a.warm;
-    f.tol = a.tol; f.dt = h->o.dt_nodes;
+    f.tol = a.tol; f.dt = h->o.dt_nodes; f.c2 = 0.5 * h->o.dt_nodes * h->o.dt_nodes;
     prof_begin(h, NMPC_PROF_QP_FUSED);
     nmpc_qp_fused_kernel<<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
     prof_end(h);

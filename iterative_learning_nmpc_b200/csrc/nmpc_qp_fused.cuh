@@ -151,7 +151,7 @@ struct FqArgs {
     const double* dx0_ext; const double* x0; const double* x;
     const int32_t* sqp_done;
     int N, b0, max_iter, warm;
-    double tol, dt;
+    double tol, dt, c2;              // c2 = dt^2 / 2 (host-computed: both stay constant-bank operands)
 };
 
 // shared memory carve-up (doubles)
@@ -497,7 +497,8 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     double* sv = smem + FS_V;
     double* sU = smem + FS_U;
     double* red = sv + FV_RED;
-    const double dt = a.dt, c2 = 0.5 * a.dt * a.dt;
+    const double dt = a.dt, c2 = a.c2;
+    const int tid_k = tid;
 
     // Base pointers of this OCP are NOT kept in registers for the lifetime of the kernel (seven 64-bit values that the
     // register peak of the panel factorisation would push into local memory): every use recomputes them from the
@@ -548,7 +549,6 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 
     int status = 1, iters = 0, nc_total = 0;
     double alpha_p = 1.0, alpha_d = 1.0, mu = 0.0;
-    double res4[4] = {0.0, 0.0, 0.0, 0.0};
 
     for (int it = 0; it <= a.max_iter; it++) {
         const bool last = (it >= a.max_iter);
@@ -558,6 +558,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             alpha_d *= (1.0 - alpha_d) * 0.99 + alpha_d * 0.9999999;
             if (alpha_p < IPM_ALPHA_MIN && alpha_d < IPM_ALPHA_MIN) { status = 2; break; }
             for (int k = 0; k <= N; k++) {
+                const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
                 const double* vk = vb + (size_t)k * V_STAGE;
                 const double* Dm = SRb + (size_t)k * SR_SZ + SR_D + 2 * NG;
                 if (tid < NZ) qz[(size_t)k * NZ + tid] += alpha_p * vk[V_DZ + tid];
@@ -585,6 +586,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             bulk_g2s(S, SRb + (size_t)N * SR_SZ, SR_SZ * 8, &bar);
         }
         for (int k = N; k >= 0; k--) {
+            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
             const bool term = (k == N);
             double* vk = vb + (size_t)k * V_STAGE;
             double* qlam = qlamb + (size_t)k * 2 * NG;
@@ -928,6 +930,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 
         FMARK(7);
         // ================= norms, mu, exit tests (nmpc_qp_decide_kernel) =================
+        double res4[4];
         res4[0] = fq_block_max(acc[0], red, tid);
         res4[1] = fq_block_max(acc[FQ_THREADS], red, tid);
         res4[2] = fq_block_max(acc[2 * FQ_THREADS], red, tid);
@@ -941,6 +944,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             for (int i = 0; i < 4; i++) {
                 if (isinf(res4[i]) || !(res4[i] == res4[i])) bad = true;
                 if (!(res4[i] < a.tol)) conv = false;
+                if (tid == 0) a.qp_res[(size_t)b * 4 + i] = res4[i];      // residuals of the last iterate that was evaluated
             }
             if (bad) { status = 3; break; }
             if (conv) { status = 0; break; }
@@ -954,6 +958,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         if (tid == 0) bulk_store_wait_all();                         // the factor records are in global memory
         __syncthreads();
         for (int k = 0; k <= N; k++) {
+            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
             const bool term = (k == N);
             double* vk = vb + (size_t)k * V_STAGE;
             if (tid == 0) {
@@ -978,6 +983,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         {
             double s = 0.0;
             for (int k = 0; k <= N; k++) {
+                const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
                 if (tid < 2 * NG && SRb[(size_t)k * SR_SZ + SR_D + 2 * NG + tid] > 0.5) {
                     const double* vk = vb + (size_t)k * V_STAGE;
                     s += (qlamb[(size_t)k * 2 * NG + tid] + alpha_aff * vk[V_DLAM + tid]) *
@@ -994,6 +1000,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         FMARK(10);
         // ================= corrector: backward vector sweep on the stored factorisation =================
         for (int k = N; k >= 0; k--) {
+            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
             const bool term = (k == N);
             double* vk = vb + (size_t)k * V_STAGE;
             if (tid == 0) {
@@ -1091,6 +1098,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         if (tid < NX) sv[FV_DX + tid] = 0.0;
         __syncthreads();
         for (int k = 0; k <= N; k++) {
+            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
             const bool term = (k == N);
             double* vk = vb + (size_t)k * V_STAGE;
             if (tid == 0) {
@@ -1127,7 +1135,6 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         bulk_store_wait_all();
         a.qp_iter[b] = iters;
         a.qp_status[b] = status;
-        for (int i = 0; i < 4; i++) a.qp_res[(size_t)b * 4 + i] = res4[i];
     }
 #undef SRb
 #undef FRb
