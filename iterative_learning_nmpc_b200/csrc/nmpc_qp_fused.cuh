@@ -321,7 +321,8 @@ __device__ __forceinline__ double fq_block_sum(double v, double* red, int tid)
 template <bool CORR>
 __device__ __forceinline__ void fq_forward_stage(const double* sM, const double* sP, const double* S, double* sv,
                                                  double* vk, double* dpi_prev, const double* qlam, const double* qt,
-                                                 bool term, int tid, double dt, double c2, double& a_p, double& a_d)
+                                                 bool term, int tid, double dt, double c2, double& a_p, double& a_d,
+                                                 double (&cs)[3])
 {
     const int lane = tid & 31;
     if (CORR && dpi_prev && tid >= 64 && tid < 64 + NX) {           // dpi_{k-1} = P_k dx_k + p_k
@@ -381,6 +382,9 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
             dl = -(vk[V_RM + tid] + lam * dtv) / t;
             if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
             if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
+            if (!CORR) {      // sum (lam + a dlam)(t + a dt) = cs0 + a cs1 + a^2 cs2: the centring parameter needs no extra pass
+                cs[0] = fma(lam, t, cs[0]); cs[1] += fma(lam, dtv, t * dl); cs[2] = fma(dl, dtv, cs[2]);
+            }
         }
         vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
     }
@@ -954,6 +958,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         FMARK(8);
         // ================= forward sweep: affine direction, step lengths =================
         double a_p = 1.0, a_d = 1.0;
+        double cs[3] = {0.0, 0.0, 0.0};
         if (tid < NX) sv[FV_DX + tid] = 0.0;
         if (tid == 0) bulk_store_wait_all();                         // the factor records are in global memory
         __syncthreads();
@@ -971,7 +976,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             __syncthreads();
             mbar_wait(&bar, phase); phase ^= 1;
             fq_forward_stage<false>(sM, sP, S, sv, vk, nullptr, qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG,
-                                    term, tid, dt, c2, a_p, a_d);
+                                    term, tid, dt, c2, a_p, a_d, cs);
         }
         a_p = fq_block_min(a_p, red, tid);
         a_d = fq_block_min(a_d, red, tid);
@@ -981,16 +986,10 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         // ================= centring parameter (nmpc_qp_sigma_kernel) =================
         double sigma_mu;
         {
-            double s = 0.0;
-            for (int k = 0; k <= N; k++) {
-                const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
-                if (tid < 2 * NG && SRb[(size_t)k * SR_SZ + SR_D + 2 * NG + tid] > 0.5) {
-                    const double* vk = vb + (size_t)k * V_STAGE;
-                    s += (qlamb[(size_t)k * 2 * NG + tid] + alpha_aff * vk[V_DLAM + tid]) *
-                         (qtb[(size_t)k * 2 * NG + tid] + alpha_aff * vk[V_DT + tid]);
-                }
-            }
-            s = fq_block_sum(s, red, tid);
+            const double s0 = fq_block_sum(cs[0], red, tid);
+            const double s1 = fq_block_sum(cs[1], red, tid);
+            const double s2 = fq_block_sum(cs[2], red, tid);
+            const double s = fma(alpha_aff, fma(alpha_aff, s2, s1), s0);
             const double mu_aff = nc_total > 0 ? s / nc_total : 0.0;
             double sg = mu > 0.0 ? mu_aff / mu : 0.0;
             sg = sg * sg * sg;
@@ -1117,7 +1116,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             if (!term && tid < NU) sM[lp_idx(NZ, tid)] = vk[V_LROW + tid];      // the corrector's lu replaces the affine one
             __syncthreads();
             fq_forward_stage<true>(sM, sP, S, sv, vk, k > 0 ? vb + (size_t)(k - 1) * V_STAGE + V_DPI : nullptr,
-                                   qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG, term, tid, dt, c2, a_p, a_d);
+                                   qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG, term, tid, dt, c2, a_p, a_d, cs);
         }
         alpha_p = fq_block_min(a_p, red, tid);
         alpha_d = fq_block_min(a_d, red, tid);
