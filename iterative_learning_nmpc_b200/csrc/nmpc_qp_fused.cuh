@@ -325,6 +325,9 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
                                                  double (&cs)[3])
 {
     const int lane = tid & 31;
+    // this thread's multiplier data, requested before the serial chain below so that the loads are not on it
+    double g_lam = 0.0, g_t = 1.0, g_rd = 0.0, g_rm = 0.0;
+    if (tid < 2 * NG) { g_lam = qlam[tid]; g_t = qt[tid]; g_rd = vk[V_RD + tid]; g_rm = vk[V_RM + tid]; }
     if (CORR && dpi_prev && tid >= 64 && tid < 64 + NX) {           // dpi_{k-1} = P_k dx_k + p_k
         const int i = tid - 64;
         const double* row = sP + i * P_LD;
@@ -376,10 +379,10 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
         const int e = tid / NG, j = tid % NG;
         double dtv = 0.0, dl = 0.0;
         if (S[SR_D + 2 * NG + tid] > 0.5) {
-            const double lam = qlam[tid], t = qt[tid];
+            const double lam = g_lam, t = g_t;
             const double cdz = sv[FV_CZ + j];
-            dtv = (e ? -cdz : cdz) + vk[V_RD + tid];
-            dl = -(vk[V_RM + tid] + lam * dtv) / t;
+            dtv = (e ? -cdz : cdz) + g_rd;
+            dl = -(g_rm + lam * dtv) / t;
             if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
             if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
             if (!CORR) {      // sum (lam + a dlam)(t + a dt) = cs0 + a cs1 + a^2 cs2: the centring parameter needs no extra pass
@@ -1010,6 +1013,11 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
                 if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
             }
+            double g_lam = 0.0, g_t = 1.0, g_dt = 0.0, g_dl = 0.0, g_rd = 0.0;
+            if (tid < 2 * NG) {                                      // requested before the waits below
+                g_lam = qlamb[(size_t)k * 2 * NG + tid]; g_t = qtb[(size_t)k * 2 * NG + tid];
+                g_dt = vk[V_DT + tid]; g_dl = vk[V_DLAM + tid]; g_rd = vk[V_RD + tid];
+            }
             if (!term && tid < NX) sv[FV_RB + tid] = vk[V_RB + tid];
             if (tid < NZ) sv[FV_RG + tid] = vk[V_RG + tid];
             __syncthreads();
@@ -1020,10 +1028,10 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             if (tid < 2 * NG) {
                 double v = 0.0;
                 if (S[SR_D + 2 * NG + tid] > 0.5) {
-                    const double lam = qlamb[(size_t)k * 2 * NG + tid], t = qtb[(size_t)k * 2 * NG + tid];
-                    const double rmc = lam * t + vk[V_DT + tid] * vk[V_DLAM + tid] - sigma_mu;
+                    const double lam = g_lam, t = g_t;
+                    const double rmc = lam * t + g_dt * g_dl - sigma_mu;
                     vk[V_RM + tid] = rmc;
-                    v = (rmc + lam * vk[V_RD + tid]) / t;
+                    v = (rmc + lam * g_rd) / t;
                 }
                 sv[FV_RD + tid] = v;                                 // scratch: per-side gamma
             }
