@@ -234,9 +234,13 @@ def main() -> None:
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
     torch.cuda.set_device(local)
+    out_stream = sys.stdout
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+        # rank 0 prints ONE JSON line on stdout: NCCL's version banner (and anything else a library writes to
+        # file descriptor 1) is sent to stderr for the whole run; the JSON line goes to the saved descriptor
+        sys.stdout.flush()
+        out_stream = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     B = args.batch
@@ -386,7 +390,7 @@ def main() -> None:
                     "ms_per_step": max(ms_e2e, wall_e2e) / args.steps},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
             "status_counts": status_counts,
-        }))
+        }), file=out_stream, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
