@@ -283,6 +283,17 @@ class Graph:
         # use counts to inline single-use NEG / constants
         lines: List[str] = []
         ref: Dict[int, str] = {}
+        # An output is stored as soon as its node has been computed, not at the end of the body: with all stores at
+        # the end every output value (735 record slots per stage) stayed live across the whole function and ptxas
+        # spilled 20-40 KB per thread.
+        stores: Dict[int, List[str]] = {}
+        for lv, n in outputs:
+            stores.setdefault(n, []).append(lv)
+        pending: List[Tuple[str, int]] = []
+
+        def flush(n: int) -> None:
+            for lv in stores.get(n, ()):
+                lines.append(f"{indent}{lv} = {ref[n]};")
         n_flops = 0
         n_trig = 0
         # pair sin/cos
@@ -295,12 +306,15 @@ class Graph:
             o = self.op[n]
             if o == CONST:
                 ref[n] = repr(self.val[n]) if self.val[n] >= 0 else f"({self.val[n]!r})"
+                flush(n)
                 continue
             if o == SYM:
                 ref[n] = sym_expr[self.name[n]]
+                flush(n)
                 continue
             if o == NEG:
                 ref[n] = f"(-{ref[self.a[n]]})"
+                flush(n)
                 continue
             t = f"t{n}"
             if o in (SIN, COS):
@@ -315,23 +329,25 @@ class Graph:
                         emitted_trig.add(arg)
                         n_trig += 1
                     ref[n] = t
+                    flush(n)
                     continue
                 fn = "sin" if o == SIN else "cos"
                 lines.append(f"{indent}const double {t} = {fn}({ref[arg]});")
                 n_trig += 1
                 ref[n] = t
+                flush(n)
                 continue
             if o == SQRT:
                 lines.append(f"{indent}const double {t} = sqrt({ref[self.a[n]]});")
                 n_flops += 1
                 ref[n] = t
+                flush(n)
                 continue
             sym = {ADD: "+", SUB: "-", MUL: "*", DIV: "/"}[o]
             lines.append(f"{indent}const double {t} = {ref[self.a[n]]} {sym} {ref[self.b[n]]};")
             n_flops += 1
             ref[n] = t
-        for lv, n in outputs:
-            lines.append(f"{indent}{lv} = {ref[n]};")
+            flush(n)
         return "\n".join(lines) + "\n", {"flops": n_flops, "trig": n_trig, "nodes": len(nodes)}
 
 

@@ -34,7 +34,7 @@ struct ModelArgs {
     int n_inst, N, b0;
 };
 
-__global__ void __launch_bounds__(MODEL_THREADS) nmpc_model_kernel(ModelArgs a)
+__global__ void __launch_bounds__(MODEL_THREADS, 2) nmpc_model_kernel(ModelArgs a)
 {
     const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
     if (i >= a.n_inst) return;
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_kernel(LinArgs 
 // ---------------------------------------------------------------------------------------------
 // values-only kinematics: feet, CoM, centroidal momentum (update_pin / get_feet_position_w)
 // ---------------------------------------------------------------------------------------------
-__global__ void nmpc_kin0_kernel(const double* qv, int n, double* feet, double* com, double* hg)
+__global__ void __launch_bounds__(64, 4) nmpc_kin0_kernel(const double* qv, int n, double* feet, double* com, double* hg)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -384,8 +384,10 @@ __global__ void nmpc_kin0_kernel(const double* qv, int n, double* feet, double* 
     if (hg) for (int j = 0; j < 6; j++) hg[(size_t)i * 6 + j] = h[j];
 }
 
+// (launch bounds on the kernels that call the generated, non-inlined model functions: without a minimum-blocks hint
+// ptxas gave them 32 registers and the straight-line code spilled 20-100 KB per thread)
 // feed-forward joint torques (QuadrupedDynamics.id_torques, dynamics.py:136-163): thread per instance
-__global__ void nmpc_rnea_kernel(const double* qva, const double* f, int n, double* tau)
+__global__ void __launch_bounds__(64, 4) nmpc_rnea_kernel(const double* qva, const double* f, int n, double* tau)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -399,7 +401,7 @@ __global__ void nmpc_rnea_kernel(const double* qva, const double* f, int n, doub
 }
 
 // x0 = [q, v, hg(q, v)]; also overwrites node 0 of the iterate (solver.py:179-192)
-__global__ void nmpc_set_x0_kernel(const double* qv, int B, int N, double* x0, double* x)
+__global__ void __launch_bounds__(64, 4) nmpc_set_x0_kernel(const double* qv, int B, int N, double* x0, double* x)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -421,7 +423,7 @@ __global__ void nmpc_copy_x0_kernel(int B, int N, const double* x0, double* x)
 }
 
 // setup_initial_feet_pos (solver.py:194-210)
-__global__ void nmpc_pin_feet_kernel(int B, int N, const double* x0, const int32_t* i_node, double* p)
+__global__ void __launch_bounds__(64, 4) nmpc_pin_feet_kernel(int B, int N, const double* x0, const int32_t* i_node, double* p)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;

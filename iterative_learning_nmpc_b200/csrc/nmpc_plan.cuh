@@ -24,7 +24,7 @@ struct PlanArgs {
     double dt, kp, kd;
 };
 
-__global__ void __launch_bounds__(64) nmpc_plan_torque_kernel(PlanArgs a)
+__global__ void __launch_bounds__(64, 4) nmpc_plan_torque_kernel(PlanArgs a)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.B * a.n_steps) return;
