@@ -9,6 +9,8 @@ free), forward/reverse differentiation by graph traversal, and an emitter that w
 """
 from __future__ import annotations
 
+import os
+
 import math
 from typing import Dict, Iterable, List, Sequence, Tuple
 
@@ -160,6 +162,30 @@ class Graph:
                 stack.append(self.a[n])
         return sorted(seen)
 
+    def dfs_order(self, outputs: Iterable[int]) -> List[int]:
+        """Depth-first post-order from the outputs, in output order: the operands of an output are computed
+        right before it instead of in creation order (shorter live ranges in the emitted straight-line code)."""
+        seen = set()
+        order: List[int] = []
+        for root in outputs:
+            stack = [(root, False)]
+            while stack:
+                n, done = stack.pop()
+                if done:
+                    order.append(n)
+                    continue
+                if n in seen:
+                    continue
+                seen.add(n)
+                stack.append((n, True))
+                o = self.op[n]
+                if o in _BINARY:
+                    stack.append((self.b[n], False))
+                    stack.append((self.a[n], False))
+                elif o in _UNARY:
+                    stack.append((self.a[n], False))
+        return order
+
     # ---- differentiation ---------------------------------------------------------------
     def jvp(self, outputs: Sequence[int], wrt: Sequence[int], tangents: Sequence[int]) -> List[int]:
         """Forward mode: d(outputs)/d(wrt) . tangents, tangents being expressions."""
@@ -279,8 +305,13 @@ class Graph:
         `sym_expr` maps symbol names to C rvalues (e.g. "q[3]").  Returns (code, stats).
         sin/cos of the same argument are emitted as one `sincos` call.
         """
-        nodes = self.topo([n for _, n in outputs])
-        # use counts to inline single-use NEG / constants
+        # Depth-first order (operands right before their first use) instead of creation order: 37 % fewer spill
+        # stores / 39 % fewer reloads in the sm_100a build of the model parts, inverse-dynamics frame 10.6 -> 2.1 KB
+        # (heavier-operand-first variants were no better).  NMPC_EMIT_ORDER=topo gives the old order.
+        if os.environ.get("NMPC_EMIT_ORDER", "dfs") == "dfs":
+            nodes = self.dfs_order([n for _, n in outputs])
+        else:
+            nodes = self.topo([n for _, n in outputs])
         lines: List[str] = []
         ref: Dict[int, str] = {}
         # An output is stored as soon as its node has been computed, not at the end of the body: with all stores at

@@ -395,7 +395,7 @@ static void launch_linearize_sr(nmpc_handle* h, int b0, int Bc)
     nmpc_model_kernel<<<dim3((n_inst + MODEL_THREADS - 1) / MODEL_THREADS, NMPC_MODEL_PARTS), MODEL_THREADS, 0,
                         h->stream>>>(ma);
     LinArgs la = lin_args(h, b0);
-    nmpc_linearize_sr_kernel<<<dim3(N + 1, Bc), LIN_THREADS, 0, h->stream>>>(la, h->SR);
+    nmpc_linearize_sr_kernel<<<dim3(N + 1, Bc), LIN_SR_THREADS, 0, h->stream>>>(la, h->SR);
     h->launches += 2;
 }
 

@@ -10,7 +10,16 @@
 #include "nmpc_qp_fused.cuh"
 #include "nmpc_sqp.cuh"
 
-__global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinArgs a, double* SR)
+// Small CTAs: the kernel is a chain of short, unevenly filled phases between barriers, so what counts is how many
+// independent CTAs an SM holds (profiles/r1w_linearize.md: 256 threads x 4 CTAs 0.50 ms, 64 threads x 16 CTAs 0.30 ms).
+#ifndef LIN_SR_THREADS
+#define LIN_SR_THREADS 64
+#endif
+#ifndef LIN_MINB
+#define LIN_MINB 16
+#endif
+static_assert(LIN_SR_THREADS >= 64 && LIN_SR_THREADS % 32 == 0, "warp 1 computes the lever arms");
+__global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_kernel(LinArgs a, double* SR)
 {
     const int k = blockIdx.x, bl = blockIdx.y, b = a.b0 + bl;
     const int tid = threadIdx.x;
@@ -21,34 +30,32 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
     __shared__ double rec[NMPC_REC_SIZE];
     __shared__ double s_x[NX], s_u[NU], s_xn[NX], s_p[NPAR], s_yr[NY], s_W[NY];
     __shared__ double s_n[NF][3], s_t1[NF][3], s_t2[NF][3], s_r[NF][3];
-    __shared__ double s_cost[LIN_THREADS / 32];
+    __shared__ double s_cost[LIN_SR_THREADS / 32];
 
     const int ny = term ? NYE : NY;
-    for (int i = tid; i < NX; i += LIN_THREADS) {
+    for (int i = tid; i < NX; i += LIN_SR_THREADS) {
         s_x[i] = a.x[((size_t)b * (N + 1) + k) * NX + i];
         s_xn[i] = term ? 0.0 : a.x[((size_t)b * (N + 1) + k + 1) * NX + i];
     }
-    for (int i = tid; i < NU; i += LIN_THREADS) s_u[i] = term ? 0.0 : a.u[((size_t)b * N + k) * NU + i];
-    for (int i = tid; i < NPAR; i += LIN_THREADS) s_p[i] = a.p[((size_t)b * (N + 1) + k) * NPAR + i];
-    for (int i = tid; i < ny; i += LIN_THREADS) {
+    for (int i = tid; i < NU; i += LIN_SR_THREADS) s_u[i] = term ? 0.0 : a.u[((size_t)b * N + k) * NU + i];
+    for (int i = tid; i < NPAR; i += LIN_SR_THREADS) s_p[i] = a.p[((size_t)b * (N + 1) + k) * NPAR + i];
+    for (int i = tid; i < ny; i += LIN_SR_THREADS) {
         s_yr[i] = term ? a.yref_e[(size_t)b * NYE + i] : a.yref[((size_t)b * N + k) * NY + i];
         s_W[i] = term ? a.We[(size_t)b * NYE + i] : a.W[(size_t)b * NY + i];
     }
-    __syncthreads();
-
     double* S = SR + ((size_t)bl * (N + 1) + k) * SR_SZ;
     double* Dp = S + SR_D;
-
     {
+        // the model record is gathered in the same round trip as the stage inputs
         const int inst = bl * (N + 1) + k;
         const double* rp = a.rec + (size_t)(inst / REC_BLK) * NMPC_REC_SIZE * REC_BLK + (inst % REC_BLK);
-        for (int i = tid; i < NMPC_REC_SIZE; i += LIN_THREADS) rec[i] = rp[(size_t)i * REC_BLK];
-        if (tid < NF) tangent_basis(&s_p[tid * NMPC_NP_FOOT + P_NORMAL], s_n[tid], s_t1[tid], s_t2[tid]);
+        for (int i = tid; i < NMPC_REC_SIZE; i += LIN_SR_THREADS) rec[i] = rp[(size_t)i * REC_BLK];
         // the record is small: zero it, then write the structured entries
         double2 z2 = make_double2(0.0, 0.0);
-        for (int i = tid; i < SR_SZ / 2; i += LIN_THREADS) reinterpret_cast<double2*>(S)[i] = z2;
+        for (int i = tid; i < SR_SZ / 2; i += LIN_SR_THREADS) reinterpret_cast<double2*>(S)[i] = z2;
     }
     __syncthreads();
+    if (tid < NF) tangent_basis(&s_p[tid * NMPC_NP_FOOT + P_NORMAL], s_n[tid], s_t1[tid], s_t2[tid]);
 
     const double* q = s_x;
     const double* v = s_x + NQ;
@@ -66,12 +73,12 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
     const double* HV = rec + NMPC_REC_H_V;
     const double dt = a.dt;
 
-    if (tid < NF * 3) s_r[tid / 3][tid % 3] = FP[tid] - COM[tid % 3];
+    if (tid >= 32 && tid < 32 + NF * 3) s_r[(tid - 32) / 3][(tid - 32) % 3] = FP[tid - 32] - COM[(tid - 32) % 3];
     __syncthreads();
 
     // ---------------- dynamics block G = [B A b] ----------------
     if (!term) {
-        for (int i = tid; i < NQ; i += LIN_THREADS) {
+        for (int i = tid; i < NQ; i += LIN_SR_THREADS) {
             S[SR_B + i] = q[i] + dt * v[i] + 0.5 * dt * dt * acc_u[i] - s_xn[i];
             S[SR_B + NQ + i] = v[i] + dt * acc_u[i] - s_xn[NQ + i];
         }
@@ -92,7 +99,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
             S[SR_B + 2 * NQ + i] = hh[i] + dt * hd - s_xn[2 * NQ + i];
         }
         // d h+/d f
-        for (int e = tid; e < NF * 9; e += LIN_THREADS) {
+        for (int e = tid; e < NF * 9; e += LIN_SR_THREADS) {
             const int ft = e / 9, i = (e % 9) / 3, j = e % 3;
             const double act = s_p[ft * NMPC_NP_FOOT + P_ACTIVE];
             const double* r = s_r[ft];
@@ -105,7 +112,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
             S[SR_HF + 12 * (3 + i) + 3 * ft + j] = dt * act * rx;
         }
         // d (angular part)/d q = dt sum_ft act * (-[f]_x (Jp - Jc))
-        for (int e = tid; e < 3 * NQ; e += LIN_THREADS) {
+        for (int e = tid; e < 3 * NQ; e += LIN_SR_THREADS) {
             const int i = e / NQ, j = e % NQ;
             double s = 0.0;
             for (int ft = 0; ft < NF; ft++) {
@@ -131,7 +138,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
     const int ysw = term ? 36 : 48, ypos = term ? 40 : 64;
     double cost = 0.0;
     // u diagonal + gradient
-    for (int i = tid; i < NU; i += LIN_THREADS) {
+    for (int i = tid; i < NU; i += LIN_SR_THREADS) {
         double w = 0.0, e = 0.0;
         if (!term) {
             if (i >= 6 && i < NQ) { w = s_W[36 + i - 6]; e = acc_u[i] - s_yr[36 + i - 6]; }
@@ -142,7 +149,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
         cost += 0.5 * w * e * e;
     }
     // v and h diagonal + gradient
-    for (int i = tid; i < NQ + 6; i += LIN_THREADS) {
+    for (int i = tid; i < NQ + 6; i += LIN_SR_THREADS) {
         if (i < NQ) {
             const int yi = (i < 6) ? yb + 6 + i : yj + 12 + (i - 6);
             const double w = s_W[yi], e = v[i] - s_yr[yi];
@@ -155,7 +162,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
         }
     }
     // q block (dense symmetric 18x18) and q gradient
-    for (int e = tid; e < NQ * NQ; e += LIN_THREADS) {
+    for (int e = tid; e < NQ * NQ; e += LIN_SR_THREADS) {
         const int i = e / NQ, j = e % NQ;      // both triangles: the stage kernel multiplies by rows
         double s = 0.0;
         for (int ft = 0; ft < NF; ft++) {
@@ -175,7 +182,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
         }
         S[SR_QQ + NQ * i + j] = s;
     }
-    for (int j = tid; j < NQ; j += LIN_THREADS) {
+    for (int j = tid; j < NQ; j += LIN_SR_THREADS) {
         const int yi = (j < 6) ? yb + j : yj + (j - 6);
         const double e0 = q[j] - s_yr[yi];
         double g = s_W[yi] * e0;
@@ -230,7 +237,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
     }
     if (k > 0) {
         // stance kinematics rows: [n.(p - pp)], [t1.v_foot], [t2.v_foot]; state-only
-        for (int e = tid; e < NF * 3 * NQ; e += LIN_THREADS) {
+        for (int e = tid; e < NF * 3 * NQ; e += LIN_SR_THREADS) {
             const int ft = e / (3 * NQ), r = (e / NQ) % 3, j = e % NQ;
             const double* n = s_n[ft]; const double* t1 = s_t1[ft]; const double* t2 = s_t2[ft];
             const int row = GR_CNT + 3 * ft + r;
@@ -267,7 +274,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
             ml[row] = on ? 1.0 : 0.0; mu[row] = on ? 1.0 : 0.0;
         }
         // contact patch rows
-        for (int e = tid; e < NF * NQ; e += LIN_THREADS) {
+        for (int e = tid; e < NF * NQ; e += LIN_SR_THREADS) {
             const int ft = e / NQ, j = e % NQ;
             const double* pf = &s_p[ft * NMPC_NP_FOOT];
             const double rad = pf[P_RADIUS];
@@ -289,7 +296,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
             }
         }
         // centroidal consistency rows h - h_model(q, v) = 0
-        for (int e = tid; e < 6 * NQ; e += LIN_THREADS) {
+        for (int e = tid; e < 6 * NQ; e += LIN_SR_THREADS) {
             const int i = e / NQ, j = e % NQ;
             const int row = GR_CONS + i;
             S[SR_CX + 36 * (row - NGF) + j] = -HQ[i * NQ + j];
@@ -303,7 +310,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_sr_kernel(LinAr
     __syncthreads();
     if (tid == 0) {
         double c = 0.0;
-        for (int w = 0; w < LIN_THREADS / 32; w++) c += s_cost[w];
+        for (int w = 0; w < LIN_SR_THREADS / 32; w++) c += s_cost[w];
         a.cost_stage[(size_t)bl * (N + 1) + k] = c;
     }
 }
