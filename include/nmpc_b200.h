@@ -7,8 +7,18 @@
  * (acados SQP / SQP_RTI + HPIPM + BLASFEO + CasADi-generated model code).
  *
  * Every entry point names the reference interface it replaces.  All arrays are fp64, C order,
- * batch-first; pointers may be HOST or DEVICE (detected with cudaPointerGetAttributes); no torch
- * types cross this boundary.  A handle is single-caller; distinct handles are independent.
+ * batch-first; pointers may be HOST or DEVICE (cudaMemcpyDefault); no torch types cross this boundary.
+ *
+ * Streams.  A handle owns two non-blocking CUDA streams: the solve stream (nmpc_stream) that every
+ * entry point uses except nmpc_kinematics / nmpc_inverse_dynamics, which run on a private utility
+ * stream with their own staging buffer.  Nothing is ordered against the caller's streams: a DEVICE
+ * input must be complete before the call (the Python binding awaits torch's current stream), and
+ * every getter synchronises its stream before returning, so outputs are complete on return.
+ *
+ * Threads.  The reference solves on a worker thread while the control thread evaluates id_torques
+ * at 1 kHz on the same solver object (mpc.py:164,516,544-545).  The handle supports exactly that:
+ * the solve path and the utility path are serialised by two independent locks, so concurrent calls
+ * are safe and a utility call never waits for a queued solve.  Distinct handles are independent.
  * Return value: 0 on success, a negative NMPC_E* code for API misuse, a positive cudaError_t
  * for CUDA failures.  Per-problem solver outcome is reported in status[B] with acados numbering
  * (0 success, 1 NaN, 2 max-iter, 3 min-step, 4 QP failure).
@@ -71,10 +81,17 @@ typedef struct nmpc_opts {
     int32_t max_iter;         /* SQP iterations (1; 15 on the first tick, mpc.py:465-467)   */
     int32_t max_qp_iter;      /* IPM iterations per QP (6, mpc_opt.py:27)                   */
     int32_t real_time_it;     /* 1: SQP_RTI (one linearise + one QP + full step)            */
-    int32_t warm_start_qp;    /* 0 cold, 1 primal (+pi) from previous QP, 2 also lam/t      */
+    int32_t warm_start_qp;    /* acados qp_solver_warm_start = HPIPM warm_start level: 0 cold, 1 primal
+                                 iterate of the previous QP (pi, lam, t re-initialised), 2 primal and
+                                 dual ("hot": lam, t kept, clipped at 0.1 from below).  The reference's
+                                 `warm_start_qp = True` (config_abstract.py:62) maps to 1             */
     int32_t warm_start_nlp;   /* kept for API parity; the iterate always lives in the handle */
     int32_t hpipm_mode;       /* NMPC_HPIPM_*; this build implements SPEED                  */
     int32_t enable_time_opt;  /* must be 0 in this build (nu = 30)                          */
+    int32_t warm_start_first_qp; /* acados `warm_start_first_qp` (default 0): the first QP of every
+                                 nmpc_solve call is cold-started whatever warm_start_qp says       */
+    int32_t cond_pred_corr;   /* HPIPM `cond_pred_corr` (1 in every HPIPM mode): fall back to the
+                                 centring direction when the corrector predicts mu > 2 mu_aff      */
     double dt_nodes;          /* MPCOptConfig.get_dt_nodes()                                */
     double dt_min, dt_max;    /* MPCOptConfig.get_dt_bounds(); unused unless time-opt       */
     double nlp_tol;           /* SQP exit: all four residual inf-norms below (1e-1)         */
@@ -91,6 +108,8 @@ typedef struct nmpc_stats {
     double* res;         /* [B,4] NLP residual inf-norms stat, eq, ineq, comp at the last linearisation */
     double* qp_res;      /* [B,4] QP residual inf-norms at IPM exit                 */
     double* cost;        /* [B]   NLS cost at the last linearisation point          */
+    int32_t* qp_ncond;   /* [B]   IPM iterations of the last QP in which the conditional predictor-corrector
+                                  replaced the corrector direction by the centring direction */
 } nmpc_stats;
 
 /* ---- lifetime ------------------------------------------------------------------------- */
@@ -157,6 +176,13 @@ int nmpc_synchronize(nmpc_handle* h);
  * lam [B,N+1,84] (lower | upper multipliers of g).  Any pointer may be NULL. */
 int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* pi, double* lam);
 int nmpc_get_stats(nmpc_handle* h, nmpc_stats* stats);
+/* per-problem status [B] int32 of the last nmpc_solve (host or device pointer) */
+int nmpc_get_status(nmpc_handle* h, int32_t* status);
+/* Packed result rows for the one collective of the use case (Rollout_MPC.py:275,298: every rollout's
+ * plan ends up with the dataset writer): out [B, (N+1)*42 + N*30 + N + 1] = per problem x | u | dt_node | status,
+ * i.e. the 1867 numbers `parse_sol` returns at N = 25 (solver.py:403-429) plus the status, written into a DEVICE
+ * buffer by a kernel on the solve stream (no synchronisation, no host round trip): hand it to ncclAllGather. */
+int nmpc_pack_solution(nmpc_handle* h, double* out_device);
 /* QP step of the last SQP iteration: dz [B,N+1,72] ([du|dx] per node; du of node N is 0) */
 int nmpc_get_qp_step(nmpc_handle* h, double* dz);
 
@@ -190,25 +216,28 @@ int nmpc_export_qp(nmpc_handle* h, double* BAbt, double* RSQrq, double* DCt,
                    double* lg, double* ug, double* mask);
 /* Solve externally supplied OCP-QPs (same layouts as nmpc_export_qp) with the device IPM;
  * dx0 [B,42]; outputs dz [B,N+1,72], pi [B,N,42], lam [B,N+1,84], t [B,N+1,84],
- * qp_iter/qp_status [B] int32.  Cold start (warm_start 0). */
+ * qp_iter/qp_status [B] int32.  Cold start (warm_start 0).  The six stage-block arrays must be HOST
+ * pointers (they are repacked on the host; NMPC_EINVAL otherwise).  NMPC_ENOSYS if the QP lacks the
+ * structure of this OCP family (see nmpc_last_qp_path). */
 int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* RSQrq, const double* DCt,
                   const double* lg, const double* ug, const double* mask, const double* dx0,
                   double* dz, double* pi, double* lam, double* t,
                   int32_t* qp_iter, int32_t* qp_status);
 
-/* which solver nmpc_solve_qp used for the last call: 1 = the fused structured kernel (the product
- * path; taken whenever the supplied QP has the structure of this OCP family), 0 = generic dense */
+/* outcome of the structure check of the last nmpc_solve_qp call: 1 = solved by the fused structured kernel
+ * (the product path); -1 = refused with NMPC_ENOSYS because the supplied QP does not have the structure of
+ * this OCP family (this build has no generic dense QP solver) */
 int nmpc_last_qp_path(const nmpc_handle* h);
 
 /* Per-kernel device timing with CUDA events recorded on the handle's stream around the launches,
  * grouped by kind.  Replaces acados' print_time / the reference's @time_fn("solve")
  * (solver.py:396) at kernel granularity.  ms / count have NMPC_PROF_KINDS entries. */
 #define NMPC_PROF_LINEARIZE 0   /* model evaluation + stage assembly                    */
-#define NMPC_PROF_QP_STAGE 1    /* stage-parallel residuals / Gamma / barrier Hessian   */
+#define NMPC_PROF_QP_STAGE 1    /* unused (split-kernel IPM removed)                    */
 #define NMPC_PROF_RESIDUAL 2    /* NLP residual norms (full SQP only)                   */
-#define NMPC_PROF_QP_FACTOR 3   /* Riccati factorisation + affine forward sweep         */
-#define NMPC_PROF_QP_CORR 4     /* corrector solve on the stored factorisation          */
-#define NMPC_PROF_QP_OTHER 5    /* init / decide / step lengths / sigma / rhs / update  */
+#define NMPC_PROF_QP_FACTOR 3   /* unused                                               */
+#define NMPC_PROF_QP_CORR 4     /* unused                                               */
+#define NMPC_PROF_QP_OTHER 5    /* SQP full step                                        */
 #define NMPC_PROF_QP_FUSED 6    /* the fused per-OCP interior-point kernel (product path) */
 #define NMPC_PROF_KINDS 7
 int nmpc_set_profiling(nmpc_handle* h, int32_t on);

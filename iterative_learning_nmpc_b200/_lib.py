@@ -20,6 +20,7 @@ class NmpcOpts(C.Structure):
         ("n_nodes", C.c_int32), ("max_iter", C.c_int32), ("max_qp_iter", C.c_int32),
         ("real_time_it", C.c_int32), ("warm_start_qp", C.c_int32), ("warm_start_nlp", C.c_int32),
         ("hpipm_mode", C.c_int32), ("enable_time_opt", C.c_int32),
+        ("warm_start_first_qp", C.c_int32), ("cond_pred_corr", C.c_int32),
         ("dt_nodes", C.c_double), ("dt_min", C.c_double), ("dt_max", C.c_double),
         ("nlp_tol", C.c_double), ("qp_tol", C.c_double),
         ("reg_eps", C.c_double), ("reg_eps_e", C.c_double), ("mu_contact", C.c_double),
@@ -33,12 +34,13 @@ class NmpcOpts(C.Structure):
 
 class NmpcStats(C.Structure):
     _fields_ = [("sqp_iter", C.c_void_p), ("qp_iter", C.c_void_p), ("qp_status", C.c_void_p),
-                ("res", C.c_void_p), ("qp_res", C.c_void_p), ("cost", C.c_void_p)]
+                ("res", C.c_void_p), ("qp_res", C.c_void_p), ("cost", C.c_void_p),
+                ("qp_ncond", C.c_void_p)]
 
 
 def default_opts(**kw) -> NmpcOpts:
     o = NmpcOpts(n_nodes=25, max_iter=1, max_qp_iter=6, real_time_it=0, warm_start_qp=1,
-                 warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, dt_nodes=0.04, dt_min=0.02,
+                 warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, warm_start_first_qp=0, cond_pred_corr=1, dt_nodes=0.04, dt_min=0.02,
                  dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8)
     for k, v in kw.items():
         if not hasattr(o, k):
@@ -71,6 +73,8 @@ _SIGS = {
     "nmpc_synchronize": (C.c_int, [C.c_void_p]),
     "nmpc_get_solution": (C.c_int, [C.c_void_p] + [C.c_void_p] * 4),
     "nmpc_get_stats": (C.c_int, [C.c_void_p, C.POINTER(NmpcStats)]),
+    "nmpc_get_status": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nmpc_pack_solution": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_get_qp_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 3),
     "nmpc_inverse_dynamics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),

@@ -2,8 +2,8 @@
 
 Replaces the CasADi-generated C that acados links for the reference's dynamics / cost /
 constraint functions.  One header, two consumers:
-`oracle/` (plain C, the checker) and `csrc/` (CUDA device code, the product); both are written by
-this script from the same URDF so they cannot drift apart.
+`csrc/` (CUDA device code, the product) and `oracle/` (plain C, the checker, which includes the
+same file by path: there is exactly one copy in the tree).
 
 usage: python -m iterative_learning_nmpc_b200.codegen.emit [--urdf PATH] [--feet FL_foot ...]
 """
@@ -182,7 +182,6 @@ def main() -> None:
     ap.add_argument("--feet", nargs="*", default=DEFAULT_FEET)
     ap.add_argument("--out", nargs="*", default=[
         os.path.join(PKG, "csrc", "nmpc_gen_model.h"),
-        os.path.join(REPO, "oracle", "nmpc_gen_model.h"),
     ])
     args = ap.parse_args()
     text, meta = generate(args.urdf, args.feet)

@@ -26,9 +26,25 @@ def _i32(a, shape):
     return np.ascontiguousarray(np.broadcast_to(np.asarray(a), shape), dtype=np.int32)
 
 
+def _order_after_torch(solver, *arrays):
+    """Stream contract of the C ABI (include/nmpc_b200.h): the handle works on its own non-blocking stream, so a
+    DEVICE buffer handed in must be complete before the call.  For CUDA tensors this is arranged here: the work queued
+    on torch's current stream is awaited once per call (a host-side wait on an event; outputs need nothing, every
+    getter synchronises the handle's stream before it returns)."""
+    for a in arrays:
+        if a is not None and hasattr(a, "is_cuda") and a.is_cuda:
+            import torch
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(a.device))
+            ev.synchronize()
+            return
+
+
 class NmpcSolver:
     """Batch of B quadruped OCPs resident on one B200.  Methods mirror include/nmpc_b200.h; array
-    arguments may be numpy arrays (host) or fp64 torch tensors (host or CUDA)."""
+    arguments may be numpy arrays (host) or fp64 torch tensors (host or CUDA).  A solver object may be shared by the
+    two threads of `LocomotionMPC` (solve worker + control loop): the library serialises the solve path and the
+    utility path (kinematics / inverse dynamics) with separate locks, streams and staging buffers."""
 
     def __init__(self, batch: int, opts: Optional[NmpcOpts] = None, device: int = 0):
         self.lib = L.load_library()
@@ -59,17 +75,20 @@ class NmpcSolver:
     # -- problem data -------------------------------------------------------------------
     def set_x0(self, qv):
         a = _f64(qv, (self.B, 36))
+        _order_after_torch(self, a)
         check(self.lib.nmpc_set_x0(self._h, ptr(a)), "nmpc_set_x0")
         self.synchronize_if_host(a)
 
     def set_x0_full(self, x0):
         a = _f64(x0, (self.B, NX))
+        _order_after_torch(self, a)
         check(self.lib.nmpc_set_x0_full(self._h, ptr(a)), "nmpc_set_x0_full")
         self.synchronize_if_host(a)
 
     def set_yref(self, yref, yref_e):
         a = _f64(yref, (self.B, self.N, NY))
         b = _f64(yref_e, (self.B, NYE))
+        _order_after_torch(self, a, b)
         check(self.lib.nmpc_set_yref(self._h, ptr(a), ptr(b)), "nmpc_set_yref")
         self.synchronize_if_host(a)
 
@@ -78,11 +97,13 @@ class NmpcSolver:
         per = int(W.ndim == 2)
         a = _f64(W, (self.B, NY) if per else (NY,))
         b = _f64(W_e, (self.B, NYE) if per else (NYE,))
+        _order_after_torch(self, a, b)
         check(self.lib.nmpc_set_weights(self._h, ptr(a), ptr(b), per), "nmpc_set_weights")
         self.synchronize_if_host(a)
 
     def set_params(self, p):
         a = _f64(p, (self.B, self.N + 1, NP))
+        _order_after_torch(self, a)
         check(self.lib.nmpc_set_params(self._h, ptr(a)), "nmpc_set_params")
         self.synchronize_if_host(a)
 
@@ -107,6 +128,7 @@ class NmpcSolver:
         peak = None if swing_peak is None else np.ascontiguousarray(swing_peak, dtype=np.int8).reshape(B, 4, N1)
         loc = None if cnt_locations is None else _f64(cnt_locations, (B, 4, N1, 3))
         gain = np.ascontiguousarray(p_gain, dtype=np.float64).reshape(4)
+        _order_after_torch(self, ref, ref_e, loc)
         check(self.lib.nmpc_init_tick(self._h, ptr(ref), ptr(ref_e), ptr(jr), jpp, ptr(sh), hpp, ptr(cnt), ptr(peak),
                                       ptr(loc), ptr(gain), float(cnt_radius), float(height_offset), int(bool(restrict_cnt))),
               "nmpc_init_tick")
@@ -123,17 +145,20 @@ class NmpcSolver:
 
     def pin_stance_feet(self, i_node):
         a = _i32(i_node, (self.B,))
+        _order_after_torch(self, a)
         check(self.lib.nmpc_pin_stance_feet(self._h, ptr(a)), "nmpc_pin_stance_feet")
         self.synchronize_if_host(a)
 
     def set_guess(self, x=None, u=None):
         a = None if x is None else _f64(x, (self.B, self.N + 1, NX))
         b = None if u is None else _f64(u, (self.B, self.N, NU))
+        _order_after_torch(self, a, b)
         check(self.lib.nmpc_set_guess(self._h, ptr(a), ptr(b)), "nmpc_set_guess")
         self.synchronize_if_host(a if a is not None else b)
 
     def shift_warm_start(self, start_node, repeat_last: bool = False):
         a = _i32(start_node, (self.B,))
+        _order_after_torch(self, a)
         check(self.lib.nmpc_shift_warm_start(self._h, ptr(a), int(repeat_last)), "nmpc_shift_warm_start")
         self.synchronize_if_host(a)
 
@@ -170,12 +195,40 @@ class NmpcSolver:
     def get_solution_into(self, x=None, u=None, pi=None, lam=None):
         check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
 
+    def get_status_into(self, status):
+        """Per-problem status of the last solve into an int32 array / tensor (host or device)."""
+        check(self.lib.nmpc_get_status(self._h, ptr(status)), "nmpc_get_status")
+
+    def solve_status(self) -> np.ndarray:
+        st = np.zeros(self.B, dtype=np.int32)
+        self.get_status_into(st)
+        return st
+
+    def pack_solution(self, out):
+        """Packed result rows [B, (N+1)*42 + N*31 + 1] (x | u | dt_node | status) into a CUDA fp64 tensor, on the
+        solver's stream and without synchronising: the send buffer of the gather to the dataset-writer rank."""
+        assert out.is_cuda and out.is_contiguous() and out.numel() == self.B * self.sol_row
+        check(self.lib.nmpc_pack_solution(self._h, ptr(out)), "nmpc_pack_solution")
+
+    @property
+    def sol_row(self) -> int:
+        return (self.N + 1) * NX + self.N * (NU + 1) + 1
+
+    def plan_torques_into(self, n_interp: int, step0: int, n_steps: int, kp: float = 20.0, kd: float = 1.75,
+                          q_plan=None, v_plan=None, tau_ff=None, tau=None, action=None, qv_meas=None):
+        """`plan_torques` with caller-owned outputs (host arrays or CUDA tensors; any may be None)."""
+        _order_after_torch(self, qv_meas)
+        check(self.lib.nmpc_plan_torques(self._h, ptr(qv_meas), int(n_interp), int(step0), int(n_steps), float(kp),
+                                         float(kd), ptr(q_plan), ptr(v_plan), ptr(tau_ff), ptr(tau), ptr(action)),
+              "nmpc_plan_torques")
+
     def get_stats(self) -> dict:
         B = self.B
         out = dict(sqp_iter=np.zeros(B, np.int32), qp_iter=np.zeros(B, np.int32),
                    qp_status=np.zeros(B, np.int32), res=np.zeros((B, 4)), qp_res=np.zeros((B, 4)),
-                   cost=np.zeros(B))
-        st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost")])
+                   cost=np.zeros(B), qp_ncond=np.zeros(B, np.int32))
+        st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost",
+                                                      "qp_ncond")])
         check(self.lib.nmpc_get_stats(self._h, C.byref(st)), "nmpc_get_stats")
         return out
 
@@ -186,6 +239,7 @@ class NmpcSolver:
 
     def kinematics(self, qv):
         a = _f64(qv, (-1, 36))
+        _order_after_torch(self, a)
         n = a.shape[0]
         feet, com, hg = np.zeros((n, 4, 3)), np.zeros((n, 3)), np.zeros((n, 6))
         check(self.lib.nmpc_kinematics(self._h, ptr(a), n, ptr(feet), ptr(com), ptr(hg)), "nmpc_kinematics")
@@ -200,6 +254,7 @@ class NmpcSolver:
         a = _f64(qva, (-1, 54))
         n = a.shape[0]
         b = _f64(f, (n, 12))
+        _order_after_torch(self, a, b)
         tau = np.zeros((n, 12))
         check(self.lib.nmpc_inverse_dynamics(self._h, ptr(a), ptr(b), n, ptr(tau)), "nmpc_inverse_dynamics")
         return tau
@@ -214,6 +269,7 @@ class NmpcSolver:
         out = {k: np.zeros((B, n_steps, w)) for k, w in
                (("q_plan", 18), ("v_plan", 18), ("tau_ff", 12), ("tau", 12), ("action", 12))}
         m = None if qv_meas is None else _f64(qv_meas, (B, n_steps, 36))
+        _order_after_torch(self, m)
         check(self.lib.nmpc_plan_torques(self._h, None if m is None else ptr(m), int(n_interp), int(step0), n_steps,
                                          float(kp), float(kd), ptr(out["q_plan"]), ptr(out["v_plan"]),
                                          ptr(out["tau_ff"]), ptr(out["tau"]), ptr(out["action"])), "nmpc_plan_torques")
@@ -230,7 +286,11 @@ class NmpcSolver:
         return out
 
     def solve_qp(self, qp: dict, dx0) -> dict:
+        """Solve externally supplied OCP-QPs (host arrays; the library repacks them on the host and refuses device
+        pointers with NMPC_EINVAL).  QPs without the structure of this OCP family raise (NMPC_ENOSYS)."""
         B, N = self.B, self.N
+        if any(hasattr(qp[k], "is_cuda") and qp[k].is_cuda for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")):
+            raise ValueError("nmpc_solve_qp takes host arrays")
         arrs = [_f64(qp[k], s) for k, s in (("BAbt", (B, N, NZ + 1, NX)), ("RSQrq", (B, N + 1, NZ + 1, NZ)),
                                              ("DCt", (B, N + 1, NZ, NG)), ("lg", (B, N + 1, NG)),
                                              ("ug", (B, N + 1, NG)), ("mask", (B, N + 1, 2 * NG)))]
@@ -244,14 +304,14 @@ class NmpcSolver:
 
     @property
     def last_qp_path(self) -> str:
-        return {1: "fused", 0: "dense"}.get(int(self.lib.nmpc_last_qp_path(self._h)), "?")
+        return {1: "fused", -1: "refused"}.get(int(self.lib.nmpc_last_qp_path(self._h)), "?")
 
     def set_profiling(self, on: bool = True):
         check(self.lib.nmpc_set_profiling(self._h, int(on)), "nmpc_set_profiling")
 
     def kernel_times(self) -> dict:
         """{kernel: (ms, launches)} accumulated since the last call (CUDA events, handle stream)."""
-        kinds = ("linearize", "qp_stage", "residual", "qp_factor", "qp_corr", "qp_other", "qp_fused")
+        kinds = ("linearize", "unused1", "residual", "unused3", "unused4", "qp_other", "qp_fused")
         ms = np.zeros(len(kinds))
         cnt = np.zeros(len(kinds), dtype=np.int64)
         check(self.lib.nmpc_get_kernel_times(self._h, ptr(ms), ptr(cnt)), "nmpc_get_kernel_times")

@@ -6,11 +6,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "nmpc_common.cuh"
 #include "nmpc_linearize.cuh"
-#include "nmpc_qp_ipm.cuh"
+#include "nmpc_qp_layout.cuh"
 #include "nmpc_qp_fused.cuh"
 #include "nmpc_sqp.cuh"
 #include "nmpc_linearize_sr.cuh"
@@ -27,22 +28,30 @@ struct nmpc_handle {
     nmpc_opts o;
     int B, N, device, Bc;        // Bc: problems per chunk of QP workspace
     cudaStream_t stream;
-    long long launches;
+    long long launches;      // kernels launched on `stream` (guarded by mtx)
+    long long ulaunches;     // kernels launched on `ustream` (guarded by umtx)
     // iterate and problem data [B]
     double *x, *u, *pi, *lam, *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;
     double *res, *qp_res, *cost;
-    unsigned long long *res_acc, *qp_res_acc, *qp_alpha;
-    int32_t *status, *done, *sqp_iter, *qp_iter, *qp_status, *itmp, *qp_done, *qp_nc;
-    double *qp_mu_part, *qp_mu, *qp_sigma_mu;
+    unsigned long long *res_acc;
+    int32_t *status, *done, *sqp_iter, *qp_iter, *qp_status, *qp_ncond, *itmp;
     // QP workspace [Bc]
-    double *G, *M, *C, *D, *Ht, *L, *vec, *cost_stage, *rec;
+    double *vec, *cost_stage, *rec;
     double *SR, *FR;             // structured stage / factor records of the fused QP path
+    double *G, *M, *C, *D;       // dense stage blocks: diagnostics only (nmpc_export_qp / nmpc_solve_qp), allocated on first use
     int32_t* sr_flag;
-    int last_qp_path;            // nmpc_solve_qp: 1 fused, 0 generic dense
-    int dense_qp;                // NMPC_DENSE_QP=1: generic dense kernels (nmpc_qp_ipm.cuh) instead of the fused path
-    double* scratch;             // staging for kinematics / dx0
+    int last_qp_path;            // nmpc_solve_qp: 1 fused (the only solver), -1 refused (QP without the OCP's structure)
+    double* scratch;             // staging of the solve path (init tick, x0, dx0, plan -> torque)
     size_t scratch_bytes;
+    // Utility calls that do not touch the solver state (nmpc_kinematics, nmpc_inverse_dynamics) have their own
+    // stream, staging buffer and lock: LocomotionMPC's control thread evaluates id_torques at 1 kHz while the
+    // worker thread's solve is queued on `stream` (mpc.py:164,516,544-545); neither waits for the other.
+    cudaStream_t ustream;
+    double* uscratch;
+    size_t uscratch_bytes;
+    std::mutex* mtx;             // solve path: every entry point that uses `stream` / `scratch` / the iterate
+    std::mutex* umtx;            // utility path
     // optional per-kernel timing with CUDA events on the handle's stream (bench.py roofline)
     int profiling;
     std::vector<cudaEvent_t>* ev;    // start/stop pairs
@@ -70,15 +79,21 @@ static void prof_end(nmpc_handle* h)
     h->ev_used += 2;
 }
 
-static int ensure_scratch(nmpc_handle* h, size_t bytes)
+// grows a staging buffer; the caller holds the lock that guards it, and the stream that uses it is drained first so
+// that no queued kernel or copy still refers to the old allocation
+static int ensure_buf(cudaStream_t st, double** buf, size_t* have, size_t bytes)
 {
-    if (bytes <= h->scratch_bytes) return 0;
-    if (h->scratch) cudaFree(h->scratch);
-    h->scratch = nullptr; h->scratch_bytes = 0;
-    CK(cudaMalloc(&h->scratch, bytes));
-    h->scratch_bytes = bytes;
+    if (bytes <= *have) return 0;
+    if (*buf) { CK(cudaStreamSynchronize(st)); cudaFree(*buf); }
+    *buf = nullptr; *have = 0;
+    CK(cudaMalloc(buf, bytes));
+    *have = bytes;
     return 0;
 }
+static int ensure_scratch(nmpc_handle* h, size_t bytes) { return ensure_buf(h->stream, &h->scratch, &h->scratch_bytes, bytes); }
+static int ensure_uscratch(nmpc_handle* h, size_t bytes) { return ensure_buf(h->ustream, &h->uscratch, &h->uscratch_bytes, bytes); }
+#define LOCK(h) std::lock_guard<std::mutex> lock_(*(h)->mtx)
+#define ULOCK(h) std::lock_guard<std::mutex> ulock_(*(h)->umtx)
 
 template <typename T>
 static cudaError_t dalloc(T** p, size_t n)
@@ -88,7 +103,7 @@ static cudaError_t dalloc(T** p, size_t n)
     return e;
 }
 
-extern "C" const char* nmpc_version(void) { return "nmpc_b200 0.1 (sm_100a, fp64, nx=42 nu=30 ng=42)"; }
+extern "C" const char* nmpc_version(void) { return "nmpc_b200 0.2 (sm_100a, fp64, nx=42 nu=30 ng=42)"; }
 
 extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t device, int32_t* err)
 {
@@ -106,35 +121,26 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     nmpc_handle* h = (nmpc_handle*)calloc(1, sizeof(nmpc_handle));
     h->o = *o; h->B = batch; h->N = o->n_nodes; h->device = device;
     h->ev = new std::vector<cudaEvent_t>(); h->ev_kind = new std::vector<int>();
+    h->mtx = new std::mutex(); h->umtx = new std::mutex();
     int cap = 4096;
     if (const char* s = getenv("NMPC_CHUNK")) { int v = atoi(s); if (v > 0) cap = v; }
     h->Bc = batch < cap ? batch : cap;
     const size_t B = batch, N = h->N, Bc = h->Bc;
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->ustream, cudaStreamNonBlocking);
 #define A_(ptr, n) if (e == cudaSuccess) e = dalloc(&h->ptr, (n))
     A_(x, B * (N + 1) * NX); A_(u, B * N * NU); A_(pi, B * N * NX); A_(lam, B * (N + 1) * 2 * NG);
     A_(x0, B * NX); A_(p, B * (N + 1) * NPAR); A_(yref, B * N * NY); A_(yref_e, B * NYE);
     A_(W, B * NY); A_(We, B * NYE);
     A_(qz, B * (N + 1) * NZ); A_(qpi, B * N * NX); A_(qlam, B * (N + 1) * 2 * NG); A_(qt, B * (N + 1) * 2 * NG);
     A_(res, B * 4); A_(qp_res, B * 4); A_(cost, B); A_(res_acc, B * 4);
-    A_(status, B); A_(done, B); A_(sqp_iter, B); A_(qp_iter, B); A_(qp_status, B); A_(itmp, B);
-    A_(G, Bc * N * G_SZ); A_(M, Bc * (N + 1) * M_SZ); A_(C, Bc * (N + 1) * C_SZ); A_(D, Bc * (N + 1) * D_SZ);
-    A_(qp_res_acc, B * 4); A_(qp_alpha, B * 2); A_(qp_done, B); A_(qp_nc, B);
-    A_(qp_mu_part, B * (N + 1)); A_(qp_mu, B); A_(qp_sigma_mu, B);
-    A_(Ht, Bc * (N + 1) * LP_SZ);
-    A_(L, Bc * (N + 1) * LP_SZ); A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
+    A_(status, B); A_(done, B); A_(sqp_iter, B); A_(qp_iter, B); A_(qp_status, B); A_(qp_ncond, B); A_(itmp, B);
+    A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
     A_(rec, ((Bc * (N + 1) + REC_BLK - 1) / REC_BLK) * NMPC_REC_SIZE * REC_BLK);
     A_(SR, Bc * (N + 1) * SR_SZ); A_(FR, Bc * (N + 1) * FR_SZ); A_(sr_flag, 1);
 #undef A_
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM_BYTES);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K3_SMEM_BYTES);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_corr_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM_BYTES);
-    if (e == cudaSuccess)
         e = cudaFuncSetAttribute(nmpc_qp_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
-    if (const char* s = getenv("NMPC_DENSE_QP")) h->dense_qp = atoi(s) != 0;
     if (e != cudaSuccess) {
         *err = (e == cudaErrorMemoryAllocation) ? NMPC_ENOMEM : (int)e;
         nmpc_destroy(h);
@@ -149,13 +155,15 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->ustream) cudaStreamSynchronize(h->ustream);
     void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
                     h->qlam, h->qt, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
-                    h->qp_iter, h->qp_status, h->itmp, h->G, h->M, h->C, h->D, h->Ht, h->L, h->vec, h->cost_stage,
-                    h->rec, h->scratch, h->SR, h->FR, h->sr_flag, h->qp_res_acc, h->qp_alpha, h->qp_done, h->qp_nc, h->qp_mu_part,
-                    h->qp_mu, h->qp_sigma_mu};
+                    h->qp_iter, h->qp_status, h->qp_ncond, h->itmp, h->G, h->M, h->C, h->D, h->vec, h->cost_stage,
+                    h->rec, h->scratch, h->uscratch, h->SR, h->FR, h->sr_flag};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->ustream) cudaStreamDestroy(h->ustream);
+    delete h->mtx; delete h->umtx;
     if (h->ev) { for (cudaEvent_t e : *h->ev) cudaEventDestroy(e); delete h->ev; }
     delete h->ev_kind;
     free(h);
@@ -164,6 +172,7 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
 extern "C" int nmpc_set_opts(nmpc_handle* h, const nmpc_opts* o)
 {
     if (!h || !o || o->n_nodes != h->N) return NMPC_EINVAL;
+    LOCK(h);
     if (o->enable_time_opt) return NMPC_ENOSYS;
     h->o = *o;
     return 0;
@@ -184,7 +193,7 @@ extern "C" int nmpc_stream(const nmpc_handle* h, void** s)
     return 0;
 }
 
-extern "C" int64_t nmpc_launch_count(const nmpc_handle* h) { return h ? h->launches : 0; }
+extern "C" int64_t nmpc_launch_count(const nmpc_handle* h) { return h ? h->launches + h->ulaunches : 0; }
 
 static int d2h(nmpc_handle* h, void* dst, const void* src, size_t bytes);
 static int h2d(nmpc_handle* h, void* dst, const void* src, size_t bytes)
@@ -197,6 +206,7 @@ static int h2d(nmpc_handle* h, void* dst, const void* src, size_t bytes)
 extern "C" int nmpc_set_x0(nmpc_handle* h, const double* qv)
 {
     if (!h || !qv) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     if (int r = ensure_scratch(h, (size_t)h->B * 36 * 8)) return r;
     CK(cudaMemcpyAsync(h->scratch, qv, (size_t)h->B * 36 * 8, cudaMemcpyDefault, h->stream));
@@ -208,6 +218,7 @@ extern "C" int nmpc_set_x0(nmpc_handle* h, const double* qv)
 extern "C" int nmpc_set_x0_full(nmpc_handle* h, const double* x0)
 {
     if (!h || !x0) return NMPC_EINVAL;
+    LOCK(h);
     if (int r = h2d(h, h->x0, x0, (size_t)h->B * NX * 8)) return r;
     nmpc_copy_x0_kernel<<<(h->B * NX + 127) / 128, 128, 0, h->stream>>>(h->B, h->N, h->x0, h->x);
     h->launches++;
@@ -217,6 +228,7 @@ extern "C" int nmpc_set_x0_full(nmpc_handle* h, const double* x0)
 extern "C" int nmpc_set_yref(nmpc_handle* h, const double* yref, const double* yref_e)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     if (yref) if (int r = h2d(h, h->yref, yref, (size_t)h->B * h->N * NY * 8)) return r;
     if (yref_e) if (int r = h2d(h, h->yref_e, yref_e, (size_t)h->B * NYE * 8)) return r;
     return 0;
@@ -225,6 +237,7 @@ extern "C" int nmpc_set_yref(nmpc_handle* h, const double* yref, const double* y
 extern "C" int nmpc_set_weights(nmpc_handle* h, const double* W, const double* We, int32_t per_problem)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     if (per_problem) {
         if (W) if (int r = h2d(h, h->W, W, (size_t)h->B * NY * 8)) return r;
         if (We) if (int r = h2d(h, h->We, We, (size_t)h->B * NYE * 8)) return r;
@@ -252,6 +265,7 @@ extern "C" int nmpc_set_weights(nmpc_handle* h, const double* W, const double* W
 extern "C" int nmpc_set_params(nmpc_handle* h, const double* p)
 {
     if (!h || !p) return NMPC_EINVAL;
+    LOCK(h);
     return h2d(h, h->p, p, (size_t)h->B * (h->N + 1) * NPAR * 8);
 }
 
@@ -263,6 +277,7 @@ extern "C" int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const doub
 {
     if (!h || !base_ref || !joint_ref || !step_height || !cnt_sequence || !p_gain) return NMPC_EINVAL;
     if (restrict_cnt && !cnt_locations) return NMPC_EINVAL;           // "Contact plan not provided" (solver.py:377)
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t B = h->B, N1 = h->N + 1;
     const size_t n_ref = B * 12, n_jr = joint_per_problem ? B * 12 : 12, n_sh = height_per_problem ? B : 1;
@@ -300,6 +315,7 @@ extern "C" int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const doub
 extern "C" int nmpc_cold_guess(nmpc_handle* h)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     nmpc_cold_guess_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->x0, h->p, h->x, h->u);
     h->launches++;
@@ -310,6 +326,7 @@ extern "C" int nmpc_cold_guess(nmpc_handle* h)
 extern "C" int nmpc_get_problem_data(nmpc_handle* h, double* p, double* yref, double* yref_e, double* x0)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t B = h->B, N = h->N;
     if (p) if (int r = d2h(h, p, h->p, B * (N + 1) * NPAR * 8)) return r;
@@ -323,6 +340,7 @@ extern "C" int nmpc_get_problem_data(nmpc_handle* h, double* p, double* yref, do
 extern "C" int nmpc_pin_stance_feet(nmpc_handle* h, const int32_t* i_node)
 {
     if (!h || !i_node) return NMPC_EINVAL;
+    LOCK(h);
     if (int r = h2d(h, h->itmp, i_node, (size_t)h->B * 4)) return r;
     nmpc_pin_feet_kernel<<<(h->B + 63) / 64, 64, 0, h->stream>>>(h->B, h->N, h->x0, h->itmp, h->p);
     h->launches++;
@@ -332,6 +350,7 @@ extern "C" int nmpc_pin_stance_feet(nmpc_handle* h, const int32_t* i_node)
 extern "C" int nmpc_set_guess(nmpc_handle* h, const double* x, const double* u)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     if (x) if (int r = h2d(h, h->x, x, (size_t)h->B * (h->N + 1) * NX * 8)) return r;
     if (u) if (int r = h2d(h, h->u, u, (size_t)h->B * h->N * NU * 8)) return r;
     return 0;
@@ -340,6 +359,7 @@ extern "C" int nmpc_set_guess(nmpc_handle* h, const double* x, const double* u)
 extern "C" int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, int32_t repeat_last)
 {
     if (!h || !start_node) return NMPC_EINVAL;
+    LOCK(h);
     if (int r = h2d(h, h->itmp, start_node, (size_t)h->B * 4)) return r;
     nmpc_shift_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->itmp, repeat_last, h->x, h->u, h->pi, h->lam);
     h->launches++;
@@ -349,6 +369,7 @@ extern "C" int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, 
 extern "C" int nmpc_reset_duals(nmpc_handle* h)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t B = h->B, N = h->N;
     CK(cudaMemsetAsync(h->pi, 0, B * N * NX * 8, h->stream));
@@ -363,6 +384,20 @@ extern "C" int nmpc_reset_duals(nmpc_handle* h)
 // ---------------------------------------------------------------------------------------------
 // solve
 // ---------------------------------------------------------------------------------------------
+// dense stage blocks (3.6 MB per OCP of the chunk): only the diagnostics below touch them, so they are
+// allocated on the first nmpc_export_qp / nmpc_solve_qp call and not by nmpc_create
+static int ensure_dense(nmpc_handle* h)
+{
+    if (h->G) return 0;
+    const size_t Bc = h->Bc, N = h->N;
+    cudaError_t e = dalloc(&h->G, Bc * N * G_SZ);
+    if (e == cudaSuccess) e = dalloc(&h->M, Bc * (N + 1) * M_SZ);
+    if (e == cudaSuccess) e = dalloc(&h->C, Bc * (N + 1) * C_SZ);
+    if (e == cudaSuccess) e = dalloc(&h->D, Bc * (N + 1) * D_SZ);
+    if (e != cudaSuccess) return e == cudaErrorMemoryAllocation ? NMPC_ENOMEM : (int)e;
+    return 0;
+}
+
 static LinArgs lin_args(nmpc_handle* h, int b0)
 {
     LinArgs a;
@@ -402,89 +437,27 @@ static void launch_linearize_sr(nmpc_handle* h, int b0, int Bc)
 static QpArgs qp_args(nmpc_handle* h, int b0)
 {
     QpArgs a;
-    a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.Ht = h->Ht; a.L = h->L; a.vec = h->vec;
     a.qz = h->qz; a.qpi = h->qpi; a.qlam = h->qlam; a.qt = h->qt;
-    a.res_acc = h->qp_res_acc; a.alpha = h->qp_alpha; a.nc = h->qp_nc; a.mu_part = h->qp_mu_part;
-    a.mu = h->qp_mu; a.sigma_mu = h->qp_sigma_mu; a.qp_done = h->qp_done;
-    a.qp_iter = h->qp_iter; a.qp_status = h->qp_status; a.qp_res = h->qp_res;
+    a.qp_iter = h->qp_iter; a.qp_status = h->qp_status; a.qp_ncond = h->qp_ncond; a.qp_res = h->qp_res;
     a.dx0_ext = nullptr; a.x0 = h->x0; a.x = h->x; a.u = h->u; a.pi = h->pi; a.lam = h->lam;
     a.sqp_done = h->done; a.sqp_iter = h->sqp_iter;
-    a.N = h->N; a.b0 = b0; a.max_iter = h->o.max_qp_iter; a.warm = h->o.warm_start_qp; a.it = 0; a.last = 0;
+    a.N = h->N; a.b0 = b0; a.max_iter = h->o.max_qp_iter; a.warm = h->o.warm_start_qp;
+    a.cond_pred_corr = h->o.cond_pred_corr;
     a.tol = h->o.qp_tol;
     return a;
 }
 
-// One OCP-QP solve for the problems [b0, b0+Bc): the interior-point iteration as a sequence of
-// stage-parallel and per-problem kernels on the handle's stream (no host synchronisation; problems
-// that have finished are skipped through qp_done).
-static void run_qp(nmpc_handle* h, QpArgs a, int Bc, bool apply)
+// The product path: ONE fused kernel per QP (nmpc_qp_fused.cuh) on the stage records the linearisation wrote.
+static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply)
 {
     const int N = h->N;
     cudaStream_t s = h->stream;
-    const dim3 gs(N + 1, Bc);
-    const int tb = (Bc + 127) / 128;
-    prof_begin(h, NMPC_PROF_QP_OTHER);
-    nmpc_qp_init_kernel<<<Bc, 128, 0, s>>>(a);
-    prof_end(h);
-    h->launches++;
-    for (int it = 0; it <= a.max_iter; it++) {
-        a.it = it; a.last = (it >= a.max_iter);
-        if (it > 0) {
-            prof_begin(h, NMPC_PROF_QP_OTHER);
-            nmpc_qp_update_kernel<<<gs, 128, 0, s>>>(a);
-            prof_end(h);
-            h->launches++;
-        }
-        prof_begin(h, NMPC_PROF_QP_STAGE);
-        nmpc_qp_stage_kernel<<<gs, QP_THREADS, K1_SMEM_BYTES, s>>>(a);
-        prof_end(h);
-        prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_decide_kernel<<<tb, 128, 0, s>>>(a, Bc);
-        prof_end(h);
-        h->launches += 2;
-        if (a.last) break;
-        prof_begin(h, NMPC_PROF_QP_FACTOR);
-        nmpc_qp_factor_kernel<<<Bc, QP_THREADS, K3_SMEM_BYTES, s>>>(a);
-        prof_end(h);
-        prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_step_kernel<<<gs, 128, 0, s>>>(a);
-        nmpc_qp_sigma_kernel<<<Bc, QP_THREADS, 0, s>>>(a);
-        nmpc_qp_corr_rhs_kernel<<<gs, 96, 0, s>>>(a);
-        prof_end(h);
-        prof_begin(h, NMPC_PROF_QP_CORR);
-        nmpc_qp_corr_solve_kernel<<<Bc, QP_THREADS, K7_SMEM_BYTES, s>>>(a);
-        prof_end(h);
-        prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_step_kernel<<<gs, 128, 0, s>>>(a);
-        prof_end(h);
-        h->launches += 6;
-    }
-    if (apply) {
-        prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_apply_kernel<<<Bc, 128, 0, s>>>(a);
-        prof_end(h);
-        h->launches++;
-    }
-}
-
-// The product path: dense stage blocks -> stage records, then ONE fused kernel per QP (nmpc_qp_fused.cuh).
-static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, bool from_dense)
-{
-    const int N = h->N;
-    cudaStream_t s = h->stream;
-    if (from_dense) {              // externally supplied dense QP: extract the stage records first
-        SrArgs sa;
-        sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
-        sa.done = a.sqp_done; sa.N = N; sa.b0 = a.b0; sa.check = 0; sa.dt = h->o.dt_nodes;
-        prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, s>>>(sa);
-        prof_end(h);
-        h->launches++;
-    }
     FqArgs f;
     f.SR = h->SR; f.FR = h->FR; f.vec = h->vec; f.qz = a.qz; f.qpi = a.qpi; f.qlam = a.qlam; f.qt = a.qt;
-    f.qp_iter = a.qp_iter; f.qp_status = a.qp_status; f.qp_res = a.qp_res; f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
+    f.qp_iter = a.qp_iter; f.qp_status = a.qp_status; f.qp_ncond = a.qp_ncond; f.qp_res = a.qp_res;
+    f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
     f.x = a.x; f.sqp_done = a.sqp_done; f.N = N; f.b0 = a.b0; f.max_iter = a.max_iter; f.warm = a.warm;
+    f.cond_pred_corr = a.cond_pred_corr;
     f.tol = a.tol; f.dt = h->o.dt_nodes; f.c2 = 0.5 * h->o.dt_nodes * h->o.dt_nodes;
     prof_begin(h, NMPC_PROF_QP_FUSED);
     nmpc_qp_fused_kernel<<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
@@ -502,34 +475,27 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
 {
     if (!h) return NMPC_EINVAL;
     if (h->o.hpipm_mode != NMPC_HPIPM_SPEED) return NMPC_ENOSYS;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const int B = h->B, N = h->N;
     const int rti = h->o.real_time_it != 0;
     const int max_iter = rti ? 1 : h->o.max_iter;
     nmpc_sqp_begin_kernel<<<(B + 127) / 128, 128, 0, h->stream>>>(B, rti, h->status, h->done, h->sqp_iter,
-                                                                 h->qp_iter, h->qp_status, h->res_acc);
+                                                                 h->qp_iter, h->qp_status, h->qp_ncond, h->res_acc);
     h->launches++;
     for (int b0 = 0; b0 < B; b0 += h->Bc) {
         const int Bc = (B - b0 < h->Bc) ? (B - b0) : h->Bc;
         for (int it = 0; it <= max_iter; it++) {
             if (rti && it == 1) break;
             prof_begin(h, NMPC_PROF_LINEARIZE);
-            if (h->dense_qp) launch_linearize(h, b0, Bc);
-            else launch_linearize_sr(h, b0, Bc);
+            launch_linearize_sr(h, b0, Bc);
             prof_end(h);
             if (!rti) {
                 prof_begin(h, NMPC_PROF_RESIDUAL);
-                if (h->dense_qp) {
-                    ResArgs ra;
-                    ra.G = h->G; ra.M = h->M; ra.C = h->C; ra.D = h->D; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi;
-                    ra.lam = h->lam; ra.res_acc = h->res_acc; ra.done = h->done; ra.N = N; ra.b0 = b0;
-                    nmpc_residual_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
-                } else {
-                    ResSrArgs ra;
-                    ra.SR = h->SR; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi; ra.lam = h->lam; ra.res_acc = h->res_acc;
-                    ra.done = h->done; ra.N = N; ra.b0 = b0; ra.dt = h->o.dt_nodes;
-                    nmpc_residual_sr_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
-                }
+                ResSrArgs ra;
+                ra.SR = h->SR; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi; ra.lam = h->lam; ra.res_acc = h->res_acc;
+                ra.done = h->done; ra.N = N; ra.b0 = b0; ra.dt = h->o.dt_nodes;
+                nmpc_residual_sr_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
                 prof_end(h);
                 nmpc_sqp_decide_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(
                     b0, Bc, N, it, max_iter, h->o.nlp_tol, h->res_acc, h->cost_stage, h->res, h->cost,
@@ -540,8 +506,11 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
                 nmpc_cost_sum_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, N, h->cost_stage, h->cost);
                 h->launches++;
             }
-            if (h->dense_qp) run_qp(h, qp_args(h, b0), Bc, true);
-            else run_qp_fused(h, qp_args(h, b0), Bc, true, false);
+            QpArgs qa = qp_args(h, b0);
+            // acados ocp_nlp_sqp / sqp_rti: "(typically) no warm start at first iteration" -- the QP solver's
+            // warm_start is forced to 0 for the first QP of a solve unless opts->warm_start_first_qp
+            if (it == 0 && !h->o.warm_start_first_qp) qa.warm = 0;
+            run_qp_fused(h, qa, Bc, true);
             nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
             h->launches++;
         }
@@ -557,6 +526,7 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
 extern "C" int nmpc_set_profiling(nmpc_handle* h, int32_t on)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     h->profiling = on ? 1 : 0;
     h->ev_used = 0;
     return 0;
@@ -566,6 +536,7 @@ extern "C" int nmpc_set_profiling(nmpc_handle* h, int32_t on)
 extern "C" int nmpc_get_kernel_times(nmpc_handle* h, double* ms, int64_t* count)
 {
     if (!h || !ms || !count) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     for (int i = 0; i < NMPC_PROF_KINDS; i++) { ms[i] = 0.0; count[i] = 0; }
@@ -582,6 +553,7 @@ extern "C" int nmpc_get_kernel_times(nmpc_handle* h, double* ms, int64_t* count)
 extern "C" int nmpc_synchronize(nmpc_handle* h)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     return (int)cudaGetLastError();
@@ -596,6 +568,7 @@ static int d2h(nmpc_handle* h, void* dst, const void* src, size_t bytes)
 extern "C" int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* pi, double* lam)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t B = h->B, N = h->N;
     if (x) if (int r = d2h(h, x, h->x, B * (N + 1) * NX * 8)) return r;
@@ -606,9 +579,35 @@ extern "C" int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* p
     return 0;
 }
 
+// per-problem status of the last solve (host or device pointer); synchronises the solve stream
+extern "C" int nmpc_get_status(nmpc_handle* h, int32_t* status)
+{
+    if (!h || !status) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(status, h->status, (size_t)h->B * 4, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// packed result rows [B, (N+1)*42 + N*31 + 1] into a DEVICE buffer, enqueued on the solve stream without a
+// synchronisation: the send buffer of the gather to the dataset-writer rank
+extern "C" int nmpc_pack_solution(nmpc_handle* h, double* out_dev)
+{
+    if (!h || !out_dev) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, out_dev) != cudaSuccess || at.type != cudaMemoryTypeDevice) { cudaGetLastError(); return NMPC_EINVAL; }
+    nmpc_pack_solution_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->o.dt_nodes, h->x, h->u, h->status, out_dev);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
 extern "C" int nmpc_get_stats(nmpc_handle* h, nmpc_stats* s)
 {
     if (!h || !s) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t B = h->B;
     if (s->sqp_iter) if (int r = d2h(h, s->sqp_iter, h->sqp_iter, B * 4)) return r;
@@ -617,6 +616,7 @@ extern "C" int nmpc_get_stats(nmpc_handle* h, nmpc_stats* s)
     if (s->res) if (int r = d2h(h, s->res, h->res, B * 4 * 8)) return r;
     if (s->qp_res) if (int r = d2h(h, s->qp_res, h->qp_res, B * 4 * 8)) return r;
     if (s->cost) if (int r = d2h(h, s->cost, h->cost, B * 8)) return r;
+    if (s->qp_ncond) if (int r = d2h(h, s->qp_ncond, h->qp_ncond, B * 4)) return r;
     CK(cudaStreamSynchronize(h->stream));
     return 0;
 }
@@ -624,6 +624,7 @@ extern "C" int nmpc_get_stats(nmpc_handle* h, nmpc_stats* s)
 extern "C" int nmpc_get_qp_step(nmpc_handle* h, double* dz)
 {
     if (!h || !dz) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     if (int r = d2h(h, dz, h->qz, (size_t)h->B * (h->N + 1) * NZ * 8)) return r;
     CK(cudaStreamSynchronize(h->stream));
@@ -633,20 +634,21 @@ extern "C" int nmpc_get_qp_step(nmpc_handle* h, double* dz)
 extern "C" int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, double* feet, double* com, double* hg)
 {
     if (!h || !qv || n <= 0) return NMPC_EINVAL;
+    ULOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t in_b = (size_t)n * 36 * 8, out_d = (size_t)n * (12 + 3 + 6);
-    if (int r = ensure_scratch(h, in_b + out_d * 8)) return r;
-    double* d_in = h->scratch;
-    double* d_feet = h->scratch + (size_t)n * 36;
+    if (int r = ensure_uscratch(h, in_b + out_d * 8)) return r;
+    double* d_in = h->uscratch;
+    double* d_feet = h->uscratch + (size_t)n * 36;
     double* d_com = d_feet + (size_t)n * 12;
     double* d_hg = d_com + (size_t)n * 3;
-    CK(cudaMemcpyAsync(d_in, qv, in_b, cudaMemcpyDefault, h->stream));
-    nmpc_kin0_kernel<<<(n + 63) / 64, 64, 0, h->stream>>>(d_in, n, d_feet, d_com, d_hg);
-    h->launches++;
-    if (feet) CK(cudaMemcpyAsync(feet, d_feet, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
-    if (com) CK(cudaMemcpyAsync(com, d_com, (size_t)n * 3 * 8, cudaMemcpyDefault, h->stream));
-    if (hg) CK(cudaMemcpyAsync(hg, d_hg, (size_t)n * 6 * 8, cudaMemcpyDefault, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpyAsync(d_in, qv, in_b, cudaMemcpyDefault, h->ustream));
+    nmpc_kin0_kernel<<<(n + 63) / 64, 64, 0, h->ustream>>>(d_in, n, d_feet, d_com, d_hg);
+    h->ulaunches++;
+    if (feet) CK(cudaMemcpyAsync(feet, d_feet, (size_t)n * 12 * 8, cudaMemcpyDefault, h->ustream));
+    if (com) CK(cudaMemcpyAsync(com, d_com, (size_t)n * 3 * 8, cudaMemcpyDefault, h->ustream));
+    if (hg) CK(cudaMemcpyAsync(hg, d_hg, (size_t)n * 6 * 8, cudaMemcpyDefault, h->ustream));
+    CK(cudaStreamSynchronize(h->ustream));
     return (int)cudaGetLastError();
 }
 
@@ -655,18 +657,19 @@ extern "C" double nmpc_model_mass(void) { return NMPC_MASS; }
 extern "C" int nmpc_inverse_dynamics(nmpc_handle* h, const double* qva, const double* f, int32_t n, double* tau)
 {
     if (!h || !qva || !f || !tau || n <= 0) return NMPC_EINVAL;
+    ULOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t nd = (size_t)n * (54 + 12 + 12);
-    if (int r = ensure_scratch(h, nd * 8)) return r;
-    double* d_qva = h->scratch;
+    if (int r = ensure_uscratch(h, nd * 8)) return r;
+    double* d_qva = h->uscratch;
     double* d_f = d_qva + (size_t)n * 54;
     double* d_tau = d_f + (size_t)n * 12;
-    CK(cudaMemcpyAsync(d_qva, qva, (size_t)n * 54 * 8, cudaMemcpyDefault, h->stream));
-    CK(cudaMemcpyAsync(d_f, f, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
-    nmpc_rnea_kernel<<<(n + 63) / 64, 64, 0, h->stream>>>(d_qva, d_f, n, d_tau);
-    h->launches++;
-    CK(cudaMemcpyAsync(tau, d_tau, (size_t)n * 12 * 8, cudaMemcpyDefault, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpyAsync(d_qva, qva, (size_t)n * 54 * 8, cudaMemcpyDefault, h->ustream));
+    CK(cudaMemcpyAsync(d_f, f, (size_t)n * 12 * 8, cudaMemcpyDefault, h->ustream));
+    nmpc_rnea_kernel<<<(n + 63) / 64, 64, 0, h->ustream>>>(d_qva, d_f, n, d_tau);
+    h->ulaunches++;
+    CK(cudaMemcpyAsync(tau, d_tau, (size_t)n * 12 * 8, cudaMemcpyDefault, h->ustream));
+    CK(cudaStreamSynchronize(h->ustream));
     return (int)cudaGetLastError();
 }
 
@@ -676,6 +679,7 @@ extern "C" int nmpc_plan_torques(nmpc_handle* h, const double* qv_meas, int32_t 
                                  double* action)
 {
     if (!h || n_interp < 2 || n_steps <= 0 || step0 < 0 || step0 + n_steps > n_interp || !(kp != 0.0)) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t n = (size_t)h->B * n_steps;
     // scratch: [meas 36 | q 18 | v 18 | tau_ff 12 | tau 12 | action 12] per (problem, step)
@@ -711,7 +715,9 @@ extern "C" int nmpc_export_qp(nmpc_handle* h, double* BAbt, double* RSQrq, doubl
                               double* mask)
 {
     if (!h) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
+    if (int r = ensure_dense(h)) return r;
     const int B = h->B, N = h->N;
     std::vector<double> hG((size_t)h->Bc * N * G_SZ), hM((size_t)h->Bc * (N + 1) * M_SZ),
         hC((size_t)h->Bc * (N + 1) * C_SZ), hD((size_t)h->Bc * (N + 1) * D_SZ);
@@ -761,7 +767,17 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
                              double* dz, double* pi, double* lam, double* t, int32_t* qp_iter, int32_t* qp_status)
 {
     if (!h || !BAbt || !RSQrq || !DCt || !lg || !ug || !mask || !dx0) return NMPC_EINVAL;
+    LOCK(h);
     CK(cudaSetDevice(h->device));
+    {   // the stage blocks are repacked on the host below: device pointers would be dereferenced there
+        const void* in[] = {BAbt, RSQrq, DCt, lg, ug, mask};
+        for (const void* q : in) {
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, q) == cudaSuccess && at.type == cudaMemoryTypeDevice) return NMPC_EINVAL;
+            cudaGetLastError();
+        }
+    }
+    if (int r = ensure_dense(h)) return r;
     const int B = h->B, N = h->N;
     if (int r = ensure_scratch(h, (size_t)B * NX * 8)) return r;
     CK(cudaMemcpyAsync(h->scratch, dx0, (size_t)B * NX * 8, cudaMemcpyDefault, h->stream));
@@ -800,21 +816,21 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
         CK(cudaMemcpyAsync(h->D, hD.data(), (size_t)Bc * (N + 1) * D_SZ * 8, cudaMemcpyHostToDevice, h->stream));
         QpArgs qa = qp_args(h, b0);
         qa.dx0_ext = h->scratch; qa.warm = 0; qa.sqp_done = nullptr; qa.sqp_iter = nullptr;
-        // QPs with the structure of this OCP family (every QP the solver itself builds) take the fused
-        // product path; anything else is solved by the generic dense kernels
-        int32_t generic = h->dense_qp;
-        if (!generic) {
-            CK(cudaMemsetAsync(h->sr_flag, 0, 4, h->stream));
-            SrArgs sa;
-            sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
-            sa.done = nullptr; sa.N = N; sa.b0 = b0; sa.check = 1; sa.dt = h->o.dt_nodes;
-            nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, h->stream>>>(sa);
-            CK(cudaMemcpyAsync(&generic, h->sr_flag, 4, cudaMemcpyDeviceToHost, h->stream));
-            CK(cudaStreamSynchronize(h->stream));
-        }
-        h->last_qp_path = generic ? 0 : 1;
-        if (generic) run_qp(h, qa, Bc, false);
-        else run_qp_fused(h, qa, Bc, false, false);   // the check pass above already wrote the records
+        // Only QPs with the structure of this OCP family (every QP the solver itself builds) can be solved:
+        // the dense blocks are converted into stage records and checked entry by entry against what the
+        // records expand to; anything else is refused (there is no generic dense solver in this build).
+        int32_t unstructured = 0;
+        CK(cudaMemsetAsync(h->sr_flag, 0, 4, h->stream));
+        SrArgs sa;
+        sa.G = h->G; sa.M = h->M; sa.C = h->C; sa.D = h->D; sa.SR = h->SR; sa.flag = h->sr_flag;
+        sa.done = nullptr; sa.N = N; sa.b0 = b0; sa.check = 1; sa.dt = h->o.dt_nodes;
+        nmpc_dense2sr_kernel<<<dim3(N + 1, Bc), 128, 0, h->stream>>>(sa);
+        h->launches++;
+        CK(cudaMemcpyAsync(&unstructured, h->sr_flag, 4, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        h->last_qp_path = unstructured ? -1 : 1;
+        if (unstructured) return NMPC_ENOSYS;
+        run_qp_fused(h, qa, Bc, false);
         CK(cudaStreamSynchronize(h->stream));
     }
     CK(cudaGetLastError());
@@ -831,21 +847,16 @@ extern "C" int nmpc_solve_qp(nmpc_handle* h, const double* BAbt, const double* R
 
 extern "C" int nmpc_last_qp_path(const nmpc_handle* h) { return h ? h->last_qp_path : -1; }
 
-// debug builds (-DNMPC_TIMING): per-phase cycle counts of CTA 0 of nmpc_qp_factor_kernel
-extern "C" int nmpc_debug_phase_cycles(unsigned long long* out16, int reset)
+// debug builds (-DNMPC_TIMING): per-phase cycle counts of CTA 0 of nmpc_qp_fused_kernel (24 counters)
+extern "C" int nmpc_debug_phase_cycles(unsigned long long* out24, int reset)
 {
 #ifdef NMPC_TIMING
     CK(cudaDeviceSynchronize());
-    if (reset >= 2) {            // fused kernel: 24 counters (out16 must hold 24 entries)
-        CK(cudaMemcpyFromSymbol(out16, g_fq_cycles, sizeof(unsigned long long) * 24));
-        if (reset == 3) { unsigned long long z[24] = {0}; CK(cudaMemcpyToSymbol(g_fq_cycles, z, sizeof(z))); }
-        return 0;
-    }
-    CK(cudaMemcpyFromSymbol(out16, g_phase_cycles, sizeof(unsigned long long) * 16));
-    if (reset) { unsigned long long z[16] = {0}; CK(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z))); }
+    CK(cudaMemcpyFromSymbol(out24, g_fq_cycles, sizeof(unsigned long long) * 24));
+    if (reset) { unsigned long long z[24] = {0}; CK(cudaMemcpyToSymbol(g_fq_cycles, z, sizeof(z))); }
     return 0;
 #else
-    (void)out16; (void)reset;
+    (void)out24; (void)reset;
     return NMPC_ENOSYS;
 #endif
 }

@@ -9,7 +9,7 @@
 //     C  [42][72]   row j = constraint j over z = [u;x]                  (DCt^T,  ld 72)
 //     lg [42] ug [42] mask [84]
 //   factor block  L [2880] panel-packed lower Cholesky factor of M_k + row 72 = L^-1 m
-//                 (twelve 6-column panels, nmpc_qp_ipm.cuh); Ht uses the same packing
+//                 (twelve 6-column panels, nmpc_qp_layout.cuh)
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -63,6 +63,7 @@
 #define IPM_LAM_MIN 1e-16
 #define IPM_T_MIN 1e-16
 #define IPM_ALPHA_MIN 1e-12
+#define IPM_TAU_MIN 1e-16
 
 
 // ---------------------------------------------------------------------------------------------

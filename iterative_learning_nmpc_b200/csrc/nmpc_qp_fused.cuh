@@ -2,7 +2,7 @@
 // whole Mehrotra predictor-corrector IPM (all iterations, all stages) with a Riccati recursion
 // specialised to the structure of this OCP family.
 //
-// Same algorithm as nmpc_qp_ipm.cuh (HPIPM `speed` semantics; oracle:
+// HPIPM `speed` semantics (oracle:
 // oracle/nmpc_oracle.c::qp_ipm) -- the Newton directions are identical in exact arithmetic -- but
 // the arithmetic is organised around what the stage matrices of THIS problem look like:
 //
@@ -23,7 +23,7 @@
 // step lengths, sigma) are CTA-local, and nothing but the per-stage vectors and the factors
 // (needed again by the forward / corrector sweeps) goes back to HBM.  One kernel launch per QP.
 #pragma once
-#include "nmpc_qp_ipm.cuh"
+#include "nmpc_qp_layout.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // stage record (doubles)
@@ -147,10 +147,10 @@ struct FqArgs {
     double* FR;                     // [Bc][N+1][FR_SZ]
     double* vec;                    // [Bc][(N+1)*V_STAGE]
     double* qz; double* qpi; double* qlam; double* qt;       // QP iterate, global problem index
-    int32_t* qp_iter; int32_t* qp_status; double* qp_res;
+    int32_t* qp_iter; int32_t* qp_status; int32_t* qp_ncond; double* qp_res;
     const double* dx0_ext; const double* x0; const double* x;
     const int32_t* sqp_done;
-    int N, b0, max_iter, warm;
+    int N, b0, max_iter, warm, cond_pred_corr;   // warm: HPIPM warm_start level 0 / 1 / 2 (see nmpc_b200.h)
     double tol, dt, c2;              // c2 = dt^2 / 2 (host-computed: both stay constant-bank operands)
 };
 
@@ -385,9 +385,9 @@ __device__ __forceinline__ void fq_forward_stage(const double* sM, const double*
             dl = -(g_rm + lam * dtv) / t;
             if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
             if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
-            if (!CORR) {      // sum (lam + a dlam)(t + a dt) = cs0 + a cs1 + a^2 cs2: the centring parameter needs no extra pass
-                cs[0] = fma(lam, t, cs[0]); cs[1] += fma(lam, dtv, t * dl); cs[2] = fma(dl, dtv, cs[2]);
-            }
+            // sum (lam + a dlam)(t + a dt) = cs0 + a cs1 + a^2 cs2: neither the centring parameter (affine sweep) nor the
+            // conditional predictor-corrector test (corrector sweep) needs an extra pass over the stages
+            cs[0] = fma(lam, t, cs[0]); cs[1] += fma(lam, dtv, t * dl); cs[2] = fma(dl, dtv, cs[2]);
         }
         vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
     }
@@ -522,10 +522,10 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
 
     // ---- start of the QP (nmpc_qp_init_kernel) ----
-    if (a.warm == 0) {
+    if (a.warm == 0)
         for (int i = tid; i < (N + 1) * NZ; i += FQ_THREADS) qz[i] = 0.0;
+    if (a.warm < 2)
         for (int i = tid; i < N * NX; i += FQ_THREADS) qpi[i] = 0.0;
-    }
     __syncthreads();
     if (tid < NX)
         qz[NU + tid] = a.dx0_ext ? a.dx0_ext[(size_t)b * NX + tid]
@@ -554,7 +554,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     const int xrt = (tx_ >> 12) & 3u, xct = (tx_ >> 14) & 3u, xr = (tx_ >> 16) & 15u, xc = (tx_ >> 20) & 15u;    \
     (void)xrt; (void)xct; (void)xr; (void)xc; (void)has_xt
 
-    int status = 1, iters = 0, nc_total = 0;
+    int status = 1, iters = 0, nc_total = 0, ncond = 0;
     double alpha_p = 1.0, alpha_d = 1.0, mu = 0.0;
 
     for (int it = 0; it <= a.max_iter; it++) {
@@ -619,8 +619,11 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 const double cz = sv[FV_CZ + j];
                 const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
                 double t = sv[FV_T + tid], lam = sv[FV_LAM + tid];
-                if (it == 0 && (a.warm < 2 || !(t > 0.0) || !(lam > 0.0))) {
-                    if (msk > 0.5) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; } else { t = 1.0; lam = 0.0; }
+                if (it == 0) {               // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
+                    if (msk > 0.5) {
+                        if (a.warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; }
+                        else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
+                    } else { t = 1.0; lam = 0.0; }
                     sv[FV_T + tid] = t; sv[FV_LAM + tid] = lam;
                     qt[tid] = t; qlam[tid] = lam;
                 }
@@ -987,19 +990,24 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 
         FMARK(9);
         // ================= centring parameter (nmpc_qp_sigma_kernel) =================
-        double sigma_mu;
+        double sigma_mu, mu_aff;
         {
             const double s0 = fq_block_sum(cs[0], red, tid);
             const double s1 = fq_block_sum(cs[1], red, tid);
             const double s2 = fq_block_sum(cs[2], red, tid);
             const double s = fma(alpha_aff, fma(alpha_aff, s2, s1), s0);
-            const double mu_aff = nc_total > 0 ? s / nc_total : 0.0;
+            mu_aff = nc_total > 0 ? s / nc_total : 0.0;
             double sg = mu > 0.0 ? mu_aff / mu : 0.0;
             sg = sg * sg * sg;
-            sigma_mu = sg * mu;
+            sigma_mu = fmax(sg * mu, IPM_TAU_MIN);
         }
 
         FMARK(10);
+        // Corrector on the stored factorisation.  Pass 0 is Mehrotra's centring-corrector direction (HPIPM
+        // COMPUTE_CENTERING_CORRECTION_QP); pass 1 runs only when the conditional predictor-corrector rejects it
+        // (HPIPM arg->cond_pred_corr): if the complementarity predicted along it exceeds twice the affine
+        // prediction, the centring direction alone (COMPUTE_CENTERING_QP: rm = lam t - sigma mu) is solved for.
+        for (int cpass = 0; cpass < 2; cpass++) {
         // ================= corrector: backward vector sweep on the stored factorisation =================
         for (int k = N; k >= 0; k--) {
             const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
@@ -1029,7 +1037,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                 double v = 0.0;
                 if (S[SR_D + 2 * NG + tid] > 0.5) {
                     const double lam = g_lam, t = g_t;
-                    const double rmc = lam * t + g_dt * g_dl - sigma_mu;
+                    const double rmc = fma(lam, t, cpass == 0 ? g_dt * g_dl : 0.0) - sigma_mu;
                     vk[V_RM + tid] = rmc;
                     v = (rmc + lam * g_rd) / t;
                 }
@@ -1102,6 +1110,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         FMARK(11);
         // ================= corrector: forward sweep with multiplier directions =================
         a_p = 1.0; a_d = 1.0;
+        cs[0] = 0.0; cs[1] = 0.0; cs[2] = 0.0;
         if (tid < NX) sv[FV_DX + tid] = 0.0;
         __syncthreads();
         for (int k = 0; k <= N; k++) {
@@ -1128,6 +1137,17 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         }
         alpha_p = fq_block_min(a_p, red, tid);
         alpha_d = fq_block_min(a_d, red, tid);
+        if (cpass == 1 || !a.cond_pred_corr) break;
+        {
+            const double s0 = fq_block_sum(cs[0], red, tid);
+            const double s1 = fq_block_sum(cs[1], red, tid);
+            const double s2 = fq_block_sum(cs[2], red, tid);
+            const double al = fmin(alpha_p, alpha_d);
+            const double mu_c = nc_total > 0 ? fma(al, fma(al, s2, s1), s0) / nc_total : 0.0;
+            if (!(mu_c > 2.0 * mu_aff)) break;
+            ncond++;
+        }
+        }
         FMARK(12);
     }
 
@@ -1142,6 +1162,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         bulk_store_wait_all();
         a.qp_iter[b] = iters;
         a.qp_status[b] = status;
+        a.qp_ncond[b] = ncond;
     }
 #undef SRb
 #undef FRb

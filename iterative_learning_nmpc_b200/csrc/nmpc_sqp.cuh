@@ -9,14 +9,6 @@
 
 #define RES_THREADS 128
 
-struct ResArgs {
-    const double* G; const double* M; const double* C; const double* D;
-    const double* x; const double* x0; const double* pi; const double* lam;
-    unsigned long long* res_acc;   // [B][4] bit patterns of non-negative doubles (atomicMax)
-    const int32_t* done;
-    int N, b0;
-};
-
 __device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, double v)
 {
     // NaN is reported as +inf so that it survives the max
@@ -24,61 +16,15 @@ __device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, doub
     atomicMax(addr, (unsigned long long)__double_as_longlong(v));
 }
 
-// inf-norms of the KKT residuals of the NLP at the current linearisation: one CTA per node
-__global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_kernel(ResArgs a)
-{
-    const int k = blockIdx.x, bl = blockIdx.y, b = a.b0 + bl, tid = threadIdx.x;
-    if (a.done && a.done[b]) return;
-    const int N = a.N;
-    const bool term = (k == N);
-    __shared__ double s_pik[NX], s_pin[NX], s_dl[NG], s_red[4][RES_THREADS / 32];
-    const double* Gp = term ? nullptr : a.G + ((size_t)bl * N + k) * G_SZ;
-    const double* Mp = a.M + ((size_t)bl * (N + 1) + k) * M_SZ;
-    const double* Cp = a.C + ((size_t)bl * (N + 1) + k) * C_SZ;
-    const double* Dp = a.D + ((size_t)bl * (N + 1) + k) * D_SZ;
-    const double* lam = a.lam + ((size_t)b * (N + 1) + k) * 2 * NG;
-    double r_s = 0, r_e = 0, r_i = 0, r_c = 0;
-    for (int i = tid; i < NX; i += RES_THREADS) {
-        s_pik[i] = k > 0 ? a.pi[((size_t)b * N + k - 1) * NX + i] : 0.0;
-        s_pin[i] = term ? 0.0 : a.pi[((size_t)b * N + k) * NX + i];
-        if (k == 0) r_e = nanmax(r_e, fabs(a.x[(size_t)b * (N + 1) * NX + i] - a.x0[(size_t)b * NX + i]));
-        if (!term) r_e = nanmax(r_e, fabs(Gp[i * G_LD + NZ]));
-    }
-    for (int j = tid; j < NG; j += RES_THREADS) {
-        const double ml = Dp[2 * NG + j], mu = Dp[3 * NG + j];
-        const double c = -Dp[j];
-        double dl = 0.0;
-        if (ml > 0.5) { dl += lam[j]; r_i = nanmax(r_i, -c); r_c = nanmax(r_c, fabs(lam[j] * c)); }
-        if (mu > 0.5) { dl -= lam[NG + j]; r_i = nanmax(r_i, c); r_c = nanmax(r_c, fabs(lam[NG + j] * c)); }
-        s_dl[j] = dl;
-    }
-    __syncthreads();
-    for (int c = tid; c < NZ; c += RES_THREADS) {
-        if ((k == 0 && c >= NU) || (term && c < NU)) continue;
-        double s = Mp[NZ * M_LD + c];
-        if (!term) for (int l = 0; l < NX; l++) s += Gp[l * G_LD + c] * s_pin[l];
-        if (k > 0 && c >= NU) s -= s_pik[c - NU];
-        for (int j = 0; j < NG; j++) s -= Cp[j * C_LD + c] * s_dl[j];
-        r_s = nanmax(r_s, fabs(s));
-    }
-    r_s = warp_max(r_s); r_e = warp_max(r_e); r_i = warp_max(r_i); r_c = warp_max(r_c);
-    if ((tid & 31) == 0) { s_red[0][tid >> 5] = r_s; s_red[1][tid >> 5] = r_e; s_red[2][tid >> 5] = r_i; s_red[3][tid >> 5] = r_c; }
-    __syncthreads();
-    if (tid < 4) {
-        double v = 0.0;
-        for (int w = 0; w < RES_THREADS / 32; w++) v = nanmax(v, s_red[tid][w]);
-        atomic_max_nonneg(a.res_acc + (size_t)b * 4 + tid, v);
-    }
-}
-
 // start of a solve: clear flags
 __global__ void nmpc_sqp_begin_kernel(int B, int rti, int32_t* status, int32_t* done, int32_t* sqp_iter,
-                                      int32_t* qp_iter, int32_t* qp_status, unsigned long long* res_acc)
+                                      int32_t* qp_iter, int32_t* qp_status, int32_t* qp_ncond,
+                                      unsigned long long* res_acc)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     status[b] = rti ? NMPC_STATUS_SUCCESS : NMPC_STATUS_MAXITER;
-    done[b] = 0; sqp_iter[b] = 0; qp_iter[b] = 0; qp_status[b] = 0;
+    done[b] = 0; sqp_iter[b] = 0; qp_iter[b] = 0; qp_status[b] = 0; qp_ncond[b] = 0;
     for (int i = 0; i < 4; i++) res_acc[(size_t)b * 4 + i] = 0ULL;
 }
 
@@ -170,4 +116,23 @@ __global__ void __launch_bounds__(128, 4) nmpc_shift_kernel(int N, const int32_t
             if (k < N - 1) ub[k * NU + i] = ub[(N - 1) * NU + i];
         }
     }
+}
+
+// Packed result rows for the gather to the dataset-writer rank: per problem
+// [x (N+1)*42 | u N*30 | dt_node N | status] = 1868 doubles at N = 25 -- the 1867 numbers parse_sol returns
+// (solver.py:403-429: q, v, h per node, a, f, dt per interval) plus the solver status.
+__global__ void __launch_bounds__(128) nmpc_pack_solution_kernel(int N, double dt, const double* __restrict__ x,
+                                                                 const double* __restrict__ u,
+                                                                 const int32_t* __restrict__ status,
+                                                                 double* __restrict__ out)
+{
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int nx = (N + 1) * NX, nu = N * NU, row = nx + nu + N + 1;
+    double* o = out + (size_t)b * row;
+    const double* xb = x + (size_t)b * nx;
+    const double* ub = u + (size_t)b * nu;
+    for (int i = tid; i < nx; i += 128) o[i] = xb[i];
+    for (int i = tid; i < nu; i += 128) o[nx + i] = ub[i];
+    for (int i = tid; i < N; i += 128) o[nx + nu + i] = dt;
+    if (tid == 0) o[row - 1] = (double)status[b];
 }

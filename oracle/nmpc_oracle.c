@@ -39,7 +39,7 @@
 #define NMPC_HD static
 #define NMPC_REC(i) rec[(i)]
 #define NMPC_WITH_RNEA 1
-#include "nmpc_gen_model.h"
+#include "../iterative_learning_nmpc_b200/csrc/nmpc_gen_model.h"
 
 /* z = [u; x] index helpers */
 #define IA 0          /* a   in u */
@@ -68,6 +68,7 @@
 #define IPM_LAM_MIN 1e-16
 #define IPM_T_MIN 1e-16
 #define IPM_ALPHA_MIN 1e-12
+#define IPM_TAU_MIN 1e-16
 static const double GRAV[3] = {0.0, 0.0, -9.81};
 /* running inf-norm that keeps a NaN once it has seen one (plain > comparisons drop NaNs) */
 #define NORM_ACC(r, a) do { const double a_ = fabs(a); if (a_ > (r) || a_ != a_) (r) = a_; } while (0)
@@ -351,6 +352,7 @@ typedef struct {
     int iter, status;           /* HPIPM numbering 0 ok, 1 max-iter, 2 min-step, 3 NaN */
     double res[4];              /* stat, eq, ineq, comp inf-norms at exit */
     double mu;
+    int ncond;                  /* iterations in which the conditional predictor-corrector fell back to centring */
 } qp_info;
 
 static int stage_off(int k) { return k == 0 ? 1 : 0; }   /* unused placeholder for clarity */
@@ -477,18 +479,19 @@ static int riccati(workspace* w, int N, const double* dx0, int do_fact)
 }
 
 /* QP of the SQP step at the current linearisation held in w->lin.
- * in/out: z [N+1][NZ], pi [N][NX], lam/t [N+1][2NG] (lower | upper).  warm: 0 cold, 1 keep z,pi,
- * 2 keep everything (entries whose stored lam or t is not positive, e.g. after reset_duals, are
- * initialised as in a cold start).  dx0 = x0 - xbar_0 is imposed on stage 0. */
+ * in/out: z [N+1][NZ], pi [N][NX], lam/t [N+1][2NG] (lower | upper).  dx0 = x0 - xbar_0 is imposed on stage 0.
+ * warm = HPIPM's `warm_start` level (d_ocp_qp_ipm.c, INIT_VAR):
+ *   0 cold: z = 0, pi = 0, t = max(slack(z), thr0), lam = mu0 / t
+ *   1 primal: z kept, otherwise as 0 (pi is zeroed as well)
+ *   2 primal and dual ("hot"): z, pi, lam, t kept; lam and t of the masked rows clipped from below at thr0
+ *     (rows whose stored lam or t is not positive -- never initialised, e.g. after reset_duals -- are initialised as in 1) */
 static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, int warm,
                    double (*z)[NZ], double (*pi)[NX], double (*lam)[2 * NG], double (*t)[2 * NG],
                    qp_info* info)
 {
     const double tol = o->qp_tol;
-    if (warm == 0) {
-        memset(z, 0, sizeof(double) * (N + 1) * NZ);
-        memset(pi, 0, sizeof(double) * N * NX);
-    }
+    if (warm == 0) memset(z, 0, sizeof(double) * (N + 1) * NZ);
+    if (warm < 2) memset(pi, 0, sizeof(double) * N * NX);
     for (int i = 0; i < NX; i++) z[0][NU + i] = dx0[i];
     for (int i = 0; i < NU; i++) z[N][i] = 0.0;
     int nc = 0;
@@ -500,15 +503,18 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
             if (s->ml[j] > 0.5) {
                 nc++;
                 if (warm < 2 || !(t[k][j] > 0.0) || !(lam[k][j] > 0.0)) { double tl = cz - s->lgq[j]; t[k][j] = tl > IPM_THR0 ? tl : IPM_THR0; lam[k][j] = IPM_MU0 / t[k][j]; }
+                else { if (t[k][j] < IPM_THR0) t[k][j] = IPM_THR0; if (lam[k][j] < IPM_THR0) lam[k][j] = IPM_THR0; }
             } else { t[k][j] = 1.0; lam[k][j] = 0.0; }
             if (s->mu[j] > 0.5) {
                 nc++;
                 if (warm < 2 || !(t[k][NG + j] > 0.0) || !(lam[k][NG + j] > 0.0)) { double tu = s->ugq[j] - cz; t[k][NG + j] = tu > IPM_THR0 ? tu : IPM_THR0; lam[k][NG + j] = IPM_MU0 / t[k][NG + j]; }
+                else { if (t[k][NG + j] < IPM_THR0) t[k][NG + j] = IPM_THR0; if (lam[k][NG + j] < IPM_THR0) lam[k][NG + j] = IPM_THR0; }
             } else { t[k][NG + j] = 1.0; lam[k][NG + j] = 0.0; }
         }
     }
     const double inv_nc = nc > 0 ? 1.0 / nc : 0.0;
     info->status = 1;
+    info->ncond = 0;
     int it = 0;
     for (;; it++) {
         /* ---- residuals ---- */
@@ -606,43 +612,64 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
         mu_aff *= inv_nc;
         double sigma = mu > 0 ? mu_aff / mu : 0.0;
         sigma = sigma * sigma * sigma;
-        /* ---- corrector: rm <- lam*t + dt_a*dlam_a - sigma*mu, same factorisation ---- */
-        for (int k = 0; k <= N; k++) {
-            stage_lin* s = &w->lin[k];
-            double gam[NG];
-            for (int j = 0; j < NG; j++) {
-                for (int e = 0; e < 2; e++) {
-                    const int id = e * NG + j;
-                    const double msk = e ? s->mu[j] : s->ml[j];
-                    if (msk > 0.5) w->rm[k][id] = lam[k][id] * t[k][id] + w->dt_a[k][id] * w->dlam_a[k][id] - sigma * mu;
-                }
-                gam[j] = s->ml[j] * (w->rm[k][j] + lam[k][j] * w->rd[k][j]) / t[k][j]
-                       - s->mu[j] * (w->rm[k][NG + j] + lam[k][NG + j] * w->rd[k][NG + j]) / t[k][NG + j];
-            }
-            for (int c = 0; c < NZ; c++) {
-                double acc = w->rg[k][c];
-                for (int j = 0; j < NG; j++) acc += s->C[j][c] * gam[j];
-                w->qt[k][c] = acc;
-            }
-        }
-        riccati(w, N, zero0, 0);
+        /* ---- corrector: rm <- lam*t + dt_a*dlam_a - sigma*mu, same factorisation (HPIPM
+         *      COMPUTE_CENTERING_CORRECTION_QP); pass 1 only if the conditional predictor-corrector
+         *      (arg->cond_pred_corr, on in every HPIPM mode) rejects that direction: when the complementarity
+         *      it predicts, mu(alpha), exceeds twice the affine prediction mu_aff, the centring direction
+         *      rm <- lam*t - sigma*mu (COMPUTE_CENTERING_QP) is solved for instead ---- */
+        double sigma_mu = sigma * mu;
+        if (sigma_mu < IPM_TAU_MIN) sigma_mu = IPM_TAU_MIN;
         double alpha_p = 1.0, alpha_d = 1.0;
-        for (int k = 0; k <= N; k++) {
-            stage_lin* s = &w->lin[k];
-            for (int j = 0; j < NG; j++) {
-                double cdz = 0;
-                for (int c = 0; c < NZ; c++) cdz += s->C[j][c] * w->dz[k][c];
-                for (int e = 0; e < 2; e++) {
-                    const int id = e * NG + j;
-                    const double msk = e ? s->mu[j] : s->ml[j];
-                    if (msk < 0.5) { w->dt[k][id] = 0; w->dlam[k][id] = 0; continue; }
-                    double dtv = (e ? -cdz : cdz) + w->rd[k][id];
-                    double dl = -(w->rm[k][id] + lam[k][id] * dtv) / t[k][id];
-                    w->dt[k][id] = dtv; w->dlam[k][id] = dl;
-                    if (dtv < 0 && -t[k][id] / dtv < alpha_p) alpha_p = -t[k][id] / dtv;
-                    if (dl < 0 && -lam[k][id] / dl < alpha_d) alpha_d = -lam[k][id] / dl;
+        for (int pass = 0; pass < 2; pass++) {
+            for (int k = 0; k <= N; k++) {
+                stage_lin* s = &w->lin[k];
+                double gam[NG];
+                for (int j = 0; j < NG; j++) {
+                    for (int e = 0; e < 2; e++) {
+                        const int id = e * NG + j;
+                        const double msk = e ? s->mu[j] : s->ml[j];
+                        if (msk > 0.5)
+                            w->rm[k][id] = lam[k][id] * t[k][id] + (pass == 0 ? w->dt_a[k][id] * w->dlam_a[k][id] : 0.0) - sigma_mu;
+                    }
+                    gam[j] = s->ml[j] * (w->rm[k][j] + lam[k][j] * w->rd[k][j]) / t[k][j]
+                           - s->mu[j] * (w->rm[k][NG + j] + lam[k][NG + j] * w->rd[k][NG + j]) / t[k][NG + j];
+                }
+                for (int c = 0; c < NZ; c++) {
+                    double acc = w->rg[k][c];
+                    for (int j = 0; j < NG; j++) acc += s->C[j][c] * gam[j];
+                    w->qt[k][c] = acc;
                 }
             }
+            riccati(w, N, zero0, 0);
+            alpha_p = 1.0; alpha_d = 1.0;
+            for (int k = 0; k <= N; k++) {
+                stage_lin* s = &w->lin[k];
+                for (int j = 0; j < NG; j++) {
+                    double cdz = 0;
+                    for (int c = 0; c < NZ; c++) cdz += s->C[j][c] * w->dz[k][c];
+                    for (int e = 0; e < 2; e++) {
+                        const int id = e * NG + j;
+                        const double msk = e ? s->mu[j] : s->ml[j];
+                        if (msk < 0.5) { w->dt[k][id] = 0; w->dlam[k][id] = 0; continue; }
+                        double dtv = (e ? -cdz : cdz) + w->rd[k][id];
+                        double dl = -(w->rm[k][id] + lam[k][id] * dtv) / t[k][id];
+                        w->dt[k][id] = dtv; w->dlam[k][id] = dl;
+                        if (dtv < 0 && -t[k][id] / dtv < alpha_p) alpha_p = -t[k][id] / dtv;
+                        if (dl < 0 && -lam[k][id] / dl < alpha_d) alpha_d = -lam[k][id] / dl;
+                    }
+                }
+            }
+            if (pass == 1 || !o->cond_pred_corr) break;
+            const double alpha_c = alpha_p < alpha_d ? alpha_p : alpha_d;
+            double mu_c = 0;
+            for (int k = 0; k <= N; k++)
+                for (int id = 0; id < 2 * NG; id++) {
+                    const double msk = id < NG ? w->lin[k].ml[id] : w->lin[k].mu[id - NG];
+                    if (msk > 0.5) mu_c += (lam[k][id] + alpha_c * w->dlam[k][id]) * (t[k][id] + alpha_c * w->dt[k][id]);
+                }
+            mu_c *= inv_nc;
+            if (!(mu_c > 2.0 * mu_aff)) break;
+            info->ncond++;
         }
         /* keep strictly inside the cone (HPIPM's step scaling) */
         alpha_p *= (1.0 - alpha_p) * 0.99 + alpha_p * 0.9999999;
@@ -674,7 +701,7 @@ typedef struct {
     double *x, *u, *pi, *lam;            /* iterate */
     double *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;        /* stored QP solution (warm start) */
-    int32_t *status, *sqp_iter, *qp_iter, *qp_status;
+    int32_t *status, *sqp_iter, *qp_iter, *qp_status, *qp_ncond;
     double *res, *qp_res, *cost;
 } oracle_handle;
 
@@ -692,7 +719,7 @@ oracle_handle* oracle_create(const nmpc_opts* o, int32_t B)
     ALLOC(h->yref_e, B * NYE); ALLOC(h->W, B * NY); ALLOC(h->We, B * NYE);
     ALLOC(h->qz, B * (N + 1) * NZ); ALLOC(h->qpi, B * N * NX);
     ALLOC(h->qlam, B * (N + 1) * 2 * NG); ALLOC(h->qt, B * (N + 1) * 2 * NG);
-    ALLOC(h->status, B); ALLOC(h->sqp_iter, B); ALLOC(h->qp_iter, B); ALLOC(h->qp_status, B);
+    ALLOC(h->status, B); ALLOC(h->sqp_iter, B); ALLOC(h->qp_iter, B); ALLOC(h->qp_status, B); ALLOC(h->qp_ncond, B);
     ALLOC(h->res, B * 4); ALLOC(h->qp_res, B * 4); ALLOC(h->cost, B);
     return h;
 }
@@ -702,7 +729,7 @@ void oracle_destroy(oracle_handle* h)
     if (!h) return;
     free(h->x); free(h->u); free(h->pi); free(h->lam); free(h->x0); free(h->p); free(h->yref);
     free(h->yref_e); free(h->W); free(h->We); free(h->qz); free(h->qpi); free(h->qlam); free(h->qt);
-    free(h->status); free(h->sqp_iter); free(h->qp_iter); free(h->qp_status);
+    free(h->status); free(h->sqp_iter); free(h->qp_iter); free(h->qp_status); free(h->qp_ncond);
     free(h->res); free(h->qp_res); free(h->cost);
     free(h);
 }
@@ -922,7 +949,7 @@ static void solve_one(oracle_handle* h, int b, workspace* w)
     int status = NMPC_STATUS_MAXITER;
     int it = 0;
     const int max_iter = o->real_time_it ? 1 : o->max_iter;
-    h->qp_iter[b] = 0; h->qp_status[b] = 0;
+    h->qp_iter[b] = 0; h->qp_status[b] = 0; h->qp_ncond[b] = 0;
     for (;; it++) {
         linearize_all(h, b, w);
         nlp_residuals(h, b, w, h->res + 4 * b, h->cost + b);
@@ -935,8 +962,11 @@ static void solve_one(oracle_handle* h, int b, workspace* w)
         double dx0[NX];
         for (int i = 0; i < NX; i++) dx0[i] = x0[i] - x[i];
         qp_info info;
-        qp_ipm(w, o, N, dx0, o->warm_start_qp, qz, qpi, qlam, qt, &info);
-        h->qp_iter[b] = info.iter; h->qp_status[b] = info.status;
+        /* acados ocp_nlp_sqp: "(typically) no warm start at first iteration" -- the QP solver's warm_start option
+         * is forced to 0 for the first QP of a solve unless opts->warm_start_first_qp, then restored */
+        const int warm = (it == 0 && !o->warm_start_first_qp) ? 0 : o->warm_start_qp;
+        qp_ipm(w, o, N, dx0, warm, qz, qpi, qlam, qt, &info);
+        h->qp_iter[b] = info.iter; h->qp_status[b] = info.status; h->qp_ncond[b] = info.ncond;
         memcpy(h->qp_res + 4 * b, info.res, sizeof(info.res));
         if (info.status != 0 && info.status != 1) { status = NMPC_STATUS_QP_FAILURE; it++; break; }
         /* full step; multipliers are replaced by the QP's */
@@ -995,6 +1025,7 @@ int oracle_get_stats(oracle_handle* h, nmpc_stats* s)
     if (s->res) memcpy(s->res, h->res, sizeof(double) * B * 4);
     if (s->qp_res) memcpy(s->qp_res, h->qp_res, sizeof(double) * B * 4);
     if (s->cost) memcpy(s->cost, h->cost, sizeof(double) * B);
+    if (s->qp_ncond) memcpy(s->qp_ncond, h->qp_ncond, sizeof(int32_t) * B);
     return 0;
 }
 

@@ -24,6 +24,7 @@ class NmpcOpts(C.Structure):
         ("n_nodes", C.c_int32), ("max_iter", C.c_int32), ("max_qp_iter", C.c_int32),
         ("real_time_it", C.c_int32), ("warm_start_qp", C.c_int32), ("warm_start_nlp", C.c_int32),
         ("hpipm_mode", C.c_int32), ("enable_time_opt", C.c_int32),
+        ("warm_start_first_qp", C.c_int32), ("cond_pred_corr", C.c_int32),
         ("dt_nodes", C.c_double), ("dt_min", C.c_double), ("dt_max", C.c_double),
         ("nlp_tol", C.c_double), ("qp_tol", C.c_double),
         ("reg_eps", C.c_double), ("reg_eps_e", C.c_double), ("mu_contact", C.c_double),
@@ -32,12 +33,13 @@ class NmpcOpts(C.Structure):
 
 class NmpcStats(C.Structure):
     _fields_ = [("sqp_iter", C.c_void_p), ("qp_iter", C.c_void_p), ("qp_status", C.c_void_p),
-                ("res", C.c_void_p), ("qp_res", C.c_void_p), ("cost", C.c_void_p)]
+                ("res", C.c_void_p), ("qp_res", C.c_void_p), ("cost", C.c_void_p),
+                ("qp_ncond", C.c_void_p)]
 
 
 def default_opts(**kw) -> NmpcOpts:
     o = NmpcOpts(n_nodes=25, max_iter=1, max_qp_iter=6, real_time_it=0, warm_start_qp=1,
-                 warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, dt_nodes=0.04, dt_min=0.02,
+                 warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, warm_start_first_qp=0, cond_pred_corr=1, dt_nodes=0.04, dt_min=0.02,
                  dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8)
     for k, v in kw.items():
         setattr(o, k, v)
@@ -218,8 +220,9 @@ class OracleSolver:
         B = self.B
         out = dict(sqp_iter=np.zeros(B, np.int32), qp_iter=np.zeros(B, np.int32),
                    qp_status=np.zeros(B, np.int32), res=np.zeros((B, 4)), qp_res=np.zeros((B, 4)),
-                   cost=np.zeros(B))
-        st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost")])
+                   cost=np.zeros(B), qp_ncond=np.zeros(B, np.int32))
+        st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost",
+                                                      "qp_ncond")])
         lib().oracle_get_stats(self._h, C.byref(st))
         return out
 

@@ -25,7 +25,10 @@ from oracle import oracle as O  # noqa: E402
 CASES = {
     # name: (B, seed, gaits, solver options)
     "rti_trot": (4, 11, ("trot",), dict(real_time_it=1, max_iter=1, max_qp_iter=6, warm_start_qp=0)),
-    "sqp_mixed": (3, 12, ("trot", "pace", "bound"), dict(real_time_it=0, max_iter=15, max_qp_iter=6, warm_start_qp=0)),
+    # reference defaults (config_abstract.py:58-64): warm_start_qp = True -> HPIPM level 1, first QP of the solve cold
+    "sqp_mixed": (3, 12, ("trot", "pace", "bound"), dict(real_time_it=0, max_iter=15, max_qp_iter=6, warm_start_qp=1)),
+    # the same with HPIPM's hot start (level 2): the setting under which max_qp_iter = 6 converges
+    "sqp_hot": (4, 14, ("trot", "pace", "bound"), dict(real_time_it=0, max_iter=15, max_qp_iter=6, warm_start_qp=2)),
     "qp_cap2": (2, 13, ("trot",), dict(real_time_it=1, max_iter=1, max_qp_iter=2, warm_start_qp=0)),
 }
 
@@ -48,7 +51,7 @@ def run_case(name):
     x, u, pi, lam = s.get_solution()
     st = s.get_stats()
     return batch, dict(inputs_sha256=np.array(digest(batch)), feet=feet, com=com, hg=hg, status=status, x=x, u=u,
-                       pi=pi, lam=lam, sqp_iter=st["sqp_iter"], qp_iter=st["qp_iter"], res=st["res"])
+                       pi=pi, lam=lam, sqp_iter=st["sqp_iter"], qp_iter=st["qp_iter"], res=st["res"], qp_ncond=st["qp_ncond"])
 
 
 if __name__ == "__main__":

@@ -21,9 +21,9 @@ names = ["0 update", "1 bwd: vec loads", "2 bwd: wait SR", "3 bwd: residual part
 out = (C.c_ulonglong * 24)()
 for rep in range(2):
     WL.load_into(s, batch, hg)
-    lib.nmpc_debug_phase_cycles(out, 3)
+    lib.nmpc_debug_phase_cycles(out, 1)
     s.solve()
-    lib.nmpc_debug_phase_cycles(out, 2)
+    lib.nmpc_debug_phase_cycles(out, 0)
     v = np.array(list(out), dtype=float)[:20]
     tot = v.sum()
     print(f"rep {rep}: B={B} total {tot/1e6:.2f} Mcycles for one QP (CTA 0), {tot/6/1e3:.0f} kcycles per IPM iteration")

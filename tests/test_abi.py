@@ -39,9 +39,10 @@ def test_binding_table_covers_header():
 
 def test_opts_struct_layout_matches_header():
     from iterative_learning_nmpc_b200._lib import NmpcOpts
-    # 8 x int32 followed by 8 x double, no padding
-    assert C.sizeof(NmpcOpts) == 8 * 4 + 8 * 8
-    assert NmpcOpts.dt_nodes.offset == 32 and NmpcOpts.mu_contact.offset == 32 + 7 * 8
+    # 10 x int32 followed by 8 x double, no padding
+    assert C.sizeof(NmpcOpts) == 10 * 4 + 8 * 8
+    assert NmpcOpts.warm_start_first_qp.offset == 32 and NmpcOpts.cond_pred_corr.offset == 36
+    assert NmpcOpts.dt_nodes.offset == 40 and NmpcOpts.mu_contact.offset == 40 + 7 * 8
 
 
 def test_version_and_argument_errors(lib):

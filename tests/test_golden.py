@@ -19,8 +19,7 @@ def _load(name):
     return dict(np.load(os.path.join(HERE, "golden", name + ".npz")))
 
 
-def rel_err(a, b):
-    return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1.0))
+from parity_metric import rel_err  # noqa: E402  per problem, per block (tests/parity_metric.py)
 
 
 @pytest.mark.parametrize("name", sorted(MG.CASES))

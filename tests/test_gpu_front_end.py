@@ -13,9 +13,7 @@ pytestmark = pytest.mark.gpu
 REL = 1e-6
 
 
-def rel_err(a, b):
-    a, b = np.asarray(a, float), np.asarray(b, float)
-    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1.0))
+from parity_metric import rel_err, report  # noqa: E402  per problem, per block (tests/parity_metric.py)
 
 
 def _on_oracle(obj):
