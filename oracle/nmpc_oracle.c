@@ -692,12 +692,15 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
     info->iter = it;
 }
 
+#include "nmpc_oracle_fast.h"
+
 /* ------------------------------------------------------------------------------------------ */
 /* batch state ("handle")                                                                     */
 /* ------------------------------------------------------------------------------------------ */
 typedef struct {
     nmpc_opts o;
     int B, N;
+    int fast;                            /* 1: structured interior point (nmpc_oracle_fast.h), the timed CPU baseline */
     double *x, *u, *pi, *lam;            /* iterate */
     double *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;        /* stored QP solution (warm start) */
@@ -738,6 +741,14 @@ int oracle_set_opts(oracle_handle* h, const nmpc_opts* o)
 {
     if (!h || !o || o->n_nodes != h->N || o->enable_time_opt) return NMPC_EINVAL;
     h->o = *o;
+    return 0;
+}
+
+/* 0: dense restatement (the checker), 1: structured variant (timed CPU baseline; same iterates to rounding) */
+int oracle_set_fast(oracle_handle* h, int32_t fast)
+{
+    if (!h) return NMPC_EINVAL;
+    h->fast = fast != 0;
     return 0;
 }
 
@@ -933,7 +944,19 @@ static void nlp_residuals(const oracle_handle* h, int b, const workspace* w, dou
     res[0] = rs; res[1] = re; res[2] = ri; res[3] = rc; *cost = cst;
 }
 
-static void solve_one(oracle_handle* h, int b, workspace* w)
+/* one QP on the linearisation in w->lin, dense or structured */
+static void qp_solve(const oracle_handle* h, workspace* w, fast_ws* f, int N, const double* dx0, int warm,
+                     double (*z)[NZ], double (*pi)[NX], double (*lam)[2 * NG], double (*t)[2 * NG], qp_info* info)
+{
+    if (h->fast && f) {
+        int bad = 0;
+        for (int k = 0; k <= N; k++) bad |= sr_from_lin(&w->lin[k], k == N, h->o.dt_nodes, &f->sr[k]);
+        if (!bad) { qp_ipm_fast(w, f, &h->o, N, dx0, warm, z, pi, lam, t, info); return; }
+    }
+    qp_ipm(w, &h->o, N, dx0, warm, z, pi, lam, t, info);
+}
+
+static void solve_one(oracle_handle* h, int b, workspace* w, fast_ws* f)
 {
     const int N = h->N;
     const nmpc_opts* o = &h->o;
@@ -965,7 +988,7 @@ static void solve_one(oracle_handle* h, int b, workspace* w)
         /* acados ocp_nlp_sqp: "(typically) no warm start at first iteration" -- the QP solver's warm_start option
          * is forced to 0 for the first QP of a solve unless opts->warm_start_first_qp, then restored */
         const int warm = (it == 0 && !o->warm_start_first_qp) ? 0 : o->warm_start_qp;
-        qp_ipm(w, o, N, dx0, warm, qz, qpi, qlam, qt, &info);
+        qp_solve(h, w, f, N, dx0, warm, qz, qpi, qlam, qt, &info);
         h->qp_iter[b] = info.iter; h->qp_status[b] = info.status; h->qp_ncond[b] = info.ncond;
         memcpy(h->qp_res + 4 * b, info.res, sizeof(info.res));
         if (info.status != 0 && info.status != 1) { status = NMPC_STATUS_QP_FAILURE; it++; break; }
@@ -996,11 +1019,13 @@ int oracle_solve(oracle_handle* h, int32_t* status, int32_t n_threads)
 #endif
     {
         workspace* w = malloc(sizeof(workspace));
+        fast_ws* f = h->fast ? malloc(sizeof(fast_ws)) : NULL;
 #ifdef _OPENMP
 #pragma omp for schedule(dynamic)
 #endif
-        for (int b = 0; b < h->B; b++) solve_one(h, b, w);
+        for (int b = 0; b < h->B; b++) solve_one(h, b, w, f);
         free(w);
+        free(f);
     }
     if (status) memcpy(status, h->status, sizeof(int32_t) * h->B);
     return 0;
@@ -1085,6 +1110,7 @@ int oracle_solve_qp(oracle_handle* h, const double* BAbt, const double* RSQrq, c
 {
     const int N = h->N;
     workspace* w = malloc(sizeof(workspace));
+    fast_ws* f = h->fast ? malloc(sizeof(fast_ws)) : NULL;
     for (int b = 0; b < h->B; b++) {
         for (int k = 0; k <= N; k++) {
             stage_lin* s = &w->lin[k];
@@ -1110,15 +1136,16 @@ int oracle_solve_qp(oracle_handle* h, const double* BAbt, const double* RSQrq, c
             }
         }
         qp_info info;
-        qp_ipm(w, &h->o, N, dx0 + (size_t)b * NX, 0,
-               (double (*)[NZ])(dz + (size_t)b * (N + 1) * NZ), (double (*)[NX])(pi + (size_t)b * N * NX),
-               (double (*)[2 * NG])(lam + (size_t)b * (N + 1) * 2 * NG),
-               (double (*)[2 * NG])(t + (size_t)b * (N + 1) * 2 * NG), &info);
+        qp_solve(h, w, f, N, dx0 + (size_t)b * NX, 0,
+                 (double (*)[NZ])(dz + (size_t)b * (N + 1) * NZ), (double (*)[NX])(pi + (size_t)b * N * NX),
+                 (double (*)[2 * NG])(lam + (size_t)b * (N + 1) * 2 * NG),
+                 (double (*)[2 * NG])(t + (size_t)b * (N + 1) * 2 * NG), &info);
         if (qp_iter) qp_iter[b] = info.iter;
         if (qp_status) qp_status[b] = info.status;
         if (qp_res) memcpy(qp_res + 4 * b, info.res, sizeof(info.res));
     }
     free(w);
+    free(f);
     return 0;
 }
 

@@ -68,7 +68,7 @@ def lib():
                      "oracle_pin_stance_feet", "oracle_set_guess", "oracle_reset_duals",
                      "oracle_shift_warm_start", "oracle_solve", "oracle_get_solution",
                      "oracle_get_stats", "oracle_get_qp_step", "oracle_export_qp", "oracle_solve_qp",
-                     "oracle_inverse_dynamics"):
+                     "oracle_inverse_dynamics", "oracle_set_fast"):
             getattr(_lib, name).restype = C.c_int
     return _lib
 
@@ -161,6 +161,10 @@ class OracleSolver:
         if getattr(self, "_h", None):
             lib().oracle_destroy(self._h)
             self._h = None
+
+    def set_fast(self, fast: bool = True):
+        """Structured interior point (nmpc_oracle_fast.h) instead of the dense restatement: the timed CPU baseline."""
+        assert lib().oracle_set_fast(self._h, C.c_int32(int(fast))) == 0
 
     def set_opts(self, opts: NmpcOpts):
         self.opts = opts

@@ -117,3 +117,36 @@ def test_nan_is_reported_not_propagated(oracle_mod, qp_case):
     assert r["qp_status"][1] == 3
     assert r["qp_status"][0] in (0, 1) and r["qp_status"][2] in (0, 1)
     assert np.isfinite(r["dz"][0]).all() and np.isfinite(r["dz"][2]).all()
+
+
+def test_structured_variant_reproduces_dense_restatement(oracle_mod):
+    """oracle/nmpc_oracle_fast.h (the timed CPU baseline and the host statement of the kernel's arithmetic) against
+    the dense restatement: same status / iteration counts, iterates equal to rounding on single QPs (RTI), cold and
+    with the conditional predictor-corrector path; a short hot-started chain inside 1e-6 for nine problems in ten."""
+    from parity_metric import chain_ok, rel_err
+    from iterative_learning_nmpc_b200 import workloads as WL
+    O = oracle_mod
+    B = 24
+    batch = WL.make_batch(B, seed=46, gaits=("trot", "pace", "bound"))
+    _, _, hg = O.kinematics(batch["qv"])
+
+    def run(fast, **opts):
+        s = O.OracleSolver(B, O.default_opts(**opts))
+        s.set_fast(fast)
+        WL.load_into(s, batch, hg)
+        st = s.solve(0)
+        return st, s.get_solution(), s.get_stats()
+
+    for opts in (dict(real_time_it=1), dict(real_time_it=1, max_qp_iter=2)):
+        (s0, sol0, st0), (s1, sol1, st1) = run(False, **opts), run(True, **opts)
+        np.testing.assert_array_equal(s0, s1)
+        np.testing.assert_array_equal(st0["qp_iter"], st1["qp_iter"])
+        for a, b in zip(sol1, sol0):
+            assert rel_err(a, b) < 1e-9
+    opts = dict(real_time_it=0, max_iter=3, warm_start_qp=2)
+    (s0, sol0, st0), (s1, sol1, st1) = run(False, **opts), run(True, **opts)
+    np.testing.assert_array_equal(s0, s1)
+    np.testing.assert_array_equal(st0["qp_ncond"], st1["qp_ncond"])
+    assert st0["qp_ncond"].sum() > 0
+    for name, a, b in zip(("x", "u", "pi", "lam"), sol1, sol0):
+        assert chain_ok("fast vs dense " + name, a, b, 1e-6)
