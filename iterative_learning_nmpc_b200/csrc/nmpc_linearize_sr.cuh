@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
             if (r == 0) {
                 double jn = 0.0;
                 for (int i = 0; i < 3; i++) jn += n[i] * FJ[(3 * ft + i) * NQ + j];
-                S[SR_CX + 36 * (row - NGF) + j] = jn;
+                S[SR_CX + SR_CXLD * (row - NGF) + j] = jn;
             } else {
                 const double* t = (r == 1) ? t1 : t2;
                 double vq = 0.0, vv = 0.0;
@@ -252,8 +252,8 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
                     vq += t[i] * FVQ[(3 * ft + i) * NQ + j];
                     vv += t[i] * FJ[(3 * ft + i) * NQ + j];
                 }
-                S[SR_CX + 36 * (row - NGF) + j] = vq;
-                S[SR_CX + 36 * (row - NGF) + NQ + j] = vv;
+                S[SR_CX + SR_CXLD * (row - NGF) + j] = vq;
+                S[SR_CX + SR_CXLD * (row - NGF) + NQ + j] = vv;
             }
         }
         if (tid < NF * 3) {
@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
                 j2 += t2[i] * FJ[(3 * ft + i) * NQ + j];
             }
             const int row = GR_PATCH + ft;
-            S[SR_CX + 36 * (row - NGF) + j] = 2 * d1 * j1 + 2 * d2 * j2;
+            S[SR_CX + SR_CXLD * (row - NGF) + j] = 2 * d1 * j1 + 2 * d2 * j2;
             if (j == 0) {
                 const double cv = d1 * d1 + d2 * d2 - rad * rad;
                 lg[row] = -cv; ug[row] = -cv; mu[row] = 1.0;
@@ -299,8 +299,8 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
         for (int e = tid; e < 6 * NQ; e += LIN_SR_THREADS) {
             const int i = e / NQ, j = e % NQ;
             const int row = GR_CONS + i;
-            S[SR_CX + 36 * (row - NGF) + j] = -HQ[i * NQ + j];
-            S[SR_CX + 36 * (row - NGF) + NQ + j] = -HV[i * NQ + j];
+            S[SR_CX + SR_CXLD * (row - NGF) + j] = -HQ[i * NQ + j];
+            S[SR_CX + SR_CXLD * (row - NGF) + NQ + j] = -HV[i * NQ + j];
             if (j == 0) {
                 const double cv = hh[i] - HM[i];
                 lg[row] = -cv; ug[row] = -cv; ml[row] = 1.0; mu[row] = 1.0;

@@ -37,20 +37,20 @@
 #define SR_QQ (SR_QH + 6)            // [18][18] Hessian, q block (full symmetric)
 #define SR_GR (SR_QQ + NQ * NQ)      // [72]     gradient
 #define SR_CF (SR_GR + NZ)           // [20][3]  friction rows over their foot's force
-#define SR_CX (SR_CF + 20 * 3)       // [22][36] contact / patch / centroidal rows over (q, v)
-#define SR_D (SR_CX + 22 * 36)       // lg[42] ug[42] mask_l[42] mask_u[42]
-#define SR_SZ (SR_D + 4 * NG)        // 1692
+#define SR_CXLD 37                   // row stride of CX: 36 + 1, so that thread-per-row and thread-per-column reads are both free of bank conflicts
+#define SR_CX (SR_CF + 20 * 3)       // [22][37] contact / patch / centroidal rows over (q, v)
+#define SR_D (SR_CX + 22 * SR_CXLD)       // lg[42] ug[42] mask_l[42] mask_u[42]
+#define SR_SZ (SR_D + 4 * NG)        // 1714
 #define NGX 22                       // constraint rows on the state
 #define NGF 20                       // friction rows
 
-// factor record (doubles): u panels of the stage factor (Luu, Lxu, row 72 = lu) | P | p
-#define FR_MU 0
+// factor record (doubles): u panels of the stage factor (Luu, Lxu, row 72 = lu) | cost-to-go Hessian P_k
 #define P_LD 43
+#define FR_MU 0
 #define FR_P (FR_MU + LP_UPANELS)            // 1830
-#define FR_PV (FR_P + NX * P_LD)             // 3636
-#define FR_SZ (FR_PV + NX + 2)               // 3680
+#define FR_SZ 3680                           // 1830 + 42 * 43 = 3636, padded
 
-static_assert(SR_SZ % 2 == 0 && FR_P % 2 == 0 && FR_PV % 2 == 0 && FR_SZ % 2 == 0, "16-byte alignment of bulk copies");
+static_assert(SR_SZ % 2 == 0 && SR_CF % 2 == 0 && FR_P % 2 == 0 && FR_SZ % 2 == 0, "16-byte alignment of bulk copies");
 
 // ---------------------------------------------------------------------------------------------
 // dense stage blocks -> stage record (used for externally supplied QPs and, for now, after the
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(128) nmpc_dense2sr_kernel(SrArgs a)
     for (int e = tid; e < NQ * NQ; e += 128) S[SR_QQ + e] = Mp[(IQ + e / NQ) * M_LD + IQ + e % NQ];
     for (int e = tid; e < NZ; e += 128) S[SR_GR + e] = Mp[NZ * M_LD + e];
     for (int e = tid; e < NGF * 3; e += 128) { const int j = e / 3; S[SR_CF + e] = Cp[j * C_LD + IFRC + 3 * (j / 5) + e % 3]; }
-    for (int e = tid; e < NGX * 36; e += 128) S[SR_CX + e] = Cp[(NGF + e / 36) * C_LD + IQ + e % 36];
+    for (int e = tid; e < NGX * 36; e += 128) S[SR_CX + SR_CXLD * (e / 36) + e % 36] = Cp[(NGF + e / 36) * C_LD + IQ + e % 36];
     for (int e = tid; e < 4 * NG; e += 128) S[SR_D + e] = Dp[e];
     if (!a.check) return;
     // ---- structure check: the dense blocks must be exactly what the record expands to ----
@@ -137,59 +137,6 @@ __global__ void __launch_bounds__(128) nmpc_dense2sr_kernel(SrArgs a)
 // ---------------------------------------------------------------------------------------------
 // fused IPM kernel
 // ---------------------------------------------------------------------------------------------
-#define FQ_THREADS 128
-#define FQ_WARPS (FQ_THREADS / 32)
-#define N_UTILES 100                 // 3x6 tiles of rows 0..71 x columns 0..29 at or below the diagonal
-#define N_XTILES 105                 // 3x3 tiles of the lower triangle of the 42x42 state block
-
-struct FqArgs {
-    const double* SR;               // [Bc][N+1][SR_SZ]
-    double* FR;                     // [Bc][N+1][FR_SZ]
-    double* vec;                    // [Bc][(N+1)*V_STAGE]
-    double* qz; double* qpi; double* qlam; double* qt;       // QP iterate, global problem index
-    int32_t* qp_iter; int32_t* qp_status; int32_t* qp_ncond; double* qp_res;
-    const double* dx0_ext; const double* x0; const double* x;
-    const int32_t* sqp_done;
-    int N, b0, max_iter, warm, cond_pred_corr;   // warm: HPIPM warm_start level 0 / 1 / 2 (see nmpc_b200.h)
-    double tol, dt, c2;              // c2 = dt^2 / 2 (host-computed: both stay constant-bank operands)
-};
-
-// shared memory carve-up (doubles)
-#define FS_P 0                               // P_{k+1}, full symmetric, ld 43
-#define FS_M (FS_P + NX * P_LD)              // u panels of the stage matrix (LP_UPANELS); before the
-                                             // factorisation the same space holds U and PGh
-#define FS_SR (FS_M + LP_UPANELS)            // stage record
-#define FS_V (FS_SR + SR_SZ)                 // vectors
-#define FS_U FS_M                            // U[42][30] = P[:,h] [Hf | Hq]   (ld 30)
-#define FS_PGH (FS_U + NX * NU)              // PGh[6][72] = (P G)[h rows]     (1260 + 432 <= 1830)
-// vectors
-#define FV_Z 0
-#define FV_ZXN (FV_Z + NZ)
-#define FV_PIK (FV_ZXN + NX)
-#define FV_PIN (FV_PIK + NX)
-#define FV_LAM (FV_PIN + NX)
-#define FV_T (FV_LAM + 2 * NG)
-#define FV_CZ (FV_T + 2 * NG)
-#define FV_RD (FV_CZ + NG)
-#define FV_RM (FV_RD + 2 * NG)
-#define FV_GAM (FV_RM + 2 * NG)
-#define FV_GAMV (FV_GAM + NG)
-#define FV_DL (FV_GAMV + NG)
-#define FV_RG (FV_DL + NG)
-#define FV_QT (FV_RG + NZ)                   // m: linear term, row 72 of the stage matrix (NZ)
-#define FV_RB (FV_QT + NZ)
-#define FV_W (FV_RB + NX)
-#define FV_PN (FV_W + NX)                    // p_{k+1}
-#define FV_DX (FV_PN + NX)
-#define FV_DXN (FV_DX + NX)
-#define FV_DZ (FV_DXN + NX)
-#define FV_RED (FV_DZ + NZ)                  // 16 reduction slots
-#define FV_END (FV_RED + 16)
-// per-thread running norms / complementarity sum of the backward pass (5 x 128): in shared memory rather than in
-// registers that would be spilled across the panel factorisation of every stage
-#define FS_ACC (FS_V + FV_END)
-#define FQ_SMEM_BYTES ((FS_ACC + 5 * FQ_THREADS) * 8)
-
 // C z for the current stage: sv[FV_CZ + j] = sum_c C(j, c) zz[c], zz over [u; x]
 __device__ __forceinline__ void fq_cz(const double* S, const double* zz, double* out, int tid)
 {
@@ -201,7 +148,7 @@ __device__ __forceinline__ void fq_cz(const double* S, const double* zz, double*
             const double* f = zz + IFRC + 3 * (j / 5);
             s0 = cf[0] * f[0] + cf[1] * f[1] + cf[2] * f[2];
         } else {
-            const double* cx = S + SR_CX + 36 * (j - NGF);
+            const double* cx = S + SR_CX + SR_CXLD * (j - NGF);
             const double* xx = zz + IQ;
 #pragma unroll
             for (int c = 0; c < 36; c += 4) {
@@ -228,7 +175,7 @@ __device__ __forceinline__ double fq_ct(const double* S, const double* g, int c)
         const double* cx = S + SR_CX + (c - IQ);
         double s1 = 0.0;
 #pragma unroll
-        for (int jj = 0; jj < NGX; jj += 2) { s += cx[36 * jj] * g[NGF + jj]; s1 += cx[36 * (jj + 1)] * g[NGF + jj + 1]; }
+        for (int jj = 0; jj < NGX; jj += 2) { s += cx[SR_CXLD * jj] * g[NGF + jj]; s1 += cx[SR_CXLD * (jj + 1)] * g[NGF + jj + 1]; }
         return s + s1;
     }
     return g[GR_CONS + c - IH];
@@ -287,7 +234,7 @@ __device__ __forceinline__ double fq_h(const double* S, const double* zz, int c)
     return S[SR_QH + c - IH] * zz[c];
 }
 
-__device__ __forceinline__ double fq_block_max(double v, double* red, int tid)
+__device__ __noinline__ double fq_block_max(double v, double* red, int tid)
 {
     v = warp_max(v);
     __syncthreads();
@@ -295,7 +242,7 @@ __device__ __forceinline__ double fq_block_max(double v, double* red, int tid)
     __syncthreads();
     return nanmax(nanmax(red[0], red[1]), nanmax(red[2], red[3]));
 }
-__device__ __forceinline__ double fq_block_min(double v, double* red, int tid)
+__device__ __noinline__ double fq_block_min(double v, double* red, int tid)
 {
     v = warp_min(v);
     __syncthreads();
@@ -303,96 +250,13 @@ __device__ __forceinline__ double fq_block_min(double v, double* red, int tid)
     __syncthreads();
     return fmin(fmin(red[0], red[1]), fmin(red[2], red[3]));
 }
-__device__ __forceinline__ double fq_block_sum(double v, double* red, int tid)
+__device__ __noinline__ double fq_block_sum(double v, double* red, int tid)
 {
     v = warp_sum(v);
     __syncthreads();
     if ((tid & 31) == 0) red[tid >> 5] = v;
     __syncthreads();
     return ((red[0] + red[1]) + red[2]) + red[3];
-}
-
-// ---------------------------------------------------------------------------------------------
-// forward sweep, one stage.  In: sM = u panels of stage k (Luu, Lxu, row 72 = lu), S = SR_k,
-// sv[FV_DX] = dx_k, sv[FV_RB] = rb_k; CORR: sP = P_k, sv[FV_PN] = p_k.
-// Out: dz_k, dt_k, dlam_k (and CORR: dpi_{k-1}) to the stage vectors, step-length candidates
-// folded into a_p / a_d, sv[FV_DX] = dx_{k+1}.
-// ---------------------------------------------------------------------------------------------
-template <bool CORR>
-__device__ __forceinline__ void fq_forward_stage(const double* sM, const double* sP, const double* S, double* sv,
-                                                 double* vk, double* dpi_prev, const double* qlam, const double* qt,
-                                                 bool term, int tid, double dt, double c2, double& a_p, double& a_d,
-                                                 double (&cs)[3])
-{
-    const int lane = tid & 31;
-    // this thread's multiplier data, requested before the serial chain below so that the loads are not on it
-    double g_lam = 0.0, g_t = 1.0, g_rd = 0.0, g_rm = 0.0;
-    if (tid < 2 * NG) { g_lam = qlam[tid]; g_t = qt[tid]; g_rd = vk[V_RD + tid]; g_rm = vk[V_RM + tid]; }
-    if (CORR && dpi_prev && tid >= 64 && tid < 64 + NX) {           // dpi_{k-1} = P_k dx_k + p_k
-        const int i = tid - 64;
-        const double* row = sP + i * P_LD;
-        double s0 = sv[FV_PN + i], s1 = 0.0;
-#pragma unroll
-        for (int j = 0; j < NX; j += 2) { s0 += row[j] * sv[FV_DX + j]; s1 += row[j + 1] * sv[FV_DX + j + 1]; }
-        dpi_prev[i] = s0 + s1;
-    }
-    if (!term) {
-        if (tid < 32) {             // du = -Luu^-T (lu + Lxu' dx)
-            double rhs = 0.0;
-            if (lane < NU) {
-                double r1 = 0.0;
-                rhs = sM[lp_idx(NZ, lane)];
-                for (int l = 0; l < NX; l += 2) {
-                    rhs += sM[lp_idx(NU + l, lane)] * sv[FV_DX + l];
-                    r1 += sM[lp_idx(NU + l + 1, lane)] * sv[FV_DX + l + 1];
-                }
-                rhs += r1;
-            }
-            // back substitution with Luu': branch-free, one shuffle + multiply + fused multiply-add per step;
-            // lane l keeps rhs_l * (1 / L_ll) ready so the broadcast value is already the solution component
-            double du = 0.0, myinv = 0.0;
-            const int ll = lane < NU ? lane : NU - 1;
-            { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
-            // L(i, ll) for i >= ll sits at colb + 6 i (panel-packed, 6 doubles per row): one register instead of a
-            // table of 30 per-lane addresses, which the compiler hoisted out of the stage loop and kept in local memory
-            const double* colb = sM + P_OFF(ll / PB) - PB * PB * (ll / PB) + ll % PB;
-#pragma unroll
-            for (int i = NU - 1; i >= 0; i--) {
-                const double dui = -__shfl_sync(0xffffffffu, rhs * myinv, i);
-                const double lv = (lane < i) ? colb[PB * i] : 0.0;
-                du = (lane == i) ? dui : du;
-                rhs = (lane < i) ? fma(lv, dui, rhs) : rhs;
-            }
-            if (lane < NU) sv[FV_DZ + lane] = du;
-        }
-    } else if (tid < NU) sv[FV_DZ + tid] = 0.0;
-    if (tid >= 32 && tid < 32 + NX) sv[FV_DZ + NU + tid - 32] = sv[FV_DX + tid - 32];
-    __syncthreads();
-    if (tid < NZ) vk[V_DZ + tid] = sv[FV_DZ + tid];
-    fq_cz(S, sv + FV_DZ, sv + FV_CZ, tid);                           // threads 0..41
-    if (!term && tid >= 64 && tid < 64 + NX) {                      // dx+ = G dz + rb
-        const int l = tid - 64;
-        sv[FV_DXN + l] = fq_g(S, sv + FV_DZ, l, dt, c2) + sv[FV_RB + l];
-    }
-    __syncthreads();
-    if (tid < 2 * NG) {
-        const int e = tid / NG, j = tid % NG;
-        double dtv = 0.0, dl = 0.0;
-        if (S[SR_D + 2 * NG + tid] > 0.5) {
-            const double lam = g_lam, t = g_t;
-            const double cdz = sv[FV_CZ + j];
-            dtv = (e ? -cdz : cdz) + g_rd;
-            dl = -(g_rm + lam * dtv) / t;
-            if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
-            if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
-            // sum (lam + a dlam)(t + a dt) = cs0 + a cs1 + a^2 cs2: neither the centring parameter (affine sweep) nor the
-            // conditional predictor-corrector test (corrector sweep) needs an extra pass over the stages
-            cs[0] = fma(lam, t, cs[0]); cs[1] += fma(lam, dtv, t * dl); cs[2] = fma(dl, dtv, cs[2]);
-        }
-        vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
-    }
-    if (!term && tid < NX) sv[FV_DX + tid] = sv[FV_DXN + tid];
-    __syncthreads();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -476,67 +340,343 @@ __device__ __forceinline__ void fq_asm_x(const double* sP, const double* sU, con
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// fused IPM kernel: one persistent CTA per OCP-QP.  An IPM iteration is a sequence of PASSES over the stages:
+//
+//   R   k = N..0  bulk   apply the previous step; residuals rd rm rg rb, Gamma, q~, norms, mu       (pipelined)
+//       exit tests
+//   F   k = N..0  CHAIN  Riccati factorisation on P (the only pass with a long per-stage chain); leaves per stage
+//                        the feedback gain K = Luu^-T Lxu', W = Luu^-1, P_k and P_{k+1} rb_k
+//   A1  k = 0..N  chain  affine direction: du = -(kff + K dx), dx+ = G dz + rb   (two short phases per stage)
+//   A2  all k     bulk   C dz, dt, dlam, step lengths, sums for the centring parameter               (pipelined)
+//   C1  all k     bulk   corrector complementarity residual, gamma_c, m0 = rg + C' gamma_c + G' P+ rb (pipelined)
+//   C2  k = N..0  chain  p_k = m_x - K' m_u with m = m0 + G' p+;  off the chain: kff = W' W m_u
+//   D1  k = 0..N  chain  corrector direction (as A1)
+//   D2  all k     bulk   dpi_{k-1} = P_k dx_k + p_k, C dz, dt, dlam, step lengths                    (pipelined)
+//
+// Only F carries the long dependent chain; in every other pass the serial dependence between stages is a handful
+// of short dot products (no triangular solve: the gains are explicit), and everything that does not depend on the
+// neighbouring stage is done in a bulk pass whose inputs arrive through a ring of bulk (TMA) copies several stages
+// ahead.  Every pass is a separate non-inlined function: the register peak of the factorisation does not leak.
+// ---------------------------------------------------------------------------------------------
+#define FQ_THREADS 128
+#define FQ_WARPS (FQ_THREADS / 32)
+#define N_UTILES 100                 // 3x6 tiles of rows 0..71 x columns 0..29 at or below the diagonal
+#define N_XTILES 105                 // 3x3 tiles of the lower triangle of the 42x42 state block
+
+struct FqArgs {
+    const double* SR;               // [Bc][N+1][SR_SZ]
+    double* FR;                     // [Bc][N+1][FR_SZ]
+    double* vec;                    // [Bc][(N+1)*V_STAGE]
+    double* qz; double* qpi; double* qlam; double* qt;       // QP iterate, global problem index
+    int32_t* qp_iter; int32_t* qp_status; int32_t* qp_ncond; double* qp_res;
+    const double* dx0_ext; const double* x0; const double* x;
+    const int32_t* sqp_done;
+    int N, b0, max_iter, warm, cond_pred_corr;   // warm: HPIPM warm_start level 0 / 1 / 2 (see nmpc_b200.h)
+    double tol, dt, c2;              // c2 = dt^2 / 2
+};
+
+// per-CTA context in shared memory: base pointers of this OCP (no registers held across the passes)
+struct FqCtx {
+    const double* SRb; double* FRb; double* vb; double* qz; double* qpi; double* qlam; double* qt;
+    double dt, c2;
+    int N;
+};
+
+extern __shared__ __align__(16) double fq_smem[];
+__shared__ FqCtx fq_ctx;
+__shared__ __align__(8) uint64_t fq_bars[4];
+
+#define FQ_SMEM_DOUBLES 7096
+#define FQ_SMEM_BYTES (FQ_SMEM_DOUBLES * 8)
+#define FQ_ISSUER 96                         // the thread that issues the bulk copies of the rings: first lane of warp 3, whose
+                                             // lanes have the least work in every pass (thread 0 is on every critical path)
+#define FQ_RED (FQ_SMEM_DOUBLES - 16)        // 16 reduction slots, the same place in every pass
+
+// ---- pass R: ring of 2 slots (a stage of this pass takes far longer than the latency of its copies) ----
+#define R_SR 0
+#define R_Z (R_SR + SR_SZ)
+#define R_DZ (R_Z + NZ)
+#define R_PI (R_DZ + NZ)                     // pi_{k-1}
+#define R_DPI (R_PI + NX)
+#define R_LAM (R_DPI + NX)
+#define R_T (R_LAM + 2 * NG)
+#define R_DT (R_T + 2 * NG)                  // dt | dlam
+#define R_SLOT (R_DT + 4 * NG)               // 2256
+#define R_DEPTH 2
+#define RV_BASE (R_DEPTH * R_SLOT)           // 6768
+#define RV_ZC 0                              // [2][72] updated z_k, ping-pong by stage parity (x part = "next state" of stage k-1)
+#define RV_PIN (RV_ZC + 2 * NZ)              // [2][42] updated pi_{k-1}, ping-pong
+#define RV_CZ (RV_PIN + 2 * NX)              // 42: C z, then lam_l - lam_u
+#define RV_GAMV (RV_CZ + NG)                 // 42
+#define RV_END (RV_GAMV + NG)                // 312
+static_assert(RV_BASE + RV_END <= FQ_RED, "pass R shared memory");
+static_assert(R_SLOT % 2 == 0 && R_PI % 2 == 0 && R_DPI % 2 == 0 && R_LAM % 2 == 0, "alignment");
+
+// ---- pass F ----
+#define F_P 0                                // P_{k+1}, full symmetric, ld 43
+#define F_M (F_P + NX * P_LD)                // u panels of the stage matrix; before the factorisation U = P[:,h][Hf|Hq]; after it K | W
+#define F_S (F_M + LP_UPANELS)               // stage record | QT GAM KFF RB of the stage (186)
+#define F_SV (F_S + SR_SZ)
+#define F_V (F_SV + 186)
+#define FV_QT 0                              // 72  working linear term m (row 72 of the stage matrix)
+#define FV_W (FV_QT + NZ)                    // 42
+#define FV_PN (FV_W + NX)                    // 42  p_{k+1}
+#define FV_END (FV_PN + NX)
+static_assert(F_V + FV_END <= FQ_RED, "pass F shared memory");
+
+// ---- passes A1 / D1: ring of 3 slots ----
+#define A_MU 0                               // u panels of the stage factor: Luu, Lxu
+#define A_H (A_MU + LP_UPANELS)              // Hq | Hf (180)
+#define A_LU (A_H + 180)                     // lu of this direction
+#define A_RB (A_LU + NU)
+#define A_SLOT (A_RB + NX)                   // 2082
+#define A_DEPTH 3
+#define AV_BASE (A_DEPTH * A_SLOT)
+#define AV_DX 0                              // [2][42]
+#define AV_DZ (AV_DX + 2 * NX)               // 72
+static_assert(AV_BASE + AV_DZ + NZ <= FQ_RED, "pass A1 shared memory");
+
+// ---- pass A2: ring of 4 slots ----
+#define B_C 0                                // constraint part of the stage record: SR_CF .. SR_SZ (1020)
+#define SR_CSZ (SR_SZ - SR_CF)
+#define B_DZ (B_C + SR_CSZ)                  // DZ RD RM (240)
+#define B_RD (B_DZ + NZ)
+#define B_RM (B_RD + 2 * NG)
+#define B_LAM (B_RM + 2 * NG)
+#define B_T (B_LAM + 2 * NG)
+#define B_SLOT (B_T + 2 * NG)                // 1428
+#define B_DEPTH 4
+#define BV_BASE (B_DEPTH * B_SLOT)
+static_assert(BV_BASE + NG <= FQ_RED, "pass A2 shared memory");
+
+// ---- pass C1: ring of 4 slots ----
+#define C_H 0
+#define C_C (C_H + 180)
+#define C_RG (C_C + SR_CSZ)                  // RG PRB (114)
+#define C_PRB (C_RG + NZ)
+#define C_DT (C_PRB + NX)                    // DT DLAM (168)
+#define C_DLAM (C_DT + 2 * NG)
+#define C_RD (C_DLAM + 2 * NG)
+#define C_LAM (C_RD + 2 * NG)
+#define C_T (C_LAM + 2 * NG)
+#define C_SLOT (C_T + 2 * NG)                // 1734
+#define C_DEPTH 4
+#define CV_BASE (C_DEPTH * C_SLOT)           // 6936
+static_assert(CV_BASE + NG <= FQ_RED, "pass C1 shared memory");
+
+// ---- pass C2: ring of 3 slots ----
+#define E_MU 0
+#define E_H (E_MU + LP_UPANELS)
+#define E_M0 (E_H + 180)
+#define E_SLOT (E_M0 + NZ)                   // 2082
+#define E_DEPTH 3
+#define EV_BASE (E_DEPTH * E_SLOT)           // 6246
+#define EV_M 0                               // 72
+#define EV_PN (EV_M + NZ)                    // [2][42]
+#define EV_LU (EV_PN + 2 * NX)               // 32
+static_assert(EV_BASE + EV_LU + 32 <= FQ_RED, "pass C2 shared memory");
+
+// ---- pass D2: ring of 2 slots ----
+#define D_P 0
+#define D_C (D_P + NX * P_LD)
+#define D_DZ (D_C + SR_CSZ)
+#define D_RD (D_DZ + NZ)
+#define D_RM (D_RD + 2 * NG)
+#define D_LAM (D_RM + 2 * NG)
+#define D_T (D_LAM + 2 * NG)
+#define D_PV (D_T + 2 * NG)
+#define D_SLOT (D_PV + NX)                   // 3276
+#define D_DEPTH 2
+#define DV_BASE (D_DEPTH * D_SLOT)
+static_assert(DV_BASE + NG <= FQ_RED, "pass D2 shared memory");
+
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+__device__ __noinline__ void fq_mbar_wait(uint32_t slot, uint32_t parity) { mbar_wait(&fq_bars[slot], parity); }
+
+__device__ __forceinline__ void fq_ring_wait(int slot, uint32_t& ph)
+{
+    fq_mbar_wait(slot, (ph >> slot) & 1u);
+    ph ^= (1u << slot);
+}
+
+// end of a pass: this thread's global and shared writes become visible to the bulk copies of the next pass
+__device__ __forceinline__ void fq_pass_end()
+{
+    fence_proxy_async_all();
+    __syncthreads();
+}
+
 #ifdef NMPC_TIMING
 __device__ unsigned long long g_fq_cycles[24];
-#define FMARK(ph) do { const long long t_ = clock64(); f_acc[ph] += (unsigned long long)(t_ - f_prev); f_prev = t_; } while (0)
+__shared__ unsigned long long fq_tacc[24];
+__shared__ long long fq_tprev;
+#define FMARK(ph_) do { if (threadIdx.x == 0) { const long long t_ = clock64(); fq_tacc[ph_] += (unsigned long long)(t_ - fq_tprev); fq_tprev = t_; } } while (0)
 #else
-#define FMARK(ph) do { } while (0)
+#define FMARK(ph_) do { } while (0)
 #endif
 
-__device__ __forceinline__ int fq_opaque(int v) { asm volatile("" : "+r"(v)); return v; }
-
-__global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
+// =============================================================================================
+// pass R: update with the previous step, residuals of every stage, norms
+// out: [0] |rg| [1] |rb| [2] |rd| [3] |rm| [4] sum lam t [5] number of constraint sides
+// =============================================================================================
+__device__ __noinline__ void fq_issue_R(int k, int slot, bool upd)
 {
-#ifdef NMPC_TIMING
-    unsigned long long f_acc[24];
-#pragma unroll
-    for (int i = 0; i < 24; i++) f_acc[i] = 0ULL;
-    long long f_prev = clock64();
-#endif
-    extern __shared__ __align__(16) double smem[];
-    __shared__ __align__(8) uint64_t bar;
+    const FqCtx& c = fq_ctx;
+    double* sl = fq_smem + slot * R_SLOT;
+    uint64_t* bar = &fq_bars[slot];
+    uint32_t bytes = (SR_SZ + NZ + 4 * NG) * 8;
+    if (upd) bytes += (NZ + 4 * NG) * 8;
+    if (k > 0) bytes += (upd ? 2 : 1) * NX * 8;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_g2s(sl + R_SR, c.SRb + (size_t)k * SR_SZ, SR_SZ * 8, bar);
+    bulk_g2s(sl + R_Z, c.qz + (size_t)k * NZ, NZ * 8, bar);
+    bulk_g2s(sl + R_LAM, c.qlam + (size_t)k * 2 * NG, 2 * NG * 8, bar);
+    bulk_g2s(sl + R_T, c.qt + (size_t)k * 2 * NG, 2 * NG * 8, bar);
+    if (k > 0) bulk_g2s(sl + R_PI, c.qpi + (size_t)(k - 1) * NX, NX * 8, bar);
+    if (upd) {
+        const double* vk = c.vb + (size_t)k * V_STAGE;
+        bulk_g2s(sl + R_DZ, vk + V_DZ, NZ * 8, bar);
+        bulk_g2s(sl + R_DT, vk + V_DT, 4 * NG * 8, bar);
+        if (k > 0) bulk_g2s(sl + R_DPI, vk - V_STAGE + V_DPI, NX * 8, bar);
+    }
+}
+
+__device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double alpha_p, double alpha_d, double* out)
+{
     const int tid = threadIdx.x;
-    const int bl = blockIdx.x, b = a.b0 + bl, N = a.N;
-    if (a.sqp_done && a.sqp_done[b]) return;             // finished problems keep their statistics
-    double* sP = smem + FS_P;
-    double* sM = smem + FS_M;
-    double* S = smem + FS_SR;
-    double* sv = smem + FS_V;
-    double* sU = smem + FS_U;
-    double* red = sv + FV_RED;
-    const double dt = a.dt, c2 = a.c2;
-    const int tid_k = tid;
+    const int N = fq_ctx.N;
+    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
+    double* rv = fq_smem + RV_BASE;
+    double* red = fq_smem + FQ_RED;
+    const bool upd = it > 0;
+    double n_g = 0.0, n_b = 0.0, n_d = 0.0, n_m = 0.0, s_m = 0.0;
+    int cnt = 0;
+    if (tid == FQ_ISSUER)
+        for (int i = 0; i < R_DEPTH - 1 && i <= N; i++) fq_issue_R(N - i, i % R_DEPTH, upd);
+    for (int i = 0; i <= N; i++) {
+        const int k = N - i, slot = i % R_DEPTH;
+        const bool term = (k == N);
+        if (tid == FQ_ISSUER && i + R_DEPTH - 1 <= N) fq_issue_R(k - (R_DEPTH - 1), (i + R_DEPTH - 1) % R_DEPTH, upd);
+        fq_ring_wait(slot, ph);
+        const double* sl = fq_smem + slot * R_SLOT;
+        const double* S = sl + R_SR;
+        double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
+        double* zc = rv + RV_ZC + (k & 1) * NZ;
+        const double* zxn = rv + RV_ZC + ((k + 1) & 1) * NZ + NU;
+        double* pik = rv + RV_PIN + (k & 1) * NX;
+        const double* pin = rv + RV_PIN + ((k + 1) & 1) * NX;
+        // ---- step 1: the updated primal iterate and dynamics multiplier of the stage ----
+        if (tid < NZ) {
+            double z = sl[R_Z + tid];
+            if (upd) { z = fma(alpha_p, sl[R_DZ + tid], z); fq_ctx.qz[(size_t)k * NZ + tid] = z; }
+            zc[tid] = z;
+        } else if (tid >= 80 && tid < 80 + NX && k > 0) {
+            const int l = tid - 80;
+            double p = sl[R_PI + l];
+            if (upd) { p = fma(alpha_d, sl[R_DPI + l], p); fq_ctx.qpi[(size_t)(k - 1) * NX + l] = p; }
+            pik[l] = p;
+        }
+        __syncthreads();
+        // ---- step 2: C z; dynamics residual ----
+        fq_cz(S, zc, rv + RV_CZ, tid);
+        if (!term && tid >= 80 && tid < 80 + NX) {
+            const int l = tid - 80;
+            const double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
+            vk[V_RB + l] = rb;
+            n_b = nanmax(n_b, fabs(rb));
+        }
+        __syncthreads();
+        // ---- step 3: both sides of constraint row j: slacks, multipliers, rd, rm, Gamma, gamma ----
+        if (tid < NG) {
+            const int j = tid;
+            const double cz = rv[RV_CZ + j];
+            double Gam = 0.0, gam = 0.0, dl = 0.0;
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int row = e * NG + j;
+                const bool msk = S[SR_D + 2 * NG + row] > 0.5;
+                double t = sl[R_T + row], lam = sl[R_LAM + row];
+                if (upd && msk) {
+                    t = fmax(fma(alpha_p, sl[R_DT + row], t), IPM_T_MIN);
+                    lam = fmax(fma(alpha_d, sl[R_DT + 2 * NG + row], lam), IPM_LAM_MIN);
+                    fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
+                }
+                const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
+                if (it == 0) {               // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
+                    if (msk) {
+                        if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; }
+                        else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
+                    } else { t = 1.0; lam = 0.0; }
+                    fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
+                }
+                const double rd = msk ? (slack - t) : 0.0;
+                const double rm = msk ? lam * t : 0.0;
+                vk[V_RD + row] = rd; vk[V_RM + row] = rm;
+                s_m += rm; cnt += msk ? 1 : 0;
+                n_d = nanmax(n_d, fabs(rd));
+                n_m = nanmax(n_m, fabs(rm));
+                if (msk) {
+                    const double g = (rm + lam * rd) / t;
+                    Gam += lam / t;
+                    if (e) { gam -= g; dl -= lam; } else { gam += g; dl += lam; }
+                }
+            }
+            vk[V_GAM + j] = Gam;
+            rv[RV_GAMV + j] = gam; rv[RV_CZ + j] = dl;
+        }
+        __syncthreads();
+        // ---- step 4: stationarity residual and the linear term q~ = rg + C' gamma ----
+        if (tid < NZ) {
+            const int c = tid;
+            double s = S[SR_GR + c] + fq_h(S, zc, c);
+            if (c >= NU && k > 0) s -= pik[c - NU];
+            s -= fq_ct(S, rv + RV_CZ, c);
+            const double qp = fq_ct(S, rv + RV_GAMV, c);
+            if (!term) s += fq_gt(S, pin, c, dt, c2);
+            if ((k == 0 && c >= NU) || (term && c < NU)) s = 0.0;
+            vk[V_RG + c] = s; vk[V_QT + c] = qp + s;
+            n_g = nanmax(n_g, fabs(s));
+        }
+        __syncthreads();
+    }
+    out[0] = fq_block_max(n_g, red, tid);
+    out[1] = fq_block_max(n_b, red, tid);
+    out[2] = fq_block_max(n_d, red, tid);
+    out[3] = fq_block_max(n_m, red, tid);
+    out[4] = fq_block_sum(s_m, red, tid);
+    out[5] = (it == 0) ? fq_block_sum((double)cnt, red, tid) : 0.0;
+    fq_pass_end();
+    return ph;
+}
 
-    // Base pointers of this OCP are NOT kept in registers for the lifetime of the kernel (seven 64-bit values that the
-    // register peak of the panel factorisation would push into local memory): every use recomputes them from the
-    // kernel parameters (constant bank) and the block index, behind an opaque move so that they are not hoisted.
-#define SRb (a.SR + (size_t)fq_opaque(bl) * (N + 1) * SR_SZ)
-#define FRb (a.FR + (size_t)fq_opaque(bl) * (N + 1) * FR_SZ)
-#define vb (a.vec + (size_t)fq_opaque(bl) * (N + 1) * V_STAGE)
-#define qz (a.qz + (size_t)fq_opaque(b) * (N + 1) * NZ)
-#define qpi (a.qpi + (size_t)fq_opaque(b) * N * NX)
-#define qlamb (a.qlam + (size_t)fq_opaque(b) * (N + 1) * 2 * NG)
-#define qtb (a.qt + (size_t)fq_opaque(b) * (N + 1) * 2 * NG)
+// =============================================================================================
+// pass F: Riccati factorisation sweep (classical recursion on P), k = N..0
+// =============================================================================================
+__device__ __noinline__ void fq_issue_F(int k)
+{
+    const FqCtx& c = fq_ctx;
+    uint64_t* bar = &fq_bars[0];
+    mbar_arrive_expect_tx(bar, (SR_SZ + 186) * 8);
+    bulk_g2s(fq_smem + F_S, c.SRb + (size_t)k * SR_SZ, SR_SZ * 8, bar);
+    bulk_g2s(fq_smem + F_SV, c.vb + (size_t)k * V_STAGE + V_QT, 186 * 8, bar);
+}
 
-    uint32_t phase = 0;
-    if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+__device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
+{
+    const int tid = threadIdx.x;
+    const int N = fq_ctx.N;
+    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
+    double* sP = fq_smem + F_P;
+    double* sM = fq_smem + F_M;
+    double* sU = sM;
+    const double* S = fq_smem + F_S;
+    const double* Sv = fq_smem + F_SV;           // [V_QT 72 | V_GAM 42 | V_KFF 30 | V_RB 42] of the stage
+    double* fv = fq_smem + F_V;
 
-    // ---- start of the QP (nmpc_qp_init_kernel) ----
-    if (a.warm == 0)
-        for (int i = tid; i < (N + 1) * NZ; i += FQ_THREADS) qz[i] = 0.0;
-    if (a.warm < 2)
-        for (int i = tid; i < N * NX; i += FQ_THREADS) qpi[i] = 0.0;
-    __syncthreads();
-    if (tid < NX)
-        qz[NU + tid] = a.dx0_ext ? a.dx0_ext[(size_t)b * NX + tid]
-                                 : a.x0[(size_t)b * NX + tid] - a.x[(size_t)b * (N + 1) * NX + tid];
-    if (tid < NU) qz[(size_t)N * NZ + tid] = 0.0;
-    __syncthreads();
-
-    // tile ownership, packed into one register.  The unpacked fields (and everything derived from them) used to be
-    // kernel-lifetime values that the register peak of the panel factorisation pushed into local memory; with four
-    // CTAs per SM those reloads miss the L1 left over next to 211 KB of shared memory.  Each use site below unpacks
-    // what it needs behind an opaque move, so nothing but `tcode` stays live across the stage.
+    // tile ownership, packed into one register (unpacked at each use: nothing but `tcode` stays live across a stage)
     unsigned tcode = 0;
     if (tid < N_UTILES)
         tcode |= c_utile[tid][0] | (c_utile[tid][1] << 3) | (c_utile[tid][2] << 4) | (c_utile[tid][3] << 9) | (1u << 24);
@@ -554,202 +694,90 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     const int xrt = (tx_ >> 12) & 3u, xct = (tx_ >> 14) & 3u, xr = (tx_ >> 16) & 15u, xc = (tx_ >> 20) & 15u;    \
     (void)xrt; (void)xct; (void)xr; (void)xc; (void)has_xt
 
-    int status = 1, iters = 0, nc_total = 0, ncond = 0;
-    double alpha_p = 1.0, alpha_d = 1.0, mu = 0.0;
-
-    for (int it = 0; it <= a.max_iter; it++) {
-        const bool last = (it >= a.max_iter);
-        // ================= update with the step of the previous iteration (nmpc_qp_update_kernel) =====
-        if (it > 0) {
-            alpha_p *= (1.0 - alpha_p) * 0.99 + alpha_p * 0.9999999;
-            alpha_d *= (1.0 - alpha_d) * 0.99 + alpha_d * 0.9999999;
-            if (alpha_p < IPM_ALPHA_MIN && alpha_d < IPM_ALPHA_MIN) { status = 2; break; }
-            for (int k = 0; k <= N; k++) {
-                const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
-                const double* vk = vb + (size_t)k * V_STAGE;
-                const double* Dm = SRb + (size_t)k * SR_SZ + SR_D + 2 * NG;
-                if (tid < NZ) qz[(size_t)k * NZ + tid] += alpha_p * vk[V_DZ + tid];
-                if (k < N && tid >= 80 && tid < 80 + NX) qpi[(size_t)k * NX + tid - 80] += alpha_d * vk[V_DPI + tid - 80];
-                if (tid < 2 * NG && Dm[tid] > 0.5) {
-                    double* qt = qtb + (size_t)k * 2 * NG;
-                    double* ql = qlamb + (size_t)k * 2 * NG;
-                    qt[tid] = fmax(qt[tid] + alpha_p * vk[V_DT + tid], IPM_T_MIN);
-                    ql[tid] = fmax(ql[tid] + alpha_d * vk[V_DLAM + tid], IPM_LAM_MIN);
+    if (tid == 0) fq_issue_F(N);
+    for (int k = N; k >= 0; k--) {
+        const bool term = (k == N);
+        double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
+        fq_ring_wait(0, ph);                                 // SR_k and the stage vectors have landed
+        FMARK(2);
+        double xa[3][3], ua[3][6];
+        if (tid == 0) bulk_store_wait_read();                // the previous factor record has left sM / sP
+        if (!term) {
+            if (tid < NX) {                                  // P+ rb (kept for the corrector), w = P+ rb + p+
+                const double* row = sP + tid * P_LD;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int j = 0; j < NX; j += 2) { s0 += row[j] * Sv[V_RB + j]; s1 += row[j + 1] * Sv[V_RB + j + 1]; }
+                const double prb = s0 + s1;
+                vk[V_PRB + tid] = prb;
+                fv[FV_W + tid] = prb + fv[FV_PN + tid];
+            }
+            __syncthreads();                                 // also orders wait_read before the writes to sU
+            if (tid < 4 * NU) {                              // U = P+[:, h] [Hf | Hq]
+                const int j = tid % NU, g = tid / NU;
+                const double* hc = (j < 12) ? (S + SR_HF + j) : (S + SR_HQ + (j - 12));
+                const int ld = (j < 12) ? 12 : NQ;
+                double hcv[6];
+#pragma unroll
+                for (int h = 0; h < 6; h++) hcv[h] = hc[ld * h];
+                for (int r = g; r < NX; r += 4) {
+                    const double* ph_ = sP + r * P_LD + 2 * NQ;
+                    double s = 0.0;
+#pragma unroll
+                    for (int h = 0; h < 6; h++) s += ph_[h] * hcv[h];
+                    sU[r * NU + j] = s;
                 }
             }
+            if (tid < NZ) fv[FV_QT + tid] = Sv[V_QT + tid] + fq_gt(S, fv + FV_W, tid, dt, c2);     // m = q~ + G' w
             __syncthreads();
-        }
-        iters = it;
-        FMARK(0);
-
-        // ================= backward pass: residuals of every stage (+ factorisation unless last) =====
-        double* acc = smem + FS_ACC + tid;       // [0] n_g  [1] n_b  [2] n_d  [3] n_m  [4] sum lam t   (stride FQ_THREADS)
-#pragma unroll
-        for (int i = 0; i < 5; i++) acc[i * FQ_THREADS] = 0.0;
-        int cnt = 0;
-        if (tid == 0) {
-            bulk_store_wait_read();
-            mbar_arrive_expect_tx(&bar, SR_SZ * 8);
-            bulk_g2s(S, SRb + (size_t)N * SR_SZ, SR_SZ * 8, &bar);
-        }
-        for (int k = N; k >= 0; k--) {
-            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
-            const bool term = (k == N);
-            double* vk = vb + (size_t)k * V_STAGE;
-            double* qlam = qlamb + (size_t)k * 2 * NG;
-            double* qt = qtb + (size_t)k * 2 * NG;
-            if (tid < NZ) sv[FV_Z + tid] = qz[(size_t)k * NZ + tid];
-            if (tid >= 80 && tid < 80 + NX) {
-                const int i = tid - 80;
-                sv[FV_ZXN + i] = term ? 0.0 : qz[(size_t)(k + 1) * NZ + NU + i];
-                sv[FV_PIK + i] = (k > 0) ? qpi[(size_t)(k - 1) * NX + i] : 0.0;
-                sv[FV_PIN + i] = term ? 0.0 : qpi[(size_t)k * NX + i];
-            }
-            if (tid < 2 * NG) { sv[FV_LAM + tid] = qlam[tid]; sv[FV_T + tid] = qt[tid]; }
-            __syncthreads();
-            FMARK(1);
-            mbar_wait(&bar, phase); phase ^= 1;                      // SR_k has landed
-            FMARK(2);
-
-            fq_cz(S, sv + FV_Z, sv + FV_CZ, tid);
-            __syncthreads();
-            if (tid < 2 * NG) {
-                const int e = tid / NG, j = tid % NG;
-                const double msk = S[SR_D + 2 * NG + tid];
-                const double cz = sv[FV_CZ + j];
-                const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
-                double t = sv[FV_T + tid], lam = sv[FV_LAM + tid];
-                if (it == 0) {               // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
-                    if (msk > 0.5) {
-                        if (a.warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; }
-                        else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
-                    } else { t = 1.0; lam = 0.0; }
-                    sv[FV_T + tid] = t; sv[FV_LAM + tid] = lam;
-                    qt[tid] = t; qlam[tid] = lam;
+            FMARK(4);
+            // ---- u tile: rows ur0..+2 (z index), columns uc0..+5 (u index) ----
+            FQ_UNPACK_U;
+            const int uti = ur0 - (urt == 0 ? IA : urt == 1 ? IFRC : urt == 2 ? IQ : urt == 3 ? IV : IH);
+            const int utj = uc0 - (uct == 0 ? IA : IFRC);
+            if (has_ut) {
+                switch (uct * 5 + urt) {
+                case 0: fq_asm_u<0, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 1: fq_asm_u<1, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 2: fq_asm_u<2, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 3: fq_asm_u<3, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 4: fq_asm_u<4, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 6: fq_asm_u<1, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 7: fq_asm_u<2, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                case 8: fq_asm_u<3, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
+                default: fq_asm_u<4, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
                 }
-                const double rd = msk > 0.5 ? (slack - t) : 0.0;
-                const double rm = msk > 0.5 ? lam * t : 0.0;
-                sv[FV_RD + tid] = rd; sv[FV_RM + tid] = rm;
-                vk[V_RD + tid] = rd; vk[V_RM + tid] = rm;
-                acc[4 * FQ_THREADS] += rm; cnt += (msk > 0.5) ? 1 : 0;
-                acc[2 * FQ_THREADS] = nanmax(acc[2 * FQ_THREADS], fabs(rd));
-                acc[3 * FQ_THREADS] = nanmax(acc[3 * FQ_THREADS], fabs(rm));
-            }
-            __syncthreads();
-            if (tid < NG) {
-                const int j = tid;
-                const double ml = S[SR_D + 2 * NG + j], mu_ = S[SR_D + 3 * NG + j];
-                const double ll = sv[FV_LAM + j], lu = sv[FV_LAM + NG + j];
-                const double tl = sv[FV_T + j], tu = sv[FV_T + NG + j];
-                double Gam = 0.0, gam = 0.0, dl = 0.0;
-                if (ml > 0.5) { Gam += ll / tl; gam += (sv[FV_RM + j] + ll * sv[FV_RD + j]) / tl; dl += ll; }
-                if (mu_ > 0.5) { Gam += lu / tu; gam -= (sv[FV_RM + NG + j] + lu * sv[FV_RD + NG + j]) / tu; dl -= lu; }
-                sv[FV_GAM + j] = Gam; sv[FV_GAMV + j] = gam; sv[FV_DL + j] = dl;
-            }
-            __syncthreads();
-            if (tid < NZ) {
-                const int c = tid;
-                double s = S[SR_GR + c] + fq_h(S, sv + FV_Z, c);
-                if (c >= NU && k > 0) s -= sv[FV_PIK + c - NU];
-                s -= fq_ct(S, sv + FV_DL, c);
-                const double qp = fq_ct(S, sv + FV_GAMV, c);
-                if (!term) s += fq_gt(S, sv + FV_PIN, c, dt, c2);
-                if ((k == 0 && c >= NU) || (term && c < NU)) s = 0.0;
-                vk[V_RG + c] = s; sv[FV_QT + c] = qp + s;
-                acc[0] = nanmax(acc[0], fabs(s));
-            } else if (!term && tid >= 80 && tid < 80 + NX) {
-                const int l = tid - 80;
-                const double rb = fq_g(S, sv + FV_Z, l, dt, c2) + S[SR_B + l] - sv[FV_ZXN + l];
-                sv[FV_RB + l] = rb; vk[V_RB + l] = rb;
-                acc[FQ_THREADS] = nanmax(acc[FQ_THREADS], fabs(rb));
-            }
-            __syncthreads();
-            if (last) {
-                if (k > 0 && tid == 0) {
-                    mbar_arrive_expect_tx(&bar, SR_SZ * 8);
-                    bulk_g2s(S, SRb + (size_t)(k - 1) * SR_SZ, SR_SZ * 8, &bar);
+                if (urb / 2 == ucb) {                        // diagonal tile: Hessian diagonal + regularisation
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+#pragma unroll
+                        for (int c = 0; c < 6; c++)
+                            if (ur0 + r == uc0 + c) ua[r][c] += S[SR_RD + ur0 + r] + IPM_REG_PRIM;
                 }
-                continue;
-            }
-
-            FMARK(3);
-            // ---------------- Riccati step of stage k (classical recursion on P) ----------------
-            double xa[3][3], ua[3][6];
-            if (tid == 0) bulk_store_wait_read();                    // the previous factor record has left sM / sP
-            if (!term) {
-                if (tid < NX) {                                      // w = P+ rb + p+
-                    const double* row = sP + tid * P_LD;
-                    double s0 = sv[FV_PN + tid], s1 = 0.0;
+                if (ur0 >= IFRC && ur0 < IQ && uc0 >= IFRC) {    // friction rows: 3x3 block of the foot
+                    const int ft = (ur0 - IFRC) / 3;
+                    const int cofs = IFRC + 3 * ft - uc0;    // first column of the foot inside this tile
+                    if (cofs >= 0 && cofs < 6) {
+                        for (int r5 = 0; r5 < 5; r5++) {
+                            const double g = Sv[V_GAM + 5 * ft + r5];
+                            const double* cf = S + SR_CF + 3 * (5 * ft + r5);
 #pragma unroll
-                    for (int j = 0; j < NX; j += 2) { s0 += row[j] * sv[FV_RB + j]; s1 += row[j + 1] * sv[FV_RB + j + 1]; }
-                    sv[FV_W + tid] = s0 + s1;
-                }
-                __syncthreads();                                     // also orders wait_read before the writes to sU
-                if (tid < 4 * NU) {                                  // U = P+[:, h] [Hf | Hq]
-                    // thread = (column j, row group g): the column of [Hf | Hq] stays in registers, the six P entries
-                    // of a row are one broadcast per warp (12 loads per entry before, 6 per row now)
-                    const int j = tid % NU, g = tid / NU;
-                    const double* hc = (j < 12) ? (S + SR_HF + j) : (S + SR_HQ + (j - 12));
-                    const int ld = (j < 12) ? 12 : NQ;
-                    double hcv[6];
+                            for (int r = 0; r < 3; r++)
 #pragma unroll
-                    for (int h = 0; h < 6; h++) hcv[h] = hc[ld * h];
-                    for (int r = g; r < NX; r += 4) {
-                        const double* ph = sP + r * P_LD + 2 * NQ;
-                        double s = 0.0;
-#pragma unroll
-                        for (int h = 0; h < 6; h++) s += ph[h] * hcv[h];
-                        sU[r * NU + j] = s;
-                    }
-                }
-                if (tid < NZ) sv[FV_QT + tid] += fq_gt(S, sv + FV_W, tid, dt, c2);       // m = q tilde + G' w
-                __syncthreads();
-                FMARK(4);
-                // ---- u tile: rows ur0..+2 (z index), columns uc0..+5 (u index) ----
-                FQ_UNPACK_U;
-                // first row / column of the tile inside its block types
-                const int uti = ur0 - (urt == 0 ? IA : urt == 1 ? IFRC : urt == 2 ? IQ : urt == 3 ? IV : IH);
-                const int utj = uc0 - (uct == 0 ? IA : IFRC);
-                if (has_ut) {
-                    switch (uct * 5 + urt) {
-                    case 0: fq_asm_u<0, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 1: fq_asm_u<1, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 2: fq_asm_u<2, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 3: fq_asm_u<3, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 4: fq_asm_u<4, 0>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 6: fq_asm_u<1, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 7: fq_asm_u<2, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    case 8: fq_asm_u<3, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    default: fq_asm_u<4, 1>(sP, sU, S, uti, utj, dt, c2, ua); break;
-                    }
-                    if (urb / 2 == ucb) {                            // diagonal tile: Hessian diagonal + regularisation
-#pragma unroll
-                        for (int r = 0; r < 3; r++)
-#pragma unroll
-                            for (int c = 0; c < 6; c++)
-                                if (ur0 + r == uc0 + c) ua[r][c] += S[SR_RD + ur0 + r] + IPM_REG_PRIM;
-                    }
-                    if (ur0 >= IFRC && ur0 < IQ && uc0 >= IFRC) {    // friction rows: 3x3 block of the foot
-                        const int ft = (ur0 - IFRC) / 3;
-                        const int cofs = IFRC + 3 * ft - uc0;        // first column of the foot inside this tile
-                        if (cofs >= 0 && cofs < 6) {
-                            for (int r5 = 0; r5 < 5; r5++) {
-                                const double g = sv[FV_GAM + 5 * ft + r5];
-                                const double* cf = S + SR_CF + 3 * (5 * ft + r5);
-#pragma unroll
-                                for (int r = 0; r < 3; r++)
-#pragma unroll
-                                    for (int c = 0; c < 3; c++) {
-                                        const double add = g * cf[r] * cf[c];
-                                        if (cofs == 0) ua[r][c] += add; else ua[r][3 + c] += add;
-                                    }
-                            }
+                                for (int c = 0; c < 3; c++) {
+                                    const double add = g * cf[r] * cf[c];
+                                    if (cofs == 0) ua[r][c] += add; else ua[r][3 + c] += add;
+                                }
                         }
                     }
                 }
             }
-            // ---- x tile: rows 3xr..+2, columns 3xc..+2 of the state block ----
-            {
+        } else {
+            if (tid < NZ) fv[FV_QT + tid] = Sv[V_QT + tid];
+            __syncthreads();                                 // orders wait_read before the writes to sP below
+        }
+        // ---- x tile: rows 3xr..+2, columns 3xc..+2 of the state block ----
+        {
             FQ_UNPACK_X;
             const int xti = 3 * xr - (xrt == 0 ? 0 : xrt == 1 ? NQ : 2 * NQ);
             const int xtj = 3 * xc - (xct == 0 ? 0 : xct == 1 ? NQ : 2 * NQ);
@@ -781,44 +809,41 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                         if (!term && ii == jj) v += IPM_REG_PRIM;
                         xa[r][c] += v;
                     }
-                if (i0 < 2 * NQ) {                                   // (q,v) x (q,v): all 22 state rows
+                if (i0 < 2 * NQ) {                           // (q,v) x (q,v): all 22 state rows
                     for (int g = 0; g < NGX; g++) {
-                        const double gm = sv[FV_GAM + NGF + g];
+                        const double gm = Sv[V_GAM + NGF + g];
                         if (gm == 0.0) continue;
-                        const double* row = S + SR_CX + 36 * g;
+                        const double* row = S + SR_CX + SR_CXLD * g;
                         const double a0 = row[i0] * gm, a1 = row[i0 + 1] * gm, a2 = row[i0 + 2] * gm;
                         const double b0 = row[j0x], b1 = row[j0x + 1], b2 = row[j0x + 2];
                         xa[0][0] += a0 * b0; xa[0][1] += a0 * b1; xa[0][2] += a0 * b2;
                         xa[1][0] += a1 * b0; xa[1][1] += a1 * b1; xa[1][2] += a1 * b2;
                         xa[2][0] += a2 * b0; xa[2][1] += a2 * b1; xa[2][2] += a2 * b2;
                     }
-                } else {                                             // h rows: only the centroidal rows reach them
+                } else {                                     // h rows: only the centroidal rows reach them
 #pragma unroll
                     for (int r = 0; r < 3; r++) {
                         const int hi = i0 + r - 2 * NQ;
-                        const double gm = sv[FV_GAM + GR_CONS + hi];
+                        const double gm = Sv[V_GAM + GR_CONS + hi];
 #pragma unroll
                         for (int c = 0; c < 3; c++) {
                             const int jj = j0x + c;
-                            if (jj < 2 * NQ) xa[r][c] += gm * S[SR_CX + 36 * (16 + hi) + jj];
+                            if (jj < 2 * NQ) xa[r][c] += gm * S[SR_CX + SR_CXLD * (16 + hi) + jj];
                             else if (jj == i0 + r) xa[r][c] += gm;
                         }
                     }
                 }
             }
-            }
-            __syncthreads();                 // every read of SR_k, P+, U, PGh is done
-            FMARK(5);
-            if (k > 0 && tid == 0) {         // prefetch the next stage record under the factorisation
-                mbar_arrive_expect_tx(&bar, SR_SZ * 8);
-                bulk_g2s(S, SRb + (size_t)(k - 1) * SR_SZ, SR_SZ * 8, &bar);
-            }
-            if (!term) {
-                // ---- right-looking Cholesky of the 30 input columns; x tiles take the same rank-6 updates ----
-                for (int jb = 0; jb < 5; jb++) {
-                    const int j0 = PB * jb;
-                    double* pan = sM + P_OFF(jb);                    // rows j0..72 of columns j0..j0+5
-                    {
+        }
+        __syncthreads();                 // every read of SR_k, the stage vectors, P+, U is done
+        FMARK(5);
+        if (k > 0 && tid == 0) fq_issue_F(k - 1);            // prefetch the next stage under the factorisation
+        if (!term) {
+            // ---- right-looking Cholesky of the 30 input columns; x tiles take the same rank-6 updates ----
+            for (int jb = 0; jb < 5; jb++) {
+                const int j0 = PB * jb;
+                double* pan = sM + P_OFF(jb);                // rows j0..72 of columns j0..j0+5
+                {
                     FQ_UNPACK_U;
                     if (has_ut && ucb == jb) {
 #pragma unroll
@@ -826,98 +851,99 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 #pragma unroll
                             for (int c = 0; c < 6; c++) pan[(ur0 + r - j0) * PB + c] = ua[r][c];
                     }
+                }
+                if (tid < PB) pan[(NZ - j0) * PB + tid] = fv[FV_QT + j0 + tid];
+                __syncthreads();
+                // Panel factorisation, right-looking in registers: every row thread factors the 6x6 diagonal block
+                // redundantly and carries its own row along as a seventh row, so the dependent chain per pivot is one
+                // rsqrt, one multiply and one fused multiply-add.  Non-positive pivots zero their column (BLASFEO
+                // potrf rule).
+                const int nrow = NZ + 1 - j0;
+                double drow[PB] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                if (tid < nrow) {
+                    double A[PB][PB], rv[PB];
+#pragma unroll
+                    for (int aa = 0; aa < PB; aa++)
+#pragma unroll
+                        for (int c = 0; c <= aa; c++) A[aa][c] = pan[aa * PB + c];
+                    load6(pan + tid * PB, rv);
+#pragma unroll
+                    for (int j = 0; j < PB; j++) {
+                        const double v = A[j][j];
+                        double d = 0.0, inv = 0.0;
+                        if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
+                        A[j][j] = d;
+#pragma unroll
+                        for (int i = j + 1; i < PB; i++) A[i][j] *= inv;
+                        rv[j] *= inv;
+#pragma unroll
+                        for (int c = j + 1; c < PB; c++) {
+#pragma unroll
+                            for (int i = c; i < PB; i++) A[i][c] -= A[i][j] * A[c][j];
+                            rv[c] -= rv[j] * A[c][j];
+                        }
                     }
-                    if (tid < PB) pan[(NZ - j0) * PB + tid] = sv[FV_QT + j0 + tid];
-                    __syncthreads();
-                    // Panel factorisation, right-looking in registers: every row thread factors the 6x6 diagonal
-                    // block redundantly and carries its own row along as a seventh row, so the dependent chain per
-                    // pivot is one rsqrt, one multiply and one fused multiply-add.  Non-positive pivots zero their
-                    // column (BLASFEO potrf rule).
-                    const int nrow = NZ + 1 - j0;
-                    double drow[PB] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-                    if (tid < nrow) {
-                        double A[PB][PB], rv[PB];
+                    if (tid >= PB) {
+#pragma unroll
+                        for (int jj = 0; jj < PB; jj++) pan[tid * PB + jj] = rv[jj];
+                    } else {
 #pragma unroll
                         for (int aa = 0; aa < PB; aa++)
 #pragma unroll
-                            for (int c = 0; c <= aa; c++) A[aa][c] = pan[aa * PB + c];
-                        load6(pan + tid * PB, rv);
-#pragma unroll
-                        for (int j = 0; j < PB; j++) {
-                            const double v = A[j][j];
-                            double d = 0.0, inv = 0.0;
-                            if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
-                            A[j][j] = d;
-#pragma unroll
-                            for (int i = j + 1; i < PB; i++) A[i][j] *= inv;
-                            rv[j] *= inv;
-#pragma unroll
-                            for (int c = j + 1; c < PB; c++) {
-#pragma unroll
-                                for (int i = c; i < PB; i++) A[i][c] -= A[i][j] * A[c][j];
-                                rv[c] -= rv[j] * A[c][j];
-                            }
-                        }
-                        if (tid >= PB) {
-#pragma unroll
-                            for (int jj = 0; jj < PB; jj++) pan[tid * PB + jj] = rv[jj];
-                        } else {
-#pragma unroll
-                            for (int aa = 0; aa < PB; aa++)
-#pragma unroll
-                                for (int c = 0; c <= aa; c++) if (tid == aa) drow[c] = A[aa][c];
-                        }
+                            for (int c = 0; c <= aa; c++) if (tid == aa) drow[c] = A[aa][c];
                     }
-                    __syncthreads();
-                    if (tid < PB) {
-#pragma unroll
-                        for (int c = 0; c < PB; c++) pan[tid * PB + c] = drow[c];
-                    }
-                    FQ_UNPACK_U;
-                    FQ_UNPACK_X;
-                    if (has_ut && ucb > jb) {
-                        const double* pa = pan + (ur0 - j0) * PB;
-                        const double* pb = pan + (uc0 - j0) * PB;
-#pragma unroll
-                        for (int kk = 0; kk < PB; kk++) {
-                            const double a0 = pa[kk], a1 = pa[PB + kk], a2 = pa[2 * PB + kk];
-#pragma unroll
-                            for (int c = 0; c < 6; c++) {
-                                const double bv = pb[c * PB + kk];
-                                ua[0][c] -= a0 * bv; ua[1][c] -= a1 * bv; ua[2][c] -= a2 * bv;
-                            }
-                        }
-                    }
-                    if (has_xt) {
-                        const double* pa = pan + (NU + 3 * xr - j0) * PB;
-                        const double* pb = pan + (NU + 3 * xc - j0) * PB;
-                        double av[3][PB], bv[3][PB];
-#pragma unroll
-                        for (int r = 0; r < 3; r++) { load6(pa + r * PB, av[r]); load6(pb + r * PB, bv[r]); }
-#pragma unroll
-                        for (int r = 0; r < 3; r++)
-#pragma unroll
-                            for (int c = 0; c < 3; c++)
-#pragma unroll
-                                for (int kk = 0; kk < PB; kk++) xa[r][c] -= av[r][kk] * bv[c][kk];
-                    }
-                    if (tid < NZ - j0 - PB) {                        // row 72: m_c -= lu . L(c, j0..j0+5)
-                        const double* pa = pan + (NZ - j0) * PB;
-                        const double* pb = pan + (PB + tid) * PB;
-                        double av[6], bv[6];
-                        load6(pa, av);
-                        load6(pb, bv);
-                        double sm_ = sv[FV_QT + j0 + PB + tid];
-#pragma unroll
-                        for (int kk = 0; kk < PB; kk++) sm_ -= av[kk] * bv[kk];
-                        sv[FV_QT + j0 + PB + tid] = sm_;
-                    }
-                    // the next panel's owners write a different panel; the m row is ordered by the next barrier
                 }
+                __syncthreads();
+                if (tid < PB) {
+#pragma unroll
+                    for (int c = 0; c < PB; c++) pan[tid * PB + c] = drow[c];
+                }
+                FQ_UNPACK_U;
+                FQ_UNPACK_X;
+                if (has_ut && ucb > jb) {
+                    const double* pa = pan + (ur0 - j0) * PB;
+                    const double* pb = pan + (uc0 - j0) * PB;
+#pragma unroll
+                    for (int kk = 0; kk < PB; kk++) {
+                        const double a0 = pa[kk], a1 = pa[PB + kk], a2 = pa[2 * PB + kk];
+#pragma unroll
+                        for (int c = 0; c < 6; c++) {
+                            const double bv = pb[c * PB + kk];
+                            ua[0][c] -= a0 * bv; ua[1][c] -= a1 * bv; ua[2][c] -= a2 * bv;
+                        }
+                    }
+                }
+                if (has_xt) {
+                    const double* pa = pan + (NU + 3 * xr - j0) * PB;
+                    const double* pb = pan + (NU + 3 * xc - j0) * PB;
+                    double av[3][PB], bv[3][PB];
+#pragma unroll
+                    for (int r = 0; r < 3; r++) { load6(pa + r * PB, av[r]); load6(pb + r * PB, bv[r]); }
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+#pragma unroll
+                        for (int c = 0; c < 3; c++)
+#pragma unroll
+                            for (int kk = 0; kk < PB; kk++) xa[r][c] -= av[r][kk] * bv[c][kk];
+                }
+                if (tid < NZ - j0 - PB) {                    // row 72: m_c -= lu . L(c, j0..j0+5)
+                    const double* pa = pan + (NZ - j0) * PB;
+                    const double* pb = pan + (PB + tid) * PB;
+                    double av[6], bv[6];
+                    load6(pa, av);
+                    load6(pb, bv);
+                    double sm_ = fv[FV_QT + j0 + PB + tid];
+#pragma unroll
+                    for (int kk = 0; kk < PB; kk++) sm_ -= av[kk] * bv[kk];
+                    fv[FV_QT + j0 + PB + tid] = sm_;
+                }
+                // the next panel's owners write a different panel; the m row is ordered by the next barrier
             }
-            __syncthreads();
-            FMARK(6);
-            // ---- P_k (both triangles) -> sP, p_k -> sv; factor record -> HBM ----
+        }
+        __syncthreads();
+        FMARK(6);
+        // ---- P_k (both triangles) -> sP, p_k -> fv ----
+        {
             FQ_UNPACK_X;
             if (has_xt) {
 #pragma unroll
@@ -928,247 +954,469 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
                         if (ii >= jj) { sP[ii * P_LD + jj] = xa[r][c]; sP[jj * P_LD + ii] = xa[r][c]; }
                     }
             }
-            if (tid < NX) { const double pv = sv[FV_QT + NU + tid]; sv[FV_PN + tid] = pv; vk[V_P + tid] = pv; }
-            fence_proxy_async();
-            __syncthreads();
-            if (tid == 0) {
-                double* fr = FRb + (size_t)k * FR_SZ;
-                if (!term) bulk_s2g(fr + FR_MU, sM, LP_UPANELS * 8);
-                bulk_s2g(fr + FR_P, sP, NX * P_LD * 8);
-            }
         }
-
+        if (tid < NX) fv[FV_PN + tid] = fv[FV_QT + NU + tid];
+        if (!term && tid < NU) vk[V_KFF + tid] = sM[lp_idx(NZ, tid)];     // lu of the affine direction, for pass A1
+        fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            double* fr = fq_ctx.FRb + (size_t)k * FR_SZ;
+            if (!term) bulk_s2g(fr + FR_MU, sM, LP_UPANELS * 8);
+            bulk_s2g(fr + FR_P, sP, NX * P_LD * 8);
+        }
         FMARK(7);
-        // ================= norms, mu, exit tests (nmpc_qp_decide_kernel) =================
-        double res4[4];
-        res4[0] = fq_block_max(acc[0], red, tid);
-        res4[1] = fq_block_max(acc[FQ_THREADS], red, tid);
-        res4[2] = fq_block_max(acc[2 * FQ_THREADS], red, tid);
-        res4[3] = fq_block_max(acc[3 * FQ_THREADS], red, tid);
-        const double mu_sum = fq_block_sum(acc[4 * FQ_THREADS], red, tid);
-        if (it == 0) nc_total = (int)(fq_block_sum((double)cnt, red, tid) + 0.5);
-        mu = nc_total > 0 ? mu_sum / nc_total : 0.0;
+    }
+    if (tid == 0) bulk_store_wait_all();                     // the factor records are in global memory
+    fq_pass_end();
+    return ph;
+#undef FQ_UNPACK_U
+#undef FQ_UNPACK_X
+}
+
+// =============================================================================================
+// passes A1 / D1: forward chain  du = -Luu^-T (lu + Lxu' dx),  dx+ = G [du; dx] + rb
+// =============================================================================================
+__device__ __noinline__ void fq_issue_A(int k, int slot)
+{
+    const FqCtx& c = fq_ctx;
+    double* sl = fq_smem + slot * A_SLOT;
+    uint64_t* bar = &fq_bars[slot];
+    mbar_arrive_expect_tx(bar, (LP_UPANELS + 180 + NU + NX) * 8);
+    bulk_g2s(sl + A_MU, c.FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, bar);
+    bulk_g2s(sl + A_H, c.SRb + (size_t)k * SR_SZ + SR_HQ, 180 * 8, bar);
+    bulk_g2s(sl + A_LU, c.vb + (size_t)k * V_STAGE + V_KFF, (NU + NX) * 8, bar);
+}
+
+__device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int N = fq_ctx.N;
+    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
+    double* av = fq_smem + AV_BASE;
+    if (tid < NX) av[AV_DX + tid] = 0.0;                     // dx_0 = 0 (the initial state is fixed)
+    if (tid == FQ_ISSUER)
+        for (int i = 0; i < A_DEPTH - 1 && i < N; i++) fq_issue_A(i, i % A_DEPTH);
+    __syncthreads();
+    for (int k = 0; k <= N; k++) {
+        const bool term = (k == N);
+        const int slot = k % A_DEPTH;
+        double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
+        const double* dx = av + AV_DX + (k & 1) * NX;
+        double* dxn = av + AV_DX + ((k + 1) & 1) * NX;
+        double* dz = av + AV_DZ;
+        if (!term) {
+            if (tid == FQ_ISSUER && k + A_DEPTH - 1 < N) fq_issue_A(k + A_DEPTH - 1, (k + A_DEPTH - 1) % A_DEPTH);
+            fq_ring_wait(slot, ph);
+            const double* sl = fq_smem + slot * A_SLOT;
+            const double* sM = sl + A_MU;
+            if (tid < 32) {             // du = -Luu^-T (lu + Lxu' dx)
+                double rhs = 0.0;
+                if (lane < NU) {
+                    double r1 = 0.0;
+                    rhs = sl[A_LU + lane];
+#pragma unroll
+                    for (int l = 0; l < NX; l += 2) {
+                        rhs = fma(sM[lp_idx(NU + l, lane)], dx[l], rhs);
+                        r1 = fma(sM[lp_idx(NU + l + 1, lane)], dx[l + 1], r1);
+                    }
+                    rhs += r1;
+                }
+                // back substitution with Luu': branch-free, one shuffle + multiply + fused multiply-add per step;
+                // lane l keeps rhs_l * (1 / L_ll) ready so the broadcast value is already the solution component
+                double du = 0.0, myinv = 0.0;
+                const int ll = lane < NU ? lane : NU - 1;
+                { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
+                // L(i, ll) for i >= ll sits at colb + 6 i (panel-packed, 6 doubles per row).  The loop is kept rolled:
+                // the chain is latency-bound either way, and 30 unrolled steps are 14 KB of code
+                const double* colb = sM + P_OFF(ll / PB) - PB * PB * (ll / PB) + ll % PB;
+#pragma unroll 1
+                for (int i = NU - 1; i >= 0; i--) {
+                    const double dui = -__shfl_sync(0xffffffffu, rhs * myinv, i);
+                    const double lv = (lane < i) ? colb[PB * i] : 0.0;
+                    du = (lane == i) ? dui : du;
+                    rhs = fma(lv, dui, rhs);
+                }
+                if (lane < NU) dz[lane] = du;
+            } else if (tid < 32 + NX) dz[NU + tid - 32] = dx[tid - 32];
+            __syncthreads();
+            if (tid < NZ) vk[V_DZ + tid] = dz[tid];
+            if (tid < 2 * NQ) dxn[tid] = fq_g(sl + A_H, dz, tid, dt, c2) + sl[A_RB + tid];
+            else if (tid >= 64 && tid < 96) {                // momentum rows: four threads per row (warp 2, all lanes shuffle)
+                const int hi = min((tid - 64) >> 2, 5), part = tid & 3;
+                const double* hq = sl + A_H + SR_HQ + NQ * hi;
+                const double* hf = sl + A_H + SR_HF + 12 * hi;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int j = part; j < NQ; j += 8) {
+                    s0 = fma(hq[j], dz[IQ + j], s0);
+                    if (j + 4 < NQ) s1 = fma(hq[j + 4], dz[IQ + j + 4], s1);
+                }
+#pragma unroll
+                for (int j = part; j < 12; j += 8) {
+                    s0 = fma(hf[j], dz[IFRC + j], s0);
+                    if (j + 4 < 12) s1 = fma(hf[j + 4], dz[IFRC + j + 4], s1);
+                }
+                double s = s0 + s1;
+                s += __shfl_xor_sync(0xffffffffu, s, 1);
+                s += __shfl_xor_sync(0xffffffffu, s, 2);
+                if (part == 0 && tid < 64 + 24) dxn[2 * NQ + hi] = s + dz[IH + hi] + sl[A_RB + 2 * NQ + hi];
+            }
+            __syncthreads();
+        } else {
+            if (tid < NU) vk[V_DZ + tid] = 0.0;
+            else if (tid < NZ) vk[V_DZ + tid] = dx[tid - NU];
+        }
+    }
+    fq_pass_end();
+    return ph;
+}
+
+// =============================================================================================
+// passes A2 / D2: C dz, slack and multiplier directions, step lengths (and, D2, dpi_{k-1} = P_k dx_k + p_k)
+// out: [0] alpha_p [1] alpha_d [2..4] sum (lam + a dlam)(t + a dt) = c0 + a c1 + a^2 c2
+// =============================================================================================
+template <bool CORR>
+__device__ __noinline__ void fq_issue_B(int k, int slot)
+{
+    const FqCtx& c = fq_ctx;
+    constexpr int SLOT = CORR ? D_SLOT : B_SLOT;
+    constexpr int OC = CORR ? D_C : B_C, ODZ = CORR ? D_DZ : B_DZ, OLAM = CORR ? D_LAM : B_LAM, OT = CORR ? D_T : B_T;
+    double* sl = fq_smem + slot * SLOT;
+    uint64_t* bar = &fq_bars[slot];
+    uint32_t bytes = (SR_CSZ + NZ + 8 * NG) * 8;
+    if (CORR && k > 0) bytes += (NX * P_LD + NX) * 8;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_g2s(sl + OC, c.SRb + (size_t)k * SR_SZ + SR_CF, SR_CSZ * 8, bar);
+    bulk_g2s(sl + ODZ, c.vb + (size_t)k * V_STAGE + V_DZ, (NZ + 4 * NG) * 8, bar);
+    bulk_g2s(sl + OLAM, c.qlam + (size_t)k * 2 * NG, 2 * NG * 8, bar);
+    bulk_g2s(sl + OT, c.qt + (size_t)k * 2 * NG, 2 * NG * 8, bar);
+    if (CORR && k > 0) {
+        bulk_g2s(sl + D_P, c.FRb + (size_t)k * FR_SZ + FR_P, NX * P_LD * 8, bar);
+        bulk_g2s(sl + D_PV, c.vb + (size_t)k * V_STAGE + V_P, NX * 8, bar);
+    }
+}
+
+template <bool CORR>
+__device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
+{
+    constexpr int SLOT = CORR ? D_SLOT : B_SLOT, DEPTH = CORR ? D_DEPTH : B_DEPTH;
+    constexpr int OC = CORR ? D_C : B_C, ODZ = CORR ? D_DZ : B_DZ, ORD = CORR ? D_RD : B_RD, ORM = CORR ? D_RM : B_RM;
+    constexpr int OLAM = CORR ? D_LAM : B_LAM, OT = CORR ? D_T : B_T;
+    const int tid = threadIdx.x;
+    const int N = fq_ctx.N;
+    double* cz = fq_smem + (CORR ? DV_BASE : BV_BASE);
+    double* red = fq_smem + FQ_RED;
+    double a_p = 1.0, a_d = 1.0, cs0 = 0.0, cs1 = 0.0, cs2 = 0.0;
+    if (tid == FQ_ISSUER)
+        for (int i = 0; i < DEPTH - 1 && i <= N; i++) fq_issue_B<CORR>(i, i % DEPTH);
+    for (int k = 0; k <= N; k++) {
+        const int slot = k % DEPTH;
+        if (!CORR) FMARK(9);
+        if (tid == FQ_ISSUER && k + DEPTH - 1 <= N) fq_issue_B<CORR>(k + DEPTH - 1, (k + DEPTH - 1) % DEPTH);
+        if (!CORR) FMARK(14);
+        fq_ring_wait(slot, ph);
+        if (!CORR) FMARK(15);
+        const double* sl = fq_smem + slot * SLOT;
+        const double* Sc = sl + OC - SR_CF;                  // the helpers index the constraint part by its stage-record offsets
+        double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
+        fq_cz(Sc, sl + ODZ, cz, tid);                        // threads 0..41
+        if (CORR && k > 0 && tid >= 64 && tid < 64 + NX) {   // dpi_{k-1} = P_k dx_k + p_k
+            const int i = tid - 64;
+            const double* row = sl + D_P + i * P_LD;
+            const double* dx = sl + ODZ + NU;
+            double s0 = sl[D_PV + i], s1 = 0.0;
+#pragma unroll
+            for (int j = 0; j < NX; j += 2) { s0 = fma(row[j], dx[j], s0); s1 = fma(row[j + 1], dx[j + 1], s1); }
+            vk[V_DPI - V_STAGE + i] = s0 + s1;
+        }
+        __syncthreads();
+        if (!CORR) FMARK(16);
+        if (tid < 2 * NG) {
+            const int e = tid / NG, j = tid % NG;
+            double dtv = 0.0, dl = 0.0;
+            if (Sc[SR_D + 2 * NG + tid] > 0.5) {
+                const double lam = sl[OLAM + tid], t = sl[OT + tid];
+                const double cdz = cz[j];
+                dtv = (e ? -cdz : cdz) + sl[ORD + tid];
+                dl = -(sl[ORM + tid] + lam * dtv) / t;
+                if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
+                if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
+                cs0 = fma(lam, t, cs0); cs1 += fma(lam, dtv, t * dl); cs2 = fma(dl, dtv, cs2);
+            }
+            vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
+        }
+        __syncthreads();
+        if (!CORR) FMARK(17);
+    }
+    out[0] = fq_block_min(a_p, red, tid);
+    out[1] = fq_block_min(a_d, red, tid);
+    out[2] = fq_block_sum(cs0, red, tid);
+    out[3] = fq_block_sum(cs1, red, tid);
+    out[4] = fq_block_sum(cs2, red, tid);
+    fq_pass_end();
+    return ph;
+}
+
+// =============================================================================================
+// pass C1: corrector complementarity residual, gamma_c, m0 = rg + C' gamma_c + G' (P+ rb)
+// =============================================================================================
+__device__ __noinline__ void fq_issue_C1(int k, int slot)
+{
+    const FqCtx& c = fq_ctx;
+    double* sl = fq_smem + slot * C_SLOT;
+    uint64_t* bar = &fq_bars[slot];
+    const double* vk = c.vb + (size_t)k * V_STAGE;
+    mbar_arrive_expect_tx(bar, (180 + SR_CSZ + NZ + NX + 10 * NG) * 8);
+    bulk_g2s(sl + C_H, c.SRb + (size_t)k * SR_SZ + SR_HQ, 180 * 8, bar);
+    bulk_g2s(sl + C_C, c.SRb + (size_t)k * SR_SZ + SR_CF, SR_CSZ * 8, bar);
+    bulk_g2s(sl + C_RG, vk + V_RG, (NZ + NX) * 8, bar);
+    bulk_g2s(sl + C_DT, vk + V_DT, 4 * NG * 8, bar);
+    bulk_g2s(sl + C_RD, vk + V_RD, 2 * NG * 8, bar);
+    bulk_g2s(sl + C_LAM, c.qlam + (size_t)k * 2 * NG, 2 * NG * 8, bar);
+    bulk_g2s(sl + C_T, c.qt + (size_t)k * 2 * NG, 2 * NG * 8, bar);
+}
+
+__device__ __noinline__ uint32_t fq_pass_C1(uint32_t ph, int cpass, double sigma_mu)
+{
+    const int tid = threadIdx.x;
+    const int N = fq_ctx.N;
+    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
+    double* gamc = fq_smem + CV_BASE;
+    if (tid == FQ_ISSUER)
+        for (int i = 0; i < C_DEPTH - 1 && i <= N; i++) fq_issue_C1(i, i % C_DEPTH);
+    for (int k = 0; k <= N; k++) {
+        const int slot = k % C_DEPTH;
+        const bool term = (k == N);
+        if (tid == FQ_ISSUER && k + C_DEPTH - 1 <= N) fq_issue_C1(k + C_DEPTH - 1, (k + C_DEPTH - 1) % C_DEPTH);
+        fq_ring_wait(slot, ph);
+        const double* sl = fq_smem + slot * C_SLOT;
+        const double* Sc = sl + C_C - SR_CF;
+        double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
+        if (tid < NG) {
+            double g = 0.0;
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int row = e * NG + tid;
+                if (Sc[SR_D + 2 * NG + row] > 0.5) {
+                    const double lam = sl[C_LAM + row], t = sl[C_T + row];
+                    const double rmc = fma(lam, t, cpass == 0 ? sl[C_DT + row] * sl[C_DLAM + row] : 0.0) - sigma_mu;
+                    vk[V_RM + row] = rmc;
+                    const double v = (rmc + lam * sl[C_RD + row]) / t;
+                    g += e ? -v : v;
+                }
+            }
+            gamc[tid] = g;
+        }
+        __syncthreads();
+        if (tid < NZ) {
+            double s = sl[C_RG + tid] + fq_ct(Sc, gamc, tid);
+            if (!term) s += fq_gt(sl + C_H, sl + C_PRB, tid, dt, c2);
+            vk[V_M0 + tid] = s;
+        }
+        __syncthreads();
+    }
+    fq_pass_end();
+    return ph;
+}
+
+// =============================================================================================
+// pass C2: corrector backward chain  m = m0 + G' p+,  lu = Luu^-1 m_u,  p = m_x - Lxu lu
+// =============================================================================================
+__device__ __noinline__ void fq_issue_C2(int k, int slot)
+{
+    const FqCtx& c = fq_ctx;
+    double* sl = fq_smem + slot * E_SLOT;
+    uint64_t* bar = &fq_bars[slot];
+    mbar_arrive_expect_tx(bar, (LP_UPANELS + 180 + NZ) * 8);
+    bulk_g2s(sl + E_MU, c.FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, bar);
+    bulk_g2s(sl + E_H, c.SRb + (size_t)k * SR_SZ + SR_HQ, 180 * 8, bar);
+    bulk_g2s(sl + E_M0, c.vb + (size_t)k * V_STAGE + V_M0, NZ * 8, bar);
+}
+
+__device__ __noinline__ uint32_t fq_pass_C2(uint32_t ph)
+{
+    const int tid = threadIdx.x;
+    const int N = fq_ctx.N;
+    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
+    double* ev = fq_smem + EV_BASE;
+    // terminal stage: p_N = m_x (read straight from the workspace)
+    {
+        double* vk = fq_ctx.vb + (size_t)N * V_STAGE;
+        if (tid < NX) { const double pv = vk[V_M0 + NU + tid]; ev[EV_PN + (N & 1) * NX + tid] = pv; vk[V_P + tid] = pv; }
+    }
+    if (tid == FQ_ISSUER)
+        for (int i = 0; i < E_DEPTH - 1 && i < N; i++) fq_issue_C2(N - 1 - i, i % E_DEPTH);
+    __syncthreads();
+    for (int i = 0; i < N; i++) {
+        const int k = N - 1 - i, slot = i % E_DEPTH;
+        if (tid == FQ_ISSUER && i + E_DEPTH - 1 < N) fq_issue_C2(k - (E_DEPTH - 1), (i + E_DEPTH - 1) % E_DEPTH);
+        fq_ring_wait(slot, ph);
+        const double* sl = fq_smem + slot * E_SLOT;
+        const double* sM = sl + E_MU;
+        double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
+        double* ms = ev + EV_M;
+        double* lus = ev + EV_LU;
+        const double* pnn = ev + EV_PN + ((k + 1) & 1) * NX;
+        double* pnk = ev + EV_PN + (k & 1) * NX;
+        if (tid < NZ) ms[tid] = sl[E_M0 + tid] + fq_gt(sl + E_H, pnn, tid, dt, c2);
+        __syncthreads();
+        if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
+            double m0 = tid < NU ? ms[tid] : 0.0, myinv = 0.0;
+            const int ll = tid < NU ? tid : NU - 1;
+            { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
+            // L(ll, j) for j < ll: row ll of the panels, 6 doubles per row (rolled loops: see pass A1)
+#pragma unroll 1
+            for (int jb = 0; jb < 5; jb++) {
+                const double* rowb = sM + P_OFF(jb) + (ll - PB * jb) * PB;
+#pragma unroll 1
+                for (int jj = 0; jj < PB; jj++) {
+                    const int j = PB * jb + jj;
+                    const double xj = __shfl_sync(0xffffffffu, m0 * myinv, j);
+                    const double lv = (tid > j && tid < NU) ? rowb[jj] : 0.0;
+                    m0 = (tid == j) ? xj : fma(-lv, xj, m0);
+                }
+            }
+            if (tid < NU) { lus[tid] = m0; vk[V_KFF + tid] = m0; }
+        }
+        __syncthreads();
+        if (tid < NX) {                                      // p = m_x - Lxu lu
+            double s0 = ms[NU + tid], s1 = 0.0;
+#pragma unroll
+            for (int jb = 0; jb < 5; jb++) {
+                double lv[6];
+                load6(sM + P_OFF(jb) + (NU + tid - PB * jb) * PB, lv);
+#pragma unroll
+                for (int c = 0; c < 6; c += 2) { s0 -= lv[c] * lus[PB * jb + c]; s1 -= lv[c + 1] * lus[PB * jb + c + 1]; }
+            }
+            const double pv = s0 + s1;
+            pnk[tid] = pv; vk[V_P + tid] = pv;
+        }
+        __syncthreads();
+    }
+    fq_pass_end();
+    return ph;
+}
+
+// =============================================================================================
+// the kernel
+// =============================================================================================
+__global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
+{
+    const int tid = threadIdx.x;
+    const int bl = blockIdx.x, b = a.b0 + bl, N = a.N;
+    if (a.sqp_done && a.sqp_done[b]) return;             // finished problems keep their statistics
+    if (tid == 0) {
+        fq_ctx.SRb = a.SR + (size_t)bl * (N + 1) * SR_SZ;
+        fq_ctx.FRb = a.FR + (size_t)bl * (N + 1) * FR_SZ;
+        fq_ctx.vb = a.vec + (size_t)bl * (N + 1) * V_STAGE;
+        fq_ctx.qz = a.qz + (size_t)b * (N + 1) * NZ;
+        fq_ctx.qpi = a.qpi + (size_t)b * N * NX;
+        fq_ctx.qlam = a.qlam + (size_t)b * (N + 1) * 2 * NG;
+        fq_ctx.qt = a.qt + (size_t)b * (N + 1) * 2 * NG;
+        fq_ctx.dt = a.dt; fq_ctx.c2 = a.c2; fq_ctx.N = N;
+#pragma unroll
+        for (int i = 0; i < 4; i++) mbar_init(&fq_bars[i], 1);
+        fence_barrier_init();
+#ifdef NMPC_TIMING
+        for (int i = 0; i < 24; i++) fq_tacc[i] = 0ULL;
+        fq_tprev = clock64();
+#endif
+    }
+    __syncthreads();
+
+    // ---- start of the QP ----
+    {
+        double* qz = fq_ctx.qz;
+        double* qpi = fq_ctx.qpi;
+        if (a.warm == 0)
+            for (int i = tid; i < (N + 1) * NZ; i += FQ_THREADS) qz[i] = 0.0;
+        if (a.warm < 2)
+            for (int i = tid; i < N * NX; i += FQ_THREADS) qpi[i] = 0.0;
+        __syncthreads();
+        if (tid < NX)
+            qz[NU + tid] = a.dx0_ext ? a.dx0_ext[(size_t)b * NX + tid]
+                                     : a.x0[(size_t)b * NX + tid] - a.x[(size_t)b * (N + 1) * NX + tid];
+        if (tid < NU) qz[(size_t)N * NZ + tid] = 0.0;
+        fq_pass_end();
+    }
+
+    uint32_t ph = 0;
+    int status = 1, iters = 0, nc_total = 0, ncond = 0;
+    double alpha_p = 1.0, alpha_d = 1.0;
+
+    for (int it = 0; it <= a.max_iter; it++) {
+        const bool last = (it >= a.max_iter);
+        if (it > 0) {
+            alpha_p *= (1.0 - alpha_p) * 0.99 + alpha_p * 0.9999999;
+            alpha_d *= (1.0 - alpha_d) * 0.99 + alpha_d * 0.9999999;
+            if (alpha_p < IPM_ALPHA_MIN && alpha_d < IPM_ALPHA_MIN) { status = 2; break; }
+        }
+        iters = it;
+        FMARK(0);
+        // ================= update + residuals of every stage, norms, mu, exit tests =================
+        double o[6];
+        ph = fq_pass_R(ph, it, a.warm, alpha_p, alpha_d, o);
+        FMARK(1);
+        if (it == 0) nc_total = (int)(o[5] + 0.5);
+        const double mu = nc_total > 0 ? o[4] / nc_total : 0.0;
         {
             bool bad = false, conv = true;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                if (isinf(res4[i]) || !(res4[i] == res4[i])) bad = true;
-                if (!(res4[i] < a.tol)) conv = false;
-                if (tid == 0) a.qp_res[(size_t)b * 4 + i] = res4[i];      // residuals of the last iterate that was evaluated
+                if (isinf(o[i]) || !(o[i] == o[i])) bad = true;
+                if (!(o[i] < a.tol)) conv = false;
+                if (tid == 0) a.qp_res[(size_t)b * 4 + i] = o[i];         // residuals of the last iterate that was evaluated
             }
             if (bad) { status = 3; break; }
             if (conv) { status = 0; break; }
             if (last) { status = 1; break; }
         }
-
+        // ================= factorisation sweep =================
+        ph = fq_pass_F(ph);
+        FMARK(3);
+        // ================= affine direction, step lengths, centring parameter =================
+        ph = fq_pass_A1(ph);
         FMARK(8);
-        // ================= forward sweep: affine direction, step lengths =================
-        double a_p = 1.0, a_d = 1.0;
-        double cs[3] = {0.0, 0.0, 0.0};
-        if (tid < NX) sv[FV_DX + tid] = 0.0;
-        if (tid == 0) bulk_store_wait_all();                         // the factor records are in global memory
-        __syncthreads();
-        for (int k = 0; k <= N; k++) {
-            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
-            const bool term = (k == N);
-            double* vk = vb + (size_t)k * V_STAGE;
-            if (tid == 0) {
-                const uint32_t bytes = (SR_SZ + (term ? 0 : LP_UPANELS)) * 8;
-                mbar_arrive_expect_tx(&bar, bytes);
-                bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
-                if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
-            }
-            if (!term && tid < NX) sv[FV_RB + tid] = vk[V_RB + tid];
-            __syncthreads();
-            mbar_wait(&bar, phase); phase ^= 1;
-            fq_forward_stage<false>(sM, sP, S, sv, vk, nullptr, qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG,
-                                    term, tid, dt, c2, a_p, a_d, cs);
-        }
-        a_p = fq_block_min(a_p, red, tid);
-        a_d = fq_block_min(a_d, red, tid);
-        const double alpha_aff = fmin(a_p, a_d);
-
+        ph = fq_pass_B<false>(ph, o);
         FMARK(9);
-        // ================= centring parameter (nmpc_qp_sigma_kernel) =================
         double sigma_mu, mu_aff;
         {
-            const double s0 = fq_block_sum(cs[0], red, tid);
-            const double s1 = fq_block_sum(cs[1], red, tid);
-            const double s2 = fq_block_sum(cs[2], red, tid);
-            const double s = fma(alpha_aff, fma(alpha_aff, s2, s1), s0);
+            const double alpha_aff = fmin(o[0], o[1]);
+            const double s = fma(alpha_aff, fma(alpha_aff, o[4], o[3]), o[2]);
             mu_aff = nc_total > 0 ? s / nc_total : 0.0;
             double sg = mu > 0.0 ? mu_aff / mu : 0.0;
             sg = sg * sg * sg;
             sigma_mu = fmax(sg * mu, IPM_TAU_MIN);
         }
-
-        FMARK(10);
         // Corrector on the stored factorisation.  Pass 0 is Mehrotra's centring-corrector direction (HPIPM
         // COMPUTE_CENTERING_CORRECTION_QP); pass 1 runs only when the conditional predictor-corrector rejects it
         // (HPIPM arg->cond_pred_corr): if the complementarity predicted along it exceeds twice the affine
         // prediction, the centring direction alone (COMPUTE_CENTERING_QP: rm = lam t - sigma mu) is solved for.
         for (int cpass = 0; cpass < 2; cpass++) {
-        // ================= corrector: backward vector sweep on the stored factorisation =================
-        for (int k = N; k >= 0; k--) {
-            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
-            const bool term = (k == N);
-            double* vk = vb + (size_t)k * V_STAGE;
-            if (tid == 0) {
-                // SR_k, the u panels of stage k, and (once, for the terminal stage) nothing else: P_{k+1} is
-                // already in sP from the previous step of this sweep
-                const uint32_t bytes = (SR_SZ + (term ? 0 : LP_UPANELS)) * 8;
-                mbar_arrive_expect_tx(&bar, bytes);
-                bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
-                if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
-            }
-            double g_lam = 0.0, g_t = 1.0, g_dt = 0.0, g_dl = 0.0, g_rd = 0.0;
-            if (tid < 2 * NG) {                                      // requested before the waits below
-                g_lam = qlamb[(size_t)k * 2 * NG + tid]; g_t = qtb[(size_t)k * 2 * NG + tid];
-                g_dt = vk[V_DT + tid]; g_dl = vk[V_DLAM + tid]; g_rd = vk[V_RD + tid];
-            }
-            if (!term && tid < NX) sv[FV_RB + tid] = vk[V_RB + tid];
-            if (tid < NZ) sv[FV_RG + tid] = vk[V_RG + tid];
-            __syncthreads();
+            ph = fq_pass_C1(ph, cpass, sigma_mu);
+            FMARK(10);
+            ph = fq_pass_C2(ph);
+            FMARK(11);
+            ph = fq_pass_A1(ph);
+            FMARK(12);
+            ph = fq_pass_B<true>(ph, o);
             FMARK(13);
-            mbar_wait(&bar, phase); phase ^= 1;
-            FMARK(14);
-            // corrector complementarity residual, gamma
-            if (tid < 2 * NG) {
-                double v = 0.0;
-                if (S[SR_D + 2 * NG + tid] > 0.5) {
-                    const double lam = g_lam, t = g_t;
-                    const double rmc = fma(lam, t, cpass == 0 ? g_dt * g_dl : 0.0) - sigma_mu;
-                    vk[V_RM + tid] = rmc;
-                    v = (rmc + lam * g_rd) / t;
-                }
-                sv[FV_RD + tid] = v;                                 // scratch: per-side gamma
-            }
-            __syncthreads();
-            if (tid < NG) sv[FV_GAMV + tid] = sv[FV_RD + tid] - sv[FV_RD + NG + tid];
-            if (!term && tid >= 64 && tid < 64 + NX) {               // w = P+ rb + p+
-                const int i = tid - 64;
-                const double* row = sP + i * P_LD;
-                double s0 = sv[FV_PN + i], s1 = 0.0;
-#pragma unroll
-                for (int j = 0; j < NX; j += 2) { s0 += row[j] * sv[FV_RB + j]; s1 += row[j + 1] * sv[FV_RB + j + 1]; }
-                sv[FV_W + i] = s0 + s1;
-            }
-            __syncthreads();
-            FMARK(15);
-            if (tid < NZ) {                                          // m = rg + C' gamma + G' w
-                double s = sv[FV_RG + tid] + fq_ct(S, sv + FV_GAMV, tid);
-                if (!term) s += fq_gt(S, sv + FV_W, tid, dt, c2);
-                sv[FV_QT + tid] = s;
-            }
-            __syncthreads();
-            FMARK(16);
-            if (tid == 0) {                                          // sP is free: fetch P_k for the next step
-                mbar_arrive_expect_tx(&bar, NX * P_LD * 8);
-                bulk_g2s(sP, FRb + (size_t)k * FR_SZ + FR_P, NX * P_LD * 8, &bar);
-            }
-            __syncwarp();         // reconverge warp 0 before its shuffles: a split warp takes the slow shuffle path
-            if (!term) {
-                if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
-                    double m0 = tid < NU ? sv[FV_QT + tid] : 0.0, myinv = 0.0;
-                    const int ll = tid < NU ? tid : NU - 1;
-                    { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
-#pragma unroll
-                    for (int j = 0; j < NU; j++) {
-                        const double xj = __shfl_sync(0xffffffffu, m0 * myinv, j);
-                        // L(ll, j), ll > j: compile-time panel offset + 6 ll
-                        const double lv = (tid > j && tid < NU) ? sM[P_OFF(j / PB) - PB * PB * (j / PB) + j % PB + PB * ll] : 0.0;
-                        m0 = (tid == j) ? xj : ((tid > j && tid < NU) ? fma(-lv, xj, m0) : m0);
-                    }
-                    if (tid < NU) { sv[FV_DZ + tid] = m0; vk[V_LROW + tid] = m0; }
-                }
-                __syncthreads();
-                FMARK(17);
-                if (tid < NX) {                                      // p = m_x - Lxu lu
-                    double s0 = sv[FV_QT + NU + tid], s1 = 0.0;
-                    const double* row = sM;                          // panel-packed: gather per panel
-#pragma unroll
-                    for (int jb = 0; jb < 5; jb++) {
-                        double lv[6];
-                        load6(row + P_OFF(jb) + (NU + tid - PB * jb) * PB, lv);
-#pragma unroll
-                        for (int c = 0; c < 6; c += 2) { s0 -= lv[c] * sv[FV_DZ + PB * jb + c]; s1 -= lv[c + 1] * sv[FV_DZ + PB * jb + c + 1]; }
-                    }
-                    const double pv = s0 + s1;
-                    sv[FV_PN + tid] = pv; vk[V_P + tid] = pv;
-                }
-            } else if (tid < NX) {
-                const double pv = sv[FV_QT + NU + tid];
-                sv[FV_PN + tid] = pv; vk[V_P + tid] = pv;
-            }
-            __syncthreads();
-            FMARK(18);
-            mbar_wait(&bar, phase); phase ^= 1;                      // P_k is in sP
-            __syncthreads();      // nobody may still be polling this phase when thread 0 re-arms the barrier
-            FMARK(19);
-        }
-
-        FMARK(11);
-        // ================= corrector: forward sweep with multiplier directions =================
-        a_p = 1.0; a_d = 1.0;
-        cs[0] = 0.0; cs[1] = 0.0; cs[2] = 0.0;
-        if (tid < NX) sv[FV_DX + tid] = 0.0;
-        __syncthreads();
-        for (int k = 0; k <= N; k++) {
-            const int tid = fq_opaque(tid_k);        // per-stage copy: thread-invariant addresses are not hoisted (and spilled)
-            const bool term = (k == N);
-            double* vk = vb + (size_t)k * V_STAGE;
-            if (tid == 0) {
-                const uint32_t bytes = (SR_SZ + (term ? 0 : LP_UPANELS) + (k > 0 ? NX * P_LD : 0)) * 8;
-                mbar_arrive_expect_tx(&bar, bytes);
-                bulk_g2s(S, SRb + (size_t)k * SR_SZ, SR_SZ * 8, &bar);
-                if (!term) bulk_g2s(sM, FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, &bar);
-                if (k > 0) bulk_g2s(sP, FRb + (size_t)k * FR_SZ + FR_P, NX * P_LD * 8, &bar);
-            }
-            if (tid < NX) {
-                sv[FV_RB + tid] = term ? 0.0 : vk[V_RB + tid];
-                sv[FV_PN + tid] = vk[V_P + tid];
-            }
-            __syncthreads();
-            mbar_wait(&bar, phase); phase ^= 1;
-            if (!term && tid < NU) sM[lp_idx(NZ, tid)] = vk[V_LROW + tid];      // the corrector's lu replaces the affine one
-            __syncthreads();
-            fq_forward_stage<true>(sM, sP, S, sv, vk, k > 0 ? vb + (size_t)(k - 1) * V_STAGE + V_DPI : nullptr,
-                                   qlamb + (size_t)k * 2 * NG, qtb + (size_t)k * 2 * NG, term, tid, dt, c2, a_p, a_d, cs);
-        }
-        alpha_p = fq_block_min(a_p, red, tid);
-        alpha_d = fq_block_min(a_d, red, tid);
-        if (cpass == 1 || !a.cond_pred_corr) break;
-        {
-            const double s0 = fq_block_sum(cs[0], red, tid);
-            const double s1 = fq_block_sum(cs[1], red, tid);
-            const double s2 = fq_block_sum(cs[2], red, tid);
+            alpha_p = o[0]; alpha_d = o[1];
+            if (cpass == 1 || !a.cond_pred_corr) break;
             const double al = fmin(alpha_p, alpha_d);
-            const double mu_c = nc_total > 0 ? fma(al, fma(al, s2, s1), s0) / nc_total : 0.0;
+            const double mu_c = nc_total > 0 ? fma(al, fma(al, o[4], o[3]), o[2]) / nc_total : 0.0;
             if (!(mu_c > 2.0 * mu_aff)) break;
             ncond++;
         }
-        }
-        FMARK(12);
     }
-
 #ifdef NMPC_TIMING
-    if (bl == 0 && tid == 0) {
-#pragma unroll
-        for (int i = 0; i < 24; i++) g_fq_cycles[i] += f_acc[i];
-    }
+    if (bl == 0 && tid == 0)
+        for (int i = 0; i < 24; i++) g_fq_cycles[i] += fq_tacc[i];
 #endif
     // ---- statistics of this QP ----
     if (tid == 0) {
-        bulk_store_wait_all();
         a.qp_iter[b] = iters;
         a.qp_status[b] = status;
         a.qp_ncond[b] = ncond;
     }
-#undef SRb
-#undef FRb
-#undef vb
-#undef qz
-#undef qpi
-#undef qlamb
-#undef qtb
 }

@@ -22,19 +22,32 @@ __host__ __device__ __forceinline__ int lp_idx(int i, int j)
     return P_OFF(jb) + (i - PB * jb) * PB + (j - PB * jb);
 }
 
-// per-stage slots of the per-problem vector workspace (doubles)
-#define V_RG 0
-#define V_RB (V_RG + NZ)
-#define V_RD (V_RB + NX)
-#define V_RM (V_RD + 2 * NG)
-#define V_QT (V_RM + 2 * NG)
-#define V_DZ (V_QT + NZ)
-#define V_DPI (V_DZ + NZ)
-#define V_DT (V_DPI + NX)
-#define V_DLAM (V_DT + 2 * NG)
-#define V_P (V_DLAM + 2 * NG)
-#define V_LROW (V_P + NX)                // l = L^-1 m of the corrector solve
-#define V_STAGE 752                      // 750 rounded up to a multiple of 8
+// per-stage record of the per-problem vector workspace `vec` (doubles).  Grouped so that every pass of the
+// interior point fetches what it needs with one or two bulk copies (all offsets and spans are multiples of 16 B):
+//   F  (factorisation sweep)   QT GAM KFF RB   one span of 186
+//   A1 / D1 (forward chain)    KFF RB          72
+//   A2 / D2 (forward bulk)     DZ RD RM        240
+//   R  (update + residuals)    DZ | DT DLAM | DPI of the previous stage
+//   C1 (corrector bulk)        RG PRB | DT DLAM | RD
+//   C2 (corrector chain)       M0
+#define V_QT 0                           // 72  q~ = rg + C' gamma: linear term of the stage before G' w
+#define V_GAM (V_QT + NZ)                // 42  Gamma = lam_l / t_l + lam_u / t_u
+#define V_KFF (V_GAM + NG)               // 30  feed-forward input step  Luu^-T lu
+#define V_RB (V_KFF + NU)                // 42  dynamics residual
+#define V_DZ (V_RB + NX)                 // 72  primal direction
+#define V_RD (V_DZ + NZ)                 // 84  slack residual
+#define V_RM (V_RD + 2 * NG)             // 84  complementarity residual (affine, then corrector)
+#define V_DT (V_RM + 2 * NG)             // 84
+#define V_DLAM (V_DT + 2 * NG)           // 84
+#define V_RG (V_DLAM + 2 * NG)           // 72  stationarity residual
+#define V_PRB (V_RG + NZ)                // 42  P_{k+1} rb_k (kept from the factorisation for the corrector)
+#define V_M0 (V_PRB + NX)                // 72  corrector: rg + C' gamma_c + G' (P+ rb)
+#define V_P (V_M0 + NZ)                  // 42  corrector: linear term p_k of the cost-to-go
+#define V_DPI (V_P + NX)                 // 42  direction of the dynamics multiplier pi_k
+#define V_STAGE (V_DPI + NX)             // 864
+static_assert(V_GAM % 2 == 0 && V_KFF % 2 == 0 && V_RB % 2 == 0 && V_DZ % 2 == 0 && V_RD % 2 == 0 && V_RM % 2 == 0 &&
+              V_DT % 2 == 0 && V_DLAM % 2 == 0 && V_RG % 2 == 0 && V_PRB % 2 == 0 && V_M0 % 2 == 0 && V_P % 2 == 0 &&
+              V_DPI % 2 == 0 && V_STAGE % 2 == 0, "16-byte alignment of bulk copies");
 
 #define POS_INF_BITS 0x7ff0000000000000ULL
 #define ONE_BITS 0x3ff0000000000000ULL
