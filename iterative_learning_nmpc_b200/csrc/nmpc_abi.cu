@@ -852,8 +852,8 @@ extern "C" int nmpc_debug_phase_cycles(unsigned long long* out24, int reset)
 {
 #ifdef NMPC_TIMING
     CK(cudaDeviceSynchronize());
-    CK(cudaMemcpyFromSymbol(out24, g_fq_cycles, sizeof(unsigned long long) * 24));
-    if (reset) { unsigned long long z[24] = {0}; CK(cudaMemcpyToSymbol(g_fq_cycles, z, sizeof(z))); }
+    CK(cudaMemcpyFromSymbol(out24, g_fq_cycles, sizeof(unsigned long long) * 32));
+    if (reset) { unsigned long long z[32] = {0}; CK(cudaMemcpyToSymbol(g_fq_cycles, z, sizeof(z))); }
     return 0;
 #else
     (void)out24; (void)reset;

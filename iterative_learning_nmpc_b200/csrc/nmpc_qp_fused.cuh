@@ -181,6 +181,31 @@ __device__ __forceinline__ double fq_ct(const double* S, const double* g, int c)
     return g[GR_CONS + c - IH];
 }
 
+// (C' g1)[c] and (C' g2)[c] with one pass over the matrix entries
+__device__ __forceinline__ void fq_ct2(const double* S, const double* g1, const double* g2, int c, double& o1, double& o2)
+{
+    double s = 0.0, q = 0.0;
+    if (c < IFRC) { o1 = 0.0; o2 = 0.0; return; }
+    if (c < IQ) {
+        const int ft = (c - IFRC) / 3, i = (c - IFRC) % 3;
+#pragma unroll
+        for (int r = 0; r < 5; r++) { const double m = S[SR_CF + 3 * (5 * ft + r) + i]; s = fma(m, g1[5 * ft + r], s); q = fma(m, g2[5 * ft + r], q); }
+        o1 = s; o2 = q; return;
+    }
+    if (c < IH) {
+        const double* cx = S + SR_CX + (c - IQ);
+        double s1 = 0.0, q1 = 0.0;
+#pragma unroll
+        for (int jj = 0; jj < NGX; jj += 2) {
+            const double m0 = cx[SR_CXLD * jj], m1 = cx[SR_CXLD * (jj + 1)];
+            s = fma(m0, g1[NGF + jj], s); s1 = fma(m1, g1[NGF + jj + 1], s1);
+            q = fma(m0, g2[NGF + jj], q); q1 = fma(m1, g2[NGF + jj + 1], q1);
+        }
+        o1 = s + s1; o2 = q + q1; return;
+    }
+    o1 = g1[GR_CONS + c - IH]; o2 = g2[GR_CONS + c - IH];
+}
+
 // (G' w)[c] for w over the next state (structured dynamics)
 __device__ __forceinline__ double fq_gt(const double* S, const double* w, int c, double dt, double c2)
 {
@@ -510,8 +535,8 @@ __device__ __forceinline__ void fq_pass_end()
 }
 
 #ifdef NMPC_TIMING
-__device__ unsigned long long g_fq_cycles[24];
-__shared__ unsigned long long fq_tacc[24];
+__device__ unsigned long long g_fq_cycles[32];
+__shared__ unsigned long long fq_tacc[32];
 __shared__ long long fq_tprev;
 #define FMARK(ph_) do { if (threadIdx.x == 0) { const long long t_ = clock64(); fq_tacc[ph_] += (unsigned long long)(t_ - fq_tprev); fq_tprev = t_; } } while (0)
 #else
@@ -560,7 +585,9 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
         const int k = N - i, slot = i % R_DEPTH;
         const bool term = (k == N);
         if (tid == FQ_ISSUER && i + R_DEPTH - 1 <= N) fq_issue_R(k - (R_DEPTH - 1), (i + R_DEPTH - 1) % R_DEPTH, upd);
+        FMARK(1);
         fq_ring_wait(slot, ph);
+        FMARK(18);
         const double* sl = fq_smem + slot * R_SLOT;
         const double* S = sl + R_SR;
         double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
@@ -580,6 +607,7 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
             pik[l] = p;
         }
         __syncthreads();
+        FMARK(19);
         // ---- step 2: C z; dynamics residual ----
         fq_cz(S, zc, rv + RV_CZ, tid);
         if (!term && tid >= 80 && tid < 80 + NX) {
@@ -589,6 +617,7 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
             n_b = nanmax(n_b, fabs(rb));
         }
         __syncthreads();
+        FMARK(20);
         // ---- step 3: both sides of constraint row j: slacks, multipliers, rd, rm, Gamma, gamma ----
         if (tid < NG) {
             const int j = tid;
@@ -607,7 +636,7 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
                 const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
                 if (it == 0) {               // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
                     if (msk) {
-                        if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 / t; }
+                        if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 * __drcp_rn(t); }
                         else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
                     } else { t = 1.0; lam = 0.0; }
                     fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
@@ -619,8 +648,9 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
                 n_d = nanmax(n_d, fabs(rd));
                 n_m = nanmax(n_m, fabs(rm));
                 if (msk) {
-                    const double g = (rm + lam * rd) / t;
-                    Gam += lam / t;
+                    const double ti = __drcp_rn(t);          // one reciprocal per side instead of two divisions
+                    const double g = (rm + lam * rd) * ti;
+                    Gam += lam * ti;
                     if (e) { gam -= g; dl -= lam; } else { gam += g; dl += lam; }
                 }
             }
@@ -628,19 +658,22 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
             rv[RV_GAMV + j] = gam; rv[RV_CZ + j] = dl;
         }
         __syncthreads();
+        FMARK(21);
         // ---- step 4: stationarity residual and the linear term q~ = rg + C' gamma ----
         if (tid < NZ) {
             const int c = tid;
             double s = S[SR_GR + c] + fq_h(S, zc, c);
             if (c >= NU && k > 0) s -= pik[c - NU];
-            s -= fq_ct(S, rv + RV_CZ, c);
-            const double qp = fq_ct(S, rv + RV_GAMV, c);
+            double cdl, qp;
+            fq_ct2(S, rv + RV_CZ, rv + RV_GAMV, c, cdl, qp);
+            s -= cdl;
             if (!term) s += fq_gt(S, pin, c, dt, c2);
             if ((k == 0 && c >= NU) || (term && c < NU)) s = 0.0;
             vk[V_RG + c] = s; vk[V_QT + c] = qp + s;
             n_g = nanmax(n_g, fabs(s));
         }
         __syncthreads();
+        FMARK(22);
     }
     out[0] = fq_block_max(n_g, red, tid);
     out[1] = fq_block_max(n_b, red, tid);
@@ -870,9 +903,8 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
 #pragma unroll
                     for (int j = 0; j < PB; j++) {
                         const double v = A[j][j];
-                        double d = 0.0, inv = 0.0;
-                        if (v > 0.0) { inv = rsqrt(v); d = v * inv; }
-                        A[j][j] = d;
+                        const double inv = (v > 0.0) ? rsqrt(v) : 0.0;
+                        A[j][j] = inv;                       // the sweeps only ever divide by the diagonal: keep 1 / L_jj
 #pragma unroll
                         for (int i = j + 1; i < PB; i++) A[i][j] *= inv;
                         rv[j] *= inv;
@@ -956,6 +988,27 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
             }
         }
         if (tid < NX) fv[FV_PN + tid] = fv[FV_QT + NU + tid];
+        if (!term && tid >= N_XTILES) {
+            // Inverses of the five 6 x 6 diagonal blocks of Luu, for the blocked triangular solves of passes A1 / D1 /
+            // C2 (5 block steps instead of 30 scalar steps on the dependent chain).  The diagonal already holds
+            // 1 / L_jj; the strictly lower part of the inverse goes, transposed, into the unused upper triangle of the
+            // block, so nothing that is still being read is overwritten.  Done by the threads that own no state tile.
+            for (int col = tid - N_XTILES; col < NU; col += FQ_THREADS - N_XTILES) {
+                double* blk = sM + P_OFF(col / PB);
+                const int cc = col % PB;
+                double x[PB];
+#pragma unroll
+                for (int r = 0; r < PB; r++) {
+                    double sacc = (r == cc) ? 1.0 : 0.0;
+#pragma unroll
+                    for (int m = 0; m < r; m++) sacc = fma(-blk[r * PB + m], x[m], sacc);
+                    x[r] = sacc * blk[r * PB + r];
+                }
+#pragma unroll
+                for (int r = 1; r < PB; r++)
+                    if (r > cc) blk[cc * PB + r] = x[r];
+            }
+        }
         if (!term && tid < NU) vk[V_KFF + tid] = sM[lp_idx(NZ, tid)];     // lu of the affine direction, for pass A1
         fence_proxy_async();
         __syncthreads();
@@ -1006,7 +1059,9 @@ __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
         double* dz = av + AV_DZ;
         if (!term) {
             if (tid == FQ_ISSUER && k + A_DEPTH - 1 < N) fq_issue_A(k + A_DEPTH - 1, (k + A_DEPTH - 1) % A_DEPTH);
+            FMARK(8);
             fq_ring_wait(slot, ph);
+            FMARK(23);
             const double* sl = fq_smem + slot * A_SLOT;
             const double* sM = sl + A_MU;
             if (tid < 32) {             // du = -Luu^-T (lu + Lxu' dx)
@@ -1021,24 +1076,44 @@ __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
                     }
                     rhs += r1;
                 }
-                // back substitution with Luu': branch-free, one shuffle + multiply + fused multiply-add per step;
-                // lane l keeps rhs_l * (1 / L_ll) ready so the broadcast value is already the solution component
-                double du = 0.0, myinv = 0.0;
+                // Back substitution with Luu', blocked by the 6 x 6 diagonal blocks whose inverses the factorisation left
+                // in the panels: per block, 6 broadcasts + 6 multiply-adds solve the block, 6 + 6 more update the lanes
+                // before it.  Row li of a stored diagonal block reads [L(li, < li) | 1 / L_ii | inverse(> li, li)], so
+                // the coefficients of lane ll's block solve are one row with the leading entries masked.
                 const int ll = lane < NU ? lane : NU - 1;
-                { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
-                // L(i, ll) for i >= ll sits at colb + 6 i (panel-packed, 6 doubles per row).  The loop is kept rolled:
-                // the chain is latency-bound either way, and 30 unrolled steps are 14 KB of code
-                const double* colb = sM + P_OFF(ll / PB) - PB * PB * (ll / PB) + ll % PB;
+                const int lb = ll / PB, li = ll % PB;
+                double cf[PB];
+                load6(sM + P_OFF(lb) + li * PB, cf);
+#pragma unroll
+                for (int m = 0; m < PB; m++) cf[m] = (m >= li) ? cf[m] : 0.0;
+                // L(i, ll) for i >= ll sits at colb + 6 i (panel-packed, 6 doubles per row)
+                const double* colb = sM + P_OFF(lb) - PB * PB * lb + li;
+                double xs = 0.0;
 #pragma unroll 1
-                for (int i = NU - 1; i >= 0; i--) {
-                    const double dui = -__shfl_sync(0xffffffffu, rhs * myinv, i);
-                    const double lv = (lane < i) ? colb[PB * i] : 0.0;
-                    du = (lane == i) ? dui : du;
-                    rhs = fma(lv, dui, rhs);
+                for (int bk = NU / PB - 1; bk >= 0; bk--) {
+                    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+                    for (int m = 0; m < PB; m += 2) {
+                        a0 = fma(cf[m], __shfl_sync(0xffffffffu, rhs, PB * bk + m), a0);
+                        a1 = fma(cf[m + 1], __shfl_sync(0xffffffffu, rhs, PB * bk + m + 1), a1);
+                    }
+                    const double xb = a0 + a1;               // the solution component of the lanes of block bk
+                    xs = (lb == bk) ? xb : xs;
+                    double u0 = 0.0, u1 = 0.0;
+#pragma unroll
+                    for (int m = 0; m < PB; m += 2) {
+                        const double l0 = (lane < PB * bk) ? colb[PB * (PB * bk + m)] : 0.0;
+                        const double l1 = (lane < PB * bk) ? colb[PB * (PB * bk + m + 1)] : 0.0;
+                        u0 = fma(l0, __shfl_sync(0xffffffffu, xb, PB * bk + m), u0);
+                        u1 = fma(l1, __shfl_sync(0xffffffffu, xb, PB * bk + m + 1), u1);
+                    }
+                    rhs -= u0 + u1;
                 }
+                const double du = -xs;
                 if (lane < NU) dz[lane] = du;
             } else if (tid < 32 + NX) dz[NU + tid - 32] = dx[tid - 32];
             __syncthreads();
+            FMARK(24);
             if (tid < NZ) vk[V_DZ + tid] = dz[tid];
             if (tid < 2 * NQ) dxn[tid] = fq_g(sl + A_H, dz, tid, dt, c2) + sl[A_RB + tid];
             else if (tid >= 64 && tid < 96) {                // momentum rows: four threads per row (warp 2, all lanes shuffle)
@@ -1106,7 +1181,7 @@ __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
     const int N = fq_ctx.N;
     double* cz = fq_smem + (CORR ? DV_BASE : BV_BASE);
     double* red = fq_smem + FQ_RED;
-    double a_p = 1.0, a_d = 1.0, cs0 = 0.0, cs1 = 0.0, cs2 = 0.0;
+    double r_p = 1.0, r_d = 1.0, cs0 = 0.0, cs1 = 0.0, cs2 = 0.0;
     if (tid == FQ_ISSUER)
         for (int i = 0; i < DEPTH - 1 && i <= N; i++) fq_issue_B<CORR>(i, i % DEPTH);
     for (int k = 0; k <= N; k++) {
@@ -1138,9 +1213,11 @@ __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
                 const double lam = sl[OLAM + tid], t = sl[OT + tid];
                 const double cdz = cz[j];
                 dtv = (e ? -cdz : cdz) + sl[ORD + tid];
-                dl = -(sl[ORM + tid] + lam * dtv) / t;
-                if (dtv < 0.0) a_p = fmin(a_p, -t / dtv);
-                if (dl < 0.0) a_d = fmin(a_d, -lam / dl);
+                dl = -(sl[ORM + tid] + lam * dtv) * __drcp_rn(t);
+                // step lengths: the largest ratios -dt / t, -dlam / lam are tracked (one division at the end of the pass
+                // instead of two per row); fmax drops a NaN ratio the way the comparison dt < 0 did
+                r_p = fmax(r_p, -dtv * __drcp_rn(t));
+                r_d = fmax(r_d, -dl * __drcp_rn(lam));
                 cs0 = fma(lam, t, cs0); cs1 += fma(lam, dtv, t * dl); cs2 = fma(dl, dtv, cs2);
             }
             vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
@@ -1148,8 +1225,8 @@ __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
         __syncthreads();
         if (!CORR) FMARK(17);
     }
-    out[0] = fq_block_min(a_p, red, tid);
-    out[1] = fq_block_min(a_d, red, tid);
+    out[0] = 1.0 / fq_block_max(r_p, red, tid);              // min(1, min_i -t_i / dt_i)
+    out[1] = 1.0 / fq_block_max(r_d, red, tid);
     out[2] = fq_block_sum(cs0, red, tid);
     out[3] = fq_block_sum(cs1, red, tid);
     out[4] = fq_block_sum(cs2, red, tid);
@@ -1201,7 +1278,7 @@ __device__ __noinline__ uint32_t fq_pass_C1(uint32_t ph, int cpass, double sigma
                     const double lam = sl[C_LAM + row], t = sl[C_T + row];
                     const double rmc = fma(lam, t, cpass == 0 ? sl[C_DT + row] * sl[C_DLAM + row] : 0.0) - sigma_mu;
                     vk[V_RM + row] = rmc;
-                    const double v = (rmc + lam * sl[C_RD + row]) / t;
+                    const double v = (rmc + lam * sl[C_RD + row]) * __drcp_rn(t);
                     g += e ? -v : v;
                 }
             }
@@ -1261,20 +1338,37 @@ __device__ __noinline__ uint32_t fq_pass_C2(uint32_t ph)
         if (tid < NZ) ms[tid] = sl[E_M0 + tid] + fq_gt(sl + E_H, pnn, tid, dt, c2);
         __syncthreads();
         if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
-            double m0 = tid < NU ? ms[tid] : 0.0, myinv = 0.0;
+            // blocked forward substitution (see pass A1): row li of the inverse of the diagonal block is the column li of
+            // the stored block above the diagonal, 1 / L_ii on it
+            double r0 = tid < NU ? ms[tid] : 0.0;
             const int ll = tid < NU ? tid : NU - 1;
-            { const double d = sM[lp_idx(ll, ll)]; myinv = d != 0.0 ? __drcp_rn(d) : 0.0; }
-            // L(ll, j) for j < ll: row ll of the panels, 6 doubles per row (rolled loops: see pass A1)
+            const int lb = ll / PB, li = ll % PB;
+            double cf[PB];
+            {
+                const double* blk = sM + P_OFF(lb);
+#pragma unroll
+                for (int m = 0; m < PB; m++) cf[m] = (m <= li) ? blk[(m < li ? m : li) * PB + li] : 0.0;
+            }
+            double m0 = 0.0;
 #pragma unroll 1
-            for (int jb = 0; jb < 5; jb++) {
-                const double* rowb = sM + P_OFF(jb) + (ll - PB * jb) * PB;
-#pragma unroll 1
-                for (int jj = 0; jj < PB; jj++) {
-                    const int j = PB * jb + jj;
-                    const double xj = __shfl_sync(0xffffffffu, m0 * myinv, j);
-                    const double lv = (tid > j && tid < NU) ? rowb[jj] : 0.0;
-                    m0 = (tid == j) ? xj : fma(-lv, xj, m0);
+            for (int bk = 0; bk < NU / PB; bk++) {
+                double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+                for (int m = 0; m < PB; m += 2) {
+                    a0 = fma(cf[m], __shfl_sync(0xffffffffu, r0, PB * bk + m), a0);
+                    a1 = fma(cf[m + 1], __shfl_sync(0xffffffffu, r0, PB * bk + m + 1), a1);
                 }
+                const double yb = a0 + a1;
+                m0 = (lb == bk) ? yb : m0;
+                double lv[PB];
+                load6(sM + P_OFF(bk) + (ll - PB * bk) * PB, lv);         // L(ll, 6 bk ..), used by the lanes after the block
+                double u0 = 0.0, u1 = 0.0;
+#pragma unroll
+                for (int m = 0; m < PB; m += 2) {
+                    u0 = fma(lv[m], __shfl_sync(0xffffffffu, yb, PB * bk + m), u0);
+                    u1 = fma(lv[m + 1], __shfl_sync(0xffffffffu, yb, PB * bk + m + 1), u1);
+                }
+                r0 = (lb > bk) ? r0 - (u0 + u1) : r0;
             }
             if (tid < NU) { lus[tid] = m0; vk[V_KFF + tid] = m0; }
         }
@@ -1318,7 +1412,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         for (int i = 0; i < 4; i++) mbar_init(&fq_bars[i], 1);
         fence_barrier_init();
 #ifdef NMPC_TIMING
-        for (int i = 0; i < 24; i++) fq_tacc[i] = 0ULL;
+        for (int i = 0; i < 32; i++) fq_tacc[i] = 0ULL;
         fq_tprev = clock64();
 #endif
     }
@@ -1411,7 +1505,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
     }
 #ifdef NMPC_TIMING
     if (bl == 0 && tid == 0)
-        for (int i = 0; i < 24; i++) g_fq_cycles[i] += fq_tacc[i];
+        for (int i = 0; i < 32; i++) g_fq_cycles[i] += fq_tacc[i];
 #endif
     // ---- statistics of this QP ----
     if (tid == 0) {
