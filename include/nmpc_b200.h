@@ -87,17 +87,19 @@ typedef struct nmpc_opts {
                                  `warm_start_qp = True` (config_abstract.py:62) maps to 1             */
     int32_t warm_start_nlp;   /* kept for API parity; the iterate always lives in the handle */
     int32_t hpipm_mode;       /* NMPC_HPIPM_*; this build implements SPEED                  */
-    int32_t enable_time_opt;  /* must be 0 in this build (nu = 30)                          */
+    int32_t enable_time_opt;  /* 1: the node durations dt_k are optimised as well (nu = 31: cost weight
+                                 time_opt_weight on dt - dt_nodes, bounds dt_min <= dt_k <= dt_max)   */
     int32_t warm_start_first_qp; /* acados `warm_start_first_qp` (default 0): the first QP of every
                                  nmpc_solve call is cold-started whatever warm_start_qp says       */
     int32_t cond_pred_corr;   /* HPIPM `cond_pred_corr` (1 in every HPIPM mode): fall back to the
                                  centring direction when the corrector predicts mu > 2 mu_aff      */
     double dt_nodes;          /* MPCOptConfig.get_dt_nodes()                                */
-    double dt_min, dt_max;    /* MPCOptConfig.get_dt_bounds(); unused unless time-opt       */
+    double dt_min, dt_max;    /* MPCOptConfig.get_dt_bounds(); used when enable_time_opt    */
     double nlp_tol;           /* SQP exit: all four residual inf-norms below (1e-1)         */
     double qp_tol;            /* IPM exit: all four residual inf-norms below (1e-2)         */
     double reg_eps, reg_eps_e;/* Levenberg-Marquardt terms (MPCCostConfig.reg_eps[_e])      */
     double mu_contact;        /* friction coefficient (0.8 hard-coded at solver.py:38)      */
+    double time_opt_weight;   /* MPCCostConfig.time_opt (1e4, mpc_cost.py:69): W["dt"], solver.py:124-125 */
 } nmpc_opts;
 
 /* Per-problem statistics of the last nmpc_solve (acados print_stats / get_stats equivalent). */
@@ -158,6 +160,9 @@ int nmpc_pin_stance_feet(nmpc_handle* h, const int32_t* i_node);
 /* update_states / update_inputs (solver.py:349-350): overwrite the iterate.  x [B,N+1,42] and/or
  * u [B,N,30]; either may be NULL. */
 int nmpc_set_guess(nmpc_handle* h, const double* x, const double* u);
+/* enable_time_opt: inputs["dt"] (solver.py:189-190, 325-336), the node durations of the iterate, dt [B,N]; NULL
+ * resets them to dt_nodes (nmpc_set_guess with inputs and nmpc_cold_guess do the same) */
+int nmpc_set_dt(nmpc_handle* h, const double* dt);
 /* warm_start_solver + warm_start_multipliers (solver.py:290-342): shift the stored iterate of
  * problem b by start_node[b] nodes (states 1.., inputs, duals), zero the force tail (or repeat
  * the last node when repeat_last). start_node [B] int32. */
@@ -175,6 +180,9 @@ int nmpc_synchronize(nmpc_handle* h);
 /* x [B,N+1,42], u [B,N,30], pi [B,N,42] (multiplier of x_{k+1} = phi(x_k,u_k)),
  * lam [B,N+1,84] (lower | upper multipliers of g).  Any pointer may be NULL. */
 int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* pi, double* lam);
+/* dt_node_sol (solver.py:423-427): dt [B,N] -- dt_nodes everywhere unless enable_time_opt -- and the multipliers of
+ * dt_min <= dt <= dt_max, lam_dt [B,N,2] (lower | upper).  Either pointer may be NULL. */
+int nmpc_get_dt(nmpc_handle* h, double* dt, double* lam_dt);
 int nmpc_get_stats(nmpc_handle* h, nmpc_stats* stats);
 /* per-problem status [B] int32 of the last nmpc_solve (host or device pointer) */
 int nmpc_get_status(nmpc_handle* h, int32_t* status);

@@ -24,6 +24,7 @@ class NmpcOpts(C.Structure):
         ("dt_nodes", C.c_double), ("dt_min", C.c_double), ("dt_max", C.c_double),
         ("nlp_tol", C.c_double), ("qp_tol", C.c_double),
         ("reg_eps", C.c_double), ("reg_eps_e", C.c_double), ("mu_contact", C.c_double),
+        ("time_opt_weight", C.c_double),
     ]
 
     def copy(self) -> "NmpcOpts":
@@ -41,7 +42,8 @@ class NmpcStats(C.Structure):
 def default_opts(**kw) -> NmpcOpts:
     o = NmpcOpts(n_nodes=25, max_iter=1, max_qp_iter=6, real_time_it=0, warm_start_qp=1,
                  warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, warm_start_first_qp=0, cond_pred_corr=1, dt_nodes=0.04, dt_min=0.02,
-                 dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8)
+                 dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8,
+                 time_opt_weight=1e4)
     for k, v in kw.items():
         if not hasattr(o, k):
             raise AttributeError(k)
@@ -67,6 +69,8 @@ _SIGS = {
     "nmpc_set_params": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_pin_stance_feet": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_set_guess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nmpc_set_dt": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nmpc_get_dt": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "nmpc_shift_warm_start": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "nmpc_reset_duals": (C.c_int, [C.c_void_p]),
     "nmpc_solve": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -192,6 +192,19 @@ class NmpcSolver:
         check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
         return x, u, pi, lam
 
+    def get_dt(self, duals: bool = False):
+        """Node durations of the solution, dt [B, N] (`dt_node_sol`, solver.py:423-427: dt_nodes everywhere unless
+        enable_time_opt); with `duals` also the multipliers of dt_min <= dt <= dt_max, [B, N, 2]."""
+        dt = np.zeros((self.B, self.N))
+        lam = np.zeros((self.B, self.N, 2)) if duals else None
+        check(self.lib.nmpc_get_dt(self._h, ptr(dt), ptr(lam)), "nmpc_get_dt")
+        return (dt, lam) if duals else dt
+
+    def set_dt(self, dt=None):
+        """Node durations of the iterate (inputs["dt"], solver.py:189-190); None resets them to dt_nodes."""
+        dt = None if dt is None else _f64(dt, (self.B, self.N))
+        check(self.lib.nmpc_set_dt(self._h, ptr(dt)), "nmpc_set_dt")
+
     def get_solution_into(self, x=None, u=None, pi=None, lam=None):
         check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
 

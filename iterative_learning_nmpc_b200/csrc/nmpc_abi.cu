@@ -33,6 +33,7 @@ struct nmpc_handle {
     // iterate and problem data [B]
     double *x, *u, *pi, *lam, *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;
+    double *dtn, *lamt, *qx;     // enable_time_opt: node durations [B][N], multipliers of their bounds [B][N][2], QP iterate [B][N][QX_SZ]
     double *res, *qp_res, *cost;
     unsigned long long *res_acc;
     int32_t *status, *done, *sqp_iter, *qp_iter, *qp_status, *qp_ncond, *itmp;
@@ -111,7 +112,7 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     if (!err) err = &dummy;
     *err = NMPC_EINVAL;
     if (!o || batch <= 0 || o->n_nodes < 1 || o->n_nodes > NMPC_MAX_NODES) return nullptr;
-    if (o->enable_time_opt) { *err = NMPC_ENOSYS; return nullptr; }
+    if (o->enable_time_opt && !(o->dt_min > 0.0 && o->dt_min <= o->dt_nodes && o->dt_nodes <= o->dt_max)) return nullptr;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device >= ndev) { *err = NMPC_ENODEV; return nullptr; }
     cudaDeviceProp prop;
@@ -133,6 +134,7 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     A_(x0, B * NX); A_(p, B * (N + 1) * NPAR); A_(yref, B * N * NY); A_(yref_e, B * NYE);
     A_(W, B * NY); A_(We, B * NYE);
     A_(qz, B * (N + 1) * NZ); A_(qpi, B * N * NX); A_(qlam, B * (N + 1) * 2 * NG); A_(qt, B * (N + 1) * 2 * NG);
+    A_(dtn, B * N); A_(lamt, B * N * 2); A_(qx, B * N * QX_SZ);
     A_(res, B * 4); A_(qp_res, B * 4); A_(cost, B); A_(res_acc, B * 4);
     A_(status, B); A_(done, B); A_(sqp_iter, B); A_(qp_iter, B); A_(qp_status, B); A_(qp_ncond, B); A_(itmp, B);
     A_(vec, Bc * (N + 1) * V_STAGE); A_(cost_stage, Bc * (N + 1));
@@ -140,7 +142,13 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     A_(SR, Bc * (N + 1) * SR_SZ); A_(FR, Bc * (N + 1) * FR_SZ); A_(sr_flag, 1);
 #undef A_
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
+        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
+    if (e == cudaSuccess) {          // the node durations start at their nominal value
+        std::vector<double> d(B * N, o->dt_nodes);
+        e = cudaMemcpy(h->dtn, d.data(), d.size() * 8, cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) {
         *err = (e == cudaErrorMemoryAllocation) ? NMPC_ENOMEM : (int)e;
         nmpc_destroy(h);
@@ -157,7 +165,7 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ustream) cudaStreamSynchronize(h->ustream);
     void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
-                    h->qlam, h->qt, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
+                    h->qlam, h->qt, h->dtn, h->lamt, h->qx, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
                     h->qp_iter, h->qp_status, h->qp_ncond, h->itmp, h->G, h->M, h->C, h->D, h->vec, h->cost_stage,
                     h->rec, h->scratch, h->uscratch, h->SR, h->FR, h->sr_flag};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -173,7 +181,7 @@ extern "C" int nmpc_set_opts(nmpc_handle* h, const nmpc_opts* o)
 {
     if (!h || !o || o->n_nodes != h->N) return NMPC_EINVAL;
     LOCK(h);
-    if (o->enable_time_opt) return NMPC_ENOSYS;
+    if (o->enable_time_opt != h->o.enable_time_opt) return NMPC_EINVAL;      // fixed at nmpc_create (it changes nu)
     h->o = *o;
     return 0;
 }
@@ -319,6 +327,10 @@ extern "C" int nmpc_cold_guess(nmpc_handle* h)
     CK(cudaSetDevice(h->device));
     nmpc_cold_guess_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->x0, h->p, h->x, h->u);
     h->launches++;
+    if (h->o.enable_time_opt) {
+        nmpc_fill_kernel<<<(h->B * h->N + 255) / 256, 256, 0, h->stream>>>(h->dtn, h->B * h->N, h->o.dt_nodes);
+        h->launches++;
+    }
     return (int)cudaGetLastError();
 }
 
@@ -353,6 +365,36 @@ extern "C" int nmpc_set_guess(nmpc_handle* h, const double* x, const double* u)
     LOCK(h);
     if (x) if (int r = h2d(h, h->x, x, (size_t)h->B * (h->N + 1) * NX * 8)) return r;
     if (u) if (int r = h2d(h, h->u, u, (size_t)h->B * h->N * NU * 8)) return r;
+    if (u && h->o.enable_time_opt) {                // a new input guess restarts the node durations at dt_nodes (solver.py:189-190)
+        nmpc_fill_kernel<<<(h->B * h->N + 255) / 256, 256, 0, h->stream>>>(h->dtn, h->B * h->N, h->o.dt_nodes);
+        h->launches++;
+    }
+    return 0;
+}
+
+// enable_time_opt: node durations of the iterate, dt [B][N] (inputs["dt"], solver.py:189-190, 325-336).  A null pointer
+// resets them to the nominal dt_nodes.
+extern "C" int nmpc_set_dt(nmpc_handle* h, const double* dt)
+{
+    if (!h) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    if (dt) return h2d(h, h->dtn, dt, (size_t)h->B * h->N * 8);
+    nmpc_fill_kernel<<<(h->B * h->N + 255) / 256, 256, 0, h->stream>>>(h->dtn, h->B * h->N, h->o.dt_nodes);
+    h->launches++;
+    return (int)cudaGetLastError();
+}
+
+// dt_node_sol (solver.py:423-427): dt [B][N] (the nominal value everywhere unless enable_time_opt) and, optionally,
+// the multipliers of dt_min <= dt <= dt_max, lam_dt [B][N][2] (lower | upper)
+extern "C" int nmpc_get_dt(nmpc_handle* h, double* dt, double* lam_dt)
+{
+    if (!h) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    if (dt) if (int r = d2h(h, dt, h->dtn, (size_t)h->B * h->N * 8)) return r;
+    if (lam_dt) if (int r = d2h(h, lam_dt, h->lamt, (size_t)h->B * h->N * 2 * 8)) return r;
+    CK(cudaStreamSynchronize(h->stream));
     return 0;
 }
 
@@ -361,7 +403,9 @@ extern "C" int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, 
     if (!h || !start_node) return NMPC_EINVAL;
     LOCK(h);
     if (int r = h2d(h, h->itmp, start_node, (size_t)h->B * 4)) return r;
-    nmpc_shift_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->itmp, repeat_last, h->x, h->u, h->pi, h->lam);
+    const bool topt = h->o.enable_time_opt != 0;
+    nmpc_shift_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->itmp, repeat_last, h->x, h->u, h->pi, h->lam,
+                                                   topt ? h->dtn : nullptr, h->lamt, h->o.dt_nodes);
     h->launches++;
     return (int)cudaGetLastError();
 }
@@ -378,6 +422,8 @@ extern "C" int nmpc_reset_duals(nmpc_handle* h)
     CK(cudaMemsetAsync(h->qpi, 0, B * N * NX * 8, h->stream));
     CK(cudaMemsetAsync(h->qlam, 0, B * (N + 1) * 2 * NG * 8, h->stream));
     CK(cudaMemsetAsync(h->qt, 0, B * (N + 1) * 2 * NG * 8, h->stream));
+    CK(cudaMemsetAsync(h->lamt, 0, B * N * 2 * 8, h->stream));
+    CK(cudaMemsetAsync(h->qx, 0, B * N * QX_SZ * 8, h->stream));
     return 0;
 }
 
@@ -405,6 +451,8 @@ static LinArgs lin_args(nmpc_handle* h, int b0)
     a.G = h->G; a.M = h->M; a.C = h->C; a.D = h->D; a.cost_stage = h->cost_stage; a.done = h->done;
     a.rec = h->rec; a.N = h->N; a.b0 = b0; a.dt = h->o.dt_nodes; a.reg = h->o.reg_eps; a.reg_e = h->o.reg_eps_e;
     a.mu_c = h->o.mu_contact;
+    a.dtn = h->dtn; a.topt = h->o.enable_time_opt != 0; a.w_dt = h->o.time_opt_weight;
+    a.dt_min = h->o.dt_min; a.dt_max = h->o.dt_max;
     return a;
 }
 
@@ -437,7 +485,7 @@ static void launch_linearize_sr(nmpc_handle* h, int b0, int Bc)
 static QpArgs qp_args(nmpc_handle* h, int b0)
 {
     QpArgs a;
-    a.qz = h->qz; a.qpi = h->qpi; a.qlam = h->qlam; a.qt = h->qt;
+    a.qz = h->qz; a.qpi = h->qpi; a.qlam = h->qlam; a.qt = h->qt; a.qx = h->qx;
     a.qp_iter = h->qp_iter; a.qp_status = h->qp_status; a.qp_ncond = h->qp_ncond; a.qp_res = h->qp_res;
     a.dx0_ext = nullptr; a.x0 = h->x0; a.x = h->x; a.u = h->u; a.pi = h->pi; a.lam = h->lam;
     a.sqp_done = h->done; a.sqp_iter = h->sqp_iter;
@@ -453,19 +501,21 @@ static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply)
     const int N = h->N;
     cudaStream_t s = h->stream;
     FqArgs f;
-    f.SR = h->SR; f.FR = h->FR; f.vec = h->vec; f.qz = a.qz; f.qpi = a.qpi; f.qlam = a.qlam; f.qt = a.qt;
+    f.SR = h->SR; f.FR = h->FR; f.vec = h->vec; f.qz = a.qz; f.qpi = a.qpi; f.qlam = a.qlam; f.qt = a.qt; f.qx = a.qx;
     f.qp_iter = a.qp_iter; f.qp_status = a.qp_status; f.qp_ncond = a.qp_ncond; f.qp_res = a.qp_res;
     f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
     f.x = a.x; f.sqp_done = a.sqp_done; f.N = N; f.b0 = a.b0; f.max_iter = a.max_iter; f.warm = a.warm;
     f.cond_pred_corr = a.cond_pred_corr;
     f.tol = a.tol; f.dt = h->o.dt_nodes; f.c2 = 0.5 * h->o.dt_nodes * h->o.dt_nodes;
     prof_begin(h, NMPC_PROF_QP_FUSED);
-    nmpc_qp_fused_kernel<<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
+    const bool topt = h->o.enable_time_opt != 0 && a.dx0_ext == nullptr;      // externally supplied QPs have nu = 30
+    if (topt) nmpc_qp_fused_kernel<true><<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
+    else nmpc_qp_fused_kernel<false><<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
     prof_end(h);
     h->launches++;
     if (apply) {
         prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_apply_sr_kernel<<<Bc, 128, 0, s>>>(a, h->SR);
+        nmpc_qp_apply_sr_kernel<<<Bc, 128, 0, s>>>(a, h->SR, topt ? h->dtn : nullptr, h->lamt, h->qx);
         prof_end(h);
         h->launches++;
     }
@@ -495,6 +545,7 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
                 ResSrArgs ra;
                 ra.SR = h->SR; ra.x = h->x; ra.x0 = h->x0; ra.pi = h->pi; ra.lam = h->lam; ra.res_acc = h->res_acc;
                 ra.done = h->done; ra.N = N; ra.b0 = b0; ra.dt = h->o.dt_nodes;
+                ra.lamt = h->lamt; ra.topt = h->o.enable_time_opt != 0;
                 nmpc_residual_sr_kernel<<<dim3(N + 1, Bc), RES_THREADS, 0, h->stream>>>(ra);
                 prof_end(h);
                 nmpc_sqp_decide_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(
@@ -599,7 +650,8 @@ extern "C" int nmpc_pack_solution(nmpc_handle* h, double* out_dev)
     CK(cudaSetDevice(h->device));
     cudaPointerAttributes at;
     if (cudaPointerGetAttributes(&at, out_dev) != cudaSuccess || at.type != cudaMemoryTypeDevice) { cudaGetLastError(); return NMPC_EINVAL; }
-    nmpc_pack_solution_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->o.dt_nodes, h->x, h->u, h->status, out_dev);
+    nmpc_pack_solution_kernel<<<h->B, 128, 0, h->stream>>>(h->N, h->o.dt_nodes, h->o.enable_time_opt ? h->dtn : nullptr,
+                                                           h->x, h->u, h->status, out_dev);
     h->launches++;
     return (int)cudaGetLastError();
 }

@@ -57,6 +57,8 @@ struct LinArgs {
     const int32_t* done;     // [B] or null
     int N; int b0;
     double dt, reg, reg_e, mu_c;
+    // enable_time_opt (stage-record kernel only): per-node durations [B][N], weight, bounds
+    const double* dtn; int topt; double w_dt, dt_min, dt_max;
 };
 
 __global__ void __launch_bounds__(LIN_THREADS, 4) nmpc_linearize_kernel(LinArgs a)

@@ -71,7 +71,8 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
     const double* HM = rec + NMPC_REC_H;
     const double* HQ = rec + NMPC_REC_H_Q;
     const double* HV = rec + NMPC_REC_H_V;
-    const double dt = a.dt;
+    // enable_time_opt: the node duration is an optimisation variable with its own iterate
+    const double dt = (a.topt && !term) ? a.dtn[(size_t)b * N + k] : a.dt;
 
     if (tid >= 32 && tid < 32 + NF * 3) s_r[(tid - 32) / 3][(tid - 32) % 3] = FP[tid - 32] - COM[(tid - 32) % 3];
     __syncthreads();
@@ -97,6 +98,22 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
                 hd += act * val;
             }
             S[SR_B + 2 * NQ + i] = hh[i] + dt * hd - s_xn[2 * NQ + i];
+            if (a.topt) S[SR_X + SRX_B + 2 * NQ + i] = hd;              // d h+ / d dt
+        }
+        if (a.topt) {
+            // d q+ / d dt = v + dt a,  d v+ / d dt = a; cost weight (dt - dt_nodes)^2 / 2; bounds dt_min <= dt <= dt_max
+            for (int i = tid; i < NQ; i += LIN_SR_THREADS) {
+                S[SR_X + SRX_B + i] = v[i] + dt * acc_u[i];
+                S[SR_X + SRX_B + NQ + i] = acc_u[i];
+            }
+            if (tid == 0) {
+                S[SR_X + SRX_H] = a.w_dt + a.reg;
+                S[SR_X + SRX_G] = a.w_dt * (dt - a.dt);
+                S[SR_X + SRX_LB] = a.dt_min - dt;
+                S[SR_X + SRX_UB] = a.dt_max - dt;
+                S[SR_X + SRX_DT] = dt;
+                S[SR_X + SRX_C2] = 0.5 * dt * dt;
+            }
         }
         // d h+/d f
         for (int e = tid; e < NF * 9; e += LIN_SR_THREADS) {
@@ -208,6 +225,7 @@ __global__ void __launch_bounds__(LIN_SR_THREADS, LIN_MINB) nmpc_linearize_sr_ke
             cost += 0.5 * s_W[ypos + 3 * ft + d] * ep * ep;
         }
     }
+    if (a.topt && !term && tid == 0) cost += 0.5 * a.w_dt * (dt - a.dt) * (dt - a.dt);
     cost = warp_sum(cost);
     if ((tid & 31) == 0) s_cost[tid >> 5] = cost;
 
@@ -327,6 +345,7 @@ struct ResSrArgs {
     const int32_t* done;
     int N, b0;
     double dt;
+    const double* lamt; int topt;       // enable_time_opt: multipliers of the dt bounds [B][N][2]
 };
 
 __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_sr_kernel(ResSrArgs a)
@@ -338,7 +357,7 @@ __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_sr_kernel(ResSrA
     __shared__ double s_pik[NX], s_pin[NX], s_dl[NG], s_red[4][RES_THREADS / 32];
     const double* S = a.SR + ((size_t)bl * (N + 1) + k) * SR_SZ;
     const double* lam = a.lam + ((size_t)b * (N + 1) + k) * 2 * NG;
-    const double dt = a.dt, c2 = 0.5 * a.dt * a.dt;
+    const double dt = (a.topt && !term) ? S[SR_X + SRX_DT] : a.dt, c2 = 0.5 * dt * dt;
     double r_s = 0, r_e = 0, r_i = 0, r_c = 0;
     for (int i = tid; i < NX; i += RES_THREADS) {
         s_pik[i] = k > 0 ? a.pi[((size_t)b * N + k - 1) * NX + i] : 0.0;
@@ -363,6 +382,16 @@ __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_sr_kernel(ResSrA
         s -= fq_ct(S, s_dl, c);
         r_s = nanmax(r_s, fabs(s));
     }
+    if (a.topt && !term && tid == RES_THREADS - 1) {
+        // the node duration: stationarity g + b' pi_k - (lam_l - lam_u), its two bounds, complementarity
+        const double* lt = a.lamt + ((size_t)b * N + k) * 2;
+        double s = S[SR_X + SRX_G] - (lt[0] - lt[1]);
+        for (int l = 0; l < NX; l++) s += S[SR_X + SRX_B + l] * s_pin[l];
+        r_s = nanmax(r_s, fabs(s));
+        const double cl = -S[SR_X + SRX_LB], cu = -S[SR_X + SRX_UB];       // dt - dt_min, dt - dt_max
+        r_i = nanmax(r_i, -cl); r_i = nanmax(r_i, cu);
+        r_c = nanmax(r_c, fabs(lt[0] * cl)); r_c = nanmax(r_c, fabs(lt[1] * cu));
+    }
     r_s = warp_max(r_s); r_e = warp_max(r_e); r_i = warp_max(r_i); r_c = warp_max(r_c);
     if ((tid & 31) == 0) { s_red[0][tid >> 5] = r_s; s_red[1][tid >> 5] = r_e; s_red[2][tid >> 5] = r_i; s_red[3][tid >> 5] = r_c; }
     __syncthreads();
@@ -377,7 +406,8 @@ __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_sr_kernel(ResSrA
 // end of a QP on the fused path: SQP full step (x, u) += dz, multipliers replaced by the QP's
 // (SR twin of nmpc_qp_apply_kernel: the masks come from the stage record)
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) nmpc_qp_apply_sr_kernel(QpArgs a, const double* SR)
+__global__ void __launch_bounds__(128) nmpc_qp_apply_sr_kernel(QpArgs a, const double* SR, double* dtn, double* lamt,
+                                                               const double* qx)
 {
     const int tid = threadIdx.x, bl = blockIdx.x, b = a.b0 + bl, N = a.N;
     if (a.sqp_done && a.sqp_done[b]) return;
@@ -399,4 +429,10 @@ __global__ void __launch_bounds__(128) nmpc_qp_apply_sr_kernel(QpArgs a, const d
         const int k = i / (2 * NG), id = i % (2 * NG);
         lam[i] = Sb[(size_t)k * SR_SZ + SR_D + 2 * NG + id] > 0.5 ? qlam[i] : 0.0;
     }
+    if (dtn)                                       // enable_time_opt: dt += tau, bound multipliers replaced by the QP's
+        for (int k = tid; k < N; k += 128) {
+            const double* q = qx + ((size_t)b * N + k) * QX_SZ;
+            dtn[(size_t)b * N + k] += q[0];
+            lamt[((size_t)b * N + k) * 2] = q[2]; lamt[((size_t)b * N + k) * 2 + 1] = q[3];
+        }
 }

@@ -40,7 +40,17 @@
 #define SR_CXLD 37                   // row stride of CX: 36 + 1, so that thread-per-row and thread-per-column reads are both free of bank conflicts
 #define SR_CX (SR_CF + 20 * 3)       // [22][37] contact / patch / centroidal rows over (q, v)
 #define SR_D (SR_CX + 22 * SR_CXLD)       // lg[42] ug[42] mask_l[42] mask_u[42]
-#define SR_SZ (SR_D + 4 * NG)        // 1714
+// time-opt extension of the stage record (enable_time_opt: the node duration dt_k is a 31st input; zero otherwise)
+#define SR_X (SR_D + 4 * NG)         // 1714
+#define SRX_B 0                      // [42] column of the dynamics over dt: d x+ / d dt = [v + dt a; a; hdot]
+#define SRX_H 42                     // Hessian entry of dt (weight + regularisation)
+#define SRX_G 43                     // gradient entry: weight (dt - dt_nodes)
+#define SRX_LB 44                    // dt_min - dt
+#define SRX_UB 45                    // dt_max - dt
+#define SRX_DT 46                    // dt_k of this linearisation
+#define SRX_C2 47                    // dt_k^2 / 2
+#define SRX_SZ 48
+#define SR_SZ (SR_X + SRX_SZ)        // 1762
 #define NGX 22                       // constraint rows on the state
 #define NGF 20                       // friction rows
 
@@ -50,7 +60,7 @@
 #define FR_P (FR_MU + LP_UPANELS)            // 1830
 #define FR_SZ 3680                           // 1830 + 42 * 43 = 3636, padded
 
-static_assert(SR_SZ % 2 == 0 && SR_CF % 2 == 0 && FR_P % 2 == 0 && FR_SZ % 2 == 0, "16-byte alignment of bulk copies");
+static_assert(SR_SZ % 2 == 0 && SR_X % 2 == 0 && SR_CF % 2 == 0 && FR_P % 2 == 0 && FR_SZ % 2 == 0, "16-byte alignment of bulk copies");
 
 // ---------------------------------------------------------------------------------------------
 // dense stage blocks -> stage record (used for externally supplied QPs and, for now, after the
@@ -395,6 +405,7 @@ struct FqArgs {
     double* FR;                     // [Bc][N+1][FR_SZ]
     double* vec;                    // [Bc][(N+1)*V_STAGE]
     double* qz; double* qpi; double* qlam; double* qt;       // QP iterate, global problem index
+    double* qx;                     // [B][N][QX_SZ] time-opt: QP iterate of dt and of its two bounds
     int32_t* qp_iter; int32_t* qp_status; int32_t* qp_ncond; double* qp_res;
     const double* dx0_ext; const double* x0; const double* x;
     const int32_t* sqp_done;
@@ -404,7 +415,7 @@ struct FqArgs {
 
 // per-CTA context in shared memory: base pointers of this OCP (no registers held across the passes)
 struct FqCtx {
-    const double* SRb; double* FRb; double* vb; double* qz; double* qpi; double* qlam; double* qt;
+    const double* SRb; double* FRb; double* vb; double* qz; double* qpi; double* qlam; double* qt; double* qx;
     double dt, c2;
     int N;
 };
@@ -428,14 +439,17 @@ __shared__ __align__(8) uint64_t fq_bars[4];
 #define R_LAM (R_DPI + NX)
 #define R_T (R_LAM + 2 * NG)
 #define R_DT (R_T + 2 * NG)                  // dt | dlam
-#define R_SLOT (R_DT + 4 * NG)               // 2256
+#define R_XQ (R_DT + 4 * NG)                 // time-opt: dt iterate record (QX_SZ)
+#define R_XV (R_XQ + QX_SZ)                  // time-opt: V_X block of the stage
+#define R_SLOT (R_XV + VX_SZ)
 #define R_DEPTH 2
 #define RV_BASE (R_DEPTH * R_SLOT)           // 6768
 #define RV_ZC 0                              // [2][72] updated z_k, ping-pong by stage parity (x part = "next state" of stage k-1)
 #define RV_PIN (RV_ZC + 2 * NZ)              // [2][42] updated pi_{k-1}, ping-pong
 #define RV_CZ (RV_PIN + 2 * NX)              // 42: C z, then lam_l - lam_u
 #define RV_GAMV (RV_CZ + NG)                 // 42
-#define RV_END (RV_GAMV + NG)                // 312
+#define RV_X (RV_GAMV + NG)                  // time-opt scalars: tau, lam_l - lam_u, gamma
+#define RV_END (RV_X + 4)
 static_assert(RV_BASE + RV_END <= FQ_RED, "pass R shared memory");
 static_assert(R_SLOT % 2 == 0 && R_PI % 2 == 0 && R_DPI % 2 == 0 && R_LAM % 2 == 0, "alignment");
 
@@ -444,11 +458,14 @@ static_assert(R_SLOT % 2 == 0 && R_PI % 2 == 0 && R_DPI % 2 == 0 && R_LAM % 2 ==
 #define F_M (F_P + NX * P_LD)                // u panels of the stage matrix; before the factorisation U = P[:,h][Hf|Hq]; after it K | W
 #define F_S (F_M + LP_UPANELS)               // stage record | QT GAM KFF RB of the stage (186)
 #define F_SV (F_S + SR_SZ)
-#define F_V (F_SV + 186)
+#define F_XV (F_SV + 186)                    // time-opt: V_X block of the stage
+#define F_V (F_XV + VX_SZ)
 #define FV_QT 0                              // 72  working linear term m (row 72 of the stage matrix)
 #define FV_W (FV_QT + NZ)                    // 42
 #define FV_PN (FV_W + NX)                    // 42  p_{k+1}
-#define FV_END (FV_PN + NX)
+#define FV_PB (FV_PN + NX)                   // 42  time-opt: P+ b
+#define FV_XS (FV_PB + NX)                   // 4   time-opt scalars: 1 / d, s
+#define FV_END (FV_XS + 4)
 static_assert(F_V + FV_END <= FQ_RED, "pass F shared memory");
 
 // ---- passes A1 / D1: ring of 3 slots ----
@@ -456,38 +473,45 @@ static_assert(F_V + FV_END <= FQ_RED, "pass F shared memory");
 #define A_H (A_MU + LP_UPANELS)              // Hq | Hf (180)
 #define A_LU (A_H + 180)                     // lu of this direction
 #define A_RB (A_LU + NU)
-#define A_SLOT (A_RB + NX)                   // 2082
+#define A_XS (A_RB + NX)                     // time-opt: stage record extension
+#define A_XV (A_XS + SRX_SZ)                 // time-opt: V_X block
+#define A_SLOT (A_XV + VX_SZ)
 #define A_DEPTH 3
 #define AV_BASE (A_DEPTH * A_SLOT)
 #define AV_DX 0                              // [2][42]
 #define AV_DZ (AV_DX + 2 * NX)               // 72
-static_assert(AV_BASE + AV_DZ + NZ <= FQ_RED, "pass A1 shared memory");
+#define AV_X (AV_DZ + NZ)                    // time-opt scalar: d tau
+static_assert(AV_BASE + AV_X + 2 <= FQ_RED, "pass A1 shared memory");
 
 // ---- pass A2: ring of 4 slots ----
-#define B_C 0                                // constraint part of the stage record: SR_CF .. SR_SZ (1020)
-#define SR_CSZ (SR_SZ - SR_CF)
+#define B_C 0                                // constraint part of the stage record: SR_CF .. SR_X (1042)
+#define SR_CSZ (SR_X - SR_CF)
 #define B_DZ (B_C + SR_CSZ)                  // DZ RD RM (240)
 #define B_RD (B_DZ + NZ)
 #define B_RM (B_RD + 2 * NG)
 #define B_LAM (B_RM + 2 * NG)
 #define B_T (B_LAM + 2 * NG)
-#define B_SLOT (B_T + 2 * NG)                // 1428
+#define B_XV (B_T + 2 * NG)
+#define B_XQ (B_XV + VX_SZ)
+#define B_SLOT (B_XQ + QX_SZ)
 #define B_DEPTH 4
 #define BV_BASE (B_DEPTH * B_SLOT)
 static_assert(BV_BASE + NG <= FQ_RED, "pass A2 shared memory");
 
-// ---- pass C1: ring of 4 slots ----
+// ---- pass C1: ring of 3 slots ----
 #define C_H 0
 #define C_C (C_H + 180)
-#define C_RG (C_C + SR_CSZ)                  // RG PRB (114)
+#define C_RG (C_C + SR_CSZ + SRX_SZ)         // RG PRB (114); the constraint part is followed by the time-opt extension
 #define C_PRB (C_RG + NZ)
 #define C_DT (C_PRB + NX)                    // DT DLAM (168)
 #define C_DLAM (C_DT + 2 * NG)
 #define C_RD (C_DLAM + 2 * NG)
 #define C_LAM (C_RD + 2 * NG)
 #define C_T (C_LAM + 2 * NG)
-#define C_SLOT (C_T + 2 * NG)                // 1734
-#define C_DEPTH 4
+#define C_XV (C_T + 2 * NG)
+#define C_XQ (C_XV + VX_SZ)
+#define C_SLOT (C_XQ + QX_SZ)
+#define C_DEPTH 3
 #define CV_BASE (C_DEPTH * C_SLOT)           // 6936
 static_assert(CV_BASE + NG <= FQ_RED, "pass C1 shared memory");
 
@@ -495,13 +519,17 @@ static_assert(CV_BASE + NG <= FQ_RED, "pass C1 shared memory");
 #define E_MU 0
 #define E_H (E_MU + LP_UPANELS)
 #define E_M0 (E_H + 180)
-#define E_SLOT (E_M0 + NZ)                   // 2082
+#define E_XS (E_M0 + NZ)
+#define E_XV (E_XS + SRX_SZ)
+#define E_SLOT (E_XV + VX_SZ)
 #define E_DEPTH 3
 #define EV_BASE (E_DEPTH * E_SLOT)           // 6246
 #define EV_M 0                               // 72
 #define EV_PN (EV_M + NZ)                    // [2][42]
 #define EV_LU (EV_PN + 2 * NX)               // 32
-static_assert(EV_BASE + EV_LU + 32 <= FQ_RED, "pass C2 shared memory");
+#define EV_PT (EV_LU + 32)                   // 42  time-opt: p+ after the elimination of dt
+#define EV_X (EV_PT + NX)                    // time-opt scalar s
+static_assert(EV_BASE + EV_X + 2 <= FQ_RED, "pass C2 shared memory");
 
 // ---- pass D2: ring of 2 slots ----
 #define D_P 0
@@ -512,7 +540,9 @@ static_assert(EV_BASE + EV_LU + 32 <= FQ_RED, "pass C2 shared memory");
 #define D_LAM (D_RM + 2 * NG)
 #define D_T (D_LAM + 2 * NG)
 #define D_PV (D_T + 2 * NG)
-#define D_SLOT (D_PV + NX)                   // 3276
+#define D_XV (D_PV + NX)
+#define D_XQ (D_XV + VX_SZ)
+#define D_SLOT (D_XQ + QX_SZ)
 #define D_DEPTH 2
 #define DV_BASE (D_DEPTH * D_SLOT)
 static_assert(DV_BASE + NG <= FQ_RED, "pass D2 shared memory");
@@ -547,6 +577,7 @@ __shared__ long long fq_tprev;
 // pass R: update with the previous step, residuals of every stage, norms
 // out: [0] |rg| [1] |rb| [2] |rd| [3] |rm| [4] sum lam t [5] number of constraint sides
 // =============================================================================================
+template <bool TOPT>
 __device__ __noinline__ void fq_issue_R(int k, int slot, bool upd)
 {
     const FqCtx& c = fq_ctx;
@@ -555,7 +586,12 @@ __device__ __noinline__ void fq_issue_R(int k, int slot, bool upd)
     uint32_t bytes = (SR_SZ + NZ + 4 * NG) * 8;
     if (upd) bytes += (NZ + 4 * NG) * 8;
     if (k > 0) bytes += (upd ? 2 : 1) * NX * 8;
+    if (TOPT && k < c.N) bytes += (QX_SZ + VX_SZ) * 8;
     mbar_arrive_expect_tx(bar, bytes);
+    if (TOPT && k < c.N) {
+        bulk_g2s(sl + R_XQ, c.qx + (size_t)k * QX_SZ, QX_SZ * 8, bar);
+        bulk_g2s(sl + R_XV, c.vb + (size_t)k * V_STAGE + V_X, VX_SZ * 8, bar);
+    }
     bulk_g2s(sl + R_SR, c.SRb + (size_t)k * SR_SZ, SR_SZ * 8, bar);
     bulk_g2s(sl + R_Z, c.qz + (size_t)k * NZ, NZ * 8, bar);
     bulk_g2s(sl + R_LAM, c.qlam + (size_t)k * 2 * NG, 2 * NG * 8, bar);
@@ -569,29 +605,33 @@ __device__ __noinline__ void fq_issue_R(int k, int slot, bool upd)
     }
 }
 
+template <bool TOPT>
 __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double alpha_p, double alpha_d, double* out)
 {
     const int tid = threadIdx.x;
     const int N = fq_ctx.N;
-    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
     double* rv = fq_smem + RV_BASE;
     double* red = fq_smem + FQ_RED;
     const bool upd = it > 0;
     double n_g = 0.0, n_b = 0.0, n_d = 0.0, n_m = 0.0, s_m = 0.0;
     int cnt = 0;
     if (tid == FQ_ISSUER)
-        for (int i = 0; i < R_DEPTH - 1 && i <= N; i++) fq_issue_R(N - i, i % R_DEPTH, upd);
+        for (int i = 0; i < R_DEPTH - 1 && i <= N; i++) fq_issue_R<TOPT>(N - i, i % R_DEPTH, upd);
     for (int i = 0; i <= N; i++) {
         const int k = N - i, slot = i % R_DEPTH;
         const bool term = (k == N);
-        if (tid == FQ_ISSUER && i + R_DEPTH - 1 <= N) fq_issue_R(k - (R_DEPTH - 1), (i + R_DEPTH - 1) % R_DEPTH, upd);
+        if (tid == FQ_ISSUER && i + R_DEPTH - 1 <= N) fq_issue_R<TOPT>(k - (R_DEPTH - 1), (i + R_DEPTH - 1) % R_DEPTH, upd);
         FMARK(1);
         fq_ring_wait(slot, ph);
         FMARK(18);
         const double* sl = fq_smem + slot * R_SLOT;
         const double* S = sl + R_SR;
+        const double dt = TOPT ? S[SR_X + SRX_DT] : fq_ctx.dt, c2 = TOPT ? S[SR_X + SRX_C2] : fq_ctx.c2;
         double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
         double* zc = rv + RV_ZC + (k & 1) * NZ;
+        // time-opt: thread 127 carries the node duration tau = dt step and its two bounds through the steps
+        const bool xthr = TOPT && !term && tid == FQ_THREADS - 1;
+        double x_tau = 0.0;
         const double* zxn = rv + RV_ZC + ((k + 1) & 1) * NZ + NU;
         double* pik = rv + RV_PIN + (k & 1) * NX;
         const double* pin = rv + RV_PIN + ((k + 1) & 1) * NX;
@@ -606,13 +646,19 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
             if (upd) { p = fma(alpha_d, sl[R_DPI + l], p); fq_ctx.qpi[(size_t)(k - 1) * NX + l] = p; }
             pik[l] = p;
         }
+        if (xthr) {
+            x_tau = sl[R_XQ];
+            if (upd) { x_tau = fma(alpha_p, sl[R_XV + VX_DTAU], x_tau); fq_ctx.qx[(size_t)k * QX_SZ] = x_tau; }
+            rv[RV_X] = x_tau;
+        }
         __syncthreads();
         FMARK(19);
         // ---- step 2: C z; dynamics residual ----
         fq_cz(S, zc, rv + RV_CZ, tid);
         if (!term && tid >= 80 && tid < 80 + NX) {
             const int l = tid - 80;
-            const double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
+            double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
+            if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
             vk[V_RB + l] = rb;
             n_b = nanmax(n_b, fabs(rb));
         }
@@ -657,6 +703,34 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
             vk[V_GAM + j] = Gam;
             rv[RV_GAMV + j] = gam; rv[RV_CZ + j] = dl;
         }
+        if (xthr) {          // the two bounds of dt: lb <= tau <= ub
+            double Gam = 0.0, gam = 0.0, dl = 0.0;
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                double t = sl[R_XQ + 4 + e], lam = sl[R_XQ + 2 + e];
+                if (upd) {
+                    t = fmax(fma(alpha_p, sl[R_XV + VX_DT + e], t), IPM_T_MIN);
+                    lam = fmax(fma(alpha_d, sl[R_XV + VX_DL + e], lam), IPM_LAM_MIN);
+                }
+                const double slack = e ? (S[SR_X + SRX_UB] - x_tau) : (x_tau - S[SR_X + SRX_LB]);
+                if (it == 0) {
+                    if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 * __drcp_rn(t); }
+                    else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
+                }
+                if (upd || it == 0) { fq_ctx.qx[(size_t)k * QX_SZ + 4 + e] = t; fq_ctx.qx[(size_t)k * QX_SZ + 2 + e] = lam; }
+                const double rd = slack - t, rm = lam * t;
+                vk[V_X + VX_RD + e] = rd; vk[V_X + VX_RM + e] = rm;
+                s_m += rm; cnt += 1;
+                n_d = nanmax(n_d, fabs(rd));
+                n_m = nanmax(n_m, fabs(rm));
+                const double ti = __drcp_rn(t);
+                const double g = (rm + lam * rd) * ti;
+                Gam += lam * ti;
+                if (e) { gam -= g; dl -= lam; } else { gam += g; dl += lam; }
+            }
+            vk[V_X + VX_GAM] = Gam;
+            rv[RV_X + 1] = dl; rv[RV_X + 2] = gam;
+        }
         __syncthreads();
         FMARK(21);
         // ---- step 4: stationarity residual and the linear term q~ = rg + C' gamma ----
@@ -671,6 +745,14 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
             if ((k == 0 && c >= NU) || (term && c < NU)) s = 0.0;
             vk[V_RG + c] = s; vk[V_QT + c] = qp + s;
             n_g = nanmax(n_g, fabs(s));
+        }
+        if (xthr) {          // stationarity in dt: g + h tau + b' pi_k - (lam_l - lam_u)
+            double s0 = fma(S[SR_X + SRX_H], x_tau, S[SR_X + SRX_G]) - rv[RV_X + 1], s1 = 0.0;
+#pragma unroll
+            for (int l = 0; l < NX; l += 2) { s0 = fma(S[SR_X + SRX_B + l], pin[l], s0); s1 = fma(S[SR_X + SRX_B + l + 1], pin[l + 1], s1); }
+            const double sg = s0 + s1;
+            vk[V_X + VX_RG] = sg; vk[V_X + VX_QT] = sg + rv[RV_X + 2];
+            n_g = nanmax(n_g, fabs(sg));
         }
         __syncthreads();
         FMARK(22);
@@ -688,20 +770,22 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
 // =============================================================================================
 // pass F: Riccati factorisation sweep (classical recursion on P), k = N..0
 // =============================================================================================
+template <bool TOPT>
 __device__ __noinline__ void fq_issue_F(int k)
 {
     const FqCtx& c = fq_ctx;
     uint64_t* bar = &fq_bars[0];
-    mbar_arrive_expect_tx(bar, (SR_SZ + 186) * 8);
+    mbar_arrive_expect_tx(bar, (SR_SZ + 186 + (TOPT ? VX_SZ : 0)) * 8);
     bulk_g2s(fq_smem + F_S, c.SRb + (size_t)k * SR_SZ, SR_SZ * 8, bar);
     bulk_g2s(fq_smem + F_SV, c.vb + (size_t)k * V_STAGE + V_QT, 186 * 8, bar);
+    if (TOPT) bulk_g2s(fq_smem + F_XV, c.vb + (size_t)k * V_STAGE + V_X, VX_SZ * 8, bar);
 }
 
+template <bool TOPT>
 __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
 {
     const int tid = threadIdx.x;
     const int N = fq_ctx.N;
-    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
     double* sP = fq_smem + F_P;
     double* sM = fq_smem + F_M;
     double* sU = sM;
@@ -727,14 +811,53 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
     const int xrt = (tx_ >> 12) & 3u, xct = (tx_ >> 14) & 3u, xr = (tx_ >> 16) & 15u, xc = (tx_ >> 20) & 15u;    \
     (void)xrt; (void)xct; (void)xr; (void)xc; (void)has_xt
 
-    if (tid == 0) fq_issue_F(N);
+    if (tid == 0) fq_issue_F<TOPT>(N);
     for (int k = N; k >= 0; k--) {
         const bool term = (k == N);
         double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
         fq_ring_wait(0, ph);                                 // SR_k and the stage vectors have landed
         FMARK(2);
         double xa[3][3], ua[3][6];
+        const double dt = TOPT ? S[SR_X + SRX_DT] : fq_ctx.dt, c2 = TOPT ? S[SR_X + SRX_C2] : fq_ctx.c2;
         if (tid == 0) bulk_store_wait_read();                // the previous factor record has left sM / sP
+        if (TOPT && !term) {
+            // Time-opt: the node duration is eliminated from the stage before anything else.  With b = d x+ / d dt,
+            // d = h_tt + Gamma_t + b' P+ b and s = q~_t + b' p+, the rest of the stage sees the cost-to-go
+            // P~ = P+ - (P+ b)(P+ b)' / d,  p~ = p+ - (P+ b) s / d, and dt follows in the forward sweeps from
+            // tau = -(s + (P+ b)' (A dx + B du + rb)) / d.
+            const double* bc = S + SR_X + SRX_B;
+            if (tid < NX) {
+                const double* row = sP + tid * P_LD;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int j = 0; j < NX; j += 2) { s0 = fma(row[j], bc[j], s0); s1 = fma(row[j + 1], bc[j + 1], s1); }
+                const double pb = s0 + s1;
+                fv[FV_PB + tid] = pb; vk[V_X + VX_PB + tid] = pb;
+            }
+            __syncthreads();                                 // also orders wait_read before the writes to sP
+            if (tid < 32) {
+                double d0 = 0.0, s0 = 0.0;
+                for (int j = tid; j < NX; j += 32) { d0 = fma(bc[j], fv[FV_PB + j], d0); s0 = fma(bc[j], fv[FV_PN + j], s0); }
+                d0 = warp_sum(d0); s0 = warp_sum(s0);
+                if (tid == 0) {
+                    const double d = S[SR_X + SRX_H] + fq_smem[F_XV + VX_GAM] + IPM_REG_PRIM + d0;
+                    const double dinv = d > 0.0 ? 1.0 / d : 0.0;
+                    const double sx = fq_smem[F_XV + VX_QT] + s0;
+                    fv[FV_XS] = dinv; fv[FV_XS + 1] = sx;
+                    vk[V_X + VX_DINV] = dinv; vk[V_X + VX_S] = sx;
+                }
+            }
+            __syncthreads();
+            {
+                const double dinv = fv[FV_XS], sx = fv[FV_XS + 1];
+                for (int e = tid; e < NX * NX; e += FQ_THREADS) {
+                    const int i = e / NX, j = e % NX;
+                    sP[i * P_LD + j] = fma(-fv[FV_PB + i] * dinv, fv[FV_PB + j], sP[i * P_LD + j]);
+                }
+                if (tid < NX) fv[FV_PN + tid] = fma(-fv[FV_PB + tid], sx * dinv, fv[FV_PN + tid]);
+            }
+            __syncthreads();
+        }
         if (!term) {
             if (tid < NX) {                                  // P+ rb (kept for the corrector), w = P+ rb + p+
                 const double* row = sP + tid * P_LD;
@@ -870,7 +993,7 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
         }
         __syncthreads();                 // every read of SR_k, the stage vectors, P+, U is done
         FMARK(5);
-        if (k > 0 && tid == 0) fq_issue_F(k - 1);            // prefetch the next stage under the factorisation
+        if (k > 0 && tid == 0) fq_issue_F<TOPT>(k - 1);            // prefetch the next stage under the factorisation
         if (!term) {
             // ---- right-looking Cholesky of the 30 input columns; x tiles take the same rank-6 updates ----
             for (int jb = 0; jb < 5; jb++) {
@@ -1029,26 +1152,31 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
 // =============================================================================================
 // passes A1 / D1: forward chain  du = -Luu^-T (lu + Lxu' dx),  dx+ = G [du; dx] + rb
 // =============================================================================================
+template <bool TOPT>
 __device__ __noinline__ void fq_issue_A(int k, int slot)
 {
     const FqCtx& c = fq_ctx;
     double* sl = fq_smem + slot * A_SLOT;
     uint64_t* bar = &fq_bars[slot];
-    mbar_arrive_expect_tx(bar, (LP_UPANELS + 180 + NU + NX) * 8);
+    mbar_arrive_expect_tx(bar, (LP_UPANELS + 180 + NU + NX + (TOPT ? SRX_SZ + VX_SZ : 0)) * 8);
+    if (TOPT) {
+        bulk_g2s(sl + A_XS, c.SRb + (size_t)k * SR_SZ + SR_X, SRX_SZ * 8, bar);
+        bulk_g2s(sl + A_XV, c.vb + (size_t)k * V_STAGE + V_X, VX_SZ * 8, bar);
+    }
     bulk_g2s(sl + A_MU, c.FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, bar);
     bulk_g2s(sl + A_H, c.SRb + (size_t)k * SR_SZ + SR_HQ, 180 * 8, bar);
     bulk_g2s(sl + A_LU, c.vb + (size_t)k * V_STAGE + V_KFF, (NU + NX) * 8, bar);
 }
 
+template <bool TOPT>
 __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
 {
     const int tid = threadIdx.x, lane = tid & 31;
     const int N = fq_ctx.N;
-    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
     double* av = fq_smem + AV_BASE;
     if (tid < NX) av[AV_DX + tid] = 0.0;                     // dx_0 = 0 (the initial state is fixed)
     if (tid == FQ_ISSUER)
-        for (int i = 0; i < A_DEPTH - 1 && i < N; i++) fq_issue_A(i, i % A_DEPTH);
+        for (int i = 0; i < A_DEPTH - 1 && i < N; i++) fq_issue_A<TOPT>(i, i % A_DEPTH);
     __syncthreads();
     for (int k = 0; k <= N; k++) {
         const bool term = (k == N);
@@ -1058,12 +1186,13 @@ __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
         double* dxn = av + AV_DX + ((k + 1) & 1) * NX;
         double* dz = av + AV_DZ;
         if (!term) {
-            if (tid == FQ_ISSUER && k + A_DEPTH - 1 < N) fq_issue_A(k + A_DEPTH - 1, (k + A_DEPTH - 1) % A_DEPTH);
+            if (tid == FQ_ISSUER && k + A_DEPTH - 1 < N) fq_issue_A<TOPT>(k + A_DEPTH - 1, (k + A_DEPTH - 1) % A_DEPTH);
             FMARK(8);
             fq_ring_wait(slot, ph);
             FMARK(23);
             const double* sl = fq_smem + slot * A_SLOT;
             const double* sM = sl + A_MU;
+            const double dt = TOPT ? sl[A_XS + SRX_DT] : fq_ctx.dt, c2 = TOPT ? sl[A_XS + SRX_C2] : fq_ctx.c2;
             if (tid < 32) {             // du = -Luu^-T (lu + Lxu' dx)
                 double rhs = 0.0;
                 if (lane < NU) {
@@ -1137,6 +1266,21 @@ __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
                 if (part == 0 && tid < 64 + 24) dxn[2 * NQ + hi] = s + dz[IH + hi] + sl[A_RB + 2 * NQ + hi];
             }
             __syncthreads();
+            if (TOPT) {
+                // time-opt: dxn holds y0 = A dx + B du + rb; tau = -(s + (P+ b)' y0) / d, then dx+ = y0 + b tau
+                if (tid >= 96) {
+                    double a0 = 0.0;
+                    for (int j = tid - 96; j < NX; j += 32) a0 = fma(sl[A_XV + VX_PB + j], dxn[j], a0);
+                    a0 = warp_sum(a0);
+                    if (tid == 96) {
+                        const double tau = -(sl[A_XV + VX_S] + a0) * sl[A_XV + VX_DINV];
+                        av[AV_X] = tau; vk[V_X + VX_DTAU] = tau;
+                    }
+                }
+                __syncthreads();
+                if (tid < NX) dxn[tid] = fma(sl[A_XS + SRX_B + tid], av[AV_X], dxn[tid]);
+                __syncthreads();
+            }
         } else {
             if (tid < NU) vk[V_DZ + tid] = 0.0;
             else if (tid < NZ) vk[V_DZ + tid] = dx[tid - NU];
@@ -1150,7 +1294,7 @@ __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
 // passes A2 / D2: C dz, slack and multiplier directions, step lengths (and, D2, dpi_{k-1} = P_k dx_k + p_k)
 // out: [0] alpha_p [1] alpha_d [2..4] sum (lam + a dlam)(t + a dt) = c0 + a c1 + a^2 c2
 // =============================================================================================
-template <bool CORR>
+template <bool CORR, bool TOPT>
 __device__ __noinline__ void fq_issue_B(int k, int slot)
 {
     const FqCtx& c = fq_ctx;
@@ -1160,7 +1304,12 @@ __device__ __noinline__ void fq_issue_B(int k, int slot)
     uint64_t* bar = &fq_bars[slot];
     uint32_t bytes = (SR_CSZ + NZ + 8 * NG) * 8;
     if (CORR && k > 0) bytes += (NX * P_LD + NX) * 8;
+    if (TOPT && k < c.N) bytes += (VX_SZ + QX_SZ) * 8;
     mbar_arrive_expect_tx(bar, bytes);
+    if (TOPT && k < c.N) {
+        bulk_g2s(sl + (CORR ? D_XV : B_XV), c.vb + (size_t)k * V_STAGE + V_X, VX_SZ * 8, bar);
+        bulk_g2s(sl + (CORR ? D_XQ : B_XQ), c.qx + (size_t)k * QX_SZ, QX_SZ * 8, bar);
+    }
     bulk_g2s(sl + OC, c.SRb + (size_t)k * SR_SZ + SR_CF, SR_CSZ * 8, bar);
     bulk_g2s(sl + ODZ, c.vb + (size_t)k * V_STAGE + V_DZ, (NZ + 4 * NG) * 8, bar);
     bulk_g2s(sl + OLAM, c.qlam + (size_t)k * 2 * NG, 2 * NG * 8, bar);
@@ -1171,7 +1320,7 @@ __device__ __noinline__ void fq_issue_B(int k, int slot)
     }
 }
 
-template <bool CORR>
+template <bool CORR, bool TOPT>
 __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
 {
     constexpr int SLOT = CORR ? D_SLOT : B_SLOT, DEPTH = CORR ? D_DEPTH : B_DEPTH;
@@ -1183,11 +1332,11 @@ __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
     double* red = fq_smem + FQ_RED;
     double r_p = 1.0, r_d = 1.0, cs0 = 0.0, cs1 = 0.0, cs2 = 0.0;
     if (tid == FQ_ISSUER)
-        for (int i = 0; i < DEPTH - 1 && i <= N; i++) fq_issue_B<CORR>(i, i % DEPTH);
+        for (int i = 0; i < DEPTH - 1 && i <= N; i++) fq_issue_B<CORR, TOPT>(i, i % DEPTH);
     for (int k = 0; k <= N; k++) {
         const int slot = k % DEPTH;
         if (!CORR) FMARK(9);
-        if (tid == FQ_ISSUER && k + DEPTH - 1 <= N) fq_issue_B<CORR>(k + DEPTH - 1, (k + DEPTH - 1) % DEPTH);
+        if (tid == FQ_ISSUER && k + DEPTH - 1 <= N) fq_issue_B<CORR, TOPT>(k + DEPTH - 1, (k + DEPTH - 1) % DEPTH);
         if (!CORR) FMARK(14);
         fq_ring_wait(slot, ph);
         if (!CORR) FMARK(15);
@@ -1221,6 +1370,19 @@ __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
                 cs0 = fma(lam, t, cs0); cs1 += fma(lam, dtv, t * dl); cs2 = fma(dl, dtv, cs2);
             }
             vk[V_DT + tid] = dtv; vk[V_DLAM + tid] = dl;
+        } else if (TOPT && k < N && tid == FQ_THREADS - 1) {     // the two bounds of dt
+            const double* xv = sl + (CORR ? D_XV : B_XV);
+            const double* xq = sl + (CORR ? D_XQ : B_XQ);
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const double lam = xq[2 + e], t = xq[4 + e];
+                const double dtv = (e ? -xv[VX_DTAU] : xv[VX_DTAU]) + xv[VX_RD + e];
+                const double dl = -(xv[VX_RM + e] + lam * dtv) * __drcp_rn(t);
+                r_p = fmax(r_p, -dtv * __drcp_rn(t));
+                r_d = fmax(r_d, -dl * __drcp_rn(lam));
+                cs0 = fma(lam, t, cs0); cs1 += fma(lam, dtv, t * dl); cs2 = fma(dl, dtv, cs2);
+                vk[V_X + VX_DT + e] = dtv; vk[V_X + VX_DL + e] = dl;
+            }
         }
         __syncthreads();
         if (!CORR) FMARK(17);
@@ -1237,15 +1399,20 @@ __device__ __noinline__ uint32_t fq_pass_B(uint32_t ph, double* out)
 // =============================================================================================
 // pass C1: corrector complementarity residual, gamma_c, m0 = rg + C' gamma_c + G' (P+ rb)
 // =============================================================================================
+template <bool TOPT>
 __device__ __noinline__ void fq_issue_C1(int k, int slot)
 {
     const FqCtx& c = fq_ctx;
     double* sl = fq_smem + slot * C_SLOT;
     uint64_t* bar = &fq_bars[slot];
     const double* vk = c.vb + (size_t)k * V_STAGE;
-    mbar_arrive_expect_tx(bar, (180 + SR_CSZ + NZ + NX + 10 * NG) * 8);
+    mbar_arrive_expect_tx(bar, (180 + SR_CSZ + (TOPT ? SRX_SZ : 0) + NZ + NX + 10 * NG + ((TOPT && k < c.N) ? VX_SZ + QX_SZ : 0)) * 8);
+    if (TOPT && k < c.N) {
+        bulk_g2s(sl + C_XV, vk + V_X, VX_SZ * 8, bar);
+        bulk_g2s(sl + C_XQ, c.qx + (size_t)k * QX_SZ, QX_SZ * 8, bar);
+    }
     bulk_g2s(sl + C_H, c.SRb + (size_t)k * SR_SZ + SR_HQ, 180 * 8, bar);
-    bulk_g2s(sl + C_C, c.SRb + (size_t)k * SR_SZ + SR_CF, SR_CSZ * 8, bar);
+    bulk_g2s(sl + C_C, c.SRb + (size_t)k * SR_SZ + SR_CF, (SR_CSZ + (TOPT ? SRX_SZ : 0)) * 8, bar);
     bulk_g2s(sl + C_RG, vk + V_RG, (NZ + NX) * 8, bar);
     bulk_g2s(sl + C_DT, vk + V_DT, 4 * NG * 8, bar);
     bulk_g2s(sl + C_RD, vk + V_RD, 2 * NG * 8, bar);
@@ -1253,18 +1420,18 @@ __device__ __noinline__ void fq_issue_C1(int k, int slot)
     bulk_g2s(sl + C_T, c.qt + (size_t)k * 2 * NG, 2 * NG * 8, bar);
 }
 
+template <bool TOPT>
 __device__ __noinline__ uint32_t fq_pass_C1(uint32_t ph, int cpass, double sigma_mu)
 {
     const int tid = threadIdx.x;
     const int N = fq_ctx.N;
-    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
     double* gamc = fq_smem + CV_BASE;
     if (tid == FQ_ISSUER)
-        for (int i = 0; i < C_DEPTH - 1 && i <= N; i++) fq_issue_C1(i, i % C_DEPTH);
+        for (int i = 0; i < C_DEPTH - 1 && i <= N; i++) fq_issue_C1<TOPT>(i, i % C_DEPTH);
     for (int k = 0; k <= N; k++) {
         const int slot = k % C_DEPTH;
         const bool term = (k == N);
-        if (tid == FQ_ISSUER && k + C_DEPTH - 1 <= N) fq_issue_C1(k + C_DEPTH - 1, (k + C_DEPTH - 1) % C_DEPTH);
+        if (tid == FQ_ISSUER && k + C_DEPTH - 1 <= N) fq_issue_C1<TOPT>(k + C_DEPTH - 1, (k + C_DEPTH - 1) % C_DEPTH);
         fq_ring_wait(slot, ph);
         const double* sl = fq_smem + slot * C_SLOT;
         const double* Sc = sl + C_C - SR_CF;
@@ -1283,11 +1450,23 @@ __device__ __noinline__ uint32_t fq_pass_C1(uint32_t ph, int cpass, double sigma
                 }
             }
             gamc[tid] = g;
+        } else if (TOPT && !term && tid == FQ_THREADS - 1) {     // the two bounds of dt
+            double g = 0.0;
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const double lam = sl[C_XQ + 2 + e], t = sl[C_XQ + 4 + e];
+                const double rmc = fma(lam, t, cpass == 0 ? sl[C_XV + VX_DT + e] * sl[C_XV + VX_DL + e] : 0.0) - sigma_mu;
+                vk[V_X + VX_RM + e] = rmc;
+                const double v = (rmc + lam * sl[C_XV + VX_RD + e]) * __drcp_rn(t);
+                g += e ? -v : v;
+            }
+            vk[V_X + VX_M0] = sl[C_XV + VX_RG] + g;
         }
         __syncthreads();
         if (tid < NZ) {
             double s = sl[C_RG + tid] + fq_ct(Sc, gamc, tid);
-            if (!term) s += fq_gt(sl + C_H, sl + C_PRB, tid, dt, c2);
+            // time-opt: the extension of the stage record follows the constraint part and is fetched with it
+            if (!term) s += fq_gt(sl + C_H, sl + C_PRB, tid, TOPT ? sl[C_C + SR_CSZ + SRX_DT] : fq_ctx.dt, TOPT ? sl[C_C + SR_CSZ + SRX_C2] : fq_ctx.c2);
             vk[V_M0 + tid] = s;
         }
         __syncthreads();
@@ -1299,22 +1478,27 @@ __device__ __noinline__ uint32_t fq_pass_C1(uint32_t ph, int cpass, double sigma
 // =============================================================================================
 // pass C2: corrector backward chain  m = m0 + G' p+,  lu = Luu^-1 m_u,  p = m_x - Lxu lu
 // =============================================================================================
+template <bool TOPT>
 __device__ __noinline__ void fq_issue_C2(int k, int slot)
 {
     const FqCtx& c = fq_ctx;
     double* sl = fq_smem + slot * E_SLOT;
     uint64_t* bar = &fq_bars[slot];
-    mbar_arrive_expect_tx(bar, (LP_UPANELS + 180 + NZ) * 8);
+    mbar_arrive_expect_tx(bar, (LP_UPANELS + 180 + NZ + (TOPT ? SRX_SZ + VX_SZ : 0)) * 8);
+    if (TOPT) {
+        bulk_g2s(sl + E_XS, c.SRb + (size_t)k * SR_SZ + SR_X, SRX_SZ * 8, bar);
+        bulk_g2s(sl + E_XV, c.vb + (size_t)k * V_STAGE + V_X, VX_SZ * 8, bar);
+    }
     bulk_g2s(sl + E_MU, c.FRb + (size_t)k * FR_SZ + FR_MU, LP_UPANELS * 8, bar);
     bulk_g2s(sl + E_H, c.SRb + (size_t)k * SR_SZ + SR_HQ, 180 * 8, bar);
     bulk_g2s(sl + E_M0, c.vb + (size_t)k * V_STAGE + V_M0, NZ * 8, bar);
 }
 
+template <bool TOPT>
 __device__ __noinline__ uint32_t fq_pass_C2(uint32_t ph)
 {
     const int tid = threadIdx.x;
     const int N = fq_ctx.N;
-    const double dt = fq_ctx.dt, c2 = fq_ctx.c2;
     double* ev = fq_smem + EV_BASE;
     // terminal stage: p_N = m_x (read straight from the workspace)
     {
@@ -1322,19 +1506,33 @@ __device__ __noinline__ uint32_t fq_pass_C2(uint32_t ph)
         if (tid < NX) { const double pv = vk[V_M0 + NU + tid]; ev[EV_PN + (N & 1) * NX + tid] = pv; vk[V_P + tid] = pv; }
     }
     if (tid == FQ_ISSUER)
-        for (int i = 0; i < E_DEPTH - 1 && i < N; i++) fq_issue_C2(N - 1 - i, i % E_DEPTH);
+        for (int i = 0; i < E_DEPTH - 1 && i < N; i++) fq_issue_C2<TOPT>(N - 1 - i, i % E_DEPTH);
     __syncthreads();
     for (int i = 0; i < N; i++) {
         const int k = N - 1 - i, slot = i % E_DEPTH;
-        if (tid == FQ_ISSUER && i + E_DEPTH - 1 < N) fq_issue_C2(k - (E_DEPTH - 1), (i + E_DEPTH - 1) % E_DEPTH);
+        if (tid == FQ_ISSUER && i + E_DEPTH - 1 < N) fq_issue_C2<TOPT>(k - (E_DEPTH - 1), (i + E_DEPTH - 1) % E_DEPTH);
         fq_ring_wait(slot, ph);
         const double* sl = fq_smem + slot * E_SLOT;
         const double* sM = sl + E_MU;
         double* vk = fq_ctx.vb + (size_t)k * V_STAGE;
         double* ms = ev + EV_M;
         double* lus = ev + EV_LU;
-        const double* pnn = ev + EV_PN + ((k + 1) & 1) * NX;
+        const double* pnn = ev + EV_PN + ((k + 1) & 1) * NX;      // p_{k+1} (time-opt: replaced by p~ below)
         double* pnk = ev + EV_PN + (k & 1) * NX;
+        const double dt = TOPT ? sl[E_XS + SRX_DT] : fq_ctx.dt, c2 = TOPT ? sl[E_XS + SRX_C2] : fq_ctx.c2;
+        if (TOPT) {
+            // time-opt: s = m0_t + b' p+, then p~ = p+ - (P+ b) s / d stands in for p+ (see pass F)
+            if (tid >= 96) {
+                double a0 = 0.0;
+                for (int j = tid - 96; j < NX; j += 32) a0 = fma(sl[E_XS + SRX_B + j], pnn[j], a0);
+                a0 = warp_sum(a0);
+                if (tid == 96) { const double sx = sl[E_XV + VX_M0] + a0; ev[EV_X] = sx; vk[V_X + VX_S] = sx; }
+            }
+            __syncthreads();
+            if (tid < NX) ev[EV_PT + tid] = fma(-sl[E_XV + VX_PB + tid], ev[EV_X] * sl[E_XV + VX_DINV], pnn[tid]);
+            __syncthreads();
+            pnn = ev + EV_PT;
+        }
         if (tid < NZ) ms[tid] = sl[E_M0 + tid] + fq_gt(sl + E_H, pnn, tid, dt, c2);
         __syncthreads();
         if (tid < 32) {                                      // lu = Luu^-1 m_u (column-oriented, one warp)
@@ -1394,6 +1592,7 @@ __device__ __noinline__ uint32_t fq_pass_C2(uint32_t ph)
 // =============================================================================================
 // the kernel
 // =============================================================================================
+template <bool TOPT>
 __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 {
     const int tid = threadIdx.x;
@@ -1407,6 +1606,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         fq_ctx.qpi = a.qpi + (size_t)b * N * NX;
         fq_ctx.qlam = a.qlam + (size_t)b * (N + 1) * 2 * NG;
         fq_ctx.qt = a.qt + (size_t)b * (N + 1) * 2 * NG;
+        fq_ctx.qx = a.qx + (size_t)b * N * QX_SZ;
         fq_ctx.dt = a.dt; fq_ctx.c2 = a.c2; fq_ctx.N = N;
 #pragma unroll
         for (int i = 0; i < 4; i++) mbar_init(&fq_bars[i], 1);
@@ -1431,6 +1631,8 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             qz[NU + tid] = a.dx0_ext ? a.dx0_ext[(size_t)b * NX + tid]
                                      : a.x0[(size_t)b * NX + tid] - a.x[(size_t)b * (N + 1) * NX + tid];
         if (tid < NU) qz[(size_t)N * NZ + tid] = 0.0;
+        if (TOPT && a.warm == 0)
+            for (int i = tid; i < N; i += FQ_THREADS) fq_ctx.qx[(size_t)i * QX_SZ] = 0.0;
         fq_pass_end();
     }
 
@@ -1449,7 +1651,7 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         FMARK(0);
         // ================= update + residuals of every stage, norms, mu, exit tests =================
         double o[6];
-        ph = fq_pass_R(ph, it, a.warm, alpha_p, alpha_d, o);
+        ph = fq_pass_R<TOPT>(ph, it, a.warm, alpha_p, alpha_d, o);
         FMARK(1);
         if (it == 0) nc_total = (int)(o[5] + 0.5);
         const double mu = nc_total > 0 ? o[4] / nc_total : 0.0;
@@ -1466,12 +1668,12 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
             if (last) { status = 1; break; }
         }
         // ================= factorisation sweep =================
-        ph = fq_pass_F(ph);
+        ph = fq_pass_F<TOPT>(ph);
         FMARK(3);
         // ================= affine direction, step lengths, centring parameter =================
-        ph = fq_pass_A1(ph);
+        ph = fq_pass_A1<TOPT>(ph);
         FMARK(8);
-        ph = fq_pass_B<false>(ph, o);
+        ph = fq_pass_B<false, TOPT>(ph, o);
         FMARK(9);
         double sigma_mu, mu_aff;
         {
@@ -1487,13 +1689,13 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         // (HPIPM arg->cond_pred_corr): if the complementarity predicted along it exceeds twice the affine
         // prediction, the centring direction alone (COMPUTE_CENTERING_QP: rm = lam t - sigma mu) is solved for.
         for (int cpass = 0; cpass < 2; cpass++) {
-            ph = fq_pass_C1(ph, cpass, sigma_mu);
+            ph = fq_pass_C1<TOPT>(ph, cpass, sigma_mu);
             FMARK(10);
-            ph = fq_pass_C2(ph);
+            ph = fq_pass_C2<TOPT>(ph);
             FMARK(11);
-            ph = fq_pass_A1(ph);
+            ph = fq_pass_A1<TOPT>(ph);
             FMARK(12);
-            ph = fq_pass_B<true>(ph, o);
+            ph = fq_pass_B<true, TOPT>(ph, o);
             FMARK(13);
             alpha_p = o[0]; alpha_d = o[1];
             if (cpass == 1 || !a.cond_pred_corr) break;

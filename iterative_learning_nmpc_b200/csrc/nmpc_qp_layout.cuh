@@ -44,16 +44,35 @@ __host__ __device__ __forceinline__ int lp_idx(int i, int j)
 #define V_M0 (V_PRB + NX)                // 72  corrector: rg + C' gamma_c + G' (P+ rb)
 #define V_P (V_M0 + NZ)                  // 42  corrector: linear term p_k of the cost-to-go
 #define V_DPI (V_P + NX)                 // 42  direction of the dynamics multiplier pi_k
-#define V_STAGE (V_DPI + NX)             // 864
+// time-opt block (enable_time_opt): everything the passes keep per stage about the node duration dt_k, its two
+// bounds and its elimination from the stage (P~ = P+ - (P+ b)(P+ b)' / d)
+#define V_X (V_DPI + NX)                 // 864
+#define VX_PB 0                          // 42  P+ b
+#define VX_DINV 42                       // 1 / d,  d = h_tt + Gamma_t + b' P+ b
+#define VX_S 43                          // q~_t + b' p+ of the direction being solved for
+#define VX_DTAU 44                       // direction of dt
+#define VX_RG 45                         // stationarity residual of dt
+#define VX_QT 46                         // q~_t = rg_t + gamma_t (affine)
+#define VX_M0 47                         // corrector: rg_t + gamma_c
+#define VX_GAM 48                        // Gamma_t
+#define VX_RD 50                         // [2] slack residuals of the bounds
+#define VX_RM 52                         // [2]
+#define VX_DT 54                         // [2] slack directions
+#define VX_DL 56                         // [2] multiplier directions
+#define VX_SZ 58
+#define V_STAGE (V_X + VX_SZ)            // 922
+// QP iterate of dt per stage: [tau, -, lam_l, lam_u, t_l, t_u]
+#define QX_SZ 6
 static_assert(V_GAM % 2 == 0 && V_KFF % 2 == 0 && V_RB % 2 == 0 && V_DZ % 2 == 0 && V_RD % 2 == 0 && V_RM % 2 == 0 &&
               V_DT % 2 == 0 && V_DLAM % 2 == 0 && V_RG % 2 == 0 && V_PRB % 2 == 0 && V_M0 % 2 == 0 && V_P % 2 == 0 &&
-              V_DPI % 2 == 0 && V_STAGE % 2 == 0, "16-byte alignment of bulk copies");
+              V_DPI % 2 == 0 && V_X % 2 == 0 && VX_SZ % 2 == 0 && V_STAGE % 2 == 0, "16-byte alignment of bulk copies");
 
 #define POS_INF_BITS 0x7ff0000000000000ULL
 #define ONE_BITS 0x3ff0000000000000ULL
 
 struct QpArgs {
     double* qz; double* qpi; double* qlam; double* qt;   // QP iterate, global problem index
+    double* qx;                     // time-opt: QP iterate of dt [B][N][QX_SZ]
     int32_t* qp_iter; int32_t* qp_status; int32_t* qp_ncond; double* qp_res;
     const double* dx0_ext;          // [B][NX] or null -> x0 - x[0]
     const double* x0;

@@ -16,6 +16,12 @@ __device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, doub
     atomicMax(addr, (unsigned long long)__double_as_longlong(v));
 }
 
+__global__ void nmpc_fill_kernel(double* p, int n, double v)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
 // start of a solve: clear flags
 __global__ void nmpc_sqp_begin_kernel(int B, int rti, int32_t* status, int32_t* done, int32_t* sqp_iter,
                                       int32_t* qp_iter, int32_t* qp_status, int32_t* qp_ncond,
@@ -76,7 +82,8 @@ __global__ void nmpc_cost_sum_kernel(int b0, int Bc, int N, const double* cost_s
 
 // shift warm start (solver.py:290-342): one CTA per problem, data staged through shared memory
 __global__ void __launch_bounds__(128, 4) nmpc_shift_kernel(int N, const int32_t* start_node, int repeat_last,
-                                                         double* x, double* u, double* pi, double* lam)
+                                                         double* x, double* u, double* pi, double* lam,
+                                                         double* dtn, double* lamt, double dt_nodes)
 {
     const int b = blockIdx.x, tid = threadIdx.x;
     const int s = start_node[b];
@@ -100,6 +107,14 @@ __global__ void __launch_bounds__(128, 4) nmpc_shift_kernel(int N, const int32_t
         for (int i = tid; i < 2 * NG; i += 128) lb[k * 2 * NG + i] = lb[(k + s) * 2 * NG + i];
         __syncthreads();
     }
+    if (dtn && tid == 0) {
+        // enable_time_opt (solver.py:324-336): dt of the warm-started nodes from the previous solution, nominal on the tail
+        double* db = dtn + (size_t)b * N;
+        double* lt = lamt + (size_t)b * N * 2;
+        for (int k = 0; k < nws; k++) { db[k] = db[k + s]; lt[2 * k] = lt[2 * (k + s)]; lt[2 * k + 1] = lt[2 * (k + s) + 1]; }
+        for (int k = nws; k < N; k++) db[k] = dt_nodes;
+        if (nws < N) { lt[2 * nws] = 0.0; lt[2 * nws + 1] = 0.0; }      // shifted in from the terminal node, which has no dt
+    }
     // force tail
     for (int e = tid; e < (N - nws) * 12; e += 128) {
         const int k = nws + e / 12, i = e % 12;
@@ -121,7 +136,8 @@ __global__ void __launch_bounds__(128, 4) nmpc_shift_kernel(int N, const int32_t
 // Packed result rows for the gather to the dataset-writer rank: per problem
 // [x (N+1)*42 | u N*30 | dt_node N | status] = 1868 doubles at N = 25 -- the 1867 numbers parse_sol returns
 // (solver.py:403-429: q, v, h per node, a, f, dt per interval) plus the solver status.
-__global__ void __launch_bounds__(128) nmpc_pack_solution_kernel(int N, double dt, const double* __restrict__ x,
+__global__ void __launch_bounds__(128) nmpc_pack_solution_kernel(int N, double dt, const double* __restrict__ dtn,
+                                                                 const double* __restrict__ x,
                                                                  const double* __restrict__ u,
                                                                  const int32_t* __restrict__ status,
                                                                  double* __restrict__ out)
@@ -133,6 +149,6 @@ __global__ void __launch_bounds__(128) nmpc_pack_solution_kernel(int N, double d
     const double* ub = u + (size_t)b * nu;
     for (int i = tid; i < nx; i += 128) o[i] = xb[i];
     for (int i = tid; i < nu; i += 128) o[nx + i] = ub[i];
-    for (int i = tid; i < N; i += 128) o[nx + nu + i] = dt;
+    for (int i = tid; i < N; i += 128) o[nx + nu + i] = dtn ? dtn[(size_t)b * N + i] : dt;
     if (tid == 0) o[row - 1] = (double)status[b];
 }

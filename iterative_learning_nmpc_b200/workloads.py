@@ -269,7 +269,11 @@ def load_into(solver, batch: Dict[str, np.ndarray], hg: Optional[np.ndarray] = N
     xg = batch["x_guess"].copy()
     if hg is not None:
         xg[:, :, 36:] = hg[:, None, :]
-    solver.set_guess(xg, batch["u_guess"])
+    ug = batch["u_guess"]
+    if getattr(solver, "NU", ug.shape[-1]) == ug.shape[-1] + 1:
+        # the oracle's time-opt build carries dt as a 31st input column: nominal node duration (solver.py:189-190)
+        ug = np.concatenate([ug, np.full(ug.shape[:2] + (1,), float(solver.opts.dt_nodes))], axis=2)
+    solver.set_guess(xg, ug)
     solver.set_x0(batch["qv"])
     solver.pin_stance_feet(batch["i_node"])
     solver.reset_duals()

@@ -25,13 +25,23 @@
 
 #include "../include/nmpc_b200.h"
 
+/* Two builds of this file: the default one (nu = 30) and, with -DNMPC_ORACLE_TOPT, the `enable_time_opt` variant
+ * (solver.py:43-44, 124-125, 166-167, 189-190, 325-336, 424-427): the node duration dt_k is a 31st input with the
+ * cost weight `time_opt` on (dt - dt_nodes), the bounds [dt_min, dt_max] (config_abstract.py:49-52, 80-88; one more
+ * two-sided constraint row) and it multiplies the dynamics.  Same algorithms, dense, nothing specialised. */
 #define NX NMPC_NX
-#define NU NMPC_NU
-#define NZ NMPC_NZ
 #define NP NMPC_NP
 #define NY NMPC_NY
 #define NYE NMPC_NYE
+#ifdef NMPC_ORACLE_TOPT
+#define NU (NMPC_NU + 1)
+#define NZ (NMPC_NZ + 1)
+#define NG (NMPC_NG + 1)
+#else
+#define NU NMPC_NU
+#define NZ NMPC_NZ
 #define NG NMPC_NG
+#endif
 #define NQ 18
 #define NF 4
 #define NMAX NMPC_MAX_NODES
@@ -44,14 +54,16 @@
 /* z = [u; x] index helpers */
 #define IA 0          /* a   in u */
 #define IFRC 18       /* f   in u */
-#define IQ 30         /* q   in z */
-#define IV 48         /* v   in z */
-#define IH 66         /* h   in z */
+#define IDT 30        /* dt  in u (time-opt build only) */
+#define IQ NU         /* q   in z */
+#define IV (NU + 18)  /* v   in z */
+#define IH (NU + 36)  /* h   in z */
 /* constraint row blocks */
 #define GR_FRIC 0     /* 4 feet x 5 */
 #define GR_CNT 20     /* 4 feet x 3 */
 #define GR_PATCH 32   /* 4 feet x 1 */
 #define GR_CONS 36    /* 6 */
+#define GR_DT 42      /* dt_min <= dt <= dt_max (time-opt build only) */
 /* parameter offsets inside one foot block (solver.py:212-252) */
 #define P_ACTIVE 0
 #define P_POINT 1
@@ -77,7 +89,8 @@ typedef struct {
     double A[NX][NX], B[NX][NU], b[NX];
     double H[NZ][NZ], g[NZ];
     double C[NG][NZ], c[NG];   /* constraint values at the linearisation point */
-    double ml[NG], mu[NG];     /* row masks: lower / upper bound present (NLP bounds are 0) */
+    double cl[NG], cu[NG];     /* value minus the lower / upper bound (= c: the bounds are 0, except on the dt row) */
+    double ml[NG], mu[NG];     /* row masks: lower / upper bound present */
     double lgq[NG], ugq[NG];   /* QP-level bounds on C dz: lg - c, ug - c */
     double cost;
 } stage_lin;
@@ -126,12 +139,16 @@ static void linearize_stage(const nmpc_opts* o, int k, int N, const double* x, c
                             const double* W, stage_lin* s)
 {
     const int term = (k == N);
-    const double dt = o->dt_nodes;
     const double* q = x;
     const double* v = x + NQ;
     const double* h = x + 2 * NQ;
     static const double zero_u[NU] = {0};
     if (term) u = zero_u;
+#ifdef NMPC_ORACLE_TOPT
+    const double dt = term ? o->dt_nodes : u[IDT];
+#else
+    const double dt = o->dt_nodes;
+#endif
     const double* a = u;
     const double* f = u + NQ;
     double rec[NMPC_REC_SIZE];
@@ -187,6 +204,10 @@ static void linearize_stage(const nmpc_opts* o, int k, int N, const double* x, c
                 }
         }
         for (int i = 0; i < 6; i++) phi[2 * NQ + i] = h[i] + dt * hd[i];
+#ifdef NMPC_ORACLE_TOPT
+        for (int i = 0; i < NQ; i++) { s->B[i][IDT] = v[i] + dt * a[i]; s->B[NQ + i][IDT] = a[i]; }
+        for (int i = 0; i < 6; i++) s->B[2 * NQ + i][IDT] = hd[i];
+#endif
         for (int i = 0; i < NX; i++) s->b[i] = phi[i] - xnext[i];
     }
 
@@ -229,6 +250,14 @@ static void linearize_stage(const nmpc_opts* o, int k, int N, const double* x, c
                 for (int d = 0; d < NZ; d++) s->H[c][d] += J[i][c] * W[i] * J[i][d];
             }
         }
+#ifdef NMPC_ORACLE_TOPT
+        if (!term) {        /* W["dt"] (dt - dt_nodes)^2 / 2  (solver.py:124-125, 166-167) */
+            const double e = dt - o->dt_nodes;
+            cost += 0.5 * o->time_opt_weight * e * e;
+            s->g[IDT] += o->time_opt_weight * e;
+            s->H[IDT][IDT] += o->time_opt_weight;
+        }
+#endif
         s->cost = cost;
         const double reg = term ? o->reg_eps_e : o->reg_eps;
         for (int c = 0; c < NZ; c++) s->H[c][c] += reg;
@@ -318,7 +347,15 @@ static void linearize_stage(const nmpc_opts* o, int k, int N, const double* x, c
             s->ml[r] = 1.0; s->mu[r] = 1.0;
         }
     }
-    for (int j = 0; j < NG; j++) { s->lgq[j] = -s->c[j]; s->ugq[j] = -s->c[j]; }
+    for (int j = 0; j < NG; j++) { s->cl[j] = s->c[j]; s->cu[j] = s->c[j]; }
+#ifdef NMPC_ORACLE_TOPT
+    if (!term) {            /* dt_min <= dt <= dt_max */
+        s->C[GR_DT][IDT] = 1.0;
+        s->c[GR_DT] = dt; s->cl[GR_DT] = dt - o->dt_min; s->cu[GR_DT] = dt - o->dt_max;
+        s->ml[GR_DT] = 1.0; s->mu[GR_DT] = 1.0;
+    }
+#endif
+    for (int j = 0; j < NG; j++) { s->lgq[j] = -s->cl[j]; s->ugq[j] = -s->cu[j]; }
 }
 
 /* ------------------------------------------------------------------------------------------ */
@@ -692,7 +729,11 @@ static void qp_ipm(workspace* w, const nmpc_opts* o, int N, const double* dx0, i
     info->iter = it;
 }
 
+#ifndef NMPC_ORACLE_TOPT
 #include "nmpc_oracle_fast.h"
+#else
+typedef struct { int unused; } fast_ws;       /* the structured variant exists for nu = 30 only */
+#endif
 
 /* ------------------------------------------------------------------------------------------ */
 /* batch state ("handle")                                                                     */
@@ -712,7 +753,11 @@ typedef struct {
 
 oracle_handle* oracle_create(const nmpc_opts* o, int32_t B)
 {
+#ifdef NMPC_ORACLE_TOPT
+    if (!o || B <= 0 || o->n_nodes < 1 || o->n_nodes > NMAX || !o->enable_time_opt) return NULL;
+#else
     if (!o || B <= 0 || o->n_nodes < 1 || o->n_nodes > NMAX || o->enable_time_opt) return NULL;
+#endif
     oracle_handle* h = calloc(1, sizeof(*h));
     h->o = *o; h->B = B; h->N = o->n_nodes;
     const size_t N = h->N;
@@ -739,7 +784,11 @@ void oracle_destroy(oracle_handle* h)
 
 int oracle_set_opts(oracle_handle* h, const nmpc_opts* o)
 {
+#ifdef NMPC_ORACLE_TOPT
+    if (!h || !o || o->n_nodes != h->N || !o->enable_time_opt) return NMPC_EINVAL;
+#else
     if (!h || !o || o->n_nodes != h->N || o->enable_time_opt) return NMPC_EINVAL;
+#endif
     h->o = *o;
     return 0;
 }
@@ -748,6 +797,9 @@ int oracle_set_opts(oracle_handle* h, const nmpc_opts* o)
 int oracle_set_fast(oracle_handle* h, int32_t fast)
 {
     if (!h) return NMPC_EINVAL;
+#ifdef NMPC_ORACLE_TOPT
+    if (fast) return NMPC_ENOSYS;
+#endif
     h->fast = fast != 0;
     return 0;
 }
@@ -883,6 +935,9 @@ int oracle_shift_warm_start(oracle_handle* h, const int32_t* start_node, int32_t
         for (int k = 0; k < nws; k++) memcpy(u + k * NU, u + (k + s) * NU, NU * sizeof(double));
         for (int k = nws; k < N; k++)
             for (int i = 0; i < 12; i++) u[k * NU + IFRC + i] = repeat_last ? u[(N - 1) * NU + IFRC + i] : 0.0;
+#ifdef NMPC_ORACLE_TOPT
+        for (int k = nws; k < N; k++) u[k * NU + IDT] = h->o.dt_nodes;      /* solver.py:334-336: nominal dt on the tail */
+#endif
         if (repeat_last && nws < N) {
             for (int k = nws; k <= N; k++) memcpy(x + k * NX, x + N * NX, NX * sizeof(double));
             for (int k = nws; k < N; k++) memcpy(u + k * NU, u + (N - 1) * NU, NQ * sizeof(double));
@@ -932,12 +987,12 @@ static void nlp_residuals(const oracle_handle* h, int b, const workspace* w, dou
         if (k < N) for (int i = 0; i < NX; i++) NORM_ACC(re, s->b[i]);
         for (int j = 0; j < NG; j++) {
             if (s->ml[j] > 0.5) {
-                if (-s->c[j] > ri || s->c[j] != s->c[j]) ri = -s->c[j];
-                NORM_ACC(rc, lam[k * 2 * NG + j] * s->c[j]);
+                if (-s->cl[j] > ri || s->cl[j] != s->cl[j]) ri = -s->cl[j];
+                NORM_ACC(rc, lam[k * 2 * NG + j] * s->cl[j]);
             }
             if (s->mu[j] > 0.5) {
-                if (s->c[j] > ri || s->c[j] != s->c[j]) ri = s->c[j];
-                NORM_ACC(rc, lam[k * 2 * NG + NG + j] * s->c[j]);
+                if (s->cu[j] > ri || s->cu[j] != s->cu[j]) ri = s->cu[j];
+                NORM_ACC(rc, lam[k * 2 * NG + NG + j] * s->cu[j]);
             }
         }
     }
@@ -948,11 +1003,15 @@ static void nlp_residuals(const oracle_handle* h, int b, const workspace* w, dou
 static void qp_solve(const oracle_handle* h, workspace* w, fast_ws* f, int N, const double* dx0, int warm,
                      double (*z)[NZ], double (*pi)[NX], double (*lam)[2 * NG], double (*t)[2 * NG], qp_info* info)
 {
+#ifndef NMPC_ORACLE_TOPT
     if (h->fast && f) {
         int bad = 0;
         for (int k = 0; k <= N; k++) bad |= sr_from_lin(&w->lin[k], k == N, h->o.dt_nodes, &f->sr[k]);
         if (!bad) { qp_ipm_fast(w, f, &h->o, N, dx0, warm, z, pi, lam, t, info); return; }
     }
+#else
+    (void)f;
+#endif
     qp_ipm(w, &h->o, N, dx0, warm, z, pi, lam, t, info);
 }
 
@@ -1089,8 +1148,8 @@ int oracle_export_qp(oracle_handle* h, double* BAbt, double* RSQrq, double* DCt,
             }
             for (int j = 0; j < NG; j++) {
                 const size_t id = ((size_t)b * (N + 1) + k) * NG + j;
-                if (lg) lg[id] = -s->c[j];
-                if (ug) ug[id] = -s->c[j];
+                if (lg) lg[id] = -s->cl[j];
+                if (ug) ug[id] = -s->cu[j];
                 if (mask) {
                     mask[((size_t)b * (N + 1) + k) * 2 * NG + j] = s->ml[j];
                     mask[((size_t)b * (N + 1) + k) * 2 * NG + NG + j] = s->mu[j];

@@ -15,6 +15,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libnmpc_oracle.so")
+LIB_PATH_TOPT = os.path.join(HERE, "libnmpc_oracle_topt.so")      # -DNMPC_ORACLE_TOPT build: nu = 31, ng = 43
 
 NX, NU, NZ, NP, NY, NYE, NG = 42, 30, 72, 44, 76, 52, 42
 
@@ -28,6 +29,7 @@ class NmpcOpts(C.Structure):
         ("dt_nodes", C.c_double), ("dt_min", C.c_double), ("dt_max", C.c_double),
         ("nlp_tol", C.c_double), ("qp_tol", C.c_double),
         ("reg_eps", C.c_double), ("reg_eps_e", C.c_double), ("mu_contact", C.c_double),
+        ("time_opt_weight", C.c_double),
     ]
 
 
@@ -40,7 +42,8 @@ class NmpcStats(C.Structure):
 def default_opts(**kw) -> NmpcOpts:
     o = NmpcOpts(n_nodes=25, max_iter=1, max_qp_iter=6, real_time_it=0, warm_start_qp=1,
                  warm_start_nlp=1, hpipm_mode=1, enable_time_opt=0, warm_start_first_qp=0, cond_pred_corr=1, dt_nodes=0.04, dt_min=0.02,
-                 dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8)
+                 dt_max=0.07, nlp_tol=1e-1, qp_tol=1e-2, reg_eps=1e-6, reg_eps_e=1e-5, mu_contact=0.8,
+                 time_opt_weight=1e4)
     for k, v in kw.items():
         setattr(o, k, v)
     return o
@@ -48,29 +51,31 @@ def default_opts(**kw) -> NmpcOpts:
 
 def build(force: bool = False) -> str:
     """Compile the oracle with its Makefile (gcc)."""
-    if force or not os.path.exists(LIB_PATH):
+    if force or not os.path.exists(LIB_PATH) or not os.path.exists(LIB_PATH_TOPT):
         subprocess.check_call(["make", "-C", HERE, "-s"] + (["-B"] if force else []))
     return LIB_PATH
 
 
-_lib = None
+_libs = {}
 
 
-def lib():
-    global _lib
-    if _lib is None:
+def lib(topt: bool = False):
+    """The oracle library: the default build, or the `enable_time_opt` build (nu = 31, ng = 43)."""
+    topt = bool(topt)
+    if topt not in _libs:
         build()
-        _lib = C.CDLL(LIB_PATH)
-        _lib.oracle_create.restype = C.c_void_p
-        _lib.oracle_create.argtypes = [C.POINTER(NmpcOpts), C.c_int32]
+        L = C.CDLL(LIB_PATH_TOPT if topt else LIB_PATH)
+        L.oracle_create.restype = C.c_void_p
+        L.oracle_create.argtypes = [C.POINTER(NmpcOpts), C.c_int32]
         for name in ("oracle_destroy", "oracle_set_opts", "oracle_set_x0", "oracle_set_x0_full",
                      "oracle_set_yref", "oracle_set_weights", "oracle_set_params",
                      "oracle_pin_stance_feet", "oracle_set_guess", "oracle_reset_duals",
                      "oracle_shift_warm_start", "oracle_solve", "oracle_get_solution",
                      "oracle_get_stats", "oracle_get_qp_step", "oracle_export_qp", "oracle_solve_qp",
                      "oracle_inverse_dynamics", "oracle_set_fast"):
-            getattr(_lib, name).restype = C.c_int
-    return _lib
+            getattr(L, name).restype = C.c_int
+        _libs[topt] = L
+    return _libs[topt]
 
 
 def _p(a: Optional[np.ndarray]):
@@ -153,71 +158,75 @@ class OracleSolver:
         self.opts = opts or default_opts()
         self.B = int(batch)
         self.N = int(self.opts.n_nodes)
-        self._h = C.c_void_p(lib().oracle_create(C.byref(self.opts), C.c_int32(self.B)))
+        self.topt = bool(self.opts.enable_time_opt)
+        self.lib = lib(self.topt)
+        # dimensions of this build: the time-opt variant carries dt as a 31st input and one more constraint row
+        self.NU, self.NZ, self.NG = (NU + 1, NZ + 1, NG + 1) if self.topt else (NU, NZ, NG)
+        self._h = C.c_void_p(self.lib.oracle_create(C.byref(self.opts), C.c_int32(self.B)))
         if not self._h:
             raise RuntimeError("oracle_create failed")
 
     def __del__(self):
         if getattr(self, "_h", None):
-            lib().oracle_destroy(self._h)
+            self.lib.oracle_destroy(self._h)
             self._h = None
 
     def set_fast(self, fast: bool = True):
         """Structured interior point (nmpc_oracle_fast.h) instead of the dense restatement: the timed CPU baseline."""
-        assert lib().oracle_set_fast(self._h, C.c_int32(int(fast))) == 0
+        assert self.lib.oracle_set_fast(self._h, C.c_int32(int(fast))) == 0
 
     def set_opts(self, opts: NmpcOpts):
         self.opts = opts
-        assert lib().oracle_set_opts(self._h, C.byref(opts)) == 0
+        assert self.lib.oracle_set_opts(self._h, C.byref(opts)) == 0
 
     def set_x0(self, qv):
         qv = _f64(qv).reshape(self.B, 36)
-        lib().oracle_set_x0(self._h, _p(qv))
+        self.lib.oracle_set_x0(self._h, _p(qv))
 
     def set_x0_full(self, x0):
         x0 = _f64(x0).reshape(self.B, NX)
-        lib().oracle_set_x0_full(self._h, _p(x0))
+        self.lib.oracle_set_x0_full(self._h, _p(x0))
 
     def set_yref(self, yref, yref_e):
         yref = _f64(yref).reshape(self.B, self.N, NY)
         yref_e = _f64(yref_e).reshape(self.B, NYE)
-        lib().oracle_set_yref(self._h, _p(yref), _p(yref_e))
+        self.lib.oracle_set_yref(self._h, _p(yref), _p(yref_e))
 
     def set_weights(self, W, W_e):
         W, W_e = _f64(W), _f64(W_e)
         per = int(W.ndim == 2)
-        lib().oracle_set_weights(self._h, _p(W), _p(W_e), C.c_int32(per))
+        self.lib.oracle_set_weights(self._h, _p(W), _p(W_e), C.c_int32(per))
 
     def set_params(self, p):
         p = _f64(p).reshape(self.B, self.N + 1, NP)
-        lib().oracle_set_params(self._h, _p(p))
+        self.lib.oracle_set_params(self._h, _p(p))
 
     def pin_stance_feet(self, i_node):
         i_node = _i32(np.broadcast_to(i_node, (self.B,)))
-        lib().oracle_pin_stance_feet(self._h, _p(i_node))
+        self.lib.oracle_pin_stance_feet(self._h, _p(i_node))
 
     def set_guess(self, x=None, u=None):
         x = None if x is None else _f64(x).reshape(self.B, self.N + 1, NX)
-        u = None if u is None else _f64(u).reshape(self.B, self.N, NU)
-        lib().oracle_set_guess(self._h, _p(x), _p(u))
+        u = None if u is None else _f64(u).reshape(self.B, self.N, self.NU)
+        self.lib.oracle_set_guess(self._h, _p(x), _p(u))
 
     def reset_duals(self):
-        lib().oracle_reset_duals(self._h)
+        self.lib.oracle_reset_duals(self._h)
 
     def shift_warm_start(self, start_node, repeat_last: bool = False):
         s = _i32(np.broadcast_to(start_node, (self.B,)))
-        lib().oracle_shift_warm_start(self._h, _p(s), C.c_int32(int(repeat_last)))
+        self.lib.oracle_shift_warm_start(self._h, _p(s), C.c_int32(int(repeat_last)))
 
     def solve(self, n_threads: int = 0) -> np.ndarray:
         status = np.zeros(self.B, dtype=np.int32)
-        lib().oracle_solve(self._h, _p(status), C.c_int32(n_threads))
+        self.lib.oracle_solve(self._h, _p(status), C.c_int32(n_threads))
         return status
 
     def get_solution(self):
         B, N = self.B, self.N
-        x, u = np.zeros((B, N + 1, NX)), np.zeros((B, N, NU))
-        pi, lam = np.zeros((B, N, NX)), np.zeros((B, N + 1, 2 * NG))
-        lib().oracle_get_solution(self._h, _p(x), _p(u), _p(pi), _p(lam))
+        x, u = np.zeros((B, N + 1, NX)), np.zeros((B, N, self.NU))
+        pi, lam = np.zeros((B, N, NX)), np.zeros((B, N + 1, 2 * self.NG))
+        self.lib.oracle_get_solution(self._h, _p(x), _p(u), _p(pi), _p(lam))
         return x, u, pi, lam
 
     def get_stats(self) -> dict:
@@ -227,29 +236,29 @@ class OracleSolver:
                    cost=np.zeros(B), qp_ncond=np.zeros(B, np.int32))
         st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost",
                                                       "qp_ncond")])
-        lib().oracle_get_stats(self._h, C.byref(st))
+        self.lib.oracle_get_stats(self._h, C.byref(st))
         return out
 
     def get_qp_step(self) -> np.ndarray:
-        dz = np.zeros((self.B, self.N + 1, NZ))
-        lib().oracle_get_qp_step(self._h, _p(dz))
+        dz = np.zeros((self.B, self.N + 1, self.NZ))
+        self.lib.oracle_get_qp_step(self._h, _p(dz))
         return dz
 
     def export_qp(self) -> dict:
         B, N = self.B, self.N
-        out = dict(BAbt=np.zeros((B, N, NZ + 1, NX)), RSQrq=np.zeros((B, N + 1, NZ + 1, NZ)),
-                   DCt=np.zeros((B, N + 1, NZ, NG)), lg=np.zeros((B, N + 1, NG)),
-                   ug=np.zeros((B, N + 1, NG)), mask=np.zeros((B, N + 1, 2 * NG)))
-        lib().oracle_export_qp(self._h, *[_p(out[k]) for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")])
+        out = dict(BAbt=np.zeros((B, N, self.NZ + 1, NX)), RSQrq=np.zeros((B, N + 1, self.NZ + 1, self.NZ)),
+                   DCt=np.zeros((B, N + 1, self.NZ, self.NG)), lg=np.zeros((B, N + 1, self.NG)),
+                   ug=np.zeros((B, N + 1, self.NG)), mask=np.zeros((B, N + 1, 2 * self.NG)))
+        self.lib.oracle_export_qp(self._h, *[_p(out[k]) for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")])
         return out
 
     def solve_qp(self, qp: dict, dx0: np.ndarray) -> dict:
         B, N = self.B, self.N
         dx0 = _f64(dx0).reshape(B, NX)
-        out = dict(dz=np.zeros((B, N + 1, NZ)), pi=np.zeros((B, N, NX)), lam=np.zeros((B, N + 1, 2 * NG)),
-                   t=np.zeros((B, N + 1, 2 * NG)), qp_iter=np.zeros(B, np.int32),
+        out = dict(dz=np.zeros((B, N + 1, self.NZ)), pi=np.zeros((B, N, NX)), lam=np.zeros((B, N + 1, 2 * self.NG)),
+                   t=np.zeros((B, N + 1, 2 * self.NG)), qp_iter=np.zeros(B, np.int32),
                    qp_status=np.zeros(B, np.int32), qp_res=np.zeros((B, 4)))
         args = [_p(_f64(qp[k])) for k in ("BAbt", "RSQrq", "DCt", "lg", "ug", "mask")]
-        lib().oracle_solve_qp(self._h, *args, _p(dx0),
+        self.lib.oracle_solve_qp(self._h, *args, _p(dx0),
                               *[_p(out[k]) for k in ("dz", "pi", "lam", "t", "qp_iter", "qp_status", "qp_res")])
         return out

@@ -434,3 +434,72 @@ def test_device_init_argument_errors():
     with pytest.raises(ValueError):              # restriction without a contact plan (solver.py:377)
         s.init_tick(np.zeros((2, 12)), joint_ref=np.zeros(12), cnt_sequence=np.ones((2, 4, N + 1)),
                     p_gain=np.zeros(4), restrict_cnt=True)
+
+
+def _split_topt(uo, lo):
+    """The oracle's time-opt build carries dt as the 31st input column and its two bounds as constraint row 42:
+    (u [.., 30], dt [..], lam [.., 84], lam_dt [.., 2]) in the product's layout."""
+    u, dt = uo[..., :30], uo[..., 30]
+    lam = np.concatenate([lo[..., :42], lo[..., 43:85]], axis=-1)
+    lam_dt = np.stack([lo[..., 42], lo[..., 85]], axis=-1)[:, :-1]
+    return u, dt, lam, lam_dt
+
+
+@pytest.mark.parametrize("cap", [1, 2, 3, 6])
+def test_time_opt_rti_parity_per_qp_iteration(oracle_mod, cap):
+    """enable_time_opt (nu = 31: node durations dt_k with the weight `time_opt`, bounds [dt_min, dt_max]; solver.py:43-44,
+    124-125, 166-167, 189-190; BASELINE config 4): one SQP_RTI step whose QP is cut after `cap` IPM iterations, so the
+    primal/dual QP iterate after 1, 2, 3, 6 iterations is compared through the full step -- x, u, the dt column with
+    its two bound multipliers, pi, lam -- against the oracle's dense nu = 31 build (the product eliminates dt from
+    every stage first: P~ = P+ - (P+ b)(P+ b)' / d)."""
+    O = oracle_mod
+    B = 12
+    so, sg, _ = _pair(O, B, seed=11, real_time_it=1, max_qp_iter=cap, qp_tol=1e-9, enable_time_opt=1)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    so_s, sg_s = so.get_stats(), sg.get_stats()
+    np.testing.assert_array_equal(sg_s["qp_iter"], so_s["qp_iter"])
+    np.testing.assert_array_equal(sg_s["qp_status"], so_s["qp_status"])
+    xo, uo, pio, lo = so.get_solution()
+    xg, ug, pig, lg = sg.get_solution()
+    dtg, ltg = sg.get_dt(duals=True)
+    uo30, dto, lo84, lto = _split_topt(uo, lo)
+    assert np.abs(dto - 0.04).max() > 1e-4          # the node durations did move
+    for name, a, b in (("x", xg, xo), ("u", ug, uo30), ("dt - dt_nodes", dtg - 0.04, dto - 0.04), ("pi", pig, pio),
+                       ("lam", lg, lo84), ("lam_dt", ltg, lto)):
+        assert report(f"time-opt cap{cap} {name}", a, b) < REL, name
+    assert report("time-opt qp_res", sg_s["qp_res"], so_s["qp_res"]) < 1e-5
+
+
+def test_time_opt_sqp_and_warm_start_parity(oracle_mod):
+    """Time optimisation through three SQP iterations with hot-started QPs, then the shift warm start (dt of the
+    warm-started nodes shifted, nominal on the tail: solver.py:324-336) and a second solve."""
+    O = oracle_mod
+    B = 8
+    opts = dict(real_time_it=0, max_iter=3, max_qp_iter=6, warm_start_qp=2, enable_time_opt=1)
+    so, sg, _ = _pair(O, B, seed=12, **opts)
+    for tick in range(2):
+        st_o, st_g = so.solve(0), sg.solve()
+        np.testing.assert_array_equal(st_g, st_o)
+        xo, uo, pio, lo = so.get_solution()
+        xg, ug, pig, lg = sg.get_solution()
+        dtg, ltg = sg.get_dt(duals=True)
+        uo30, dto, lo84, lto = _split_topt(uo, lo)
+        for name, a, b in (("x", xg, xo), ("u", ug, uo30), ("dt", dtg, dto), ("pi", pig, pio), ("lam", lg, lo84),
+                           ("lam_dt", ltg, lto)):
+            assert chain_ok(f"time-opt tick{tick} {name}", a, b, REL), name
+        so.shift_warm_start(3)
+        sg.shift_warm_start(3)
+        xo, uo, _, lo = so.get_solution()
+        dtg, ltg = sg.get_dt(duals=True)
+        _, dto, _, lto = _split_topt(uo, lo)
+        # the shifted arrays are copies of values compared above (a sub-block has a smaller norm: same absolute error)
+        assert chain_ok(f"time-opt shifted dt tick{tick}", dtg, dto, 10 * REL)
+        assert chain_ok(f"time-opt shifted lam_dt tick{tick}", ltg, lto, 10 * REL)
+        assert np.abs(dtg[:, -3:] - 0.04).max() == 0.0
+
+
+def test_time_opt_off_reports_nominal_dt():
+    NmpcSolver, default_opts = _gpu()
+    s = NmpcSolver(2, default_opts(real_time_it=1))
+    assert np.abs(s.get_dt() - 0.04).max() == 0.0
