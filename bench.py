@@ -77,7 +77,10 @@ def workload_opts(cfg: int, qp_warm: int):
         return dict(base, real_time_it=1, max_iter=1), ("trot",)
     if cfg == 3:
         return dict(base, real_time_it=0, max_iter=15), ("trot", "pace", "bound")
-    if cfg in (4, 5):     # default mpc_opt.py: SQP (not RTI), max_iter = 1 per replanning tick (mpc_opt.py:26-38)
+    if cfg == 4:          # + enable_time_opt: nu = 31, dt in [0.02, 0.07] (opt_dt_scale = (0.5, 1.75)), weight time_opt = 1e4
+        return dict(base, real_time_it=0, max_iter=1, enable_time_opt=1, dt_min=0.02, dt_max=0.07,
+                    time_opt_weight=1e4), ("trot",)
+    if cfg == 5:          # default mpc_opt.py: SQP (not RTI), max_iter = 1 per replanning tick (mpc_opt.py:26-38)
         return dict(base, real_time_it=0, max_iter=1), ("trot",)
     raise SystemExit("--config must be 1, 2, 3, 4 or 5")
 
@@ -97,7 +100,7 @@ def workload_name(cfg: int, B: int, qp_warm: int) -> str:
     if cfg == 3:
         return f"config3: Go2 trot/pace/bound mixed, {B} OCPs per GPU, full SQP max_iter=15 nlp_tol=1e-1" + tail
     if cfg == 4:
-        return (f"config4 (without enable_time_opt, which is not built): Go2 trot, {B} OCPs per GPU, "
+        return (f"config4: Go2 trot, {B} OCPs per GPU, enable_time_opt (nu=31, dt in [0.02, 0.07]), "
                 "cnt_patch_restriction with Raibert footholds + opt_peak, SQP max_iter=1" + tail)
     return f"config5: DAgger sweep tick, Go2 trot, {B} push-perturbed OCPs per GPU, SQP max_iter=1" + tail
 
@@ -159,7 +162,8 @@ def time_cpu_oracle(batch, opts: dict, n_problems: int, threads: int, repeats: i
            for k, v in batch.items()}
     _, _, hg = O.kinematics(sub["qv"])
     s = O.OracleSolver(n, O.default_opts(**opts))
-    s.set_fast(True)          # structured variant (oracle/nmpc_oracle_fast.h): 3x the dense restatement, same iterates
+    if not opts.get("enable_time_opt"):
+        s.set_fast(True)      # structured variant (oracle/nmpc_oracle_fast.h): 3x the dense restatement, same iterates
     from iterative_learning_nmpc_b200 import workloads as WL
     dt = 0.0
     for _ in range(repeats):                   # identical work every repeat, like the GPU steps

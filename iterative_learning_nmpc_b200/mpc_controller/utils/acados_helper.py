@@ -155,6 +155,11 @@ class AcadosSolverHelper:
         self.params = {v.name: np.zeros(ld + (v.dim, N + 1)) for v in problem.params.values()}
         self.cost_ref = {v.name: np.zeros(ld + (v.dim, N)) for v in problem.costs.values()}
         self.cost_ref_terminal = {v.name: np.zeros(ld + (v.dim,)) for v in problem.terminal_costs.values()}
+        if problem.enable_time_opt:
+            # the node duration: a 31st input "dt" with its own cost weight and reference (solver.py:124-125,
+            # 166-167, 189-190).  It lives beside the packed 30-wide input block: nmpc_set_dt / nmpc_get_dt.
+            self.inputs["dt"] = np.full(ld + (1, N), problem.dt)
+            self.cost_ref["dt"] = np.full(ld + (1, N), problem.dt)
         self._W = np.zeros(ld + (L.NY,))
         self._We = np.zeros(ld + (L.NYE,))
         self.status = np.zeros(self.batch, dtype=np.int32)
@@ -214,7 +219,8 @@ class AcadosSolverHelper:
         return {
             "x": {v.name: np.zeros(ld + (v.dim,)) for v in self.problem.states.values()},
             "u": {v.name: np.zeros(ld + (v.dim,)) for v in self.problem.inputs.values()},
-            "W": {v.name: np.zeros(ld + (v.dim,)) for v in self.problem.costs.values()},
+            "W": dict({v.name: np.zeros(ld + (v.dim,)) for v in self.problem.costs.values()},
+                      **({"dt": np.zeros(ld + (1,))} if self.problem.enable_time_opt else {})),
             "W_e": {v.name: np.zeros(ld + (v.dim,)) for v in self.problem.terminal_costs.values()},
         }
 
@@ -227,6 +233,11 @@ class AcadosSolverHelper:
 
     def set_cost_weight_constant(self, W: Dict[str, np.ndarray]):
         self._pack_vec(W, self.problem.costs, self._W, terminal=False)
+        if self.problem.enable_time_opt and "dt" in W:
+            w = np.unique(np.asarray(W["dt"], dtype=float))
+            if w.size != 1:
+                raise NotImplementedError("one time_opt weight per batch handle")
+            self._set_opt(time_opt_weight=float(w[0]))
 
     def set_cost_weight_terminal(self, W_e: Dict[str, np.ndarray]):
         self._pack_vec(W_e, self.problem.terminal_costs, self._We, terminal=True)
@@ -256,6 +267,8 @@ class AcadosSolverHelper:
 
     def update_inputs(self):
         self.handle.set_guess(u=self._pack_nodes(self.inputs, self.problem.inputs, L.NU, self.n_nodes))
+        if self.problem.enable_time_opt:
+            self.handle.set_dt(np.asarray(self.inputs["dt"], dtype=float).reshape(self.batch, self.n_nodes))
 
     def update_parameters(self):
         self.handle.set_params(self._pack_nodes(self.params, self.problem.params, L.NP, self.n_nodes + 1))
@@ -309,6 +322,8 @@ class AcadosSolverHelper:
         for var in self.problem.inputs.values():
             blk = u[:, :, var.offset:var.offset + var.dim]
             self.inputs[var.name] = np.ascontiguousarray(np.moveaxis(blk, 1, 2)).reshape(ld + (var.dim, self.n_nodes))
+        if self.problem.enable_time_opt:
+            self.inputs["dt"] = self.handle.get_dt().reshape(ld + (1, self.n_nodes))
 
     def get_stats(self) -> dict:
         return self.handle.get_stats()

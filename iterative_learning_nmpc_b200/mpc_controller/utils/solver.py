@@ -117,6 +117,8 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
                 w_pos[:2] = c.W_foot_displacement[0]
             W[foot.pos_cost.name] = w_pos
             We[foot.pos_cost.name] = w_pos.copy()
+        if self.enable_time_opt:                 # solver.py:124-125
+            W["dt"] = np.array(c.time_opt)
         self.set_cost_weight_constant(W)
         self.set_cost_weight_terminal(We)
 
@@ -145,6 +147,8 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
         self.cost_ref_terminal[d.swing_cost.name][:] = np.reshape(sh, ld + (1,))
         self.cost_ref[d.joint_cost.name] = self._col(joint_ref_vel, 24)
         self.cost_ref_terminal[d.joint_cost.name] = joint_ref_vel.copy()
+        if self.enable_time_opt:                 # solver.py:166-167 (the kernel's reference for dt is dt_nodes)
+            self.cost_ref["dt"][:] = self.dt_nodes
 
     def setup_initial_state(self, q_euler: np.ndarray, v_global: np.ndarray, h: Optional[np.ndarray] = None):
         """solver.py:179-192; h defaults to the momentum of the last `dyn.update_pin` (unbatched) or
@@ -159,6 +163,8 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
         self.data["x"][d.q.name] = q_euler
         self.data["x"][d.v.name] = v_global
         self.data["x"][d.h.name] = np.asarray(h, dtype=float)
+        if self.enable_time_opt and not self._has_solution:      # solver.py:189-190
+            self.inputs["dt"][:] = self.dt_nodes
         self.set_initial_state(self.data["x"])
 
     def init_contacts_parameters(self):
@@ -263,6 +269,9 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
             f = U[foot.f.name]
             f[:, :n_ws] = self.f_sol[start_node:, i, :].T
             f[:, n_ws:] = self.f_sol[-1, i][:, None] if repeat_last else 0.
+        if self.enable_time_opt:                 # solver.py:324-336: shifted node durations, nominal on the tail
+            U["dt"][:, :n_ws] = self.dt_node_sol[start_node:]
+            U["dt"][:, n_ws:] = self.dt_nodes
         if repeat_last and n_ws < N:
             S[d.q.name][:, n_ws:] = self.q_sol_euler[-1][:, None]
             S[d.v.name][:, n_ws:] = self.v_sol_euler[-1][:, None]
@@ -327,7 +336,10 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
         self.h_sol[:] = T(self.states[d.h.name])
         self.a_sol[:] = T(self.inputs[d.a.name])
         self.f_sol[:] = np.stack([T(self.inputs[foot.f.name]) for foot in d.feet], axis=-2)
-        self.dt_node_sol[:] = self.dt_nodes
+        if self.enable_time_opt:                 # solver.py:423-427
+            self.dt_node_sol[:] = self.inputs["dt"].reshape(self.dt_node_sol.shape)
+        else:
+            self.dt_node_sol[:] = self.dt_nodes
         self._has_solution = True
         return self.q_sol_euler, self.v_sol_euler, self.a_sol, self.f_sol, self.dt_node_sol
 

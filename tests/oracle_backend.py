@@ -41,7 +41,33 @@ class OracleHandle:
         return self._s.solve(1)
 
     def get_solution(self, duals=True):
-        return self._s.get_solution()
+        x, u, pi, lam = self._s.get_solution()
+        if self._s.topt:          # product layout: 30 inputs, 42 constraint rows; dt and its bounds through get_dt
+            u = np.ascontiguousarray(u[..., :30])
+            lam = np.concatenate([lam[..., :42], lam[..., 43:85]], axis=-1)
+        return x, u, pi, lam
+
+    def get_dt(self, duals=False):
+        if not self._s.topt:
+            dt = np.full((self.B, self.N), float(self.opts.dt_nodes))
+            return (dt, np.zeros((self.B, self.N, 2))) if duals else dt
+        _, u, _, lam = self._s.get_solution()
+        dt = np.ascontiguousarray(u[..., 30])
+        return (dt, np.stack([lam[:, :-1, 42], lam[:, :-1, 85]], axis=-1)) if duals else dt
+
+    def set_dt(self, dt=None):
+        if not self._s.topt:
+            return
+        _, u, _, _ = self._s.get_solution()
+        u[..., 30] = float(self.opts.dt_nodes) if dt is None else np.asarray(dt, float).reshape(self.B, self.N)
+        self._s.set_guess(None, u)
+
+    def set_guess(self, x=None, u=None):
+        if u is not None and self._s.topt:
+            u = np.asarray(u, float).reshape(self.B, self.N, -1)
+            if u.shape[-1] == 30:         # a new 30-wide input guess restarts the node durations at dt_nodes
+                u = np.concatenate([u, np.full((self.B, self.N, 1), float(self.opts.dt_nodes))], axis=-1)
+        self._s.set_guess(x, u)
 
     def kinematics(self, qv):
         return O.kinematics(qv)

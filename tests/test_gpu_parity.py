@@ -341,8 +341,9 @@ def test_device_pointers_are_accepted(oracle_mod):
 
 @pytest.mark.parametrize("cfg", ["config4_restricted_contacts", "config5_push"])
 def test_config4_and_5_workloads_parity(oracle_mod, cfg):
-    """BASELINE configs 4 (contact-patch restriction with Raibert footholds + opt_peak; without time
-    optimisation) and 5 (push-perturbed DAgger tick): default mpc_opt.py options, SQP with max_iter = 1."""
+    """BASELINE configs 4 (contact-patch restriction with Raibert footholds + opt_peak; the dense QP blocks are
+    compared without time optimisation, the nu = 31 solve follows in test_config4_as_written) and 5 (push-perturbed
+    DAgger tick): default mpc_opt.py options, SQP with max_iter = 1."""
     O = oracle_mod
     wl = dict(restrict_cnt=True, kin=O.kinematics) if cfg.startswith("config4") else dict(push=True)
     so, sg, batch = _pair(O, 48, seed=11, workload=wl, real_time_it=0, max_iter=1, warm_start_qp=0)
@@ -503,3 +504,26 @@ def test_time_opt_off_reports_nominal_dt():
     NmpcSolver, default_opts = _gpu()
     s = NmpcSolver(2, default_opts(real_time_it=1))
     assert np.abs(s.get_dt() - 0.04).max() == 0.0
+
+
+def test_config4_as_written(oracle_mod):
+    """BASELINE config 4 as written: enable_time_opt (nu = 31, dt in [0.02, 0.07]), contact-patch restriction with
+    Raibert footholds, opt_peak, default mpc_opt.py options (SQP, max_iter = 1, max_qp_iter = 6)."""
+    O = oracle_mod
+    B = 32
+    wl = dict(restrict_cnt=True, kin=O.kinematics)
+    so, sg, batch = _pair(O, B, seed=13, workload=wl, real_time_it=0, max_iter=1, enable_time_opt=1, dt_min=0.02,
+                          dt_max=0.07, time_opt_weight=1e4)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    xo, uo, pio, lo = so.get_solution()
+    xg, ug, pig, lg = sg.get_solution()
+    dtg, ltg = sg.get_dt(duals=True)
+    uo30, dto, lo84, lto = _split_topt(uo, lo)
+    for name, a, b in (("x", xg, xo), ("u", ug, uo30), ("dt", dtg, dto), ("pi", pig, pio), ("lam", lg, lo84),
+                       ("lam_dt", ltg, lto)):
+        assert report(f"config4 {name}", a, b) < REL, name
+    so_s, sg_s = so.get_stats(), sg.get_stats()
+    for k in ("sqp_iter", "qp_iter", "qp_status"):
+        np.testing.assert_array_equal(sg_s[k], so_s[k])
+    assert report("config4 nlp residuals", sg_s["res"], so_s["res"]) < 1e-6

@@ -150,3 +150,46 @@ def test_structured_variant_reproduces_dense_restatement(oracle_mod):
     assert st0["qp_ncond"].sum() > 0
     for name, a, b in zip(("x", "u", "pi", "lam"), sol1, sol0):
         assert chain_ok("fast vs dense " + name, a, b, 1e-6)
+
+
+def test_time_opt_build_tends_to_the_fixed_dt_solution_with_the_weight(oracle_mod):
+    """The oracle's enable_time_opt build (nu = 31: dt_k a 31st input, weight on dt - dt_nodes, bounds) against the
+    default build: as the weight grows the node durations are pinned to dt_nodes and the converged QP solution tends
+    to the fixed-dt one, linearly in 1 / weight."""
+    O = oracle_mod
+    B = 4
+    batch = WL.make_batch(B, seed=3)
+    hg = O.kinematics(batch["qv"])[2]
+    base = O.OracleSolver(B, O.default_opts(real_time_it=1, max_qp_iter=40, qp_tol=1e-5))
+    WL.load_into(base, batch, hg)
+    assert (base.solve(0) == 0).all() and (base.get_stats()["qp_status"] == 0).all()
+    x0, u0, _, _ = base.get_solution()
+    dev = []
+    for w in (1e8, 1e10):
+        s = O.OracleSolver(B, O.default_opts(real_time_it=1, enable_time_opt=1, max_qp_iter=40, qp_tol=1e-5,
+                                             time_opt_weight=w))
+        WL.load_into(s, batch, hg)
+        assert (s.solve(0) == 0).all() and (s.get_stats()["qp_status"] == 0).all()
+        x, u, _, _ = s.get_solution()
+        dev.append((np.abs(x - x0).max(), np.abs(u[..., :30] - u0).max(), np.abs(u[..., 30] - 0.04).max()))
+    assert dev[1][0] < 1e-3 and dev[1][2] < 1e-5
+    for a, b in zip(dev[0], dev[1]):
+        assert 50 < a / b < 200                      # 1 / weight
+
+
+def test_time_opt_converged_qp_respects_the_dt_bounds_and_is_a_kkt_point(oracle_mod):
+    O = oracle_mod
+    B = 4
+    batch = WL.make_batch(B, seed=3)
+    hg = O.kinematics(batch["qv"])[2]
+    s = O.OracleSolver(B, O.default_opts(real_time_it=1, enable_time_opt=1, max_qp_iter=60, qp_tol=1e-5))
+    WL.load_into(s, batch, hg)
+    assert (s.solve(0) == 0).all()
+    st = s.get_stats()
+    assert (st["qp_status"] == 0).all() and (st["qp_res"] < 1e-5).all()
+    _, u, _, lam = s.get_solution()
+    dt = u[..., 30]
+    assert dt.min() >= 0.02 - 1e-6 and dt.max() <= 0.07 + 1e-6 and np.ptp(dt) > 1e-3
+    # complementarity of the two dt bounds at the QP solution
+    lo, up = lam[:, :-1, 42], lam[:, :-1, 85]
+    assert np.abs(lo * (dt - 0.02)).max() < 1e-4 and np.abs(up * (0.07 - dt)).max() < 1e-4
