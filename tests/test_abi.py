@@ -39,8 +39,9 @@ def test_binding_table_covers_header():
 
 def test_opts_struct_layout_matches_header():
     from iterative_learning_nmpc_b200._lib import NmpcOpts
-    # 10 x int32 followed by 8 x double, no padding
-    assert C.sizeof(NmpcOpts) == 10 * 4 + 8 * 8
+    # 10 x int32 followed by 9 x double, no padding
+    assert C.sizeof(NmpcOpts) == 10 * 4 + 9 * 8
+    assert NmpcOpts.time_opt_weight.offset == 40 + 8 * 8
     assert NmpcOpts.warm_start_first_qp.offset == 32 and NmpcOpts.cond_pred_corr.offset == 36
     assert NmpcOpts.dt_nodes.offset == 40 and NmpcOpts.mu_contact.offset == 40 + 7 * 8
 
@@ -50,8 +51,8 @@ def test_version_and_argument_errors(lib):
     err = C.c_int32(0)
     assert not lib.nmpc_create(None, 1, 0, C.byref(err)) and err.value == -1       # EINVAL
     from iterative_learning_nmpc_b200._lib import default_opts
-    o = default_opts(enable_time_opt=1)
-    assert not lib.nmpc_create(C.byref(o), 1, 0, C.byref(err)) and err.value == -2  # ENOSYS
+    o = default_opts(enable_time_opt=1, dt_min=0.05, dt_max=0.03)                  # inconsistent dt bounds
+    assert not lib.nmpc_create(C.byref(o), 1, 0, C.byref(err)) and err.value == -1  # EINVAL
     assert lib.nmpc_solve(None, None) == -1
     assert lib.nmpc_launch_count(None) == 0
 
