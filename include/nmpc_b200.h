@@ -148,6 +148,15 @@ int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const double* base_re
                    int32_t joint_per_problem, const double* step_height, int32_t height_per_problem,
                    const int8_t* cnt_sequence, const int8_t* swing_peak, const double* cnt_locations,
                    const double* p_gain, double cnt_radius, double height_offset, int32_t restrict_cnt);
+/* The planning step of LocomotionMPC.optimize followed by QuadrupedAcadosSolver.init, on the device, for the cyclic
+ * contact planner: GaitPlanner.get_contacts / get_peaks (contact_planner.py:121-149: the window
+ * of the gait cycle at i_node[b]; gait_seq / peak_seq int8 [4, nodes_per_cycle]) and compute_base_ref_vel_tracking
+ * (mpc.py:210-272: q [B,18] Euler state, v_des [B,3], w_yaw [B], tracking [B,12] = base_ref_vel_tracking), then the
+ * expansion of nmpc_init_tick without contact restriction.  0.3 KB per problem cross PCIe. */
+int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq, const int8_t* peak_seq,
+                   int32_t nodes_per_cycle, const double* q, const double* v_des, const double* w_yaw,
+                   const double* tracking, double nom_height, double height_offset, double t_horizon,
+                   const double* joint_ref, double step_height, const double* p_gain, int32_t opt_peak);
 /* cold first guess of the batched front-end: x0 held over the horizon, zero accelerations, the robot's
  * weight shared by the stance feet of every node (from x0 and p on the device) */
 int nmpc_cold_guess(nmpc_handle* h);

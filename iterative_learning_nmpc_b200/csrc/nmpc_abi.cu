@@ -319,6 +319,64 @@ extern "C" int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const doub
     return (int)cudaGetLastError();
 }
 
+// LocomotionMPC.optimize's planning step + QuadrupedAcadosSolver.init on the device for the cyclic contact planner
+// (nmpc_init.cuh): contact / swing windows of the gait cycle at i_node, base references from q, the command and the
+// tracked pose, then the expansion of nmpc_init_tick.  Every array may be a host or a device pointer.
+extern "C" int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq, const int8_t* peak_seq,
+                              int32_t nodes_per_cycle, const double* q, const double* v_des, const double* w_yaw,
+                              const double* tracking, double nom_height, double height_offset, double t_horizon,
+                              const double* joint_ref, double step_height, const double* p_gain, int32_t opt_peak)
+{
+    if (!h || !i_node || !gait_seq || !peak_seq || nodes_per_cycle < 1 || !q || !v_des || !w_yaw || !tracking ||
+        !joint_ref || !p_gain) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B, N1 = h->N + 1, npc = nodes_per_cycle;
+    const size_t n_cnt = B * NF * N1, cnt_pad = (n_cnt + 7) & ~(size_t)7, seq_pad = (NF * npc + 7) & ~(size_t)7;
+    // doubles: q 18 | v_des 3 | w 1 | tracking 12 | ref 12 | ref_e 12 per problem, joint_ref 12, step height 1
+    const size_t n_d = B * 58 + 13;
+    const size_t bytes = n_d * 8 + ((B * 4 + 7) & ~(size_t)7) + 2 * seq_pad + 2 * cnt_pad;
+    if (int r = ensure_scratch(h, bytes)) return r;
+    double* d_q = h->scratch;
+    double* d_vd = d_q + B * 18;
+    double* d_w = d_vd + B * 3;
+    double* d_tr = d_w + B;
+    double* d_ref = d_tr + B * 12;
+    double* d_ref_e = d_ref + B * 12;
+    double* d_jr = d_ref_e + B * 12;
+    double* d_sh = d_jr + 12;
+    int32_t* d_node = reinterpret_cast<int32_t*>(d_sh + 1);
+    signed char* d_gs = reinterpret_cast<signed char*>(d_node) + ((B * 4 + 7) & ~(size_t)7);
+    signed char* d_ps = d_gs + seq_pad;
+    signed char* d_cnt = d_ps + seq_pad;
+    signed char* d_peak = d_cnt + cnt_pad;
+    CK(cudaMemcpyAsync(d_q, q, B * 18 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_vd, v_des, B * 3 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_w, w_yaw, B * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_tr, tracking, B * 12 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_jr, joint_ref, 12 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_sh, &step_height, 8, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_node, i_node, B * 4, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_gs, gait_seq, NF * npc, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_ps, peak_seq, NF * npc, cudaMemcpyDefault, h->stream));
+    PlannerArgs pa;
+    pa.i_node = d_node; pa.gait_seq = d_gs; pa.peak_seq = d_ps; pa.q = d_q; pa.v_des = d_vd; pa.w_yaw = d_w;
+    pa.tracking = d_tr; pa.nom_height = nom_height; pa.height_offset = height_offset; pa.t_horizon = t_horizon;
+    pa.npc = nodes_per_cycle; pa.N = h->N; pa.B = h->B;
+    pa.base_ref = d_ref; pa.base_ref_e = d_ref_e; pa.cnt = d_cnt; pa.peak = d_peak;
+    nmpc_plan_refs_kernel<<<h->B, 128, 0, h->stream>>>(pa);
+    TickArgs a;
+    a.base_ref = d_ref; a.base_ref_e = d_ref_e; a.joint_ref = d_jr; a.step_height = d_sh;
+    a.cnt = d_cnt; a.peak = opt_peak ? d_peak : nullptr; a.loc = nullptr;
+    for (int f = 0; f < NF; f++) a.p_gain[f] = p_gain[f];
+    a.radius = 0.0; a.height_offset = height_offset; a.restrict_cnt = 0;
+    a.joint_per_problem = 0; a.height_per_problem = 0;
+    a.p = h->p; a.yref = h->yref; a.yref_e = h->yref_e; a.B = h->B; a.N = h->N;
+    nmpc_init_tick_kernel<<<h->B, 128, 0, h->stream>>>(a);
+    h->launches += 2;
+    return (int)cudaGetLastError();
+}
+
 // cold first guess from x0 and the contact mask already on the device (call after nmpc_set_x0 and nmpc_init_tick / nmpc_set_params)
 extern "C" int nmpc_cold_guess(nmpc_handle* h)
 {

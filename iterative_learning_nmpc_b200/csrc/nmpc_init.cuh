@@ -112,3 +112,85 @@ __global__ void __launch_bounds__(128) nmpc_cold_guess_kernel(int N, const doubl
         ub[e] = v;
     }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Planning on the device: what LocomotionMPC.optimize computes on the host before `init`
+// for the cyclic contact planner --
+//   GaitPlanner.get_contacts / get_peaks   contact_planner.py:121-149   window of the gait cycle at i_node
+//   compute_base_ref_vel_tracking          mpc.py:210-272               base references from q, v_des, w_yaw
+// -- into the compact arrays nmpc_init_tick_kernel expands.  One CTA per OCP.
+// ---------------------------------------------------------------------------------------------
+struct PlannerArgs {
+    const int32_t* i_node;           // [B] optimisation node of every problem
+    const signed char* gait_seq;     // [4][npc] stance mask of one gait cycle
+    const signed char* peak_seq;     // [4][npc] swing mask of one gait cycle
+    const double* q;                 // [B][18] Euler state
+    const double* v_des;             // [B][3]  velocity command, base frame
+    const double* w_yaw;             // [B]
+    const double* tracking;          // [B][12] integrated reference pose (base_ref_vel_tracking)
+    double nom_height, height_offset, t_horizon;
+    int npc, N, B;
+    double* base_ref; double* base_ref_e;       // [B][12]
+    signed char* cnt; signed char* peak;        // [B][4][N+1]
+};
+
+// numpy.round(x, d) = rint(x * 10^d) / 10^d; Python's round(x, 1) is the correctly rounded decimal, which differs
+// from that when the product x * 10 rounds onto a tie: the fused multiply-add recovers the exact product
+__device__ __forceinline__ double np_round(double x, double p10) { return rint(x * p10) / p10; }
+__device__ __forceinline__ double py_round1(double x)
+{
+    const double p = x * 10.0, err = fma(x, 10.0, -p);
+    double r = rint(p);
+    if (fabs(p - trunc(p)) == 0.5 && err != 0.0) r = (err > 0.0) ? ceil(p) : floor(p);
+    return r / 10.0;
+}
+__device__ __forceinline__ double clip(double v, double lo, double hi) { return fmin(fmax(v, lo), hi); }
+
+__global__ void __launch_bounds__(128) nmpc_plan_refs_kernel(PlannerArgs a)
+{
+    const int b = blockIdx.x, tid = threadIdx.x, N1 = a.N + 1;
+    const int node = a.i_node[b];
+    for (int e = tid; e < NF * N1; e += 128) {
+        const int f = e / N1, j = e % N1;
+        const int idx = (node % a.npc + j) % a.npc;
+        a.cnt[(size_t)b * NF * N1 + e] = a.gait_seq[f * a.npc + idx];
+        a.peak[(size_t)b * NF * N1 + e] = a.peak_seq[f * a.npc + idx];
+    }
+    if (tid != 127) return;
+    const double* q = a.q + (size_t)b * 18;
+    const double* tr = a.tracking + (size_t)b * 12;
+    const double* vd = a.v_des + (size_t)b * 3;
+    const double wz = a.w_yaw[b], th = a.t_horizon;
+    double r[12], e[12];
+    for (int i = 0; i < 12; i++) r[i] = 0.0;
+    r[0] = np_round(q[0], 100.0); r[1] = np_round(q[1], 100.0);
+    r[2] = a.nom_height + a.height_offset;
+    r[3] = py_round1(q[3]);
+    // R_WB = rpyToMatrix(roll, pitch, yaw) of the tracked pose (stored yaw, pitch, roll)
+    {
+        const double y = tr[3], p = tr[4], ro = tr[5];
+        const double cr = cos(ro), sr = sin(ro), cp = cos(p), sp = sin(p), cy = cos(y), sy = sin(y);
+        const double R[3][3] = {{cy * cp, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr},
+                                {sy * cp, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr},
+                                {-sp, cp * sr, cp * cr}};
+        for (int i = 0; i < 3; i++) r[6 + i] = np_round((R[i][0] * vd[0] + R[i][1] * vd[1]) + R[i][2] * vd[2], 10.0);
+    }
+    r[9] = wz; r[10] = 0.0; r[11] = 0.0;             // w_des[::-1] with w_des = (0, 0, w_yaw)
+    for (int i = 0; i < 12; i++) e[i] = r[i];
+    {   // velocity at the end of the horizon: rpyToMatrix(w_des * t_horizon) = Rz(w_yaw t)
+        const double cy = cos(wz * th), sy = sin(wz * th);
+        e[6] = (cy * r[6] + -sy * r[7]) + 0.0 * r[8];
+        e[7] = (sy * r[6] + cy * r[7]) + 0.0 * r[8];
+        e[8] = (-0.0 * r[6] + 0.0 * r[7]) + 1.0 * r[8];
+    }
+    for (int i = 0; i < 2; i++) {
+        e[i] = tr[i] + r[6 + i] * th;
+        e[i] = clip(e[i], -r[i] + r[6 + i] * th * 1.2, r[i] + r[6 + i] * th * 1.2);
+    }
+    e[3] = tr[3] + wz * th;
+    e[3] = clip(e[3], -tr[3] + wz * th * 1.5, tr[3] + wz * th * 1.5);
+    r[0] += (e[0] - r[0]) * 0.75; r[1] += (e[1] - r[1]) * 0.75;
+    r[3] += (e[3] - r[3]) * 0.75;
+    e[8] = 0.0; e[4] = 0.0; e[5] = 0.0; r[4] = 0.0; r[5] = 0.0; e[10] = 0.0; e[11] = 0.0;
+    for (int i = 0; i < 12; i++) { a.base_ref[(size_t)b * 12 + i] = r[i]; a.base_ref_e[(size_t)b * 12 + i] = e[i]; }
+}

@@ -363,6 +363,8 @@ class BatchedLocomotionMPC:
         nu = 12
         self.joint_ref = np.zeros(nu) if joint_ref is None else np.asarray(joint_ref, dtype=float)[-nu:]
         self.Kp, self.Kd = self.config_opt.Kp, self.config_opt.Kd
+        self.plan_on_device = True           # False: the host planners + the reference's `init` sequence (same results)
+        self.unpack_solution = False         # device planning: keep the solution resident, do not copy 15 KB per rollout back
         self.reset(reset_solver=False)
 
     def reset(self, reset_solver: bool = True, i_node0=0) -> None:
@@ -380,12 +382,20 @@ class BatchedLocomotionMPC:
 
     def _advance_reference(self, n_steps: int) -> None:
         """`increment_base_ref_position` (mpc.py:204-208), one sim step at a time, for every rollout."""
-        for _ in range(n_steps):
-            for b in range(self.B):
-                R_WB = rpy_to_matrix(self.base_ref_vel_tracking[b, 3:6][::-1])
-                v = np.round(R_WB @ self.v_des[b], 1)
-                self.base_ref_vel_tracking[b, :2] += v[:2] * self.sim_dt
-                self.base_ref_vel_tracking[b, 3] += self.w_yaw[b] * self.sim_dt
+        from ..problem import matvec3, rpy_to_matrix_batch
+        if n_steps <= 0:
+            return
+        tr = self.base_ref_vel_tracking
+        # Vectorised over the rollouts AND over the sim steps: the yaw of step j is the running sum
+        # yaw + w dt + ... + w dt (numpy's cumsum adds in that order, like the loop), the position the running sum
+        # of the per-step increments -- the same additions in the same order as n_steps calls of the reference.
+        yaw = np.cumsum(np.concatenate((tr[:, 3:4], np.repeat((self.w_yaw * self.sim_dt)[:, None], n_steps, axis=1)),
+                                       axis=1), axis=1)                      # [B, n+1]
+        R_WB = rpy_to_matrix_batch(tr[:, 5, None], tr[:, 4, None], yaw[:, :-1])      # [B, n, 3, 3]
+        v = np.round(matvec3(R_WB, self.v_des[:, None, :]), 1)                       # [B, n, 3]
+        pos = np.cumsum(np.concatenate((tr[:, None, :2], v[:, :, :2] * self.sim_dt), axis=1), axis=1)
+        tr[:, :2] = pos[:, -1]
+        tr[:, 3] = yaw[:, -1]
 
     def set_convergence_on_first_iter(self) -> None:
         o = self.config_opt
@@ -404,8 +414,18 @@ class BatchedLocomotionMPC:
         from ..problem import base_ref_vel_tracking
         N1 = self.config_opt.n_nodes + 1
         node = self.i_node0 + self.current_opt_node
-        cnt = np.stack([self.contact_planner.get_contacts(int(i), N1) for i in node])
-        peak = np.stack([self.contact_planner.get_peaks(int(i), N1) for i in node]) if self.config_opt.opt_peak else None
+        if self.plan_on_device:
+            # contact / swing windows, base references and the expansion of `init` on the device (nmpc_plan_tick):
+            # 0.3 KB per rollout cross PCIe and the host does nothing per problem
+            self.solver.init_planned(node, q, v, self.v_des, self.w_yaw, self.base_ref_vel_tracking,
+                                     self.contact_planner, self.config_gait.nom_height, self.joint_ref,
+                                     self.config_gait.step_height)
+            # the solution stays on the device (plan -> torque reads it there); `self.solver.fetch_solution()` unpacks it
+            sol = self.solver.solve(unpack=self.unpack_solution)
+            self.status_log.append(np.array(self.solver.status).copy())
+            return sol
+        cnt = self.contact_planner.get_contacts_batch(node, N1)
+        peak = self.contact_planner.get_peaks_batch(node, N1) if self.config_opt.opt_peak else None
         ref, ref_e = base_ref_vel_tracking(q, self.v_des, self.w_yaw, self.base_ref_vel_tracking,
                                            self.config_gait.nom_height, self.height_offset, self.config_opt.time_horizon)
         self.solver.init(node, q, v, ref, ref_e, self.joint_ref, self.config_gait.step_height, cnt, None, peak)
@@ -421,10 +441,13 @@ class BatchedLocomotionMPC:
         qs, vs, taus = [], [], []
         sim_time = 0.0
         n_total = 0
+        pending = 0                      # sim steps whose reference increment has not been applied yet
         while sim_time <= trajectory_time:
             if sim_time >= (self.current_opt_node + 1) * self.dt_nodes:
                 self.current_opt_node += 1
             if self.sim_step % R == 0:
+                self._advance_reference(pending)      # only `optimize` reads the tracked pose
+                pending = 0
                 self.set_convergence_on_first_iter()
                 self.optimize(q, v)
                 self.first_solve = False
@@ -436,9 +459,10 @@ class BatchedLocomotionMPC:
             if record_torques:
                 taus.append(plan_tau[:, k].copy())
             k += 1
-            self._advance_reference(1)
+            pending += 1
             self.sim_step += 1
             n_total += 1
             sim_time += self.sim_dt
+        self._advance_reference(pending)
         res = (np.array(qs), np.array(vs))
         return res + (np.array(taus),) if record_torques else res

@@ -85,6 +85,18 @@ class GaitPlanner:
         """[n_foot, n_nodes] swing mask starting at node i_node."""
         return self._window(self.peak_swing, i_node, n_nodes)
 
+    def _window_batch(self, table: np.ndarray, i_node, n_nodes: int) -> np.ndarray:
+        i_node = np.asarray(i_node, dtype=np.int64).reshape(-1)
+        idx = (i_node[:, None] % self.nodes_per_cycle + np.arange(n_nodes)[None, :]) % self.nodes_per_cycle
+        return np.ascontiguousarray(np.moveaxis(table[:, idx], 0, 1))           # [B, n_foot, n_nodes]
+
+    def get_contacts_batch(self, i_node, n_nodes: int) -> np.ndarray:
+        """`get_contacts` for one optimisation node per problem: [B, n_foot, n_nodes]."""
+        return self._window_batch(self.gait_sequence, i_node, n_nodes)
+
+    def get_peaks_batch(self, i_node, n_nodes: int) -> np.ndarray:
+        return self._window_batch(self.peak_swing, i_node, n_nodes)
+
     def get_make_break_contacts(self, i_node: int, n_nodes) -> Tuple[np.ndarray, np.ndarray]:
         mk = (self.switch_cnt == 1).astype(self.switch_cnt.dtype)
         bk = (self.switch_cnt == -1).astype(self.switch_cnt.dtype)

@@ -324,10 +324,17 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
             self.print_contact_constraints()
 
     @time_fn("solve")
-    def solve(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray, np.ndarray, np.ndarray]:
+    def solve(self, unpack: bool = True) -> Tuple[np.ndarray, np.ndarray, np.ndarray, np.ndarray, np.ndarray]:
         """Solve and unpack (solver.py:397-429): q [N+1,18], v [N+1,18], a [N,18], f [N,4,3], dt [N]
-        (each with the leading batch dimension when batched)."""
+        (each with the leading batch dimension when batched).  `unpack=False` leaves the solution on the device
+        (the batched plan -> torque step reads it there); `fetch_solution()` unpacks it later."""
         super().solve(print_stats=self.print_info, print_time=self.print_info)
+        self._has_solution = True
+        if not unpack:
+            return None
+        return self.fetch_solution()
+
+    def fetch_solution(self):
         self.parse_sol()
         d = self.dyn
         T = lambda a: np.swapaxes(a, -1, -2)
@@ -361,6 +368,28 @@ class BatchedQuadrupedSolver(QuadrupedAcadosSolver):
                  compute_timings: bool = True, device: int = 0):
         super().__init__(path_urdf, feet_frame_names, config_opt, config_cost, height_offset, print_info,
                          compute_timings, batch=int(batch), device=device)
+
+    def init_planned(self, i_node, q: np.ndarray, v: np.ndarray, v_des: np.ndarray, w_yaw: np.ndarray,
+                     tracking: np.ndarray, planner, nom_height: float, joint_ref: np.ndarray, step_height: float):
+        """`init` for the cyclic contact planner with the planning step on the device (nmpc_plan_tick): the contact /
+        swing windows at every problem's node, the base references (mpc.py:210-272) and the per-node expansion
+        (solver.py:153-275) are computed by the GPU from i_node, q, the command and the tracked pose; x0 with its
+        momentum, the shift warm start (or the first cold guess) and the stance-foot pinning follow, all resident."""
+        if self.restrict_cnt:
+            raise NotImplementedError("contact restriction needs contact locations: use init()")
+        i_node = np.broadcast_to(np.asarray(i_node, dtype=np.int64), self._lead).copy()
+        gait_seq, peak_seq = planner.cycle_tables()
+        h = self.handle
+        h.plan_tick(i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, self.height_offset,
+                    self.config_opt.time_horizon, joint_ref, step_height, self.config_cost.W_foot_pos_constr_stab,
+                    self.config_opt.opt_peak)
+        h.set_x0(np.concatenate((np.asarray(q, dtype=float), np.asarray(v, dtype=float)), axis=-1))
+        if self.config_opt.warm_start_sol and self._has_solution:
+            h.shift_warm_start((i_node - self.last_node).astype(np.int32), False)
+        else:
+            h.cold_guess()
+        h.pin_stance_feet(i_node.astype(np.int32))
+        self.last_node = i_node
 
     def plan_torques(self, sim_dt: float = 1.0e-3, step0: int = 0, n_steps: Optional[int] = None, Kp: float = 20.,
                      Kd: float = 1.75, qv_meas: Optional[np.ndarray] = None) -> dict:

@@ -117,33 +117,57 @@ def base_ref_vel_tracking(q: np.ndarray, v_des: np.ndarray, w_yaw, tracking: np.
     w_yaw = np.broadcast_to(np.asarray(w_yaw, dtype=float), (B,))
     tracking = np.broadcast_to(np.asarray(tracking, dtype=float), (B, 12))
     nom_height = np.broadcast_to(np.asarray(nom_height, dtype=float), (B,))
-    ref = np.zeros((B, 12))
-    ref_e = np.zeros((B, 12))
-    for b in range(B):
-        w_des = np.array([0.0, 0.0, w_yaw[b]])
-        r = np.zeros(12)
-        r[:2] = np.round(q[b, :2], 2)
-        r[2] = nom_height[b] + height_offset
-        r[3] = round(float(q[b, 3]), 1)
-        R_WB = rpy_to_matrix(tracking[b, 3:6][::-1])
-        v_glob = np.round(R_WB @ v_des[b], 1)
-        r[6:9] = v_glob
-        r[-3:] = w_des[::-1]
-        e = r.copy()
-        e[6:9] = rpy_to_matrix(w_des * t_horizon) @ r[6:9]
-        pos_ref, yaw_ref = tracking[b, :3], tracking[b, 3]
-        e[:2] = pos_ref[:2] + v_glob[:2] * t_horizon
-        e[:2] = np.clip(e[:2], -r[:2] + v_glob[:2] * t_horizon * 1.2, r[:2] + v_glob[:2] * t_horizon * 1.2)
-        e[3] = yaw_ref + w_des[-1] * t_horizon
-        e[3] = np.clip(e[3], -yaw_ref + w_des[-1] * t_horizon * 1.5, yaw_ref + w_des[-1] * t_horizon * 1.5)
-        r[:2] += (e[:2] - r[:2]) * 0.75
-        r[3] += (e[3] - r[3]) * 0.75
-        e[8] = 0.0
-        e[4:6] = 0.0
-        r[4:6] = 0.0
-        e[-2:] = 0.0
-        ref[b], ref_e[b] = r, e
-    return ref, ref_e
+    # vectorised over the batch (no per-problem Python): the same operations in the same order as the reference
+    r = np.zeros((B, 12))
+    r[:, :2] = np.round(q[:, :2], 2)
+    r[:, 2] = nom_height + height_offset
+    r[:, 3] = py_round1(q[:, 3])
+    R_WB = rpy_to_matrix_batch(tracking[:, 5], tracking[:, 4], tracking[:, 3])
+    v_glob = np.round(matvec3(R_WB, v_des), 1)
+    r[:, 6:9] = v_glob
+    r[:, 9] = w_yaw                                  # w_des[::-1] with w_des = (0, 0, w_yaw)
+    e = r.copy()
+    zeros = np.zeros(B)
+    e[:, 6:9] = matvec3(rpy_to_matrix_batch(zeros, zeros, w_yaw * t_horizon), r[:, 6:9])
+    e[:, :2] = tracking[:, :2] + v_glob[:, :2] * t_horizon
+    e[:, :2] = np.clip(e[:, :2], -r[:, :2] + v_glob[:, :2] * t_horizon * 1.2, r[:, :2] + v_glob[:, :2] * t_horizon * 1.2)
+    yaw_ref = tracking[:, 3]
+    e[:, 3] = yaw_ref + w_yaw * t_horizon
+    e[:, 3] = np.clip(e[:, 3], -yaw_ref + w_yaw * t_horizon * 1.5, yaw_ref + w_yaw * t_horizon * 1.5)
+    r[:, :2] += (e[:, :2] - r[:, :2]) * 0.75
+    r[:, 3] += (e[:, 3] - r[:, 3]) * 0.75
+    e[:, 8] = 0.0
+    e[:, 4:6] = 0.0
+    r[:, 4:6] = 0.0
+    e[:, -2:] = 0.0
+    return r, e
+
+
+def py_round1(x: np.ndarray) -> np.ndarray:
+    """Python's `round(x, 1)` (correctly rounded decimal, mpc.py:222) over an array: numpy's `round` rounds the
+    rounded product x * 10 instead, which differs when that product lands on a tie.  x * 10 is exact in the x87
+    extended format (53 + 4 bits)."""
+    x = np.asarray(x, dtype=np.float64)
+    if np.finfo(np.longdouble).nmant >= 57:
+        return (np.rint(x.astype(np.longdouble) * np.longdouble(10)) / np.longdouble(10)).astype(np.float64)
+    return np.array([round(float(v), 1) for v in x.ravel()]).reshape(x.shape)
+
+
+def rpy_to_matrix_batch(roll, pitch, yaw) -> np.ndarray:
+    """`transform.rpy_to_matrix` (pin.rpy.rpyToMatrix) for arrays: [B,3,3]."""
+    roll, pitch, yaw = np.broadcast_arrays(np.asarray(roll, dtype=float), np.asarray(pitch, dtype=float),
+                                           np.asarray(yaw, dtype=float))
+    cr, sr, cp, sp, cy, sy = np.cos(roll), np.sin(roll), np.cos(pitch), np.sin(pitch), np.cos(yaw), np.sin(yaw)
+    R = np.empty(np.shape(cr) + (3, 3))
+    R[..., 0, 0], R[..., 0, 1], R[..., 0, 2] = cy * cp, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr
+    R[..., 1, 0], R[..., 1, 1], R[..., 1, 2] = sy * cp, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr
+    R[..., 2, 0], R[..., 2, 1], R[..., 2, 2] = -sp, cp * sr, cp * cr
+    return R
+
+
+def matvec3(R: np.ndarray, v: np.ndarray) -> np.ndarray:
+    """Row-by-row R @ v with the summation order of a 3-term dot product, batched."""
+    return (R[..., 0] * v[..., None, 0] + R[..., 1] * v[..., None, 1]) + R[..., 2] * v[..., None, 2]
 
 
 def nominal_state(nom_height: float = 0.30, joint_ref: np.ndarray = GO2_JOINT_HOME) -> np.ndarray:

@@ -1208,6 +1208,8 @@ int oracle_solve_qp(oracle_handle* h, const double* BAbt, const double* RSQrq, c
     return 0;
 }
 
+double oracle_model_mass(void) { return NMPC_MASS; }
+
 int oracle_dims(int32_t* out)
 {
     out[0] = NX; out[1] = NU; out[2] = NP; out[3] = NY; out[4] = NYE; out[5] = NG; out[6] = NMPC_REC_SIZE;

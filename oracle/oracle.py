@@ -74,6 +74,7 @@ def lib(topt: bool = False):
                      "oracle_get_stats", "oracle_get_qp_step", "oracle_export_qp", "oracle_solve_qp",
                      "oracle_inverse_dynamics", "oracle_set_fast"):
             getattr(L, name).restype = C.c_int
+        L.oracle_model_mass.restype = C.c_double
         _libs[topt] = L
     return _libs[topt]
 
@@ -140,6 +141,10 @@ def plan_torques(x: np.ndarray, u: np.ndarray, dt_nodes: float, n_interp: int, s
         out["q_plan"][b], out["v_plan"][b], out["tau_ff"][b], out["tau"][b] = qp, vp, tff, tau
         out["action"][b] = (tau + kd * vm[:, 6:]) / kp + qm[:, 6:]
     return out
+
+
+def model_mass() -> float:
+    return float(lib().oracle_model_mass())
 
 
 def model_record(qv: np.ndarray) -> np.ndarray:

