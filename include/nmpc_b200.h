@@ -151,12 +151,17 @@ int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const double* base_re
 /* The planning step of LocomotionMPC.optimize followed by QuadrupedAcadosSolver.init, on the device, for the cyclic
  * contact planner: GaitPlanner.get_contacts / get_peaks (contact_planner.py:121-149: the window
  * of the gait cycle at i_node[b]; gait_seq / peak_seq int8 [4, nodes_per_cycle]) and compute_base_ref_vel_tracking
- * (mpc.py:210-272: q [B,18] Euler state, v_des [B,3], w_yaw [B], tracking [B,12] = base_ref_vel_tracking), then the
- * expansion of nmpc_init_tick without contact restriction.  0.3 KB per problem cross PCIe. */
+ * (mpc.py:210-272: q [B,18] Euler state, v_des [B,3], w_yaw [B]), then the expansion of nmpc_init_tick without
+ * contact restriction.  The tracked reference pose base_ref_vel_tracking [B,12] is resident: `tracking` != NULL
+ * replaces it, and it is first advanced by `advance_steps` calls of increment_base_ref_position (mpc.py:204-208,
+ * one per sim step of length sim_dt since the last tick).  0.2 KB per problem cross PCIe. */
 int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq, const int8_t* peak_seq,
                    int32_t nodes_per_cycle, const double* q, const double* v_des, const double* w_yaw,
-                   const double* tracking, double nom_height, double height_offset, double t_horizon,
-                   const double* joint_ref, double step_height, const double* p_gain, int32_t opt_peak);
+                   const double* tracking, int32_t advance_steps, double sim_dt, double nom_height,
+                   double height_offset, double t_horizon, const double* joint_ref, double step_height,
+                   const double* p_gain, int32_t opt_peak);
+/* base_ref_vel_tracking [B,12] as held (and advanced) on the device */
+int nmpc_get_tracking(nmpc_handle* h, double* tracking);
 /* cold first guess of the batched front-end: x0 held over the horizon, zero accelerations, the robot's
  * weight shared by the stance feet of every node (from x0 and p on the device) */
 int nmpc_cold_guess(nmpc_handle* h);

@@ -85,8 +85,9 @@ _SIGS = {
     "nmpc_init_tick": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int32]),
     "nmpc_plan_tick": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
-                                 C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_double,
-                                 C.c_void_p, C.c_int32]),
+                                 C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,
+                                 C.c_void_p, C.c_double, C.c_void_p, C.c_int32]),
+    "nmpc_get_tracking": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_cold_guess": (C.c_int, [C.c_void_p]),
     "nmpc_get_problem_data": (C.c_int, [C.c_void_p] + [C.c_void_p] * 4),
     "nmpc_plan_torques": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double]

@@ -134,21 +134,30 @@ class NmpcSolver:
               "nmpc_init_tick")
 
     def plan_tick(self, i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height: float,
-                  height_offset: float, t_horizon: float, joint_ref, step_height: float, p_gain, opt_peak: bool = True):
+                  height_offset: float, t_horizon: float, joint_ref, step_height: float, p_gain, opt_peak: bool = True,
+                  advance_steps: int = 0, sim_dt: float = 1.0e-3):
         """Planning + `init` on the device for the cyclic contact planner (nmpc_plan_tick): i_node [B], the gait
-        cycle tables int8 [4, nodes_per_cycle], q [B,18], v_des [B,3], w_yaw [B], tracking [B,12]."""
+        cycle tables int8 [4, nodes_per_cycle], q [B,18], v_des [B,3], w_yaw [B]; tracking [B,12] replaces the
+        resident reference pose (None keeps it), which is first advanced by `advance_steps` sim steps."""
         B = self.B
         node = _i32(i_node, (B,))
         gs = np.ascontiguousarray(gait_seq, dtype=np.int8)
         ps = np.ascontiguousarray(peak_seq, dtype=np.int8)
         assert gs.shape == ps.shape and gs.shape[0] == 4
-        qq, vd, wy, tr = _f64(q, (B, 18)), _f64(v_des, (B, 3)), _f64(w_yaw, (B,)), _f64(tracking, (B, 12))
+        qq, vd, wy = _f64(q, (B, 18)), _f64(v_des, (B, 3)), _f64(w_yaw, (B,))
+        tr = None if tracking is None else _f64(tracking, (B, 12))
         jr = np.ascontiguousarray(joint_ref, dtype=np.float64).reshape(12)
         gain = np.ascontiguousarray(p_gain, dtype=np.float64).reshape(4)
         _order_after_torch(self, qq, vd, wy, tr)
         check(self.lib.nmpc_plan_tick(self._h, ptr(node), ptr(gs), ptr(ps), int(gs.shape[1]), ptr(qq), ptr(vd), ptr(wy),
-                                      ptr(tr), float(nom_height), float(height_offset), float(t_horizon), ptr(jr),
-                                      float(step_height), ptr(gain), int(bool(opt_peak))), "nmpc_plan_tick")
+                                      ptr(tr), int(advance_steps), float(sim_dt), float(nom_height), float(height_offset),
+                                      float(t_horizon), ptr(jr), float(step_height), ptr(gain), int(bool(opt_peak))),
+              "nmpc_plan_tick")
+
+    def get_tracking(self) -> np.ndarray:
+        tr = np.zeros((self.B, 12))
+        check(self.lib.nmpc_get_tracking(self._h, ptr(tr)), "nmpc_get_tracking")
+        return tr
 
     def cold_guess(self):
         check(self.lib.nmpc_cold_guess(self._h), "nmpc_cold_guess")

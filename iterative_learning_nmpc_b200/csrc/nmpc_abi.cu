@@ -33,6 +33,7 @@ struct nmpc_handle {
     // iterate and problem data [B]
     double *x, *u, *pi, *lam, *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;
+    double *tracking;            // [B][12] base_ref_vel_tracking of the batched MPC, resident (nmpc_plan_tick)
     double *dtn, *lamt, *qx;     // enable_time_opt: node durations [B][N], multipliers of their bounds [B][N][2], QP iterate [B][N][QX_SZ]
     double *res, *qp_res, *cost;
     unsigned long long *res_acc;
@@ -165,7 +166,7 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ustream) cudaStreamSynchronize(h->ustream);
     void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
-                    h->qlam, h->qt, h->dtn, h->lamt, h->qx, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
+                    h->qlam, h->qt, h->dtn, h->lamt, h->qx, h->tracking, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
                     h->qp_iter, h->qp_status, h->qp_ncond, h->itmp, h->G, h->M, h->C, h->D, h->vec, h->cost_stage,
                     h->rec, h->scratch, h->uscratch, h->SR, h->FR, h->sr_flag};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -324,11 +325,12 @@ extern "C" int nmpc_init_tick(nmpc_handle* h, const double* base_ref, const doub
 // tracked pose, then the expansion of nmpc_init_tick.  Every array may be a host or a device pointer.
 extern "C" int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq, const int8_t* peak_seq,
                               int32_t nodes_per_cycle, const double* q, const double* v_des, const double* w_yaw,
-                              const double* tracking, double nom_height, double height_offset, double t_horizon,
-                              const double* joint_ref, double step_height, const double* p_gain, int32_t opt_peak)
+                              const double* tracking, int32_t advance_steps, double sim_dt, double nom_height,
+                              double height_offset, double t_horizon, const double* joint_ref, double step_height,
+                              const double* p_gain, int32_t opt_peak)
 {
-    if (!h || !i_node || !gait_seq || !peak_seq || nodes_per_cycle < 1 || !q || !v_des || !w_yaw || !tracking ||
-        !joint_ref || !p_gain) return NMPC_EINVAL;
+    if (!h || !i_node || !gait_seq || !peak_seq || nodes_per_cycle < 1 || !q || !v_des || !w_yaw ||
+        !joint_ref || !p_gain || advance_steps < 0) return NMPC_EINVAL;
     LOCK(h);
     CK(cudaSetDevice(h->device));
     const size_t B = h->B, N1 = h->N + 1, npc = nodes_per_cycle;
@@ -353,7 +355,9 @@ extern "C" int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_
     CK(cudaMemcpyAsync(d_q, q, B * 18 * 8, cudaMemcpyDefault, h->stream));
     CK(cudaMemcpyAsync(d_vd, v_des, B * 3 * 8, cudaMemcpyDefault, h->stream));
     CK(cudaMemcpyAsync(d_w, w_yaw, B * 8, cudaMemcpyDefault, h->stream));
-    CK(cudaMemcpyAsync(d_tr, tracking, B * 12 * 8, cudaMemcpyDefault, h->stream));
+    if (!h->tracking) { cudaError_t e = dalloc(&h->tracking, B * 12); if (e != cudaSuccess) return (int)e; }
+    if (tracking) CK(cudaMemcpyAsync(h->tracking, tracking, B * 12 * 8, cudaMemcpyDefault, h->stream));
+    (void)d_tr;
     CK(cudaMemcpyAsync(d_jr, joint_ref, 12 * 8, cudaMemcpyDefault, h->stream));
     CK(cudaMemcpyAsync(d_sh, &step_height, 8, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(d_node, i_node, B * 4, cudaMemcpyDefault, h->stream));
@@ -361,7 +365,7 @@ extern "C" int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_
     CK(cudaMemcpyAsync(d_ps, peak_seq, NF * npc, cudaMemcpyDefault, h->stream));
     PlannerArgs pa;
     pa.i_node = d_node; pa.gait_seq = d_gs; pa.peak_seq = d_ps; pa.q = d_q; pa.v_des = d_vd; pa.w_yaw = d_w;
-    pa.tracking = d_tr; pa.nom_height = nom_height; pa.height_offset = height_offset; pa.t_horizon = t_horizon;
+    pa.tracking = h->tracking; pa.advance_steps = advance_steps; pa.sim_dt = sim_dt; pa.nom_height = nom_height; pa.height_offset = height_offset; pa.t_horizon = t_horizon;
     pa.npc = nodes_per_cycle; pa.N = h->N; pa.B = h->B;
     pa.base_ref = d_ref; pa.base_ref_e = d_ref_e; pa.cnt = d_cnt; pa.peak = d_peak;
     nmpc_plan_refs_kernel<<<h->B, 128, 0, h->stream>>>(pa);
@@ -375,6 +379,17 @@ extern "C" int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_
     nmpc_init_tick_kernel<<<h->B, 128, 0, h->stream>>>(a);
     h->launches += 2;
     return (int)cudaGetLastError();
+}
+
+// the tracked reference pose [B,12] as nmpc_plan_tick holds (and advances) it on the device
+extern "C" int nmpc_get_tracking(nmpc_handle* h, double* tracking)
+{
+    if (!h || !tracking || !h->tracking) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(tracking, h->tracking, (size_t)h->B * 12 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
 }
 
 // cold first guess from x0 and the contact mask already on the device (call after nmpc_set_x0 and nmpc_init_tick / nmpc_set_params)

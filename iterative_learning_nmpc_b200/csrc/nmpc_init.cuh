@@ -127,7 +127,8 @@ struct PlannerArgs {
     const double* q;                 // [B][18] Euler state
     const double* v_des;             // [B][3]  velocity command, base frame
     const double* w_yaw;             // [B]
-    const double* tracking;          // [B][12] integrated reference pose (base_ref_vel_tracking)
+    double* tracking;                // [B][12] integrated reference pose (base_ref_vel_tracking), advanced in place
+    int advance_steps; double sim_dt;// increment_base_ref_position (mpc.py:204-208) for the sim steps since the last tick
     double nom_height, height_offset, t_horizon;
     int npc, N, B;
     double* base_ref; double* base_ref_e;       // [B][12]
@@ -158,9 +159,23 @@ __global__ void __launch_bounds__(128) nmpc_plan_refs_kernel(PlannerArgs a)
     }
     if (tid != 127) return;
     const double* q = a.q + (size_t)b * 18;
-    const double* tr = a.tracking + (size_t)b * 12;
+    double* tr = a.tracking + (size_t)b * 12;
     const double* vd = a.v_des + (size_t)b * 3;
     const double wz = a.w_yaw[b], th = a.t_horizon;
+    if (a.advance_steps > 0) {
+        // increment_base_ref_position, once per elapsed sim step, in the reference's order of operations
+        const double p = tr[4], ro = tr[5];
+        const double cr = cos(ro), sr = sin(ro), cp = cos(p), sp = sin(p);
+        double px = tr[0], py = tr[1], yaw = tr[3];
+        for (int s = 0; s < a.advance_steps; s++) {
+            const double cy = cos(yaw), sy = sin(yaw);
+            const double vx = np_round(((cy * cp) * vd[0] + (cy * sp * sr - sy * cr) * vd[1]) + (cy * sp * cr + sy * sr) * vd[2], 10.0);
+            const double vy = np_round(((sy * cp) * vd[0] + (sy * sp * sr + cy * cr) * vd[1]) + (sy * sp * cr - cy * sr) * vd[2], 10.0);
+            px += vx * a.sim_dt; py += vy * a.sim_dt;
+            yaw += wz * a.sim_dt;
+        }
+        tr[0] = px; tr[1] = py; tr[3] = yaw;
+    }
     double r[12], e[12];
     for (int i = 0; i < 12; i++) r[i] = 0.0;
     r[0] = np_round(q[0], 100.0); r[1] = np_round(q[1], 100.0);

@@ -374,6 +374,7 @@ class BatchedLocomotionMPC:
         self.i_node0 = np.broadcast_to(np.asarray(i_node0, dtype=np.int64), (self.B,)).copy()
         self.v_des, self.w_yaw = np.zeros((self.B, 3)), np.zeros(self.B)
         self.base_ref_vel_tracking = np.zeros((self.B, 12))
+        self._tracking_on_device, self._pending_steps = False, 0
         self.status_log: List[np.ndarray] = []
 
     def set_command(self, v_des=np.zeros(3), w_yaw=0.) -> None:
@@ -382,8 +383,10 @@ class BatchedLocomotionMPC:
 
     def _advance_reference(self, n_steps: int) -> None:
         """`increment_base_ref_position` (mpc.py:204-208), one sim step at a time, for every rollout."""
-        from ..problem import matvec3, rpy_to_matrix_batch
         if n_steps <= 0:
+            return
+        if self.plan_on_device and self._tracking_on_device:
+            self._pending_steps += n_steps           # applied by nmpc_plan_tick at the next tick, on the device
             return
         tr = self.base_ref_vel_tracking
         # Vectorised over the rollouts AND over the sim steps: the yaw of step j is the running sum
@@ -391,9 +394,14 @@ class BatchedLocomotionMPC:
         # of the per-step increments -- the same additions in the same order as n_steps calls of the reference.
         yaw = np.cumsum(np.concatenate((tr[:, 3:4], np.repeat((self.w_yaw * self.sim_dt)[:, None], n_steps, axis=1)),
                                        axis=1), axis=1)                      # [B, n+1]
-        R_WB = rpy_to_matrix_batch(tr[:, 5, None], tr[:, 4, None], yaw[:, :-1])      # [B, n, 3, 3]
-        v = np.round(matvec3(R_WB, self.v_des[:, None, :]), 1)                       # [B, n, 3]
-        pos = np.cumsum(np.concatenate((tr[:, None, :2], v[:, :, :2] * self.sim_dt), axis=1), axis=1)
+        # rows x, y of R_WB(roll, pitch, yaw_j) v_des with the reference's operation order (matvec3 / rpy_to_matrix)
+        cy, sy = np.cos(yaw[:, :-1]), np.sin(yaw[:, :-1])
+        cr, sr, cp, sp = (f(tr[:, i, None]) for i, f in ((5, np.cos), (5, np.sin), (4, np.cos), (4, np.sin)))
+        v0, v1, v2 = (self.v_des[:, i, None] for i in range(3))
+        vx = np.round(((cy * cp) * v0 + (cy * sp * sr - sy * cr) * v1) + (cy * sp * cr + sy * sr) * v2, 1)
+        vy = np.round(((sy * cp) * v0 + (sy * sp * sr + cy * cr) * v1) + (sy * sp * cr - cy * sr) * v2, 1)
+        inc = np.stack((vx, vy), axis=-1) * self.sim_dt                              # [B, n, 2]
+        pos = np.cumsum(np.concatenate((tr[:, None, :2], inc), axis=1), axis=1)
         tr[:, :2] = pos[:, -1]
         tr[:, 3] = yaw[:, -1]
 
@@ -417,9 +425,12 @@ class BatchedLocomotionMPC:
         if self.plan_on_device:
             # contact / swing windows, base references and the expansion of `init` on the device (nmpc_plan_tick):
             # 0.3 KB per rollout cross PCIe and the host does nothing per problem
-            self.solver.init_planned(node, q, v, self.v_des, self.w_yaw, self.base_ref_vel_tracking,
-                                     self.contact_planner, self.config_gait.nom_height, self.joint_ref,
-                                     self.config_gait.step_height)
+            # the tracked reference pose is resident too: uploaded once, advanced by the kernel for the elapsed sim steps
+            tr = None if self._tracking_on_device else self.base_ref_vel_tracking
+            self.solver.init_planned(node, q, v, self.v_des, self.w_yaw, tr, self.contact_planner,
+                                     self.config_gait.nom_height, self.joint_ref, self.config_gait.step_height,
+                                     self._pending_steps, self.sim_dt)
+            self._tracking_on_device, self._pending_steps = True, 0
             # the solution stays on the device (plan -> torque reads it there); `self.solver.fetch_solution()` unpacks it
             sol = self.solver.solve(unpack=self.unpack_solution)
             self.status_log.append(np.array(self.solver.status).copy())

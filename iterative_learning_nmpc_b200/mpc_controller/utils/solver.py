@@ -370,7 +370,8 @@ class BatchedQuadrupedSolver(QuadrupedAcadosSolver):
                          compute_timings, batch=int(batch), device=device)
 
     def init_planned(self, i_node, q: np.ndarray, v: np.ndarray, v_des: np.ndarray, w_yaw: np.ndarray,
-                     tracking: np.ndarray, planner, nom_height: float, joint_ref: np.ndarray, step_height: float):
+                     tracking: Optional[np.ndarray], planner, nom_height: float, joint_ref: np.ndarray,
+                     step_height: float, advance_steps: int = 0, sim_dt: float = 1.0e-3):
         """`init` for the cyclic contact planner with the planning step on the device (nmpc_plan_tick): the contact /
         swing windows at every problem's node, the base references (mpc.py:210-272) and the per-node expansion
         (solver.py:153-275) are computed by the GPU from i_node, q, the command and the tracked pose; x0 with its
@@ -382,7 +383,7 @@ class BatchedQuadrupedSolver(QuadrupedAcadosSolver):
         h = self.handle
         h.plan_tick(i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, self.height_offset,
                     self.config_opt.time_horizon, joint_ref, step_height, self.config_cost.W_foot_pos_constr_stab,
-                    self.config_opt.opt_peak)
+                    self.config_opt.opt_peak, advance_steps, sim_dt)
         h.set_x0(np.concatenate((np.asarray(q, dtype=float), np.asarray(v, dtype=float)), axis=-1))
         if self.config_opt.warm_start_sol and self._has_solution:
             h.shift_warm_start((i_node - self.last_node).astype(np.int32), False)

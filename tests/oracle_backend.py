@@ -80,12 +80,25 @@ class OracleHandle:
         return O.plan_torques(x, u, float(self.opts.dt_nodes), n_interp, step0, n_steps, kp, kd, qv_meas)
 
     def plan_tick(self, i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, height_offset, t_horizon,
-                  joint_ref, step_height, p_gain, opt_peak=True):
+                  joint_ref, step_height, p_gain, opt_peak=True, advance_steps=0, sim_dt=1.0e-3):
         """Checker for nmpc_plan_tick: the host planners (problem.py restatements of contact_planner.py:121-149 and
-        mpc.py:210-272) and the host packing of `init`."""
+        mpc.py:210-272), the reference's per-step increment of the tracked pose (mpc.py:204-208) and the host packing
+        of `init`."""
         from iterative_learning_nmpc_b200 import problem as P
         from iterative_learning_nmpc_b200.mpc_controller.config.quadruped.utils import get_quadruped_config
+        from iterative_learning_nmpc_b200.mpc_controller.utils.transform import rpy_to_matrix
         B, N1 = self.B, self.N + 1
+        if tracking is not None:
+            self._tracking = np.array(tracking, dtype=float).reshape(B, 12)
+        v_des = np.broadcast_to(np.asarray(v_des, dtype=float), (B, 3))
+        w_yaw = np.broadcast_to(np.asarray(w_yaw, dtype=float), (B,))
+        for _ in range(int(advance_steps)):          # increment_base_ref_position, step by step, problem by problem
+            for b in range(B):
+                R_WB = rpy_to_matrix(self._tracking[b, 3:6][::-1])
+                vg = np.round(R_WB @ v_des[b], 1)
+                self._tracking[b, :2] += vg[:2] * sim_dt
+                self._tracking[b, 3] += w_yaw[b] * sim_dt
+        tracking = self._tracking
         gs, ps = np.asarray(gait_seq), np.asarray(peak_seq)
         npc = gs.shape[1]
         node = np.asarray(i_node, dtype=np.int64).reshape(B)
@@ -99,6 +112,9 @@ class OracleHandle:
         self._s.set_yref(yref, yref_e)
         self.set_params(P.pack_params(cnt, cost, height_offset, peak, False, None, opt_peak))
         self.last_plan = dict(base_ref=ref, base_ref_e=ref_e, cnt=cnt, peak=peak)
+
+    def get_tracking(self):
+        return self._tracking.copy()
 
     def set_params(self, p):
         self._p = np.array(p, dtype=float).reshape(self.B, self.N + 1, 4, 11)

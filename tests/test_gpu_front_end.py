@@ -169,8 +169,14 @@ def test_device_planners_match_host_planners():
     w_yaw = rng.uniform(-0.5, 0.5, B)
     tracking = np.zeros((B, 12)); tracking[:, :6] = rng.normal(0, 0.4, (B, 6))
     dev, host = NmpcSolver(B, default_opts()), NmpcSolver(B, default_opts())
+    # the tracked pose is resident and advanced by 37 sim steps on the device; the checker runs the reference's loop
     dev.plan_tick(node, gs, ps, q, v_des, w_yaw, tracking, gait.nom_height, 0.01, opt.time_horizon, P.GO2_JOINT_HOME,
-                  gait.step_height, cost.W_foot_pos_constr_stab, True)
+                  gait.step_height, cost.W_foot_pos_constr_stab, True, advance_steps=37, sim_dt=1e-3)
+    chk = OracleHandle(B, default_opts())
+    chk.plan_tick(node, gs, ps, q, v_des, w_yaw, tracking, gait.nom_height, 0.01, opt.time_horizon, P.GO2_JOINT_HOME,
+                  gait.step_height, cost.W_foot_pos_constr_stab, True, advance_steps=37, sim_dt=1e-3)
+    tracking = chk.get_tracking()
+    assert np.abs(dev.get_tracking() - tracking).max() < 1e-12 and np.abs(tracking[:, :2] - 0).max() > 0
     ref, ref_e = P.base_ref_vel_tracking(q, v_des, w_yaw, tracking, gait.nom_height, 0.01, opt.time_horizon)
     cnt, peak = planner.get_contacts_batch(node, N + 1), planner.get_peaks_batch(node, N + 1)
     for b in (0, 100, 256):       # the vectorised windows are the reference's per-problem ones

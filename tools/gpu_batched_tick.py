@@ -36,7 +36,7 @@ for on_device in (True, False):
         devs.append(sum(ms for ms, n in h.kernel_times().values()) * 1e-3)
         h.set_profiling(False)
         t0 = time.perf_counter()
-        bm._advance_reference(bm.replanning_steps)
+        bm._advance_reference(bm.replanning_steps)      # device planning: queued, applied by the next nmpc_plan_tick
         adv.append(time.perf_counter() - t0)
         bm.current_opt_node += 1
     w, d, a = np.median(walls[1:]), np.median(devs[1:]), np.median(adv[1:])
