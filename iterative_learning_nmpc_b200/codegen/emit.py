@@ -176,14 +176,58 @@ def generate(urdf: str = DEFAULT_URDF, feet: List[str] = None) -> Tuple[str, dic
     return "".join(hdr), meta
 
 
+def generate_sim(urdf: str = DEFAULT_URDF, feet: List[str] = None) -> Tuple[str, dict]:
+    """Straight-line code of the forward-dynamics terms for the batched rigid-body rollout (nmpc_rollout.cuh):
+    mass matrix M(q) (lower triangle, packed by rows), bias C(q, v) v + g(q), and the feet (positions, velocities,
+    position Jacobians) -- everything in the Euler coordinates of the solver, so that M a + bias = S' tau + sum J' f."""
+    feet = feet or DEFAULT_FEET
+    model = load_urdf(urdf)
+    sk = build_symbolic(model, feet, with_dynamics=True)
+    g, nq, nf = sk.g, model.nq, len(feet)
+    sym_expr = {f"q{i}": f"q[{i}]" for i in range(nq)}
+    sym_expr.update({f"v{i}": f"v[{i}]" for i in range(nq)})
+    outs_m = [(f"M[{i * (i + 1) // 2 + j}]", sk.M[i][j]) for i in range(nq) for j in range(i + 1)]
+    outs_b = [(f"bias[{i}]", sk.bias[i]) for i in range(nq)]
+    outs_f: List[Tuple[str, int]] = []
+    for f in range(nf):
+        for i in range(3):
+            outs_f.append((f"fp[{f * 3 + i}]", sk.foot_p[f][i]))
+            outs_f.append((f"fv[{f * 3 + i}]", sk.foot_v[f][i]))
+            for j in range(nq):
+                outs_f.append((f"fJ[{(f * 3 + i) * nq + j}]", sk.foot_J[f][i][j]))
+    body_m, st_m = g.emit_body(outs_m, sym_expr)
+    body_b, st_b = g.emit_body(outs_b, sym_expr)
+    body_f, st_f = g.emit_body(outs_f, sym_expr)
+    hdr = ["/* GENERATED by iterative_learning_nmpc_b200/codegen/emit.py --sim -- do not edit.\n"
+           f" * model: {model.name}; forward-dynamics terms of the batched rigid-body rollout (nmpc_rollout.cuh).\n */\n",
+           "#ifndef NMPC_GEN_SIM_H\n#define NMPC_GEN_SIM_H\n#ifndef NMPC_HD\n#define NMPC_HD static\n#endif\n",
+           f"/* mass matrix, lower triangle packed by rows M[i (i + 1) / 2 + j]: {st_m['flops']} flops */\n",
+           "NMPC_HD void nmpc_sim_mass(const double* __restrict__ q, double* __restrict__ M)\n{\n", body_m, "}\n",
+           f"/* bias C(q, v) v + g(q): {st_b['flops']} flops */\n",
+           "NMPC_HD void nmpc_sim_bias(const double* __restrict__ q, const double* __restrict__ v, double* __restrict__ bias)\n{\n",
+           body_b, "}\n",
+           f"/* feet: positions fp[12], velocities fv[12], position Jacobians fJ[12][{nq}]: {st_f['flops']} flops */\n",
+           "NMPC_HD void nmpc_sim_feet(const double* __restrict__ q, const double* __restrict__ v, double* __restrict__ fp,"
+           " double* __restrict__ fv, double* __restrict__ fJ)\n{\n", body_f, "}\n#endif /* NMPC_GEN_SIM_H */\n"]
+    return "".join(hdr), {"mass": st_m, "bias": st_b, "feet": st_f}
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
+    ap.add_argument("--sim", action="store_true", help="emit csrc/nmpc_gen_sim.h (forward-dynamics terms) instead")
     ap.add_argument("--urdf", default=DEFAULT_URDF)
     ap.add_argument("--feet", nargs="*", default=DEFAULT_FEET)
     ap.add_argument("--out", nargs="*", default=[
         os.path.join(PKG, "csrc", "nmpc_gen_model.h"),
     ])
     args = ap.parse_args()
+    if args.sim:
+        text, meta = generate_sim(args.urdf, args.feet)
+        path = os.path.join(PKG, "csrc", "nmpc_gen_sim.h")
+        with open(path, "w") as f:
+            f.write(text)
+        print(f"wrote {path}: {len(text)} bytes, {meta}")
+        return
     text, meta = generate(args.urdf, args.feet)
     for path in args.out:
         with open(path, "w") as f:

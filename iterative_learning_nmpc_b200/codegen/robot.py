@@ -200,6 +200,8 @@ class SymbolicKinematics:
     mass: float
     a: List[int] = field(default_factory=list)     # acceleration symbols (Euler-rate derivatives + joints)
     tau: List[int] = field(default_factory=list)   # [nq] generalised forces of inverse dynamics M a + C v + g
+    M: List[List[int]] = field(default_factory=list)   # [nq][nq] mass matrix d2T/dv2 (forward dynamics of the batched rollout)
+    bias: List[int] = field(default_factory=list)  # [nq] C v + g = tau at a = 0
 
 
 GRAVITY = 9.81
@@ -320,4 +322,6 @@ def build_symbolic(model: RobotModel, feet_frames: Sequence[str], with_dynamics:
         dV_dq = g.grad(potential.n, q)
         sk.a = acc
         sk.tau = [g.add(g.sub(md, tq), vq) for md, tq, vq in zip(mom_dot, dT_dq, dV_dq)]
+        sk.M = g.jacobian(mom, v)
+        sk.bias = [g.add(g.sub(md, tq), vq) for md, tq, vq in zip(g.jvp(mom, q, v), dT_dq, dV_dq)]
     return sk

@@ -822,6 +822,7 @@ extern "C" int nmpc_plan_torques(nmpc_handle* h, const double* qv_meas, int32_t 
     a.tau = tau ? d_tau : nullptr; a.action = action ? d_act : nullptr;
     a.B = h->B; a.N = h->N; a.n_interp = n_interp; a.step0 = step0; a.n_steps = n_steps;
     a.dt = h->o.dt_nodes; a.kp = kp; a.kd = kd;
+    a.dtn = h->o.enable_time_opt ? h->dtn : nullptr;
     nmpc_plan_torque_kernel<<<(unsigned)((n + 63) / 64), 64, 0, h->stream>>>(a);
     h->launches++;
     if (q_plan) CK(cudaMemcpyAsync(q_plan, d_q, n * 18 * 8, cudaMemcpyDefault, h->stream));

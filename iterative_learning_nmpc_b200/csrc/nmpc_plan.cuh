@@ -22,30 +22,25 @@ struct PlanArgs {
     double* q_plan; double* v_plan; double* tau_ff; double* tau; double* action;   // any may be nullptr
     int B, N, n_interp, step0, n_steps;
     double dt, kp, kd;
+    const double* dtn;      // [B][N] node durations of the solution (enable_time_opt) or nullptr
 };
 
-__global__ void __launch_bounds__(64, 4) nmpc_plan_torque_kernel(PlanArgs a)
+// Sample `ip` of the interpolated plan (sample 0 of linspace(0, T, n + 1) is dropped): cubic Hermite of (q, v) and of
+// (v, a') on the node grid.  dtn != nullptr: per-node durations (enable_time_opt: time_traj = cumsum(dt_node_sol)).
+__device__ __forceinline__ void nmpc_plan_sample(const double* xb, const double* ub, const double* dtn, double dt, int N,
+                                                 int n, int ip, double* q, double* v)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.B * a.n_steps) return;
-    const int b = i / a.n_steps, s = i % a.n_steps, N = a.N, n = a.n_interp;
-    const int ip = a.step0 + s;                       // index into the plan arrays (sample 0 is dropped)
-    const double* xb = a.x + (size_t)b * (N + 1) * NX;
-    const double* ub = a.u + (size_t)b * N * NU;
-
     // node grid by running sum (numpy.cumsum order), sample time as numpy.linspace computes it
     double T = 0.0;
-    for (int k = 0; k < N; k++) T += a.dt;
+    for (int k = 0; k < N; k++) T += dtn ? dtn[k] : dt;
     const double step = T / n;
     const int j = ip + 1;
     const double t = (j >= n) ? T : j * step;
     int k = 0;
-    double tk = 0.0, tk1 = a.dt;
-    while (k < N - 1 && t >= tk1) { k++; tk = tk1; tk1 += a.dt; }
+    double tk = 0.0, tk1 = dtn ? dtn[0] : dt;
+    while (k < N - 1 && t >= tk1) { k++; tk = tk1; tk1 += dtn ? dtn[k] : dt; }
     const double hh = tk1 - tk, tau_ = (t - tk) / hh, t2 = tau_ * tau_, t3 = t2 * tau_;
     const double h00 = 2.0 * t3 - 3.0 * t2 + 1.0, h10 = t3 - 2.0 * t2 + tau_, h01 = -2.0 * t3 + 3.0 * t2, h11 = t3 - t2;
-
-    double q[NQ], v[NQ], acc[NQ], ff[12], qm[NQ], vm[NQ], tq[NQ - 6];
     const double* x0 = xb + (size_t)k * NX;
     const double* x1 = x0 + NX;
     const double* a0 = ub + (size_t)(k > 0 ? k - 1 : 0) * NU;     // slope of v at knot k
@@ -55,10 +50,31 @@ __global__ void __launch_bounds__(64, 4) nmpc_plan_torque_kernel(PlanArgs a)
         q[c] = h00 * x0[c] + h10 * hh * x0[NQ + c] + h01 * x1[c] + h11 * hh * x1[NQ + c];
         v[c] = h00 * x0[NQ + c] + h10 * hh * a0[c] + h01 * x1[NQ + c] + h11 * hh * a1[c];
     }
-    // zero-order hold of the inputs
+}
+
+// zero-order hold of the inputs: node index of plan step ip (id_repeat, mpc.py:110)
+__device__ __forceinline__ int nmpc_plan_hold_node(int N, int n, int ip)
+{
     const double frac = (ip >= n - 1) ? 1.0 : ip * (1.0 / (n - 1));
-    const int kr = (int)(frac * (N - 1));
-    const double* ur = ub + (size_t)kr * NU;
+    return (int)(frac * (N - 1));
+}
+
+__global__ void __launch_bounds__(64, 4) nmpc_plan_torque_kernel(PlanArgs a)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.B * a.n_steps) return;
+    const int b = i / a.n_steps, s = i % a.n_steps, N = a.N, n = a.n_interp;
+    const int ip = a.step0 + s;                       // index into the plan arrays (sample 0 is dropped)
+    const double* xb = a.x + (size_t)b * (N + 1) * NX;
+    const double* ub = a.u + (size_t)b * N * NU;
+    const double* dtn = a.dtn ? a.dtn + (size_t)b * N : nullptr;
+
+    double q[NQ], v[NQ], qr[NQ], vr[NQ], acc[NQ], ff[12], qm[NQ], vm[NQ], tq[NQ - 6];
+    nmpc_plan_sample(xb, ub, dtn, a.dt, N, n, ip, q, v);
+    // The PD term tracks the NEXT plan sample: `_compute_torques_ff` uses a_plan / f_plan[plan_step], then `_step()`
+    // increments plan_step, and `_compute_pd_torques` reads q_plan / v_plan[plan_step] (mpc.py:575-599)
+    nmpc_plan_sample(xb, ub, dtn, a.dt, N, n, ip + 1 < n ? ip + 1 : n - 1, qr, vr);
+    const double* ur = ub + (size_t)nmpc_plan_hold_node(N, n, ip) * NU;
 #pragma unroll
     for (int c = 0; c < NQ; c++) acc[c] = ur[c];
 #pragma unroll
@@ -75,7 +91,7 @@ __global__ void __launch_bounds__(64, 4) nmpc_plan_torque_kernel(PlanArgs a)
     if (a.q_plan) for (int c = 0; c < NQ; c++) a.q_plan[(size_t)i * NQ + c] = q[c];
     if (a.v_plan) for (int c = 0; c < NQ; c++) a.v_plan[(size_t)i * NQ + c] = v[c];
     for (int c = 0; c < NQ - 6; c++) {
-        const double tpd = tq[c] + a.kp * (q[6 + c] - qm[6 + c]) + a.kd * (v[6 + c] - vm[6 + c]);
+        const double tpd = tq[c] + a.kp * (qr[6 + c] - qm[6 + c]) + a.kd * (vr[6 + c] - vm[6 + c]);
         if (a.tau_ff) a.tau_ff[(size_t)i * 12 + c] = tq[c];
         if (a.tau) a.tau[(size_t)i * 12 + c] = tpd;
         if (a.action) a.action[(size_t)i * 12 + c] = (tpd + a.kd * vm[6 + c]) / a.kp + qm[6 + c];

@@ -111,7 +111,7 @@ def inverse_dynamics(qva: np.ndarray, f: np.ndarray) -> np.ndarray:
     return tau
 
 
-def plan_torques(x: np.ndarray, u: np.ndarray, dt_nodes: float, n_interp: int, step0: int = 0,
+def plan_torques(x: np.ndarray, u: np.ndarray, dt_nodes, n_interp: int, step0: int = 0,
                  n_steps: Optional[int] = None, kp: float = 20.0, kd: float = 1.75, qv_meas=None) -> dict:
     """Checker for nmpc_plan_torques: the reference's own host pipeline, one problem at a time --
     scipy CubicHermiteSpline exactly as `LocomotionMPC.interpolate_trajectory_with_derivatives`
@@ -128,7 +128,8 @@ def plan_torques(x: np.ndarray, u: np.ndarray, dt_nodes: float, n_interp: int, s
            (("q_plan", 18), ("v_plan", 18), ("tau_ff", 12), ("tau", 12), ("action", 12))}
     for b in range(B):
         q_sol, v_sol, a_sol, f_sol = x[b, :, :18], x[b, :, 18:36], u[b, :, :18], u[b, :, 18:30]
-        time_traj = np.concatenate(([0.], np.cumsum(np.full(N, dt_nodes))))
+        dt_b = np.full(N, dt_nodes) if np.ndim(dt_nodes) == 0 else np.asarray(dt_nodes, float).reshape(B, N)[b]
+        time_traj = np.concatenate(([0.], np.cumsum(dt_b)))
         t = np.linspace(time_traj[0], time_traj[-1], n_interp + 1)
         pos = CubicHermiteSpline(time_traj, q_sol, v_sol)(t)[1:]
         acc = np.concatenate((a_sol[:1], a_sol))
@@ -137,7 +138,10 @@ def plan_torques(x: np.ndarray, u: np.ndarray, dt_nodes: float, n_interp: int, s
         qm, vm = (qp, vp) if qv_meas is None else (np.asarray(qv_meas)[b, :, :18], np.asarray(qv_meas)[b, :, 18:])
         ap, fp = a_sol[id_repeat][sl], f_sol[id_repeat][sl]
         tff = inverse_dynamics(np.concatenate([qm, vm, ap], axis=1), fp)
-        tau = tff + kp * (qp[:, 6:] - qm[:, 6:]) + kd * (vp[:, 6:] - vm[:, 6:])
+        # `_compute_torques_ff` reads a_plan / f_plan[plan_step], `_step()` increments plan_step, then
+        # `_compute_pd_torques` reads q_plan / v_plan[plan_step] (mpc.py:575-599): the PD target is the next sample
+        nxt = np.minimum(np.arange(step0, step0 + n_steps) + 1, n_interp - 1)
+        tau = tff + kp * (pos[nxt][:, 6:] - qm[:, 6:]) + kd * (vel[nxt][:, 6:] - vm[:, 6:])
         out["q_plan"][b], out["v_plan"][b], out["tau_ff"][b], out["tau"][b] = qp, vp, tff, tau
         out["action"][b] = (tau + kd * vm[:, 6:]) / kp + qm[:, 6:]
     return out

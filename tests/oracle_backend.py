@@ -76,8 +76,9 @@ class OracleHandle:
         return O.inverse_dynamics(qva, f)
 
     def plan_torques(self, n_interp, step0=0, n_steps=None, kp=20.0, kd=1.75, qv_meas=None):
-        x, u, _, _ = self._s.get_solution()
-        return O.plan_torques(x, u, float(self.opts.dt_nodes), n_interp, step0, n_steps, kp, kd, qv_meas)
+        x, u, _, _ = self.get_solution()
+        dt = self.get_dt() if self._s.topt else float(self.opts.dt_nodes)
+        return O.plan_torques(x, u, dt, n_interp, step0, n_steps, kp, kd, qv_meas)
 
     def plan_tick(self, i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, height_offset, t_horizon,
                   joint_ref, step_height, p_gain, opt_peak=True, advance_steps=0, sim_dt=1.0e-3):
