@@ -184,6 +184,32 @@ int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, int32_t rep
 /* forget duals and the stored QP solution (AcadosSolverHelper.reset-like) */
 int nmpc_reset_duals(nmpc_handle* h);
 
+/* ---- batched rigid-body rollout ---------------------------------- */
+/* Closes the loop around the resident plans without MuJoCo: what Rollout_MPC.run / Rollout_combined_controller do one
+ * rollout at a time (Behavior_Cloning/utils/Rollout_MPC.py:465, DAgger/utils/Rollout_combined_controller.py:484-499)
+ * -- every sim step LocomotionMPC.compute_torques_dof (mpc.py:503-599: feed-forward inverse dynamics on the measured
+ * state + PD on the plan) and one physics step -- for the whole batch on the device.  Physics: articulated-body
+ * forward dynamics of the URDF model in the solver's Euler coordinates, compliant point-foot contact with the plane
+ * z = ground_z (unilateral normal spring-damper, viscous tangential force inside the friction cone), semi-implicit
+ * Euler.  It is NOT MuJoCo's contact solver. */
+typedef struct nmpc_sim_params {
+    double sim_dt;          /* simulation step [s] (1e-3)                                     */
+    double kp, kd;          /* PD gains (MPCOptConfig.Kp, Kd)                                 */
+    double k_n, d_n;        /* contact: normal stiffness [N/m], normal damping [N s/m]        */
+    double d_t;             /* contact: tangential viscous gain [N s/m]                       */
+    double mu;              /* friction coefficient (cone cap of the tangential force)        */
+    double ground_z;        /* ground plane height                                            */
+    double tau_max;         /* joint torque limit, 0 = none                                   */
+} nmpc_sim_params;
+/* simulation state of every rollout, qv [B,36] = [q_euler 18 | v 18] */
+int nmpc_sim_set_state(nmpc_handle* h, const double* qv);
+int nmpc_sim_get_state(nmpc_handle* h, double* qv, int32_t* diverged /* [B] or NULL */);
+/* n_steps simulation steps on the plan of the last nmpc_solve, plan samples step0 .. step0+n_steps-1 of the
+ * n_interp-sample plan.  Optional outputs (host or device, NULL to skip): out_qv [B,n_steps,36] the state the
+ * controller saw at every step, out_tau [B,n_steps,12] the applied torques, out_fc [B,n_steps,12] contact forces. */
+int nmpc_sim_steps(nmpc_handle* h, const nmpc_sim_params* p, int32_t n_interp, int32_t step0, int32_t n_steps,
+                   double* out_qv, double* out_tau, double* out_fc);
+
 /* ---- solve (AcadosSolverHelper.solve, called at solver.py:402) ------------------------ */
 /* Enqueues the whole SQP / SQP_RTI solve on the handle's stream and, if status != NULL, copies
  * the per-problem status [B] back and synchronises.  status may be host or device. */

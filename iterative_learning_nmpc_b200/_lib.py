@@ -33,6 +33,22 @@ class NmpcOpts(C.Structure):
         return o
 
 
+class NmpcSimParams(C.Structure):
+    """nmpc_sim_params: batched rigid-body rollout (include/nmpc_b200.h)."""
+    _fields_ = [("sim_dt", C.c_double), ("kp", C.c_double), ("kd", C.c_double), ("k_n", C.c_double),
+                ("d_n", C.c_double), ("d_t", C.c_double), ("mu", C.c_double), ("ground_z", C.c_double),
+                ("tau_max", C.c_double)]
+
+
+def default_sim_params(**kw) -> NmpcSimParams:
+    p = NmpcSimParams(sim_dt=1.0e-3, kp=20.0, kd=1.5, k_n=2.0e4, d_n=60.0, d_t=60.0, mu=0.8, ground_z=0.0, tau_max=0.0)
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise AttributeError(k)
+        setattr(p, k, v)
+    return p
+
+
 class NmpcStats(C.Structure):
     _fields_ = [("sqp_iter", C.c_void_p), ("qp_iter", C.c_void_p), ("qp_status", C.c_void_p),
                 ("res", C.c_void_p), ("qp_res", C.c_void_p), ("cost", C.c_void_p),
@@ -92,6 +108,10 @@ _SIGS = {
     "nmpc_get_problem_data": (C.c_int, [C.c_void_p] + [C.c_void_p] * 4),
     "nmpc_plan_torques": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double]
                           + [C.c_void_p] * 5),
+    "nmpc_sim_set_state": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nmpc_sim_get_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nmpc_sim_steps": (C.c_int, [C.c_void_p, C.POINTER(NmpcSimParams), C.c_int32, C.c_int32, C.c_int32,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]),
     "nmpc_export_qp": (C.c_int, [C.c_void_p] + [C.c_void_p] * 6),
     "nmpc_solve_qp": (C.c_int, [C.c_void_p] + [C.c_void_p] * 13),
     "nmpc_launch_count": (C.c_int64, [C.c_void_p]),

@@ -231,6 +231,26 @@ class NmpcSolver:
         dt = None if dt is None else _f64(dt, (self.B, self.N))
         check(self.lib.nmpc_set_dt(self._h, ptr(dt)), "nmpc_set_dt")
 
+    # -- batched rigid-body rollout (nmpc_rollout.cuh) ---------------------------------------
+    def sim_set_state(self, qv):
+        check(self.lib.nmpc_sim_set_state(self._h, ptr(_f64(qv, (self.B, 36)))), "nmpc_sim_set_state")
+        self.synchronize()
+
+    def sim_get_state(self):
+        qv, div = np.zeros((self.B, 36)), np.zeros(self.B, dtype=np.int32)
+        check(self.lib.nmpc_sim_get_state(self._h, ptr(qv), ptr(div)), "nmpc_sim_get_state")
+        return qv, div
+
+    def sim_steps(self, params, n_interp: int, step0: int, n_steps: int, record: bool = True):
+        """`n_steps` closed-loop simulation steps of every rollout on the plan of the last solve: the controller of
+        `LocomotionMPC.compute_torques_dof` and one physics step per sim step, on the device.  With `record`:
+        dict(qv [B,n,36] state seen by the controller, tau [B,n,12], fc [B,n,12] contact forces)."""
+        B = self.B
+        out = dict(qv=np.zeros((B, n_steps, 36)), tau=np.zeros((B, n_steps, 12)), fc=np.zeros((B, n_steps, 12))) if record else {}
+        check(self.lib.nmpc_sim_steps(self._h, C.byref(params), int(n_interp), int(step0), int(n_steps),
+                                      ptr(out.get("qv")), ptr(out.get("tau")), ptr(out.get("fc"))), "nmpc_sim_steps")
+        return out
+
     def get_solution_into(self, x=None, u=None, pi=None, lam=None):
         check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
 

@@ -17,6 +17,8 @@
 #include "nmpc_linearize_sr.cuh"
 #include "nmpc_plan.cuh"
 #include "nmpc_init.cuh"
+#include "nmpc_gen_sim.h"
+#include "nmpc_rollout.cuh"
 
 #define CK(call)                                                     \
     do {                                                             \
@@ -33,6 +35,7 @@ struct nmpc_handle {
     // iterate and problem data [B]
     double *x, *u, *pi, *lam, *x0, *p, *yref, *yref_e, *W, *We;
     double *qz, *qpi, *qlam, *qt;
+    double *sim_qv; int32_t* sim_div;    // batched rollout: simulation state [B][36], divergence flags [B]
     double *tracking;            // [B][12] base_ref_vel_tracking of the batched MPC, resident (nmpc_plan_tick)
     double *dtn, *lamt, *qx;     // enable_time_opt: node durations [B][N], multipliers of their bounds [B][N][2], QP iterate [B][N][QX_SZ]
     double *res, *qp_res, *cost;
@@ -166,7 +169,7 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ustream) cudaStreamSynchronize(h->ustream);
     void* ptrs[] = {h->x, h->u, h->pi, h->lam, h->x0, h->p, h->yref, h->yref_e, h->W, h->We, h->qz, h->qpi,
-                    h->qlam, h->qt, h->dtn, h->lamt, h->qx, h->tracking, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
+                    h->qlam, h->qt, h->dtn, h->lamt, h->qx, h->tracking, h->sim_qv, h->sim_div, h->res, h->qp_res, h->cost, h->res_acc, h->status, h->done, h->sqp_iter,
                     h->qp_iter, h->qp_status, h->qp_ncond, h->itmp, h->G, h->M, h->C, h->D, h->vec, h->cost_stage,
                     h->rec, h->scratch, h->uscratch, h->SR, h->FR, h->sr_flag};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -831,6 +834,67 @@ extern "C" int nmpc_plan_torques(nmpc_handle* h, const double* qv_meas, int32_t 
     if (tau) CK(cudaMemcpyAsync(tau, d_tau, n * 12 * 8, cudaMemcpyDefault, h->stream));
     if (action) CK(cudaMemcpyAsync(action, d_act, n * 12 * 8, cudaMemcpyDefault, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// batched rigid-body rollout (nmpc_rollout.cuh)
+// ---------------------------------------------------------------------------------------------
+static int ensure_sim(nmpc_handle* h)
+{
+    if (h->sim_qv) return 0;
+    cudaError_t e = dalloc(&h->sim_qv, (size_t)h->B * 36);
+    if (e == cudaSuccess) e = dalloc(&h->sim_div, (size_t)h->B);
+    return e == cudaSuccess ? 0 : (e == cudaErrorMemoryAllocation ? NMPC_ENOMEM : (int)e);
+}
+
+extern "C" int nmpc_sim_set_state(nmpc_handle* h, const double* qv)
+{
+    if (!h || !qv) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    if (int r = ensure_sim(h)) return r;
+    CK(cudaMemcpyAsync(h->sim_qv, qv, (size_t)h->B * 36 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemsetAsync(h->sim_div, 0, (size_t)h->B * 4, h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_sim_get_state(nmpc_handle* h, double* qv, int32_t* diverged)
+{
+    if (!h || !h->sim_qv) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    if (qv) CK(cudaMemcpyAsync(qv, h->sim_qv, (size_t)h->B * 36 * 8, cudaMemcpyDefault, h->stream));
+    if (diverged) CK(cudaMemcpyAsync(diverged, h->sim_div, (size_t)h->B * 4, cudaMemcpyDefault, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_sim_steps(nmpc_handle* h, const nmpc_sim_params* p, int32_t n_interp, int32_t step0, int32_t n_steps,
+                              double* out_qv, double* out_tau, double* out_fc)
+{
+    if (!h || !p || !h->sim_qv || n_interp < 2 || n_steps <= 0 || step0 < 0 || !(p->sim_dt > 0.0)) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    const size_t n = (size_t)h->B * n_steps;
+    double *d_qv = nullptr, *d_tau = nullptr, *d_fc = nullptr;
+    if (out_qv || out_tau || out_fc) {
+        if (int r = ensure_scratch(h, n * 60 * 8)) return r;
+        d_qv = h->scratch; d_tau = d_qv + n * 36; d_fc = d_tau + n * 12;
+    }
+    SimArgs a;
+    a.x = h->x; a.u = h->u; a.dtn = h->o.enable_time_opt ? h->dtn : nullptr;
+    a.qv = h->sim_qv; a.out_qv = out_qv ? d_qv : nullptr; a.out_tau = out_tau ? d_tau : nullptr; a.out_fc = out_fc ? d_fc : nullptr;
+    a.diverged = h->sim_div;
+    a.B = h->B; a.N = h->N; a.n_interp = n_interp; a.step0 = step0; a.n_steps = n_steps; a.dt_nodes = h->o.dt_nodes;
+    a.p.sim_dt = p->sim_dt; a.p.kp = p->kp; a.p.kd = p->kd; a.p.k_n = p->k_n; a.p.d_n = p->d_n; a.p.d_t = p->d_t;
+    a.p.mu = p->mu; a.p.ground_z = p->ground_z; a.p.tau_max = p->tau_max;
+    nmpc_sim_kernel<<<(h->B + 63) / 64, 64, 0, h->stream>>>(a);
+    h->launches++;
+    if (out_qv) CK(cudaMemcpyAsync(out_qv, d_qv, n * 36 * 8, cudaMemcpyDefault, h->stream));
+    if (out_tau) CK(cudaMemcpyAsync(out_tau, d_tau, n * 12 * 8, cudaMemcpyDefault, h->stream));
+    if (out_fc) CK(cudaMemcpyAsync(out_fc, d_fc, n * 12 * 8, cudaMemcpyDefault, h->stream));
+    if (out_qv || out_tau || out_fc) CK(cudaStreamSynchronize(h->stream));
     return (int)cudaGetLastError();
 }
 

@@ -45,7 +45,7 @@ struct SimArgs {
 #define SIM_NQ 18
 
 // in-place Cholesky solve of the packed lower-triangular SPD matrix M (18 x 18): M a = r
-__host__ __device__ inline void nmpc_sim_solve(double* M, double* r)
+__device__ __forceinline__ void nmpc_sim_solve(double* M, double* r)
 {
     for (int j = 0; j < SIM_NQ; j++) {
         double d = M[j * (j + 1) / 2 + j];
@@ -72,7 +72,7 @@ __host__ __device__ inline void nmpc_sim_solve(double* M, double* r)
 }
 
 // contact force of one point foot: position p, velocity v -> f (world frame)
-__host__ __device__ inline void nmpc_sim_contact(const SimParams& sp, const double* p, const double* v, double* f)
+__device__ __forceinline__ void nmpc_sim_contact(const SimParams& sp, const double* p, const double* v, double* f)
 {
     f[0] = 0.0; f[1] = 0.0; f[2] = 0.0;
     const double pen = sp.ground_z - p[2];
@@ -86,7 +86,7 @@ __host__ __device__ inline void nmpc_sim_contact(const SimParams& sp, const doub
 }
 
 // one physics step from joint torques tau[12]: q, v advanced in place; fc[12] = contact forces used
-__host__ __device__ inline void nmpc_sim_physics(const SimParams& sp, double* q, double* v, const double* tau, double* fc)
+__device__ __forceinline__ void nmpc_sim_physics(const SimParams& sp, double* q, double* v, const double* tau, double* fc)
 {
     double M[SIM_NQ * (SIM_NQ + 1) / 2], r[SIM_NQ], fp[12], fv[12], fJ[12 * SIM_NQ];
     nmpc_sim_mass(q, M);

@@ -444,6 +444,44 @@ class BatchedLocomotionMPC:
         self.status_log.append(np.array(self.solver.status).copy())
         return sol
 
+    def closed_loop(self, q: np.ndarray, v: np.ndarray, trajectory_time: float, sim_params=None, record: bool = True):
+        """B closed-loop rollouts in lockstep on the batched rigid-body simulation (nmpc_rollout.cuh), the MuJoCo-free
+        counterpart of `Rollout_MPC.run` (Behavior_Cloning/utils/Rollout_MPC.py:465) for thousands of rollouts at
+        once: every replanning tick one batched `optimize` on the simulated states, between ticks the low-level
+        controller of `compute_torques_dof` (feed-forward inverse dynamics on the measured state + PD on the plan,
+        mpc.py:503-599) and the physics run on the device, `replanning_steps` sim steps per launch.  The solve is
+        taken to be instantaneous (the reference's `delay` is zero, as with `solve_async=False`).
+        Returns dict(qv [n_steps,B,36] states seen by the controller, tau [n_steps,B,12], fc [n_steps,B,12] contact
+        forces, diverged [B])."""
+        from .._lib import default_sim_params
+        sp = sim_params or default_sim_params(sim_dt=self.sim_dt, kp=self.Kp, kd=self.Kd, ground_z=self.height_offset)
+        h = self.solver.handle
+        q, v = np.array(q, dtype=float).reshape(self.B, 18), np.array(v, dtype=float).reshape(self.B, 18)
+        h.sim_set_state(np.concatenate((q, v), axis=1))
+        R = self.replanning_steps
+        n_total = int(np.floor(trajectory_time / self.sim_dt)) + 1
+        logs = {k: [] for k in ("qv", "tau", "fc")}
+        while self.sim_step < n_total:
+            sim_time = self.sim_step * self.sim_dt
+            while sim_time >= (self.current_opt_node + 1) * self.dt_nodes:
+                self.current_opt_node += 1
+            self.set_convergence_on_first_iter()
+            self.optimize(q, v)
+            self.first_solve = False
+            n = min(R, n_total - self.sim_step)
+            out = h.sim_steps(sp, self.n_interp_plan, 0, n, record=record)
+            if record:
+                for k in logs:
+                    logs[k].append(np.moveaxis(out[k], 0, 1))
+            qv, _ = h.sim_get_state()
+            q, v = qv[:, :18].copy(), qv[:, 18:].copy()
+            self._advance_reference(n)
+            self.sim_step += n
+        _, div = h.sim_get_state()
+        res = {k: np.concatenate(a, axis=0) for k, a in logs.items()} if record else {}
+        res["diverged"], res["q_end"], res["v_end"] = div, q, v
+        return res
+
     def open_loop(self, q: np.ndarray, v: np.ndarray, trajectory_time: float, record_torques: bool = False):
         """Roll all B rollouts forward on their own plans from Euler states q, v [B,18].
         Returns q_traj, v_traj [n_steps,B,18] (and tau [n_steps,B,12] with `record_torques`)."""

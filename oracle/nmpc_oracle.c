@@ -1210,6 +1210,158 @@ int oracle_solve_qp(oracle_handle* h, const double* BAbt, const double* RSQrq, c
 
 double oracle_model_mass(void) { return NMPC_MASS; }
 
+/* ------------------------------------------------------------------------------------------ */
+/* batched rigid-body rollout: CPU restatement of nmpc_rollout.cuh (checker of nmpc_sim_steps) */
+/* ------------------------------------------------------------------------------------------ */
+#include "../iterative_learning_nmpc_b200/csrc/nmpc_gen_sim.h"
+
+/* sample ip of the interpolated plan: scipy CubicHermiteSpline of (q, v) and (v, a') on the node grid, evaluated the
+ * way mpc.py:388-414 samples it (linspace(0, T, n + 1)[1:]); dtn: per-node durations */
+static void plan_sample(const double* x, const double* u, const double* dtn, int N, int n, int ip, double* q, double* v)
+{
+    double T = 0.0;
+    for (int k = 0; k < N; k++) T += dtn[k];
+    const double step = T / n;
+    const int j = ip + 1;
+    const double t = (j >= n) ? T : j * step;
+    int k = 0;
+    double tk = 0.0, tk1 = dtn[0];
+    while (k < N - 1 && t >= tk1) { k++; tk = tk1; tk1 += dtn[k]; }
+    const double hh = tk1 - tk, s = (t - tk) / hh, s2 = s * s, s3 = s2 * s;
+    const double h00 = 2.0 * s3 - 3.0 * s2 + 1.0, h10 = s3 - 2.0 * s2 + s, h01 = -2.0 * s3 + 3.0 * s2, h11 = s3 - s2;
+    const double* x0 = x + (size_t)k * NX;
+    const double* x1 = x0 + NX;
+    const double* a0 = u + (size_t)(k > 0 ? k - 1 : 0) * NU;
+    const double* a1 = u + (size_t)k * NU;
+    for (int c = 0; c < NQ; c++) {
+        q[c] = h00 * x0[c] + h10 * hh * x0[NQ + c] + h01 * x1[c] + h11 * hh * x1[NQ + c];
+        v[c] = h00 * x0[NQ + c] + h10 * hh * a0[c] + h01 * x1[NQ + c] + h11 * hh * a1[c];
+    }
+}
+
+typedef struct { double sim_dt, kp, kd, k_n, d_n, d_t, mu, ground_z, tau_max; } sim_params;
+
+static void sim_physics(const sim_params* sp, double* q, double* v, const double* tau, double* fc)
+{
+    double M[NQ * (NQ + 1) / 2], r[NQ], fp[12], fv[12], fJ[12 * NQ];
+    nmpc_sim_mass(q, M);
+    nmpc_sim_bias(q, v, r);
+    nmpc_sim_feet(q, v, fp, fv, fJ);
+    for (int i = 0; i < NQ; i++) r[i] = -r[i];
+    for (int j = 0; j < 12; j++) r[6 + j] += tau[j];
+    for (int ft = 0; ft < NF; ft++) {
+        double* f = fc + 3 * ft;
+        f[0] = f[1] = f[2] = 0.0;
+        const double pen = sp->ground_z - fp[3 * ft + 2];
+        if (pen > 0.0) {
+            const double fn = sp->k_n * pen - sp->d_n * fv[3 * ft + 2];
+            if (fn > 0.0) {
+                double fx = -sp->d_t * fv[3 * ft], fy = -sp->d_t * fv[3 * ft + 1];
+                const double ftn = sqrt(fx * fx + fy * fy), cap = sp->mu * fn;
+                if (ftn > cap) { const double sc = cap / ftn; fx *= sc; fy *= sc; }
+                f[0] = fx; f[1] = fy; f[2] = fn;
+            }
+        }
+        for (int c = 0; c < 3; c++)
+            if (f[c] != 0.0)
+                for (int i = 0; i < NQ; i++) r[i] += fJ[(3 * ft + c) * NQ + i] * f[c];
+    }
+    /* dense Cholesky solve M a = r on the packed lower triangle */
+    for (int j = 0; j < NQ; j++) {
+        double d = M[j * (j + 1) / 2 + j];
+        for (int l = 0; l < j; l++) d -= M[j * (j + 1) / 2 + l] * M[j * (j + 1) / 2 + l];
+        d = sqrt(d);
+        M[j * (j + 1) / 2 + j] = d;
+        const double inv = 1.0 / d;
+        for (int i = j + 1; i < NQ; i++) {
+            double s = M[i * (i + 1) / 2 + j];
+            for (int l = 0; l < j; l++) s -= M[i * (i + 1) / 2 + l] * M[j * (j + 1) / 2 + l];
+            M[i * (i + 1) / 2 + j] = s * inv;
+        }
+    }
+    for (int i = 0; i < NQ; i++) {
+        double s = r[i];
+        for (int l = 0; l < i; l++) s -= M[i * (i + 1) / 2 + l] * r[l];
+        r[i] = s / M[i * (i + 1) / 2 + i];
+    }
+    for (int i = NQ - 1; i >= 0; i--) {
+        double s = r[i];
+        for (int l = i + 1; l < NQ; l++) s -= M[l * (l + 1) / 2 + i] * r[l];
+        r[i] = s / M[i * (i + 1) / 2 + i];
+    }
+    for (int i = 0; i < NQ; i++) { v[i] += r[i] * sp->sim_dt; q[i] += v[i] * sp->sim_dt; }
+}
+
+/* forward-dynamics terms of the model (tests: M a + bias against the generated inverse dynamics) */
+int oracle_sim_terms(const double* qv, double* M_full, double* bias)
+{
+    double M[NQ * (NQ + 1) / 2];
+    nmpc_sim_mass(qv, M);
+    nmpc_sim_bias(qv, qv + NQ, bias);
+    for (int i = 0; i < NQ; i++)
+        for (int j = 0; j <= i; j++) { M_full[i * NQ + j] = M[i * (i + 1) / 2 + j]; M_full[j * NQ + i] = M[i * (i + 1) / 2 + j]; }
+    return 0;
+}
+
+/* physics only: n_steps steps from joint torques tau [n_steps][12] (or a constant tau when hold != 0) */
+int oracle_sim_physics(const double* params, double* qv, const double* tau, int32_t n_steps, int32_t hold, double* out_qv,
+                       double* out_fc)
+{
+    sim_params sp;
+    memcpy(&sp, params, sizeof(sp));
+    double* q = qv;
+    double* v = qv + NQ;
+    for (int s = 0; s < n_steps; s++) {
+        double fc[12];
+        if (out_qv) memcpy(out_qv + (size_t)s * 36, qv, 36 * sizeof(double));
+        sim_physics(&sp, q, v, tau + (hold ? 0 : (size_t)s * 12), fc);
+        if (out_fc) memcpy(out_fc + (size_t)s * 12, fc, sizeof(fc));
+    }
+    return 0;
+}
+
+/* closed loop on the plan held by the handle: the controller of LocomotionMPC.compute_torques_dof + physics */
+int oracle_sim_steps(oracle_handle* h, const double* params, int32_t n_interp, int32_t step0, int32_t n_steps, double* qv,
+                     double* out_qv, double* out_tau, double* out_fc)
+{
+    const int N = h->N, n = n_interp;
+    sim_params sp;
+    memcpy(&sp, params, sizeof(sp));
+    for (int b = 0; b < h->B; b++) {
+        const double* x = h->x + (size_t)b * (N + 1) * NX;
+        const double* u = h->u + (size_t)b * N * NU;
+        double dtn[NMAX];
+        for (int k = 0; k < N; k++) {
+#ifdef NMPC_ORACLE_TOPT
+            dtn[k] = u[k * NU + IDT];
+#else
+            dtn[k] = h->o.dt_nodes;
+#endif
+        }
+        double* q = qv + (size_t)b * 36;
+        double* v = q + NQ;
+        for (int s = 0; s < n_steps; s++) {
+            const int ip = step0 + s;
+            double qr[NQ], vr[NQ], tq[12], fc[12];
+            if (out_qv) memcpy(out_qv + ((size_t)b * n_steps + s) * 36, q, 36 * sizeof(double));
+            plan_sample(x, u, dtn, N, n, ip + 1 < n ? ip + 1 : n - 1, qr, vr);
+            const int ih = ip < n ? ip : n - 1;
+            const double frac = (ih >= n - 1) ? 1.0 : ih * (1.0 / (n - 1));
+            const double* ur = u + (size_t)((int)(frac * (N - 1))) * NU;
+            nmpc_model_rnea(q, v, ur, ur + NQ, tq);
+            for (int c = 0; c < 12; c++) {
+                double t = tq[c] + sp.kp * (qr[6 + c] - q[6 + c]) + sp.kd * (vr[6 + c] - v[6 + c]);
+                if (sp.tau_max > 0.0) t = fmin(fmax(t, -sp.tau_max), sp.tau_max);
+                tq[c] = t;
+            }
+            sim_physics(&sp, q, v, tq, fc);
+            if (out_tau) memcpy(out_tau + ((size_t)b * n_steps + s) * 12, tq, sizeof(tq));
+            if (out_fc) memcpy(out_fc + ((size_t)b * n_steps + s) * 12, fc, sizeof(fc));
+        }
+    }
+    return 0;
+}
+
 int oracle_dims(int32_t* out)
 {
     out[0] = NX; out[1] = NU; out[2] = NP; out[3] = NY; out[4] = NYE; out[5] = NG; out[6] = NMPC_REC_SIZE;

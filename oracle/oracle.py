@@ -151,6 +151,32 @@ def model_mass() -> float:
     return float(lib().oracle_model_mass())
 
 
+def sim_params_array(p) -> np.ndarray:
+    """nmpc_sim_params (ctypes struct of the product, or a dict) as the 9 doubles the oracle takes."""
+    names = ("sim_dt", "kp", "kd", "k_n", "d_n", "d_t", "mu", "ground_z", "tau_max")
+    get = (lambda k: p[k]) if isinstance(p, dict) else (lambda k: getattr(p, k))
+    return np.array([float(get(k)) for k in names])
+
+
+def sim_terms(qv: np.ndarray):
+    """Mass matrix [18,18] and bias [18] of the rollout's forward dynamics (generated code, nmpc_gen_sim.h)."""
+    qv = _f64(qv).reshape(36)
+    M, b = np.zeros((18, 18)), np.zeros(18)
+    lib().oracle_sim_terms(_p(qv), _p(M), _p(b))
+    return M, b
+
+
+def sim_physics(params, qv: np.ndarray, tau: np.ndarray, n_steps: int):
+    """n_steps physics steps of one robot from joint torques tau [12] (held) or [n_steps,12]: (qv_end, qv_traj, fc)."""
+    qv = _f64(qv).reshape(36).copy()
+    tau = _f64(tau)
+    hold = int(tau.ndim == 1)
+    out_qv, out_fc = np.zeros((n_steps, 36)), np.zeros((n_steps, 12))
+    pa = sim_params_array(params)
+    lib().oracle_sim_physics(_p(pa), _p(qv), _p(tau), C.c_int32(n_steps), C.c_int32(hold), _p(out_qv), _p(out_fc))
+    return qv, out_qv, out_fc
+
+
 def model_record(qv: np.ndarray) -> np.ndarray:
     qv = _f64(qv).reshape(36)
     dims = np.zeros(8, dtype=np.int32)
@@ -246,6 +272,16 @@ class OracleSolver:
         st = NmpcStats(*[out[k].ctypes.data for k in ("sqp_iter", "qp_iter", "qp_status", "res", "qp_res", "cost",
                                                       "qp_ncond")])
         self.lib.oracle_get_stats(self._h, C.byref(st))
+        return out
+
+    def sim_steps(self, params, qv: np.ndarray, n_interp: int, step0: int, n_steps: int):
+        """Checker of nmpc_sim_steps: closed loop of every rollout on the plan this solver holds."""
+        qv = _f64(qv).reshape(self.B, 36).copy()
+        out = dict(qv=np.zeros((self.B, n_steps, 36)), tau=np.zeros((self.B, n_steps, 12)), fc=np.zeros((self.B, n_steps, 12)))
+        pa = sim_params_array(params)
+        self.lib.oracle_sim_steps(self._h, _p(pa), C.c_int32(n_interp), C.c_int32(step0), C.c_int32(n_steps), _p(qv),
+                                  _p(out["qv"]), _p(out["tau"]), _p(out["fc"]))
+        out["qv_end"] = qv
         return out
 
     def get_qp_step(self) -> np.ndarray:
