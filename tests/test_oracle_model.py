@@ -124,7 +124,7 @@ def test_inverse_dynamics_static_is_gravity_minus_contacts(oracle_mod, num):
 
 def test_plan_torques_restatement_properties(oracle_mod):
     """oracle.plan_torques (checker of nmpc_plan_torques): Hermite interpolation reproduces the node values
-    at the node times, the inputs are held per `id_repeat`, and on the plan itself the PD term vanishes."""
+    at the node times, the inputs are held per `id_repeat`, and the PD term tracks the next plan sample."""
     O = oracle_mod
     rng = np.random.default_rng(0)
     B, N = 3, 25
@@ -135,8 +135,13 @@ def test_plan_torques_restatement_properties(oracle_mod):
     for k in range(1, N + 1):                     # sample 10k-1 of the plan is t = t_k
         np.testing.assert_allclose(r["q_plan"][:, 10 * k - 1], x[:, k, :18], atol=1e-12)
         np.testing.assert_allclose(r["v_plan"][:, 10 * k - 1], x[:, k, 18:36], atol=1e-12)
-    np.testing.assert_allclose(r["tau"], r["tau_ff"], atol=1e-12)
-    np.testing.assert_allclose(r["action"], (r["tau_ff"] + 1.75 * r["v_plan"][:, :, 6:]) / 20.0 + r["q_plan"][:, :, 6:],
+    # on the plan itself the PD term is the step to the NEXT plan sample (compute_torques_ff reads plan_step, _step()
+    # increments it, _compute_pd_torques reads the incremented one: mpc.py:575-599); it vanishes on the last sample
+    nxt = np.minimum(np.arange(n_interp) + 1, n_interp - 1)
+    pd = 20.0 * (r["q_plan"][:, nxt, 6:] - r["q_plan"][:, :, 6:]) + 1.75 * (r["v_plan"][:, nxt, 6:] - r["v_plan"][:, :, 6:])
+    np.testing.assert_allclose(r["tau"], r["tau_ff"] + pd, atol=1e-10)
+    np.testing.assert_allclose(r["tau"][:, -1], r["tau_ff"][:, -1], atol=1e-12)
+    np.testing.assert_allclose(r["action"], (r["tau"] + 1.75 * r["v_plan"][:, :, 6:]) / 20.0 + r["q_plan"][:, :, 6:],
                                atol=1e-12)
     idr = np.int32(np.linspace(0, 1, n_interp) * (N - 1))
     qva = np.concatenate([r["q_plan"][0], r["v_plan"][0], u[0, idr, :18]], axis=1)
