@@ -295,13 +295,15 @@ __device__ __noinline__ double fq_block_sum(double v, double* red, int tid)
 }
 
 // ---------------------------------------------------------------------------------------------
-// register tiles of the stage matrix, sorted by block type so that a warp meets at most three or
-// four different assembly formulas: {row type, column type, row block, column block}
+// register tiles of the stage matrix, one entry per thread: {row type, column type, row block, column block}.  Tiles of
+// one block type are kept in one warp wherever they fit (a warp executes every assembly formula it holds, one after the
+// other): warp 0 meets 2 u and 1 x formula, warps 1 and 3 two of each, warp 2 three and two.  Row type 7 (u) / 3 (x)
+// marks a thread without a tile; for those c_xtile[tid][2] numbers the 23 threads without a state tile.
 //   u tiles (3 x 6): rows of z = [a f q v h] (types 0..4) x columns a / f (types 0 / 1)
 //   x tiles (3 x 3): rows q / v / h (types 0..2) x columns q / v / h of the 42 x 42 state block
 // ---------------------------------------------------------------------------------------------
-__constant__ unsigned char c_utile[100][4] = {{0,0,0,0}, {0,0,1,0}, {0,0,2,0}, {0,0,3,0}, {0,0,4,0}, {0,0,5,0}, {0,0,2,1}, {0,0,3,1}, {0,0,4,1}, {0,0,5,1}, {0,0,4,2}, {0,0,5,2}, {1,0,6,0}, {1,0,7,0}, {1,0,8,0}, {1,0,9,0}, {1,0,6,1}, {1,0,7,1}, {1,0,8,1}, {1,0,9,1}, {1,0,6,2}, {1,0,7,2}, {1,0,8,2}, {1,0,9,2}, {2,0,10,0}, {2,0,11,0}, {2,0,12,0}, {2,0,13,0}, {2,0,14,0}, {2,0,15,0}, {2,0,10,1}, {2,0,11,1}, {2,0,12,1}, {2,0,13,1}, {2,0,14,1}, {2,0,15,1}, {2,0,10,2}, {2,0,11,2}, {2,0,12,2}, {2,0,13,2}, {2,0,14,2}, {2,0,15,2}, {3,0,16,0}, {3,0,17,0}, {3,0,18,0}, {3,0,19,0}, {3,0,20,0}, {3,0,21,0}, {3,0,16,1}, {3,0,17,1}, {3,0,18,1}, {3,0,19,1}, {3,0,20,1}, {3,0,21,1}, {3,0,16,2}, {3,0,17,2}, {3,0,18,2}, {3,0,19,2}, {3,0,20,2}, {3,0,21,2}, {4,0,22,0}, {4,0,23,0}, {4,0,22,1}, {4,0,23,1}, {4,0,22,2}, {4,0,23,2}, {1,1,6,3}, {1,1,7,3}, {1,1,8,3}, {1,1,9,3}, {1,1,8,4}, {1,1,9,4}, {2,1,10,3}, {2,1,11,3}, {2,1,12,3}, {2,1,13,3}, {2,1,14,3}, {2,1,15,3}, {2,1,10,4}, {2,1,11,4}, {2,1,12,4}, {2,1,13,4}, {2,1,14,4}, {2,1,15,4}, {3,1,16,3}, {3,1,17,3}, {3,1,18,3}, {3,1,19,3}, {3,1,20,3}, {3,1,21,3}, {3,1,16,4}, {3,1,17,4}, {3,1,18,4}, {3,1,19,4}, {3,1,20,4}, {3,1,21,4}, {4,1,22,3}, {4,1,23,3}, {4,1,22,4}, {4,1,23,4}};
-__constant__ unsigned char c_xtile[105][4] = {{0,0,0,0}, {0,0,1,0}, {0,0,1,1}, {0,0,2,0}, {0,0,2,1}, {0,0,2,2}, {0,0,3,0}, {0,0,3,1}, {0,0,3,2}, {0,0,3,3}, {0,0,4,0}, {0,0,4,1}, {0,0,4,2}, {0,0,4,3}, {0,0,4,4}, {0,0,5,0}, {0,0,5,1}, {0,0,5,2}, {0,0,5,3}, {0,0,5,4}, {0,0,5,5}, {1,0,6,0}, {1,0,6,1}, {1,0,6,2}, {1,0,6,3}, {1,0,6,4}, {1,0,6,5}, {1,0,7,0}, {1,0,7,1}, {1,0,7,2}, {1,0,7,3}, {1,0,7,4}, {1,0,7,5}, {1,0,8,0}, {1,0,8,1}, {1,0,8,2}, {1,0,8,3}, {1,0,8,4}, {1,0,8,5}, {1,0,9,0}, {1,0,9,1}, {1,0,9,2}, {1,0,9,3}, {1,0,9,4}, {1,0,9,5}, {1,0,10,0}, {1,0,10,1}, {1,0,10,2}, {1,0,10,3}, {1,0,10,4}, {1,0,10,5}, {1,0,11,0}, {1,0,11,1}, {1,0,11,2}, {1,0,11,3}, {1,0,11,4}, {1,0,11,5}, {1,1,6,6}, {1,1,7,6}, {1,1,7,7}, {1,1,8,6}, {1,1,8,7}, {1,1,8,8}, {1,1,9,6}, {1,1,9,7}, {1,1,9,8}, {1,1,9,9}, {1,1,10,6}, {1,1,10,7}, {1,1,10,8}, {1,1,10,9}, {1,1,10,10}, {1,1,11,6}, {1,1,11,7}, {1,1,11,8}, {1,1,11,9}, {1,1,11,10}, {1,1,11,11}, {2,0,12,0}, {2,0,12,1}, {2,0,12,2}, {2,0,12,3}, {2,0,12,4}, {2,0,12,5}, {2,0,13,0}, {2,0,13,1}, {2,0,13,2}, {2,0,13,3}, {2,0,13,4}, {2,0,13,5}, {2,1,12,6}, {2,1,12,7}, {2,1,12,8}, {2,1,12,9}, {2,1,12,10}, {2,1,12,11}, {2,1,13,6}, {2,1,13,7}, {2,1,13,8}, {2,1,13,9}, {2,1,13,10}, {2,1,13,11}, {2,2,12,12}, {2,2,13,12}, {2,2,13,13}};
+__constant__ unsigned char c_utile[128][4] = {{2,0,10,0}, {2,0,11,0}, {2,0,12,0}, {2,0,13,0}, {2,0,14,0}, {2,0,15,0}, {2,0,10,1}, {2,0,11,1}, {2,0,12,1}, {2,0,13,1}, {2,0,14,1}, {2,0,15,1}, {2,0,10,2}, {2,0,11,2}, {2,0,12,2}, {2,0,13,2}, {2,0,14,2}, {2,0,15,2}, {1,0,6,0}, {1,0,7,0}, {1,0,8,0}, {1,0,9,0}, {1,0,6,1}, {1,0,7,1}, {1,0,8,1}, {1,0,9,1}, {1,0,6,2}, {1,0,7,2}, {1,0,8,2}, {1,0,9,2}, {7,0,0,0}, {7,0,0,0}, {3,0,16,0}, {3,0,17,0}, {3,0,18,0}, {3,0,19,0}, {3,0,20,0}, {3,0,21,0}, {3,0,16,1}, {3,0,17,1}, {3,0,18,1}, {3,0,19,1}, {3,0,20,1}, {3,0,21,1}, {3,0,16,2}, {3,0,17,2}, {3,0,18,2}, {3,0,19,2}, {3,0,20,2}, {3,0,21,2}, {0,0,0,0}, {0,0,1,0}, {0,0,2,0}, {0,0,3,0}, {0,0,4,0}, {0,0,5,0}, {0,0,2,1}, {0,0,3,1}, {0,0,4,1}, {0,0,5,1}, {0,0,4,2}, {0,0,5,2}, {7,0,0,0}, {7,0,0,0}, {2,1,10,3}, {2,1,11,3}, {2,1,12,3}, {2,1,13,3}, {2,1,14,3}, {2,1,15,3}, {2,1,10,4}, {2,1,11,4}, {2,1,12,4}, {2,1,13,4}, {2,1,14,4}, {2,1,15,4}, {3,1,16,3}, {3,1,17,3}, {3,1,18,3}, {3,1,19,3}, {3,1,20,3}, {3,1,21,3}, {3,1,16,4}, {3,1,17,4}, {3,1,18,4}, {3,1,19,4}, {3,1,20,4}, {3,1,21,4}, {4,0,22,0}, {4,0,23,0}, {4,0,22,1}, {4,0,23,1}, {4,0,22,2}, {4,0,23,2}, {7,0,0,0}, {7,0,0,0}, {1,1,6,3}, {1,1,7,3}, {1,1,8,3}, {1,1,9,3}, {1,1,8,4}, {1,1,9,4}, {4,1,22,3}, {4,1,23,3}, {4,1,22,4}, {4,1,23,4}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}, {7,0,0,0}};
+__constant__ unsigned char c_xtile[128][4] = {{1,0,6,0}, {1,0,6,1}, {1,0,6,2}, {1,0,6,3}, {1,0,6,4}, {1,0,6,5}, {1,0,7,0}, {1,0,7,1}, {1,0,7,2}, {1,0,7,3}, {1,0,7,4}, {1,0,7,5}, {1,0,8,0}, {1,0,8,1}, {1,0,8,2}, {1,0,8,3}, {1,0,8,4}, {1,0,8,5}, {1,0,9,0}, {1,0,9,1}, {1,0,9,2}, {1,0,9,3}, {1,0,9,4}, {1,0,9,5}, {1,0,10,0}, {1,0,10,1}, {1,0,10,2}, {1,0,10,3}, {1,0,10,4}, {1,0,10,5}, {1,0,11,0}, {1,0,11,1}, {1,0,11,2}, {1,0,11,3}, {1,0,11,4}, {1,0,11,5}, {0,0,0,0}, {0,0,1,0}, {0,0,1,1}, {0,0,2,0}, {0,0,2,1}, {0,0,2,2}, {0,0,3,0}, {0,0,3,1}, {0,0,3,2}, {0,0,3,3}, {0,0,4,0}, {0,0,4,1}, {0,0,4,2}, {0,0,4,3}, {0,0,4,4}, {0,0,5,0}, {0,0,5,1}, {0,0,5,2}, {0,0,5,3}, {0,0,5,4}, {0,0,5,5}, {3,0,0,0}, {3,0,1,0}, {3,0,2,0}, {3,0,3,0}, {3,0,4,0}, {3,0,5,0}, {3,0,6,0}, {1,1,6,6}, {1,1,7,6}, {1,1,7,7}, {1,1,8,6}, {1,1,8,7}, {1,1,8,8}, {1,1,9,6}, {1,1,9,7}, {1,1,9,8}, {1,1,9,9}, {1,1,10,6}, {1,1,10,7}, {1,1,10,8}, {1,1,10,9}, {1,1,10,10}, {1,1,11,6}, {1,1,11,7}, {1,1,11,8}, {1,1,11,9}, {1,1,11,10}, {1,1,11,11}, {2,2,12,12}, {2,2,13,12}, {2,2,13,13}, {3,0,7,0}, {3,0,8,0}, {3,0,9,0}, {3,0,10,0}, {3,0,11,0}, {3,0,12,0}, {3,0,13,0}, {3,0,14,0}, {2,0,12,0}, {2,0,12,1}, {2,0,12,2}, {2,0,12,3}, {2,0,12,4}, {2,0,12,5}, {2,0,13,0}, {2,0,13,1}, {2,0,13,2}, {2,0,13,3}, {2,0,13,4}, {2,0,13,5}, {2,1,12,6}, {2,1,12,7}, {2,1,12,8}, {2,1,12,9}, {2,1,12,10}, {2,1,12,11}, {2,1,13,6}, {2,1,13,7}, {2,1,13,8}, {2,1,13,9}, {2,1,13,10}, {2,1,13,11}, {3,0,15,0}, {3,0,16,0}, {3,0,17,0}, {3,0,18,0}, {3,0,19,0}, {3,0,20,0}, {3,0,21,0}, {3,0,22,0}};
 
 // blocks of P_{k+1} (sP, ld 43; state order q 0..17, v 18..35, h 36..41) and of U = P[:,h] [Hf | Hq] (sU, ld 30)
 #define PQQ(i, j) sP[(i) * P_LD + (j)]
@@ -654,54 +656,108 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
         __syncthreads();
         FMARK(19);
         // ---- step 2: C z; dynamics residual ----
-        fq_cz(S, zc, rv + RV_CZ, tid);
-        if (!term && tid >= 80 && tid < 80 + NX) {
-            const int l = tid - 80;
-            double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
-            if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
-            vk[V_RB + l] = rb;
-            n_b = nanmax(n_b, fabs(rb));
+        // The long dot products are split so that no thread carries more than ~18 terms: the 22 state rows of C over
+        // two lanes each (threads 20..63), the six momentum rows of the dynamics over four lanes each (threads 100..123).
+        if (tid < 64) {
+            double s0 = 0.0, s1 = 0.0;
+            int j = tid;
+            if (tid < NGF) {
+                const double* cf = S + SR_CF + 3 * j;
+                const double* f = zc + IFRC + 3 * (j / 5);
+                s0 = cf[0] * f[0] + cf[1] * f[1] + cf[2] * f[2];
+            } else {
+                j = NGF + ((tid - NGF) >> 1);
+                const int half = tid & 1;
+                const double* cx = S + SR_CX + SR_CXLD * (j - NGF) + 18 * half;
+                const double* xx = zc + IQ + 18 * half;
+#pragma unroll
+                for (int c = 0; c < 18; c += 2) { s0 = fma(cx[c], xx[c], s0); s1 = fma(cx[c + 1], xx[c + 1], s1); }
+                if (half && j >= GR_CONS) s0 += zc[IH + j - GR_CONS];
+            }
+            double sres = s0 + s1;
+            const double oth = __shfl_xor_sync(0xffffffffu, sres, 1);
+            if (tid >= NGF) sres += oth;
+            if (tid < NGF || !(tid & 1)) rv[RV_CZ + j] = sres;
+        } else if (!term) {
+            if (tid < 64 + 2 * NQ) {
+                const int l = tid - 64;
+                double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
+                if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
+                vk[V_RB + l] = rb;
+                n_b = nanmax(n_b, fabs(rb));
+            }
+            if (tid >= 96) {                 // warp 3: all lanes take part in the shuffles
+                const int hi = min(max(tid - 100, 0) >> 2, 5), part = tid & 3;
+                const double* hq = S + SR_HQ + NQ * hi;
+                const double* hf = S + SR_HF + 12 * hi;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int j = part; j < NQ; j += 8) {
+                    s0 = fma(hq[j], zc[IQ + j], s0);
+                    if (j + 4 < NQ) s1 = fma(hq[j + 4], zc[IQ + j + 4], s1);
+                }
+#pragma unroll
+                for (int j = part; j < 12; j += 8) {
+                    s0 = fma(hf[j], zc[IFRC + j], s0);
+                    if (j + 4 < 12) s1 = fma(hf[j + 4], zc[IFRC + j + 4], s1);
+                }
+                double sres = s0 + s1;
+                sres += __shfl_xor_sync(0xffffffffu, sres, 1);
+                sres += __shfl_xor_sync(0xffffffffu, sres, 2);
+                if (part == 0 && tid >= 100 && tid < 124) {
+                    const int l = 2 * NQ + hi;
+                    double rb = sres + zc[IH + hi] + S[SR_B + l] - zxn[l];
+                    if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
+                    vk[V_RB + l] = rb;
+                    n_b = nanmax(n_b, fabs(rb));
+                }
+            }
         }
         __syncthreads();
         FMARK(20);
-        // ---- step 3: both sides of constraint row j: slacks, multipliers, rd, rm, Gamma, gamma ----
-        if (tid < NG) {
-            const int j = tid;
+        // ---- step 3: one side of a constraint row per thread (lanes 2j, 2j + 1): slacks, multipliers, rd, rm; Gamma,
+        //      gamma and lam_l - lam_u by one exchange inside the lane pair ----
+        if (tid < 96) {                  // warps 0..2: all lanes take part in the shuffles
+            const int j = min(tid >> 1, NG - 1), e = tid & 1, row = e * NG + j;
+            const bool live = tid < 2 * NG;
+            const bool msk = live && S[SR_D + 2 * NG + row] > 0.5;
             const double cz = rv[RV_CZ + j];
+            double t = sl[R_T + row], lam = sl[R_LAM + row];
+            if (upd && msk) {
+                t = fmax(fma(alpha_p, sl[R_DT + row], t), IPM_T_MIN);
+                lam = fmax(fma(alpha_d, sl[R_DT + 2 * NG + row], lam), IPM_LAM_MIN);
+                fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
+            }
+            const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
+            if (it == 0 && live) {       // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
+                if (msk) {
+                    if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 * __drcp_rn(t); }
+                    else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
+                } else { t = 1.0; lam = 0.0; }
+                fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
+            }
+            const double rd = msk ? (slack - t) : 0.0;
+            const double rm = msk ? lam * t : 0.0;
             double Gam = 0.0, gam = 0.0, dl = 0.0;
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-                const int row = e * NG + j;
-                const bool msk = S[SR_D + 2 * NG + row] > 0.5;
-                double t = sl[R_T + row], lam = sl[R_LAM + row];
-                if (upd && msk) {
-                    t = fmax(fma(alpha_p, sl[R_DT + row], t), IPM_T_MIN);
-                    lam = fmax(fma(alpha_d, sl[R_DT + 2 * NG + row], lam), IPM_LAM_MIN);
-                    fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
-                }
-                const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
-                if (it == 0) {               // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
-                    if (msk) {
-                        if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 * __drcp_rn(t); }
-                        else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
-                    } else { t = 1.0; lam = 0.0; }
-                    fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
-                }
-                const double rd = msk ? (slack - t) : 0.0;
-                const double rm = msk ? lam * t : 0.0;
+            if (live) {
                 vk[V_RD + row] = rd; vk[V_RM + row] = rm;
                 s_m += rm; cnt += msk ? 1 : 0;
                 n_d = nanmax(n_d, fabs(rd));
                 n_m = nanmax(n_m, fabs(rm));
-                if (msk) {
-                    const double ti = __drcp_rn(t);          // one reciprocal per side instead of two divisions
-                    const double g = (rm + lam * rd) * ti;
-                    Gam += lam * ti;
-                    if (e) { gam -= g; dl -= lam; } else { gam += g; dl += lam; }
-                }
             }
-            vk[V_GAM + j] = Gam;
-            rv[RV_GAMV + j] = gam; rv[RV_CZ + j] = dl;
+            if (msk) {
+                const double ti = __drcp_rn(t);          // one reciprocal per side instead of two divisions
+                const double g = (rm + lam * rd) * ti;
+                Gam = lam * ti;
+                gam = e ? -g : g; dl = e ? -lam : lam;
+            }
+            // lower side first, then upper: the same order of additions as the per-row form
+            const double Gam_o = __shfl_xor_sync(0xffffffffu, Gam, 1), gam_o = __shfl_xor_sync(0xffffffffu, gam, 1),
+                         dl_o = __shfl_xor_sync(0xffffffffu, dl, 1);
+            if (live && e == 0) {
+                vk[V_GAM + j] = Gam + Gam_o;
+                rv[RV_GAMV + j] = gam + gam_o; rv[RV_CZ + j] = dl + dl_o;
+            }
         }
         if (xthr) {          // the two bounds of dt: lb <= tau <= ub
             double Gam = 0.0, gam = 0.0, dl = 0.0;
@@ -795,10 +851,11 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
 
     // tile ownership, packed into one register (unpacked at each use: nothing but `tcode` stays live across a stage)
     unsigned tcode = 0;
-    if (tid < N_UTILES)
+    if (c_utile[tid][0] != 7)
         tcode |= c_utile[tid][0] | (c_utile[tid][1] << 3) | (c_utile[tid][2] << 4) | (c_utile[tid][3] << 9) | (1u << 24);
-    if (tid < N_XTILES)
+    if (c_xtile[tid][0] != 3)
         tcode |= (c_xtile[tid][0] << 12) | (c_xtile[tid][1] << 14) | (c_xtile[tid][2] << 16) | (c_xtile[tid][3] << 20) | (1u << 25);
+    const int free_ord = (c_xtile[tid][0] == 3) ? c_xtile[tid][2] : -1;      // ordinal among the threads without a state tile
 #define FQ_UNPACK_U                                                                                              \
     unsigned tc_ = tcode; asm volatile("" : "+r"(tc_));                                                          \
     const bool has_ut = (tc_ >> 24) & 1u;                                                                        \
@@ -1111,12 +1168,12 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
             }
         }
         if (tid < NX) fv[FV_PN + tid] = fv[FV_QT + NU + tid];
-        if (!term && tid >= N_XTILES) {
+        if (!term && free_ord >= 0) {
             // Inverses of the five 6 x 6 diagonal blocks of Luu, for the blocked triangular solves of passes A1 / D1 /
             // C2 (5 block steps instead of 30 scalar steps on the dependent chain).  The diagonal already holds
             // 1 / L_jj; the strictly lower part of the inverse goes, transposed, into the unused upper triangle of the
             // block, so nothing that is still being read is overwritten.  Done by the threads that own no state tile.
-            for (int col = tid - N_XTILES; col < NU; col += FQ_THREADS - N_XTILES) {
+            for (int col = free_ord; col < NU; col += FQ_THREADS - N_XTILES) {
                 double* blk = sM + P_OFF(col / PB);
                 const int cc = col % PB;
                 double x[PB];
