@@ -209,3 +209,35 @@ def test_batched_mpc_device_planning_equals_host_planning():
         out.append(bm.open_loop(q0, v0, T))
         assert all((s == 0).all() or True for s in bm.status_log) and len(bm.status_log) == 3
     assert np.abs(out[0][0] - out[1][0]).max() < 1e-9 and np.abs(out[0][1] - out[1][1]).max() < 1e-8
+
+
+def test_plan_torque_kernel_against_the_unbatched_controller_flow():
+    """nmpc_plan_torques against the reference's own control flow, step by step, on the same resident plan: the unbatched
+    `LocomotionMPC._compute_torques_ff` (feed-forward from a_plan / f_plan[plan_step], then `_step()`) followed by
+    `_compute_pd_torques` (PD on q_plan / v_plan[plan_step], already incremented; mpc.py:575-599) with measured states
+    that differ from the plan -- an independent checker of the kernel's indexing (advisor finding, round 1)."""
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import LocomotionMPC
+    from iterative_learning_nmpc_b200.mpc_controller.utils.dynamics import QuadrupedDynamics as QD
+    mpc = LocomotionMPC(None, FEET, "go2", gait_name="trot", print_info=False, solve_async=False,
+                        joint_ref=P.GO2_JOINT_HOME)
+    mpc.solver.cold_guess = "hold"
+    mpc.set_command(np.array([0.2, 0.0, 0.0]), 0.0)
+    rng = np.random.default_rng(17)
+    q = P.nominal_state(WL.STAND_HEIGHT)[:18].copy()
+    v = np.zeros(18)
+    n = 12
+    taus, meas = [], []
+    for s in range(n):
+        q_mj, v_mj = QD.convert_to_mujoco(q, v)
+        qe, ve = QD.convert_from_mujoco(q_mj, v_mj)
+        tff = mpc._compute_torques_ff(s * mpc.sim_dt, q_mj, v_mj)        # solves on the first call, then reads the plan
+        tau = mpc._compute_pd_torques(q_mj, v_mj, tff)
+        taus.append(tau); meas.append(np.concatenate((qe, ve)))
+        # the next measured state: the plan sample the controller just tracked, perturbed
+        q = mpc.q_plan[mpc.plan_step] + rng.normal(0, 0.01, 18)
+        v = mpc.v_plan[mpc.plan_step] + rng.normal(0, 0.05, 18)
+    h = mpc.solver.handle
+    out = h.plan_torques(mpc.n_interp_plan, 0, n, mpc.Kp, mpc.Kd, qv_meas=np.array(meas)[None])
+    err = np.abs(out["tau"][0] - np.array(taus)).max()
+    print("plan-torque kernel vs unbatched controller flow:", err)
+    assert err < 1e-8 and np.abs(np.array(taus)).max() > 1.0
