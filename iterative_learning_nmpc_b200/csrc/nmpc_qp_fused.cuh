@@ -656,108 +656,54 @@ __device__ __noinline__ uint32_t fq_pass_R(uint32_t ph, int it, int warm, double
         __syncthreads();
         FMARK(19);
         // ---- step 2: C z; dynamics residual ----
-        // The long dot products are split so that no thread carries more than ~18 terms: the 22 state rows of C over
-        // two lanes each (threads 20..63), the six momentum rows of the dynamics over four lanes each (threads 100..123).
-        if (tid < 64) {
-            double s0 = 0.0, s1 = 0.0;
-            int j = tid;
-            if (tid < NGF) {
-                const double* cf = S + SR_CF + 3 * j;
-                const double* f = zc + IFRC + 3 * (j / 5);
-                s0 = cf[0] * f[0] + cf[1] * f[1] + cf[2] * f[2];
-            } else {
-                j = NGF + ((tid - NGF) >> 1);
-                const int half = tid & 1;
-                const double* cx = S + SR_CX + SR_CXLD * (j - NGF) + 18 * half;
-                const double* xx = zc + IQ + 18 * half;
-#pragma unroll
-                for (int c = 0; c < 18; c += 2) { s0 = fma(cx[c], xx[c], s0); s1 = fma(cx[c + 1], xx[c + 1], s1); }
-                if (half && j >= GR_CONS) s0 += zc[IH + j - GR_CONS];
-            }
-            double sres = s0 + s1;
-            const double oth = __shfl_xor_sync(0xffffffffu, sres, 1);
-            if (tid >= NGF) sres += oth;
-            if (tid < NGF || !(tid & 1)) rv[RV_CZ + j] = sres;
-        } else if (!term) {
-            if (tid < 64 + 2 * NQ) {
-                const int l = tid - 64;
-                double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
-                if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
-                vk[V_RB + l] = rb;
-                n_b = nanmax(n_b, fabs(rb));
-            }
-            if (tid >= 96) {                 // warp 3: all lanes take part in the shuffles
-                const int hi = min(max(tid - 100, 0) >> 2, 5), part = tid & 3;
-                const double* hq = S + SR_HQ + NQ * hi;
-                const double* hf = S + SR_HF + 12 * hi;
-                double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-                for (int j = part; j < NQ; j += 8) {
-                    s0 = fma(hq[j], zc[IQ + j], s0);
-                    if (j + 4 < NQ) s1 = fma(hq[j + 4], zc[IQ + j + 4], s1);
-                }
-#pragma unroll
-                for (int j = part; j < 12; j += 8) {
-                    s0 = fma(hf[j], zc[IFRC + j], s0);
-                    if (j + 4 < 12) s1 = fma(hf[j + 4], zc[IFRC + j + 4], s1);
-                }
-                double sres = s0 + s1;
-                sres += __shfl_xor_sync(0xffffffffu, sres, 1);
-                sres += __shfl_xor_sync(0xffffffffu, sres, 2);
-                if (part == 0 && tid >= 100 && tid < 124) {
-                    const int l = 2 * NQ + hi;
-                    double rb = sres + zc[IH + hi] + S[SR_B + l] - zxn[l];
-                    if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
-                    vk[V_RB + l] = rb;
-                    n_b = nanmax(n_b, fabs(rb));
-                }
-            }
+        fq_cz(S, zc, rv + RV_CZ, tid);
+        if (!term && tid >= 80 && tid < 80 + NX) {
+            const int l = tid - 80;
+            double rb = fq_g(S, zc, l, dt, c2) + S[SR_B + l] - zxn[l];
+            if (TOPT) rb = fma(S[SR_X + SRX_B + l], rv[RV_X], rb);
+            vk[V_RB + l] = rb;
+            n_b = nanmax(n_b, fabs(rb));
         }
         __syncthreads();
         FMARK(20);
-        // ---- step 3: one side of a constraint row per thread (lanes 2j, 2j + 1): slacks, multipliers, rd, rm; Gamma,
-        //      gamma and lam_l - lam_u by one exchange inside the lane pair ----
-        if (tid < 96) {                  // warps 0..2: all lanes take part in the shuffles
-            const int j = min(tid >> 1, NG - 1), e = tid & 1, row = e * NG + j;
-            const bool live = tid < 2 * NG;
-            const bool msk = live && S[SR_D + 2 * NG + row] > 0.5;
+        // ---- step 3: both sides of constraint row j: slacks, multipliers, rd, rm, Gamma, gamma ----
+        if (tid < NG) {
+            const int j = tid;
             const double cz = rv[RV_CZ + j];
-            double t = sl[R_T + row], lam = sl[R_LAM + row];
-            if (upd && msk) {
-                t = fmax(fma(alpha_p, sl[R_DT + row], t), IPM_T_MIN);
-                lam = fmax(fma(alpha_d, sl[R_DT + 2 * NG + row], lam), IPM_LAM_MIN);
-                fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
-            }
-            const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
-            if (it == 0 && live) {       // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
-                if (msk) {
-                    if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 * __drcp_rn(t); }
-                    else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
-                } else { t = 1.0; lam = 0.0; }
-                fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
-            }
-            const double rd = msk ? (slack - t) : 0.0;
-            const double rm = msk ? lam * t : 0.0;
             double Gam = 0.0, gam = 0.0, dl = 0.0;
-            if (live) {
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int row = e * NG + j;
+                const bool msk = S[SR_D + 2 * NG + row] > 0.5;
+                double t = sl[R_T + row], lam = sl[R_LAM + row];
+                if (upd && msk) {
+                    t = fmax(fma(alpha_p, sl[R_DT + row], t), IPM_T_MIN);
+                    lam = fmax(fma(alpha_d, sl[R_DT + 2 * NG + row], lam), IPM_LAM_MIN);
+                    fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
+                }
+                const double slack = e ? (S[SR_D + NG + j] - cz) : (cz - S[SR_D + j]);
+                if (it == 0) {               // HPIPM INIT_VAR: levels 0 / 1 from the slacks, level 2 keeps lam, t clipped at thr0
+                    if (msk) {
+                        if (warm < 2 || !(t > 0.0) || !(lam > 0.0)) { t = fmax(slack, IPM_THR0); lam = IPM_MU0 * __drcp_rn(t); }
+                        else { t = fmax(t, IPM_THR0); lam = fmax(lam, IPM_THR0); }
+                    } else { t = 1.0; lam = 0.0; }
+                    fq_ctx.qt[(size_t)k * 2 * NG + row] = t; fq_ctx.qlam[(size_t)k * 2 * NG + row] = lam;
+                }
+                const double rd = msk ? (slack - t) : 0.0;
+                const double rm = msk ? lam * t : 0.0;
                 vk[V_RD + row] = rd; vk[V_RM + row] = rm;
                 s_m += rm; cnt += msk ? 1 : 0;
                 n_d = nanmax(n_d, fabs(rd));
                 n_m = nanmax(n_m, fabs(rm));
+                if (msk) {
+                    const double ti = __drcp_rn(t);          // one reciprocal per side instead of two divisions
+                    const double g = (rm + lam * rd) * ti;
+                    Gam += lam * ti;
+                    if (e) { gam -= g; dl -= lam; } else { gam += g; dl += lam; }
+                }
             }
-            if (msk) {
-                const double ti = __drcp_rn(t);          // one reciprocal per side instead of two divisions
-                const double g = (rm + lam * rd) * ti;
-                Gam = lam * ti;
-                gam = e ? -g : g; dl = e ? -lam : lam;
-            }
-            // lower side first, then upper: the same order of additions as the per-row form
-            const double Gam_o = __shfl_xor_sync(0xffffffffu, Gam, 1), gam_o = __shfl_xor_sync(0xffffffffu, gam, 1),
-                         dl_o = __shfl_xor_sync(0xffffffffu, dl, 1);
-            if (live && e == 0) {
-                vk[V_GAM + j] = Gam + Gam_o;
-                rv[RV_GAMV + j] = gam + gam_o; rv[RV_CZ + j] = dl + dl_o;
-            }
+            vk[V_GAM + j] = Gam;
+            rv[RV_GAMV + j] = gam; rv[RV_CZ + j] = dl;
         }
         if (xthr) {          // the two bounds of dt: lb <= tau <= ub
             double Gam = 0.0, gam = 0.0, dl = 0.0;
