@@ -241,3 +241,36 @@ def test_plan_torque_kernel_against_the_unbatched_controller_flow():
     err = np.abs(out["tau"][0] - np.array(taus)).max()
     print("plan-torque kernel vs unbatched controller flow:", err)
     assert err < 1e-8 and np.abs(np.array(taus)).max() > 1.0
+
+
+def test_async_solve_with_concurrent_id_torques():
+    """`solve_async=True` (the reference's default, mpc.py:164,516): the worker thread runs `optimize` (kinematics, init,
+    a 15-iteration solve) while the control thread keeps calling `id_torques` on the same handle, as the 1 kHz loop
+    does (mpc.py:544-545).  The handle serialises its solve path and runs the utility calls on their own stream and
+    staging buffer (advisor finding, round 1): the asynchronous plan equals the synchronous one bit for bit and every
+    concurrent torque equals the serial value."""
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import LocomotionMPC
+    rng = np.random.default_rng(23)
+    q = P.nominal_state(WL.STAND_HEIGHT)[:18].copy(); q[6:] += rng.uniform(-0.05, 0.05, 12)
+    v = rng.normal(0, 0.1, 18)
+    acc, f = rng.normal(0, 1.0, 18), np.tile([0.0, 0.0, 40.0], 4)
+    sols = {}
+    for mode in (True, False):
+        mpc = LocomotionMPC(None, FEET, "go2", gait_name="trot", print_info=False, solve_async=mode,
+                            joint_ref=P.GO2_JOINT_HOME)
+        mpc.solver.cold_guess = "hold"
+        mpc.set_command(np.array([0.2, 0.05, 0.0]), 0.1)
+        mpc.set_convergence_on_first_iter()                   # 15 SQP iterations: a solve of tens of milliseconds
+        if mode:
+            fut = mpc.executor.submit(mpc.optimize, q, v)
+            taus = []
+            while not fut.done():
+                taus.append(mpc.solver.dyn.id_torques(q, v, acc, f))
+            sols[mode] = [np.array(a) for a in fut.result()]
+            tau_ref = mpc.solver.dyn.id_torques(q, v, acc, f)
+            assert len(taus) >= 3, "the control thread was blocked behind the solve"
+            assert all(np.array_equal(t, tau_ref) for t in taus)
+        else:
+            sols[mode] = [np.array(a) for a in mpc.optimize(q, v)]
+    for a, b in zip(sols[True], sols[False]):
+        np.testing.assert_array_equal(a, b)
