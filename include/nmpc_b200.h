@@ -184,6 +184,13 @@ int nmpc_shift_warm_start(nmpc_handle* h, const int32_t* start_node, int32_t rep
 /* forget duals and the stored QP solution (AcadosSolverHelper.reset-like) */
 int nmpc_reset_duals(nmpc_handle* h);
 
+/* ---- checkpoint / resume ------------------------------------------ */
+/* The state a warm-started solve depends on -- iterate (x, u, pi, lam, dt), the stored QP solution, problem data --
+ * as one host blob of nmpc_state_bytes(h) bytes; import needs a handle of the same batch, horizon and nu. */
+int64_t nmpc_state_bytes(nmpc_handle* h);
+int nmpc_export_state(nmpc_handle* h, void* blob);
+int nmpc_import_state(nmpc_handle* h, const void* blob);
+
 /* ---- batched rigid-body rollout ---------------------------------- */
 /* Closes the loop around the resident plans without MuJoCo: what Rollout_MPC.run / Rollout_combined_controller do one
  * rollout at a time (Behavior_Cloning/utils/Rollout_MPC.py:465, DAgger/utils/Rollout_combined_controller.py:484-499)

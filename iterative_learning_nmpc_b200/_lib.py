@@ -108,6 +108,9 @@ _SIGS = {
     "nmpc_get_problem_data": (C.c_int, [C.c_void_p] + [C.c_void_p] * 4),
     "nmpc_plan_torques": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double]
                           + [C.c_void_p] * 5),
+    "nmpc_state_bytes": (C.c_int64, [C.c_void_p]),
+    "nmpc_export_state": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nmpc_import_state": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_sim_set_state": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_sim_get_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "nmpc_sim_steps": (C.c_int, [C.c_void_p, C.POINTER(NmpcSimParams), C.c_int32, C.c_int32, C.c_int32,

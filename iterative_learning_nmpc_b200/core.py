@@ -231,6 +231,19 @@ class NmpcSolver:
         dt = None if dt is None else _f64(dt, (self.B, self.N))
         check(self.lib.nmpc_set_dt(self._h, ptr(dt)), "nmpc_set_dt")
 
+    # -- checkpoint / resume ------------------------------------------------------------------
+    def export_state(self) -> np.ndarray:
+        """Iterate, stored QP solution and problem data as one uint8 array (nmpc_export_state)."""
+        blob = np.zeros(int(self.lib.nmpc_state_bytes(self._h)), dtype=np.uint8)
+        check(self.lib.nmpc_export_state(self._h, ptr(blob)), "nmpc_export_state")
+        return blob
+
+    def import_state(self, blob: np.ndarray):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        if blob.size != int(self.lib.nmpc_state_bytes(self._h)):
+            raise ValueError("state blob of another solver shape")
+        check(self.lib.nmpc_import_state(self._h, ptr(blob)), "nmpc_import_state")
+
     # -- batched rigid-body rollout (nmpc_rollout.cuh) ---------------------------------------
     def sim_set_state(self, qv):
         check(self.lib.nmpc_sim_set_state(self._h, ptr(_f64(qv, (self.B, 36)))), "nmpc_sim_set_state")

@@ -838,6 +838,66 @@ extern "C" int nmpc_plan_torques(nmpc_handle* h, const double* qv_meas, int32_t 
 }
 
 // ---------------------------------------------------------------------------------------------
+// checkpoint / resume of the solver state: everything a warm-started solve depends on
+// ---------------------------------------------------------------------------------------------
+struct StatePart { void* ptr; size_t bytes; };
+static int state_parts(nmpc_handle* h, StatePart* out)
+{
+    const size_t B = h->B, N = h->N;
+    int n = 0;
+    out[n++] = {h->x, B * (N + 1) * NX * 8}; out[n++] = {h->u, B * N * NU * 8}; out[n++] = {h->pi, B * N * NX * 8};
+    out[n++] = {h->lam, B * (N + 1) * 2 * NG * 8};
+    out[n++] = {h->qz, B * (N + 1) * NZ * 8}; out[n++] = {h->qpi, B * N * NX * 8};
+    out[n++] = {h->qlam, B * (N + 1) * 2 * NG * 8}; out[n++] = {h->qt, B * (N + 1) * 2 * NG * 8};
+    out[n++] = {h->dtn, B * N * 8}; out[n++] = {h->lamt, B * N * 2 * 8}; out[n++] = {h->qx, B * N * QX_SZ * 8};
+    out[n++] = {h->x0, B * NX * 8}; out[n++] = {h->p, B * (N + 1) * NPAR * 8};
+    out[n++] = {h->yref, B * N * NY * 8}; out[n++] = {h->yref_e, B * NYE * 8};
+    out[n++] = {h->W, B * NY * 8}; out[n++] = {h->We, B * NYE * 8};
+    return n;
+}
+
+extern "C" int64_t nmpc_state_bytes(nmpc_handle* h)
+{
+    if (!h) return 0;
+    StatePart parts[32];
+    const int n = state_parts(h, parts);
+    size_t tot = 16;                               // header: B, N, nu build, reserved
+    for (int i = 0; i < n; i++) tot += parts[i].bytes;
+    return (int64_t)tot;
+}
+
+// iterate (primal, dual, QP warm start, node durations) and problem data into / from a host blob of nmpc_state_bytes
+extern "C" int nmpc_export_state(nmpc_handle* h, void* blob)
+{
+    if (!h || !blob) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    StatePart parts[32];
+    const int n = state_parts(h, parts);
+    int32_t* hdr = (int32_t*)blob;
+    hdr[0] = h->B; hdr[1] = h->N; hdr[2] = NU + (h->o.enable_time_opt ? 1 : 0); hdr[3] = 0;
+    char* p = (char*)blob + 16;
+    for (int i = 0; i < n; i++) { CK(cudaMemcpyAsync(p, parts[i].ptr, parts[i].bytes, cudaMemcpyDeviceToHost, h->stream)); p += parts[i].bytes; }
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int nmpc_import_state(nmpc_handle* h, const void* blob)
+{
+    if (!h || !blob) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    const int32_t* hdr = (const int32_t*)blob;
+    if (hdr[0] != h->B || hdr[1] != h->N || hdr[2] != NU + (h->o.enable_time_opt ? 1 : 0)) return NMPC_EINVAL;
+    StatePart parts[32];
+    const int n = state_parts(h, parts);
+    const char* p = (const char*)blob + 16;
+    for (int i = 0; i < n; i++) { CK(cudaMemcpyAsync(parts[i].ptr, p, parts[i].bytes, cudaMemcpyHostToDevice, h->stream)); p += parts[i].bytes; }
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // batched rigid-body rollout (nmpc_rollout.cuh)
 // ---------------------------------------------------------------------------------------------
 static int ensure_sim(nmpc_handle* h)

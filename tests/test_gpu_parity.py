@@ -527,3 +527,28 @@ def test_config4_as_written(oracle_mod):
     for k in ("sqp_iter", "qp_iter", "qp_status"):
         np.testing.assert_array_equal(sg_s[k], so_s[k])
     assert report("config4 nlp residuals", sg_s["res"], so_s["res"]) < 1e-6
+
+
+def test_checkpoint_resume_continues_bit_identically(oracle_mod):
+    """nmpc_export_state / nmpc_import_state: a second handle resumed from the blob after tick 1 (warm-started full SQP
+    with hot-started QPs, time optimisation on) produces the same tick 2, bit for bit."""
+    O = oracle_mod
+    NmpcSolver, default_opts = _gpu()
+    B = 6
+    opts = dict(real_time_it=0, max_iter=2, warm_start_qp=2, enable_time_opt=1)
+    batch = WL.make_batch(B, seed=19)
+    _, _, hg = O.kinematics(batch["qv"])
+    a = NmpcSolver(B, default_opts(**opts))
+    WL.load_into(a, batch, hg)
+    a.solve()
+    blob = a.export_state()
+    b = NmpcSolver(B, default_opts(**opts))
+    b.import_state(blob)
+    for s in (a, b):
+        s.shift_warm_start(1)
+        s.solve()
+    for x, y in zip(a.get_solution(), b.get_solution()):
+        np.testing.assert_array_equal(x, y)
+    np.testing.assert_array_equal(a.get_dt(), b.get_dt())
+    with pytest.raises(Exception):
+        NmpcSolver(B + 1, default_opts(**opts)).import_state(blob)
