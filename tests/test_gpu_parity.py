@@ -552,3 +552,32 @@ def test_checkpoint_resume_continues_bit_identically(oracle_mod):
     np.testing.assert_array_equal(a.get_dt(), b.get_dt())
     with pytest.raises(Exception):
         NmpcSolver(B + 1, default_opts(**opts)).import_state(blob)
+
+
+@pytest.mark.parametrize("n_nodes,topt", [(1, 0), (2, 0), (5, 0), (5, 1), (40, 0), (64, 1)])
+def test_other_horizon_lengths(oracle_mod, n_nodes, topt):
+    """The horizon is a run-time parameter (1 <= N <= 64, NMPC_MAX_NODES): the rings of the passes, the shift warm start
+    and the time-opt bookkeeping at the shortest and the longest horizons, two warm-started SQP iterations."""
+    O = oracle_mod
+    NmpcSolver, default_opts = _gpu()
+    B = 5
+    opts = dict(n_nodes=n_nodes, real_time_it=0, max_iter=2, warm_start_qp=1, enable_time_opt=topt)
+    batch = WL.make_batch(B, seed=41, n_nodes=n_nodes, perturb=0.5)
+    _, _, hg = O.kinematics(batch["qv"])
+    so, sg = O.OracleSolver(B, O.default_opts(**opts)), NmpcSolver(B, default_opts(**opts))
+    WL.load_into(so, batch, hg)
+    WL.load_into(sg, batch, hg)
+    st_o, st_g = so.solve(0), sg.solve()
+    np.testing.assert_array_equal(st_g, st_o)
+    xo, uo, pio, lo = so.get_solution()
+    xg, ug, pig, lg = sg.get_solution()
+    if topt:
+        uo, dto, lo, lto = _split_topt(uo, lo)
+        dtg, ltg = sg.get_dt(duals=True)
+        assert chain_ok(f"N={n_nodes} dt", dtg, dto, REL) and chain_ok(f"N={n_nodes} lam_dt", ltg, lto, REL)
+    for name, a, b in (("x", xg, xo), ("u", ug, uo), ("pi", pig, pio), ("lam", lg, lo)):
+        assert chain_ok(f"N={n_nodes} {name}", a, b, REL), name
+    if n_nodes > 2:
+        so.shift_warm_start(1); sg.shift_warm_start(1)
+        for a, b in zip(sg.get_solution()[:2], so.get_solution()[:2]):
+            assert chain_ok(f"N={n_nodes} shifted", a, b[..., :a.shape[-1]], 10 * REL)
