@@ -581,3 +581,36 @@ def test_other_horizon_lengths(oracle_mod, n_nodes, topt):
         so.shift_warm_start(1); sg.shift_warm_start(1)
         for a, b in zip(sg.get_solution()[:2], so.get_solution()[:2]):
             assert chain_ok(f"N={n_nodes} shifted", a, b[..., :a.shape[-1]], 10 * REL)
+
+
+def test_time_opt_chunking_and_nan_containment(oracle_mod, monkeypatch):
+    """Time optimisation with the QP workspace in chunks (the dt bookkeeping is indexed by the global problem, the stage
+    records by the chunk) and with one poisoned problem: bit-identical to the unchunked solve, NaN confined."""
+    NmpcSolver, default_opts = _gpu()
+    B = 50
+    batch = WL.make_batch(B, seed=23)
+    _, _, hg = oracle_mod.kinematics(batch["qv"])
+    opts = dict(real_time_it=0, max_iter=2, enable_time_opt=1)
+    out = []
+    for chunk in (None, 16):
+        if chunk:
+            monkeypatch.setenv("NMPC_CHUNK", str(chunk))
+        else:
+            monkeypatch.delenv("NMPC_CHUNK", raising=False)
+        s = NmpcSolver(B, default_opts(**opts))
+        WL.load_into(s, batch, hg)
+        st = s.solve()
+        out.append((st, s.get_solution()[0], s.get_dt()))
+    np.testing.assert_array_equal(out[0][0], out[1][0])
+    np.testing.assert_array_equal(out[0][1], out[1][1])
+    np.testing.assert_array_equal(out[0][2], out[1][2])
+    monkeypatch.delenv("NMPC_CHUNK", raising=False)
+    bad = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in batch.items()}
+    bad["qv"][7, 20] = np.nan
+    s = NmpcSolver(B, default_opts(**opts))
+    WL.load_into(s, bad, hg)
+    st = s.solve()
+    assert st[7] == 1 and (np.delete(st, 7) == np.delete(out[0][0], 7)).all()
+    keep = np.arange(B) != 7
+    np.testing.assert_array_equal(s.get_solution()[0][keep], out[0][1][keep])
+    np.testing.assert_array_equal(s.get_dt()[keep], out[0][2][keep])
