@@ -43,10 +43,26 @@ def euler_to_mujoco(q: np.ndarray, v: np.ndarray):
     v_mj = v.copy()
     q_mj[:, :3] = q[:, :3]
     q_mj[:, 7:] = q[:, 6:]
-    for i in range(n):
-        x, y, z, w = matrix_to_quat(rpy_to_matrix(q[i, 3:6][::-1]))
-        q_mj[i, 3:7] = (w, x, y, z)
-        v_mj[i, 3:6] = euler_derivative_to_local_angular(q[i, 3:6], v[i, 3:6])
+    # vectorised over the samples (a closed-loop batch is 10^6 of them): Shepperd's branches of `matrix_to_quat`
+    # on R = Rz(yaw) Ry(pitch) Rx(roll), the Euler-rate map of `euler_derivative_to_local_angular`
+    from .problem import rpy_to_matrix_batch
+    R = rpy_to_matrix_batch(q[:, 5], q[:, 4], q[:, 3])
+    tr = R[:, 0, 0] + R[:, 1, 1] + R[:, 2, 2]
+    quat = np.zeros((n, 4))                                   # x y z w
+    pos = tr > 0
+    with np.errstate(invalid="ignore", divide="ignore"):
+        s4 = 2.0 * np.sqrt(np.where(pos, 1.0 + tr, 1.0))
+        quat[pos] = np.stack(((R[:, 2, 1] - R[:, 1, 2]) / s4, (R[:, 0, 2] - R[:, 2, 0]) / s4,
+                              (R[:, 1, 0] - R[:, 0, 1]) / s4, 0.25 * s4), axis=1)[pos]
+    for idx in np.nonzero(~pos)[0]:                           # rotations beyond 120 degrees: rare, done one by one
+        quat[idx] = matrix_to_quat(R[idx])
+    quat[pos] /= np.linalg.norm(quat[pos], axis=1, keepdims=True)
+    q_mj[:, 3], q_mj[:, 4:7] = quat[:, 3], quat[:, :3]
+    cx, sx, cy, sy = np.cos(q[:, 5]), np.sin(q[:, 5]), np.cos(q[:, 4]), np.sin(q[:, 4])
+    yd, pd, rd = v[:, 3], v[:, 4], v[:, 5]
+    v_mj[:, 3] = (-sy * yd + 0.0 * pd) + 1.0 * rd
+    v_mj[:, 4] = (cy * sx * yd + cx * pd) + 0.0 * rd
+    v_mj[:, 5] = (cx * cy * yd + -sx * pd) + 0.0 * rd
     return q_mj, v_mj
 
 
@@ -132,3 +148,22 @@ def save_hdf5(path: str, records: Sequence[Dict[str, np.ndarray]]) -> str:
         hf.create_dataset("traj_ids", data=np.concatenate([np.full(len(r["time"]), i) for i, r in enumerate(records)]))
         hf.create_dataset("traj_times", data=np.concatenate([r["time"] for r in records]))
     return path
+
+
+def closed_loop_to_rollouts(solver, res: Dict[str, np.ndarray], v_des: np.ndarray, sim_dt: float = 1.0e-3,
+                            kp: float = 20.0, kd: float = 1.5, t0: float = 0.0, contact_threshold: float = 1.0
+                            ) -> List[Dict[str, np.ndarray]]:
+    """Expert rollouts of `BatchedLocomotionMPC.closed_loop` in the reference's record layout -- what
+    `Rollout_MPC.run` records one MuJoCo rollout at a time (Rollout_MPC.py:218-298): the states are the simulated ones
+    the controller saw, `ctrl` the torques it applied, `action` the PD target that reproduces them, `contact_vec`
+    the feet whose contact force exceeds `contact_threshold` [N] (MuJoCo: the geoms in contact).
+    `res` = dict(qv [n,B,36], tau [n,B,12], fc [n,B,12]); `solver` supplies the device kinematics."""
+    qv, tau, fc = np.asarray(res["qv"]), np.asarray(res["tau"]), np.asarray(res["fc"])
+    n, B = qv.shape[:2]
+    feet, _, _ = solver.kinematics(qv.reshape(n * B, 36))
+    feet = np.asarray(feet).reshape(n, B, 4, 3)
+    times = t0 + sim_dt * np.arange(n)
+    v_des = np.broadcast_to(np.asarray(v_des, float), (B, 3))
+    contact = (fc.reshape(n, B, 4, 3)[..., 2] > contact_threshold)
+    return [rollout_record(times, qv[:, b, :18], qv[:, b, 18:], tau[:, b], feet[:, b], contact[:, b], v_des[b], kp, kd,
+                           rng=np.random.default_rng(b)) for b in range(B)]

@@ -59,3 +59,17 @@ def test_hdf5_needs_h5py(tmp_path):
     except ImportError:
         with pytest.raises(RuntimeError):
             DS.save_hdf5(str(tmp_path / "db.h5"), [])
+
+
+def test_euler_to_mujoco_vectorised_matches_the_per_sample_maps():
+    """The vectorised conversion against `QuadrupedDynamics.convert_to_mujoco` sample by sample, including rotations
+    beyond 120 degrees (the other branches of the quaternion extraction)."""
+    from iterative_learning_nmpc_b200 import dataset as DS
+    from iterative_learning_nmpc_b200.mpc_controller.utils.dynamics import QuadrupedDynamics as QD
+    rng = np.random.default_rng(0)
+    q = rng.normal(0, 0.5, (200, 18)); v = rng.normal(0, 1.0, (200, 18))
+    q[:50, 3:6] = rng.uniform(-3.1, 3.1, (50, 3)); q[:50, 4] = rng.uniform(-1.4, 1.4, 50)
+    qm, vm = DS.euler_to_mujoco(q, v)
+    for i in range(200):
+        a, b = QD.convert_to_mujoco(q[i], v[i])
+        assert np.abs(qm[i] - a).max() < 1e-12 and np.abs(vm[i] - b).max() < 1e-12

@@ -68,3 +68,33 @@ def test_closed_loop_trot_walks_forward():
     assert np.allclose(fz, mass * 9.81, rtol=0.05)
     moved = qe[:, 0] - q0[:, 0]
     assert np.abs(moved - np.round(vx, 1) * T).max() < 0.06 and moved[-1] > 0.2
+
+
+def test_closed_loop_rollouts_written_in_the_reference_format(tmp_path):
+    """Closed-loop rollouts of the batched simulation as the reference's per-rollout `.npz` (Rollout_MPC.py:183-216):
+    keys, shapes, `state` / `action` construction, real contact flags from the contact forces."""
+    from iterative_learning_nmpc_b200 import dataset as DS
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import BatchedLocomotionMPC
+    B, T = 4, 0.3
+    bm = BatchedLocomotionMPC(B, None, FEET, "go2", gait_name="trot", joint_ref=P.GO2_JOINT_HOME)
+    q0 = np.tile(P.nominal_state(bm.config_gait.nom_height)[:18], (B, 1))
+    feet, _, _ = bm.solver.handle.kinematics(np.concatenate((q0, np.zeros((B, 18))), axis=1))
+    q0[:, 2] -= feet[:, :, 2].min(axis=1)
+    v_des = np.array([[0.0, 0, 0], [0.1, 0, 0], [0.2, 0, 0], [0.3, 0, 0]])
+    bm.set_command(v_des, 0.0)
+    res = bm.closed_loop(q0, np.zeros((B, 18)), T)
+    recs = DS.closed_loop_to_rollouts(bm.solver.handle, res, v_des, bm.sim_dt, bm.Kp, bm.Kd)
+    n = res["qv"].shape[0]
+    assert len(recs) == B and n == 301
+    for b, r in enumerate(recs):
+        assert set(r) == set(DS.KEYS)
+        assert r["q"].shape == (n, 19) and r["v"].shape == (n, 18) and r["state"].shape == (n, 44)
+        assert r["action"].shape == (n, 12) and r["ctrl"].shape == (n, 12) and r["contact_vec"].shape == (n, 4)
+        # the PD target reproduces the applied torque: tau = kp (action - q_j) - kd v_j
+        tau = bm.Kp * (r["action"] - r["q"][:, 7:]) - bm.Kd * r["v"][:, 6:]
+        np.testing.assert_allclose(tau[:, np.r_[3:6, 0:3, 9:12, 6:9]], r["ctrl"], atol=1e-9)
+        assert np.allclose(np.linalg.norm(r["q"][:, 3:7], axis=1), 1.0)
+        assert 1.5 < r["contact_vec"][100:].sum(axis=1).mean() < 4.0       # a trot: about two feet on the ground
+        path = DS.save_rollout(r, str(tmp_path), nominal=False, replanning_point=b, nth_traj=0)
+        back = np.load(path)
+        assert sorted(back.files) == sorted(DS.KEYS) and np.array_equal(back["state"], r["state"])
