@@ -12,7 +12,7 @@ Reference (one rollout, one MuJoCo step at a time):
       action           (tau_FLFRRLRR + kd v[6:]) / kp + q[7:]            (PD target)
   `:205-207` file names `traj_nominal_<timestamp>.npz` / `traj_<replanning_point>_<nth>.npz`
   `Behavior_Cloning/utils/database.py:156-203` HDF5 with states, actions, vc_goals, cc_goals, traj_ids, traj_times
-  (written only when `h5py` is importable: it is not part of this image).
+  (through `h5py` when it is importable, else through the built-in writer `hdf5_min.py`: h5py is not part of this image).
 
 The rollout here is the sim-free one of `LocomotionMPC.open_loop` (mpc.py:416-462): the recorded
 states are the plan's own samples (`nmpc_plan_torques`, evaluated on the plan), `contact_vec` is the
@@ -135,19 +135,35 @@ def batch_to_rollouts(solver, batch: Dict[str, np.ndarray], sim_dt: float = 1.0e
 
 def save_hdf5(path: str, records: Sequence[Dict[str, np.ndarray]]) -> str:
     """`Database` file of the reference's training code (database.py:156-203): states, actions, vc_goals,
-    cc_goals, traj_ids, traj_times stacked over rollouts.  Needs h5py."""
+    cc_goals, traj_ids, traj_times stacked over rollouts.  Written through h5py when it is installed, else by the
+    built-in writer `hdf5_min.write_hdf5` (same dataset names, shapes and dtypes; contiguous, uncompressed)."""
+    if not len(records):
+        raise ValueError("save_hdf5 needs at least one rollout record")
+    data = {
+        "states": np.concatenate([r["state"] for r in records]).astype(np.float64),
+        "actions": np.concatenate([r["action"] for r in records]).astype(np.float64),
+        "vc_goals": np.concatenate([r["vc_goals"] for r in records]).astype(np.float64),
+        "cc_goals": np.concatenate([r["cc_goals"] for r in records]).astype(np.float64),
+        "traj_ids": np.concatenate([np.full(len(r["time"]), i, dtype=np.int64) for i, r in enumerate(records)]),
+        "traj_times": np.concatenate([r["time"] for r in records]).astype(np.float64),
+    }
     try:
         import h5py
-    except ImportError as e:                                     # not in this image: fail loudly, no silent format change
-        raise RuntimeError("h5py is not installed: write per-rollout .npz files with save_rollout instead") from e
+    except ImportError:                                          # not in this image
+        from .hdf5_min import write_hdf5
+        return write_hdf5(path, data)
     with h5py.File(path, "w") as hf:
-        hf.create_dataset("states", data=np.concatenate([r["state"] for r in records]))
-        hf.create_dataset("actions", data=np.concatenate([r["action"] for r in records]))
-        hf.create_dataset("vc_goals", data=np.concatenate([r["vc_goals"] for r in records]))
-        hf.create_dataset("cc_goals", data=np.concatenate([r["cc_goals"] for r in records]))
-        hf.create_dataset("traj_ids", data=np.concatenate([np.full(len(r["time"]), i) for i, r in enumerate(records)]))
-        hf.create_dataset("traj_times", data=np.concatenate([r["time"] for r in records]))
+        for name, arr in data.items():
+            hf.create_dataset(name, data=arr)
     return path
+
+
+def load_hdf5(path: str) -> Dict[str, np.ndarray]:
+    """Read a `Database` file back the way `Database.load_saved_database` does (database.py:172-198).  Needs h5py:
+    the built-in writer has no reader in the product (tests/hdf5_reader.py is the checker)."""
+    import h5py
+    with h5py.File(path, "r") as hf:
+        return {k: hf[k][:] for k in hf.keys()}
 
 
 def closed_loop_to_rollouts(solver, res: Dict[str, np.ndarray], v_des: np.ndarray, sim_dt: float = 1.0e-3,

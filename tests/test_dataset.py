@@ -52,13 +52,72 @@ def test_npz_round_trip_and_file_names(tmp_path):
         DS.save_rollout(bad, str(tmp_path))
 
 
-def test_hdf5_needs_h5py(tmp_path):
-    pytest.importorskip("numpy")
+def _records(n_rollouts=3, seed=0):
+    rng = np.random.default_rng(seed)
+    recs = []
+    for i in range(n_rollouts):
+        T = 5 + 3 * i
+        recs.append(dict(state=rng.normal(size=(T, 44)), action=rng.normal(size=(T, 12)),
+                         vc_goals=rng.normal(size=(T, 5)), cc_goals=rng.normal(size=(T, 8)),
+                         time=0.001 * np.arange(T)))
+    return recs
+
+
+def test_hdf5_database_file_round_trips_through_the_independent_reader(tmp_path):
+    """`save_hdf5` without h5py: the built-in writer's file parsed by tests/hdf5_reader.py (superblock -> symbol table
+    -> object headers -> raw data, every signature / version / size checked) gives back the Database datasets of
+    database.py:156-203 bit for bit."""
+    from hdf5_reader import read_hdf5
+    recs = _records()
+    path = DS.save_hdf5(str(tmp_path / "db.h5"), recs)
     try:
-        import h5py  # noqa: F401
+        import h5py
+        with h5py.File(path, "r") as hf:
+            back = {k: hf[k][:] for k in hf.keys()}
     except ImportError:
-        with pytest.raises(RuntimeError):
-            DS.save_hdf5(str(tmp_path / "db.h5"), [])
+        back = read_hdf5(path)
+    assert sorted(back) == ["actions", "cc_goals", "states", "traj_ids", "traj_times", "vc_goals"]
+    np.testing.assert_array_equal(back["states"], np.concatenate([r["state"] for r in recs]))
+    np.testing.assert_array_equal(back["actions"], np.concatenate([r["action"] for r in recs]))
+    np.testing.assert_array_equal(back["vc_goals"], np.concatenate([r["vc_goals"] for r in recs]))
+    np.testing.assert_array_equal(back["cc_goals"], np.concatenate([r["cc_goals"] for r in recs]))
+    np.testing.assert_array_equal(back["traj_times"], np.concatenate([r["time"] for r in recs]))
+    assert back["traj_ids"].dtype == np.int64 and back["states"].dtype == np.float64
+    np.testing.assert_array_equal(back["traj_ids"], np.repeat([0, 1, 2], [5, 8, 11]))
+    with pytest.raises(ValueError):
+        DS.save_hdf5(str(tmp_path / "empty.h5"), [])
+
+
+def test_hdf5_min_writer_layout(tmp_path):
+    """The built-in writer on its own: header constants, alignment, special values, the 8-dataset limit; the reader
+    rejects a corrupted file instead of returning data."""
+    from hdf5_reader import Hdf5FormatError, read_hdf5
+    from iterative_learning_nmpc_b200.hdf5_min import write_hdf5
+    d = {"a": np.array([[0.0, -0.0, np.inf], [np.nan, 1e-310, -1.5e300]]), "b": np.array([-2 ** 63, 2 ** 63 - 1, 0]),
+         "zz": np.zeros((0, 7)), "m": np.arange(24, dtype=np.float32).reshape(2, 3, 4), "s": np.float64(3.5)}
+    path = write_hdf5(str(tmp_path / "t.h5"), d)
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"\x89HDF\r\n\x1a\n" and int.from_bytes(raw[40:48], "little") == len(raw)
+    back = read_hdf5(path)
+    assert list(back) == sorted(d)
+    assert back["a"].tobytes() == d["a"].tobytes()                # bit patterns: signed zero, NaN, subnormal
+    np.testing.assert_array_equal(back["b"], d["b"])
+    assert back["zz"].shape == (0, 7) and back["m"].shape == (2, 3, 4) and back["m"].dtype == np.float64
+    np.testing.assert_array_equal(back["m"], d["m"])
+    assert back["s"].shape == (1,) and back["s"][0] == 3.5
+    with pytest.raises(ValueError):
+        write_hdf5(str(tmp_path / "many.h5"), {f"d{i}": np.zeros(2) for i in range(9)})
+    with pytest.raises(ValueError):
+        write_hdf5(str(tmp_path / "none.h5"), {})
+    for off, val in ((0, b"X"), (8, b"\x02"), (len(raw) - 1, None)):
+        bad = bytearray(raw)
+        if val is None:
+            bad = bad[:-1]                                       # truncated: end-of-file address no longer matches
+        else:
+            bad[off:off + 1] = val
+        (tmp_path / "bad.h5").write_bytes(bytes(bad))
+        with pytest.raises(Hdf5FormatError):
+            read_hdf5(str(tmp_path / "bad.h5"))
 
 
 def test_euler_to_mujoco_vectorised_matches_the_per_sample_maps():
