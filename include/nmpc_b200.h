@@ -160,6 +160,28 @@ int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq
                    const double* tracking, int32_t advance_steps, double sim_dt, double nom_height,
                    double height_offset, double t_horizon, const double* joint_ref, double step_height,
                    const double* p_gain, int32_t opt_peak);
+/* Parameters of RaiberContactPlanner (contact_planner.py:190-233) and the contact-patch radius of the cost config. */
+typedef struct nmpc_raibert_params {
+    double offset_hip_b[12];   /* [4][3] hip offsets in the base frame, x_offset / y_offset applied, z = 0 */
+    double stance_ratio[4];    /* GaitConfig.stance_ratio */
+    double nominal_period;     /* GaitConfig.nominal_period [s] */
+    double foot_size;          /* z of a planned contact */
+    double height_offset;      /* subtracted from the CoM height */
+    double gravity;            /* RaiberContactPlanner.GRAVITY = 9.81 */
+    double cnt_radius;         /* cost config cnt_radius: half-width of the contact patch (solver.py:227-252) */
+} nmpc_raibert_params;
+/* LocomotionMPC.optimize with contact_planner="raibert", on the device (BASELINE config 4):
+ * update_pin's centre of mass, GaitPlanner.get_contacts / get_peaks, RaiberContactPlanner.get_locations with
+ * cache_cnt=False as LocomotionMPC builds it (contact_planner.py:265-322; mpc.py:76-90),
+ * compute_base_ref_cnt_restricted (mpc.py:274-315), then the expansion of nmpc_init_tick with restrict_cnt = 1.
+ * make_seq int8 [4, nodes_per_cycle] is 1 on the cycle node where a foot touches down (GaitPlanner.switch_cnt == 1);
+ * qv [B,36] Euler state; t_cnt [N+1] = round(j * dt_nodes, 3) as the host computes it; cnt_locations, if not NULL,
+ * receives the planned footholds [B,4,N+1,3] (the call then synchronises). */
+int nmpc_plan_tick_raibert(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq, const int8_t* peak_seq,
+                           const int8_t* make_seq, int32_t nodes_per_cycle, const double* qv, const double* v_des,
+                           const double* w_yaw, const double* t_cnt, const nmpc_raibert_params* rp, double nom_height,
+                           double height_offset, const double* joint_ref, double step_height, const double* p_gain,
+                           int32_t opt_peak, double* cnt_locations);
 /* base_ref_vel_tracking [B,12] as held (and advanced) on the device */
 int nmpc_get_tracking(nmpc_handle* h, double* tracking);
 /* cold first guess of the batched front-end: x0 held over the horizon, zero accelerations, the robot's

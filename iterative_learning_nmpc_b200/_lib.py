@@ -40,6 +40,13 @@ class NmpcSimParams(C.Structure):
                 ("tau_max", C.c_double)]
 
 
+class NmpcRaibertParams(C.Structure):
+    """nmpc_raibert_params: RaiberContactPlanner on the device (include/nmpc_b200.h)."""
+    _fields_ = [("offset_hip_b", C.c_double * 12), ("stance_ratio", C.c_double * 4), ("nominal_period", C.c_double),
+                ("foot_size", C.c_double), ("height_offset", C.c_double), ("gravity", C.c_double),
+                ("cnt_radius", C.c_double)]
+
+
 def default_sim_params(**kw) -> NmpcSimParams:
     p = NmpcSimParams(sim_dt=1.0e-3, kp=20.0, kd=1.5, k_n=2.0e4, d_n=60.0, d_t=60.0, mu=0.8, ground_z=0.0, tau_max=0.0)
     for k, v in kw.items():
@@ -103,6 +110,9 @@ _SIGS = {
     "nmpc_plan_tick": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,
                                  C.c_void_p, C.c_double, C.c_void_p, C.c_int32]),
+    "nmpc_plan_tick_raibert": (C.c_int, [C.c_void_p] * 5 + [C.c_int32] + [C.c_void_p] * 4
+                               + [C.POINTER(NmpcRaibertParams), C.c_double, C.c_double, C.c_void_p, C.c_double,
+                                  C.c_void_p, C.c_int32, C.c_void_p]),
     "nmpc_get_tracking": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_cold_guess": (C.c_int, [C.c_void_p]),
     "nmpc_get_problem_data": (C.c_int, [C.c_void_p] + [C.c_void_p] * 4),

@@ -154,6 +154,35 @@ class NmpcSolver:
                                       float(t_horizon), ptr(jr), float(step_height), ptr(gain), int(bool(opt_peak))),
               "nmpc_plan_tick")
 
+    def plan_tick_raibert(self, i_node, gait_seq, peak_seq, make_seq, qv, v_des, w_yaw, t_cnt, offset_hip_b,
+                          stance_ratio, nominal_period: float, foot_size: float, planner_height_offset: float,
+                          cnt_radius: float, nom_height: float, height_offset: float, joint_ref, step_height: float,
+                          p_gain, opt_peak: bool = True, gravity: float = 9.81, want_locations: bool = False):
+        """Planning + `init` on the device for the Raibert contact planner (nmpc_plan_tick_raibert): i_node [B], the
+        gait cycle tables int8 [4, nodes_per_cycle] (stance, swing, touch-down), qv [B,36], v_des [B,3], w_yaw [B],
+        t_cnt [N+1] = round(j * dt_nodes, 3).  Returns the footholds [B,4,N+1,3] when `want_locations`."""
+        from ._lib import NmpcRaibertParams
+        B, N1 = self.B, self.N + 1
+        node = _i32(i_node, (B,))
+        gs, ps, ms = (np.ascontiguousarray(t, dtype=np.int8) for t in (gait_seq, peak_seq, make_seq))
+        assert gs.shape == ps.shape == ms.shape and gs.shape[0] == 4
+        q, vd, wy = _f64(qv, (B, 36)), _f64(v_des, (B, 3)), _f64(w_yaw, (B,))
+        tc = np.ascontiguousarray(t_cnt, dtype=np.float64).reshape(N1)
+        jr = np.ascontiguousarray(joint_ref, dtype=np.float64).reshape(12)
+        gain = np.ascontiguousarray(p_gain, dtype=np.float64).reshape(4)
+        rp = NmpcRaibertParams(nominal_period=float(nominal_period), foot_size=float(foot_size),
+                               height_offset=float(planner_height_offset), gravity=float(gravity),
+                               cnt_radius=float(cnt_radius))
+        rp.offset_hip_b[:] = [float(x) for x in np.asarray(offset_hip_b, dtype=float).reshape(12)]
+        rp.stance_ratio[:] = [float(x) for x in np.asarray(stance_ratio, dtype=float).reshape(4)]
+        loc = np.zeros((B, 4, N1, 3)) if want_locations else None
+        _order_after_torch(self, q, vd, wy)
+        check(self.lib.nmpc_plan_tick_raibert(self._h, ptr(node), ptr(gs), ptr(ps), ptr(ms), int(gs.shape[1]), ptr(q),
+                                              ptr(vd), ptr(wy), ptr(tc), rp, float(nom_height), float(height_offset),
+                                              ptr(jr), float(step_height), ptr(gain), int(bool(opt_peak)), ptr(loc)),
+              "nmpc_plan_tick_raibert")
+        return loc
+
     def get_tracking(self) -> np.ndarray:
         tr = np.zeros((self.B, 12))
         check(self.lib.nmpc_get_tracking(self._h, ptr(tr)), "nmpc_get_tracking")

@@ -384,6 +384,80 @@ extern "C" int nmpc_plan_tick(nmpc_handle* h, const int32_t* i_node, const int8_
     return (int)cudaGetLastError();
 }
 
+// LocomotionMPC.optimize with contact_planner="raibert" on the device (nmpc_init.cuh): centre of mass by the model
+// kernel, contact / swing windows, Raibert footholds, the contact-restricted base references, then the expansion of
+// nmpc_init_tick with the contact restriction on.  Every array may be a host or a device pointer.
+extern "C" int nmpc_plan_tick_raibert(nmpc_handle* h, const int32_t* i_node, const int8_t* gait_seq,
+                                      const int8_t* peak_seq, const int8_t* make_seq, int32_t nodes_per_cycle,
+                                      const double* qv, const double* v_des, const double* w_yaw, const double* t_cnt,
+                                      const nmpc_raibert_params* rp, double nom_height, double height_offset,
+                                      const double* joint_ref, double step_height, const double* p_gain,
+                                      int32_t opt_peak, double* cnt_locations)
+{
+    if (!h || !i_node || !gait_seq || !peak_seq || !make_seq || nodes_per_cycle < 1 || !qv || !v_des || !w_yaw ||
+        !t_cnt || !rp || !joint_ref || !p_gain) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    const size_t B = h->B, N1 = h->N + 1, npc = nodes_per_cycle;
+    const size_t n_cnt = B * NF * N1, cnt_pad = (n_cnt + 7) & ~(size_t)7, seq_pad = (NF * npc + 7) & ~(size_t)7;
+    // doubles: qv 36 | com 3 | v_des 3 | w 1 | ref 12 | ref_e 12 | loc 12 (N+1) per problem, t_cnt N+1, joint_ref 12, step height 1
+    const size_t n_d = B * (67 + 12 * N1) + N1 + 13;
+    const size_t bytes = n_d * 8 + ((B * 4 + 7) & ~(size_t)7) + 3 * seq_pad + 2 * cnt_pad;
+    if (int r = ensure_scratch(h, bytes)) return r;
+    double* d_qv = h->scratch;
+    double* d_com = d_qv + B * 36;
+    double* d_vd = d_com + B * 3;
+    double* d_w = d_vd + B * 3;
+    double* d_ref = d_w + B;
+    double* d_ref_e = d_ref + B * 12;
+    double* d_loc = d_ref_e + B * 12;
+    double* d_tc = d_loc + B * 12 * N1;
+    double* d_jr = d_tc + N1;
+    double* d_sh = d_jr + 12;
+    int32_t* d_node = reinterpret_cast<int32_t*>(d_sh + 1);
+    signed char* d_gs = reinterpret_cast<signed char*>(d_node) + ((B * 4 + 7) & ~(size_t)7);
+    signed char* d_ps = d_gs + seq_pad;
+    signed char* d_ms = d_ps + seq_pad;
+    signed char* d_cnt = d_ms + seq_pad;
+    signed char* d_peak = d_cnt + cnt_pad;
+    CK(cudaMemcpyAsync(d_qv, qv, B * 36 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_vd, v_des, B * 3 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_w, w_yaw, B * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_tc, t_cnt, N1 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_jr, joint_ref, 12 * 8, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_sh, &step_height, 8, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_node, i_node, B * 4, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_gs, gait_seq, NF * npc, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_ps, peak_seq, NF * npc, cudaMemcpyDefault, h->stream));
+    CK(cudaMemcpyAsync(d_ms, make_seq, NF * npc, cudaMemcpyDefault, h->stream));
+    nmpc_kin0_kernel<<<(h->B + 63) / 64, 64, 0, h->stream>>>(d_qv, h->B, nullptr, d_com, nullptr);
+    RaibertArgs ra;
+    ra.i_node = d_node; ra.gait_seq = d_gs; ra.peak_seq = d_ps; ra.make_seq = d_ms; ra.qv = d_qv; ra.com = d_com;
+    ra.v_des = d_vd; ra.w_yaw = d_w; ra.t_cnt = d_tc;
+    for (int i = 0; i < NF * 3; i++) ra.rp.offset_hip_b[i] = rp->offset_hip_b[i];
+    for (int f = 0; f < NF; f++) ra.rp.stance_ratio[f] = rp->stance_ratio[f];
+    ra.rp.nominal_period = rp->nominal_period; ra.rp.foot_size = rp->foot_size;
+    ra.rp.height_offset = rp->height_offset; ra.rp.gravity = rp->gravity;
+    ra.nom_height = nom_height; ra.height_offset = height_offset;
+    ra.npc = nodes_per_cycle; ra.N = h->N; ra.B = h->B;
+    ra.base_ref = d_ref; ra.base_ref_e = d_ref_e; ra.cnt = d_cnt; ra.peak = d_peak; ra.loc = d_loc;
+    nmpc_plan_raibert_kernel<<<h->B, 128, 0, h->stream>>>(ra);
+    TickArgs a;
+    a.base_ref = d_ref; a.base_ref_e = d_ref_e; a.joint_ref = d_jr; a.step_height = d_sh;
+    a.cnt = d_cnt; a.peak = opt_peak ? d_peak : nullptr; a.loc = d_loc;
+    for (int f = 0; f < NF; f++) a.p_gain[f] = p_gain[f];
+    a.radius = rp->cnt_radius; a.height_offset = height_offset; a.restrict_cnt = 1;
+    a.joint_per_problem = 0; a.height_per_problem = 0;
+    a.p = h->p; a.yref = h->yref; a.yref_e = h->yref_e; a.B = h->B; a.N = h->N;
+    nmpc_init_tick_kernel<<<h->B, 128, 0, h->stream>>>(a);
+    h->launches += 3;
+    if (cnt_locations) {
+        CK(cudaMemcpyAsync(cnt_locations, d_loc, B * 12 * N1 * 8, cudaMemcpyDefault, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return (int)cudaGetLastError();
+}
+
 // the tracked reference pose [B,12] as nmpc_plan_tick holds (and advances) it on the device
 extern "C" int nmpc_get_tracking(nmpc_handle* h, double* tracking)
 {

@@ -209,3 +209,128 @@ __global__ void __launch_bounds__(128) nmpc_plan_refs_kernel(PlannerArgs a)
     e[8] = 0.0; e[4] = 0.0; e[5] = 0.0; r[4] = 0.0; r[5] = 0.0; e[10] = 0.0; e[11] = 0.0;
     for (int i = 0; i < 12; i++) { a.base_ref[(size_t)b * 12 + i] = r[i]; a.base_ref_e[(size_t)b * 12 + i] = e[i]; }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Raibert contact planner on the device (BASELINE config 4): what LocomotionMPC.optimize does on
+// the host with contact_planner="raibert" --
+//   RaiberContactPlanner.get_locations     contact_planner.py:265-322   one foothold per touch-down of the window,
+//                                                                       held until the foot's next touch-down
+//   compute_base_ref_cnt_restricted        mpc.py:274-315               base references centred on the first / last
+//                                                                       most complete set of planned contacts
+// The reference builds the planner with cache_cnt=False (mpc.py:89): the footholds are a function of the current state
+// only, nothing is carried between ticks.  One CTA per OCP: the windows by all threads, one foot per thread for the
+// footholds, one thread for the references.
+// ---------------------------------------------------------------------------------------------
+struct RaibertParams {
+    double offset_hip_b[NF * 3];     // hip offsets in the base frame (x / y offsets already applied)
+    double stance_ratio[NF];
+    double nominal_period, foot_size, height_offset, gravity;
+};
+
+struct RaibertArgs {
+    const int32_t* i_node;           // [B]
+    const signed char* gait_seq;     // [4][npc]
+    const signed char* peak_seq;     // [4][npc]
+    const signed char* make_seq;     // [4][npc] 1 on the node of the cycle where the foot touches down
+    const double* qv;                // [B][36] Euler state
+    const double* com;               // [B][3]  centre of mass (nmpc_kin0_kernel)
+    const double* v_des;             // [B][3]
+    const double* w_yaw;             // [B]
+    const double* t_cnt;             // [N+1]   round(j * dt_nodes, 3), as the host computes it
+    RaibertParams rp;
+    double nom_height, height_offset;
+    int npc, N, B;
+    double* base_ref; double* base_ref_e;       // [B][12]
+    signed char* cnt; signed char* peak;        // [B][4][N+1]
+    double* loc;                                // [B][4][N+1][3]
+};
+
+// lexicographic order of two [4][3] slabs of contact locations (numpy.unique(axis=1) sorts the nodes this way)
+__device__ __forceinline__ int raibert_slab_cmp(const double* loc, int N1, int ja, int jb)
+{
+    for (int f = 0; f < NF; f++)
+        for (int c = 0; c < 3; c++) {
+            const double x = loc[((size_t)f * N1 + ja) * 3 + c], y = loc[((size_t)f * N1 + jb) * 3 + c];
+            if (x < y) return -1;
+            if (x > y) return 1;
+        }
+    return 0;
+}
+
+__global__ void __launch_bounds__(128) nmpc_plan_raibert_kernel(RaibertArgs a)
+{
+    const int b = blockIdx.x, tid = threadIdx.x, N1 = a.N + 1;
+    const int node = a.i_node[b];
+    for (int e = tid; e < NF * N1; e += 128) {
+        const int f = e / N1, j = e % N1;
+        const int idx = (node % a.npc + j) % a.npc;
+        a.cnt[(size_t)b * NF * N1 + e] = a.gait_seq[f * a.npc + idx];
+        a.peak[(size_t)b * NF * N1 + e] = a.peak_seq[f * a.npc + idx];
+    }
+    double* loc = a.loc + (size_t)b * NF * N1 * 3;
+    const double* vd = a.v_des + (size_t)b * 3;
+    if (tid < NF) {
+        const int f = tid;
+        const double* q = a.qv + (size_t)b * 36;
+        const double* com = a.com + (size_t)b * 3;
+        const double wz = a.w_yaw[b];
+        const double yaw = q[3], cy = cos(yaw), sy = sin(yaw);
+        const double* off = a.rp.offset_hip_b + 3 * f;
+        // R_horizontal = rpyToMatrix(0, 0, yaw): rows x, y applied to the hip offset
+        const double hx = (cy * off[0] + -sy * off[1]) + 0.0 * off[2];
+        const double hy = (sy * off[0] + cy * off[1]) + 0.0 * off[2];
+        const double ratio = a.rp.stance_ratio[f], t_stance = a.rp.nominal_period * ratio;
+        const double com_z = com[2] - a.rp.height_offset;
+        const double k_ang = 0.5 * sqrt(com_z / a.rp.gravity);
+        // cross(k v, (0, 0, w)) = (k v_y w, -k v_x w)
+        const double ax = (k_ang * vd[1]) * wz, ay = -((k_ang * vd[0]) * wz);
+        double px = 0.0, py = 0.0, pz = 0.0;
+        for (int j = 0; j < N1; j++) {
+            const int idx = (node % a.npc + j) % a.npc;
+            if (a.make_seq[f * a.npc + idx] == 1) {
+                const double t = a.t_cnt[j];
+                if (t >= 0.0) {
+                    const double gx = (com[0] + hx) + (vd[0] * t) * (1.0 + ratio);
+                    const double gy = (com[1] + hy) + (vd[1] * t) * (1.0 + ratio);
+                    px = ((gx + 0.1 * (vd[0] - q[18])) + (0.5 * vd[0]) * t_stance) + ax;
+                    py = ((gy + 0.1 * (vd[1] - q[19])) + (0.5 * vd[1]) * t_stance) + ay;
+                    pz = a.rp.foot_size;
+                }
+            }
+            double* o = loc + ((size_t)f * N1 + j) * 3;
+            o[0] = px; o[1] = py; o[2] = pz;
+        }
+    }
+    __syncthreads();
+    if (tid != 127) return;
+    // compute_base_ref_cnt_restricted: nodes with the most feet placed; among them the smallest and the largest slab
+    int best = 0, jmin = -1, jmax = -1;
+    for (int j = 0; j < N1; j++) {
+        int c = 0;
+        for (int f = 0; f < NF; f++) {
+            const double* o = loc + ((size_t)f * N1 + j) * 3;
+            c += (o[0] != 0.0 && o[1] != 0.0 && o[2] != 0.0);
+        }
+        if (c == 0) continue;
+        if (c > best) { best = c; jmin = jmax = j; }
+        else if (c == best) {
+            if (raibert_slab_cmp(loc, N1, j, jmin) < 0) jmin = j;
+            if (raibert_slab_cmp(loc, N1, j, jmax) > 0) jmax = j;
+        }
+    }
+    if (jmin < 0) { jmin = 0; jmax = N1 - 1; }       // nothing planned: first / last node as they are
+    double cf[2], cl[2];
+    for (int c = 0; c < 2; c++) {
+        cf[c] = (((loc[((size_t)0 * N1 + jmin) * 3 + c] + loc[((size_t)1 * N1 + jmin) * 3 + c]) + loc[((size_t)2 * N1 + jmin) * 3 + c]) + loc[((size_t)3 * N1 + jmin) * 3 + c]) / 4.0;
+        cl[c] = (((loc[((size_t)0 * N1 + jmax) * 3 + c] + loc[((size_t)1 * N1 + jmax) * 3 + c]) + loc[((size_t)2 * N1 + jmax) * 3 + c]) + loc[((size_t)3 * N1 + jmax) * 3 + c]) / 4.0;
+    }
+    double* r = a.base_ref + (size_t)b * 12;
+    double* e = a.base_ref_e + (size_t)b * 12;
+    for (int i = 0; i < 12; i++) { r[i] = 0.0; e[i] = 0.0; }
+    const double alpha = 0.35;
+    r[0] = alpha * cf[0] + (1.0 - alpha) * cl[0];
+    r[1] = alpha * cf[1] + (1.0 - alpha) * cl[1];
+    e[0] = cl[0]; e[1] = cl[1];
+    r[2] = a.nom_height + a.height_offset;
+    e[2] = a.nom_height + a.height_offset;
+}

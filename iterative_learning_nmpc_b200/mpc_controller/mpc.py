@@ -343,13 +343,14 @@ class BatchedLocomotionMPC:
     (`BatchedQuadrupedSolver`), one batched plan -> torque call on the device (`nmpc_plan_torques`) for the
     sim steps until the next tick; between ticks the state follows the plan, exactly as in `open_loop`.
 
-    Cyclic contact plans only (the default `ContactPlanner`); states are Euler vectors `[B,18]` (use
+    Contact planners: the cyclic `ContactPlanner` (default) and `contact_planner="raibert"` (Raibert footholds,
+    contact-patch restriction, references centred on the planned contacts), both planned on the device; states are Euler vectors `[B,18]` (use
     `dataset.euler_to_mujoco` / `QuadrupedDynamics.convert_from_mujoco` at the boundary).
     """
 
     def __init__(self, batch: int, path_urdf: Optional[str], feet_frame_names: List[str], robot_name: str,
                  gait_name: str = "trot", joint_ref: Optional[np.ndarray] = None, sim_dt: float = 1.0e-3,
-                 height_offset: float = 0., print_info: bool = False, device: int = 0):
+                 height_offset: float = 0., print_info: bool = False, device: int = 0, contact_planner: str = ""):
         from .utils.solver import BatchedQuadrupedSolver
         self.B = int(batch)
         self.config_gait, self.config_opt, self.config_cost = get_quadruped_config(gait_name, robot_name)
@@ -359,9 +360,23 @@ class BatchedLocomotionMPC:
         self.dt_nodes = self.solver.dt_nodes
         self.replanning_steps = int(1 / (self.config_opt.replanning_freq * sim_dt))
         self.n_interp_plan = round(self.config_opt.time_horizon / sim_dt)
-        self.contact_planner = ContactPlanner(feet_frame_names, self.dt_nodes, self.config_gait)
         nu = 12
         self.joint_ref = np.zeros(nu) if joint_ref is None else np.asarray(joint_ref, dtype=float)[-nu:]
+        self._contact_planner_str = contact_planner.lower()
+        if self._contact_planner_str == "raibert":           # mpc.py:76-90
+            q0 = np.zeros((1, 36))
+            q0[0, 6:18] = self.joint_ref
+            offset_hip_b = np.array(self.solver.handle.kinematics(q0)[0], dtype=float).reshape(4, 3)
+            offset_hip_b[:, -1] = 0.
+            self.contact_planner = RaiberContactPlanner(feet_frame_names, self.dt_nodes, self.config_gait, offset_hip_b,
+                                                        y_offset=0.02, x_offset=0.04, foot_size=0.0085, cache_cnt=False)
+            self.restrict_cnt = True
+        elif self._contact_planner_str in ("", "cyclic"):
+            self.contact_planner = ContactPlanner(feet_frame_names, self.dt_nodes, self.config_gait)
+            self.restrict_cnt = False
+        else:
+            raise NotImplementedError(f"batched contact planner '{contact_planner}' (cyclic and raibert are built)")
+        self.solver.set_contact_restriction(self.restrict_cnt)
         self.Kp, self.Kd = self.config_opt.Kp, self.config_opt.Kd
         self.plan_on_device = True           # False: the host planners + the reference's `init` sequence (same results)
         self.unpack_solution = False         # device planning: keep the solution resident, do not copy 15 KB per rollout back
@@ -437,9 +452,19 @@ class BatchedLocomotionMPC:
             return sol
         cnt = self.contact_planner.get_contacts_batch(node, N1)
         peak = self.contact_planner.get_peaks_batch(node, N1) if self.config_opt.opt_peak else None
-        ref, ref_e = base_ref_vel_tracking(q, self.v_des, self.w_yaw, self.base_ref_vel_tracking,
-                                           self.config_gait.nom_height, self.height_offset, self.config_opt.time_horizon)
-        self.solver.init(node, q, v, ref, ref_e, self.joint_ref, self.config_gait.step_height, cnt, None, peak)
+        loc = None
+        if self.restrict_cnt:
+            # the host planners one rollout at a time, as LocomotionMPC.optimize runs them (the checker of the device path)
+            _, com, _ = self.solver.handle.kinematics(np.concatenate((q, v), axis=1))
+            loc, ref, ref_e = np.zeros((self.B, 4, N1, 3)), np.zeros((self.B, 12)), np.zeros((self.B, 12))
+            for b in range(self.B):
+                self.contact_planner.set_state(q[b, :3], v[b, :3], q[b, 3:6][::-1], com[b], self.v_des[b], self.w_yaw[b])
+                loc[b] = self.contact_planner.get_locations(int(node[b]), N1)
+                ref[b], ref_e[b] = LocomotionMPC.compute_base_ref_cnt_restricted(self, q[b], loc[b])
+        else:
+            ref, ref_e = base_ref_vel_tracking(q, self.v_des, self.w_yaw, self.base_ref_vel_tracking,
+                                               self.config_gait.nom_height, self.height_offset, self.config_opt.time_horizon)
+        self.solver.init(node, q, v, ref, ref_e, self.joint_ref, self.config_gait.step_height, cnt, loc, peak)
         sol = self.solver.solve()
         self.status_log.append(np.array(self.solver.status).copy())
         return sol

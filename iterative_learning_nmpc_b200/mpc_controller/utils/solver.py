@@ -83,7 +83,8 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
         self.states[d.h.name][:] = np.asarray(self.data["x"][d.h.name], dtype=float)[..., None]
         self.inputs[d.a.name][:] = 0.
         weight = 9.81 * self.handle.total_mass
-        act = np.stack([self.params[f.active.name][..., 0, :-1] for f in d.feet], axis=-2)      # [..,4,N]
+        # the planner's mask, before setup_initial_feet_pos forces node 0 into stance (what nmpc_cold_guess sees)
+        act = np.asarray(self._cnt_mask, dtype=float)[..., :-1]                                   # [..,4,N]
         share = weight / np.maximum(act.sum(axis=-2, keepdims=True), 1.0)
         for i, foot in enumerate(d.feet):
             self.inputs[foot.f.name][:] = 0.
@@ -186,6 +187,7 @@ class QuadrupedAcadosSolver(AcadosSolverHelper):
             f"Invalid contact plan shape. Wrong number of optimization nodes. ({cnt_sequence.shape[-1]} vs {n1})"
         assert cnt_sequence.shape[-2] == len(self.feet_frame_names), \
             "Invalid contact plan shape. Wrong number of end effectors."
+        self._cnt_mask = cnt_sequence.copy()
         for i, foot in enumerate(self.dyn.feet):
             seq = cnt_sequence[..., i, :]
             self.params[foot.active.name][..., 0, :] = seq
@@ -372,19 +374,33 @@ class BatchedQuadrupedSolver(QuadrupedAcadosSolver):
     def init_planned(self, i_node, q: np.ndarray, v: np.ndarray, v_des: np.ndarray, w_yaw: np.ndarray,
                      tracking: Optional[np.ndarray], planner, nom_height: float, joint_ref: np.ndarray,
                      step_height: float, advance_steps: int = 0, sim_dt: float = 1.0e-3):
-        """`init` for the cyclic contact planner with the planning step on the device (nmpc_plan_tick): the contact /
+        """`init` with the planning step on the device (nmpc_plan_tick; nmpc_plan_tick_raibert when the contact
+        restriction is on and `planner` is a RaiberContactPlanner): the contact /
         swing windows at every problem's node, the base references (mpc.py:210-272) and the per-node expansion
         (solver.py:153-275) are computed by the GPU from i_node, q, the command and the tracked pose; x0 with its
         momentum, the shift warm start (or the first cold guess) and the stance-foot pinning follow, all resident."""
-        if self.restrict_cnt:
-            raise NotImplementedError("contact restriction needs contact locations: use init()")
         i_node = np.broadcast_to(np.asarray(i_node, dtype=np.int64), self._lead).copy()
         gait_seq, peak_seq = planner.cycle_tables()
         h = self.handle
-        h.plan_tick(i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, self.height_offset,
-                    self.config_opt.time_horizon, joint_ref, step_height, self.config_cost.W_foot_pos_constr_stab,
-                    self.config_opt.opt_peak, advance_steps, sim_dt)
-        h.set_x0(np.concatenate((np.asarray(q, dtype=float), np.asarray(v, dtype=float)), axis=-1))
+        qv = np.concatenate((np.asarray(q, dtype=float), np.asarray(v, dtype=float)), axis=-1)
+        if self.restrict_cnt:
+            # contact_planner="raibert" (mpc.py:76-90, 332-341): footholds and the contact-restricted references too
+            if not hasattr(planner, "offset_hip_b") or getattr(planner, "cache_cnt", False):
+                raise NotImplementedError("device planning with contact restriction: RaiberContactPlanner, cache_cnt=False")
+            N1 = self.config_opt.n_nodes + 1
+            make_seq = (planner.switch_cnt == 1).astype(np.int8)
+            t_cnt = np.array([round(j * planner.dt_nodes, 3) for j in range(N1)])
+            self.last_cnt_locations = h.plan_tick_raibert(
+                i_node, gait_seq, peak_seq, make_seq, qv, v_des, w_yaw, t_cnt, planner.offset_hip_b,
+                planner.config_gait.stance_ratio, planner.config_gait.nominal_period, planner.foot_size,
+                planner.height_offset, self.config_cost.cnt_radius, nom_height, self.height_offset, joint_ref,
+                step_height, self.config_cost.W_foot_pos_constr_stab, self.config_opt.opt_peak, planner.GRAVITY,
+                want_locations=getattr(self, "want_cnt_locations", False))
+        else:
+            h.plan_tick(i_node, gait_seq, peak_seq, q, v_des, w_yaw, tracking, nom_height, self.height_offset,
+                        self.config_opt.time_horizon, joint_ref, step_height, self.config_cost.W_foot_pos_constr_stab,
+                        self.config_opt.opt_peak, advance_steps, sim_dt)
+        h.set_x0(qv)
         if self.config_opt.warm_start_sol and self._has_solution:
             h.shift_warm_start((i_node - self.last_node).astype(np.int32), False)
         else:

@@ -114,6 +114,57 @@ class OracleHandle:
         self.set_params(P.pack_params(cnt, cost, height_offset, peak, False, None, opt_peak))
         self.last_plan = dict(base_ref=ref, base_ref_e=ref_e, cnt=cnt, peak=peak)
 
+    def plan_tick_raibert(self, i_node, gait_seq, peak_seq, make_seq, qv, v_des, w_yaw, t_cnt, offset_hip_b,
+                          stance_ratio, nominal_period, foot_size, planner_height_offset, cnt_radius, nom_height,
+                          height_offset, joint_ref, step_height, p_gain, opt_peak=True, gravity=9.81,
+                          want_locations=False):
+        """Checker for nmpc_plan_tick_raibert: Raibert footholds (contact_planner.py:265-322, cache_cnt=False) and the
+        contact-restricted references (mpc.py:274-315) restated with plain loops from the tables the device receives,
+        then the host packing of `init`."""
+        from iterative_learning_nmpc_b200 import problem as P
+        from iterative_learning_nmpc_b200.mpc_controller.config.quadruped.utils import get_quadruped_config
+        B, N1 = self.B, self.N + 1
+        gs, ps, ms = np.asarray(gait_seq), np.asarray(peak_seq), np.asarray(make_seq)
+        npc = gs.shape[1]
+        node = np.asarray(i_node, dtype=np.int64).reshape(B)
+        qv = np.asarray(qv, dtype=float).reshape(B, 36)
+        v_des = np.broadcast_to(np.asarray(v_des, dtype=float), (B, 3))
+        w_yaw = np.broadcast_to(np.asarray(w_yaw, dtype=float), (B,))
+        off = np.asarray(offset_hip_b, dtype=float).reshape(4, 3)
+        _, com, _ = O.kinematics(qv)
+        idx = (node[:, None] % npc + np.arange(N1)[None, :]) % npc
+        cnt, peak, make = (np.moveaxis(t[:, idx], 0, 1) for t in (gs, ps, ms))
+        loc, ref, ref_e = np.zeros((B, 4, N1, 3)), np.zeros((B, 12)), np.zeros((B, 12))
+        for b in range(B):
+            yaw, vt = qv[b, 3], v_des[b, :2]
+            Rz = np.array([[np.cos(yaw), -np.sin(yaw)], [np.sin(yaw), np.cos(yaw)]])
+            k = 0.5 * np.sqrt((com[b, 2] - planner_height_offset) / gravity)
+            ang = np.array([k * vt[1] * w_yaw[b], -k * vt[0] * w_yaw[b]])
+            for f in range(4):
+                for j in range(N1):
+                    if make[b, f, j] == 1 and t_cnt[j] >= 0:
+                        hip = com[b, :2] + Rz @ off[f, :2] + vt * t_cnt[j] * (1 + stance_ratio[f])
+                        xy = hip + 0.1 * (vt - qv[b, 18:20]) + 0.5 * vt * (nominal_period * stance_ratio[f]) + ang
+                        loc[b, f, j:] = (xy[0], xy[1], foot_size)
+            full = [(int((loc[b, :, j] != 0).all(-1).sum()), tuple(loc[b, :, j].reshape(-1))) for j in range(N1)]
+            best = max(c for c, _ in full)
+            if best > 0:
+                slabs = sorted(sl for c, sl in full if c == best)
+                c_first, c_last = (np.array(sl).reshape(4, 3).mean(0) for sl in (slabs[0], slabs[-1]))
+            else:
+                c_first, c_last = loc[b, :, 0].mean(0), loc[b, :, -1].mean(0)
+            ref[b, :2] = 0.35 * c_first[:2] + 0.65 * c_last[:2]
+            ref_e[b, :2] = c_last[:2]
+            ref[b, 2] = ref_e[b, 2] = nom_height + height_offset
+        _, _, cost = get_quadruped_config("trot", "go2")
+        cost.W_foot_pos_constr_stab = np.asarray(p_gain, dtype=float)
+        cost.cnt_radius = float(cnt_radius)
+        yref, yref_e = P.pack_reference(ref, ref_e, joint_ref, step_height, self.N, loc)
+        self._s.set_yref(yref, yref_e)
+        self.set_params(P.pack_params(cnt, cost, height_offset, peak, True, loc, opt_peak))
+        self.last_plan = dict(base_ref=ref, base_ref_e=ref_e, cnt=cnt, peak=peak, loc=loc)
+        return loc if want_locations else None
+
     def get_tracking(self):
         return self._tracking.copy()
 

@@ -229,3 +229,37 @@ def test_batched_locomotion_mpc_matches_unbatched_rollouts(backend):
         q_mj, _ = DS.euler_to_mujoco(qs[:, b], vs[:, b])
         err = np.abs(q_mj - single[b]).max()
         assert err < 1e-6, (b, err)
+
+
+def test_batched_raibert_mpc_matches_unbatched_rollouts(backend):
+    """`BatchedLocomotionMPC(contact_planner="raibert")` against `LocomotionMPC(contact_planner="raibert")` run one
+    rollout at a time (mpc.py:76-90, 274-315, 332-341), both on the oracle backend: the batched tick plans through
+    `plan_tick_raibert` (here the checker's loop restatement), the unbatched one through RaiberContactPlanner and
+    compute_base_ref_cnt_restricted as the reference does."""
+    from iterative_learning_nmpc_b200 import dataset as DS
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import BatchedLocomotionMPC, LocomotionMPC
+    from iterative_learning_nmpc_b200.mpc_controller.utils.dynamics import QuadrupedDynamics
+    B, T = 2, 0.0415
+    rng = np.random.default_rng(9)
+    q0 = np.tile(P.nominal_state(WL.STAND_HEIGHT)[:18], (B, 1)); q0[:, 6:] += rng.uniform(-0.05, 0.05, (B, 12))
+    q0[1, 3] = 0.4
+    v0 = np.zeros((B, 18))
+    cmds = np.array([[0.15, 0.0, 0.0], [0.1, 0.05, 0.0]])
+    single = []
+    for b in range(B):
+        mpc = LocomotionMPC(None, FEET, "go2", gait_name="trot", print_info=False, solve_async=False,
+                            joint_ref=P.GO2_JOINT_HOME, contact_planner="raibert")
+        mpc.solver.cold_guess = "hold"
+        mpc.set_command(cmds[b], 0.2)
+        q_mj, v_mj = QuadrupedDynamics.convert_to_mujoco(q0[b], v0[b])
+        single.append(mpc.open_loop(q_mj, v_mj, T))
+    for on_device in (True, False):
+        bm = BatchedLocomotionMPC(B, None, FEET, "go2", gait_name="trot", joint_ref=P.GO2_JOINT_HOME,
+                                  contact_planner="raibert")
+        bm.plan_on_device = on_device
+        bm.set_command(cmds, 0.2)
+        qs, vs = bm.open_loop(q0, v0, T)[:2]
+        for b in range(B):
+            q_mj, _ = DS.euler_to_mujoco(qs[:, b], vs[:, b])
+            err = np.abs(q_mj - single[b]).max()
+            assert err < 1e-6, (on_device, b, err)

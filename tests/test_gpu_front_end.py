@@ -190,6 +190,100 @@ def test_device_planners_match_host_planners():
     assert np.abs(h["yref"]).max() > 0.1
 
 
+def test_device_raibert_planner_matches_host_planner():
+    """nmpc_plan_tick_raibert (update_pin's CoM, the gait windows, RaiberContactPlanner.get_locations with
+    cache_cnt=False, contact_planner.py:265-322, and compute_base_ref_cnt_restricted, mpc.py:274-315, on the device)
+    against the host planners run problem by problem and fed to nmpc_init_tick: bit-exact masks and restriction
+    flags, footholds and references within 1e-12.  Mixed nodes (0, 1, 2 and 3 touch-downs per foot in the window,
+    windows that start on a touch-down), yawed bases, nonzero yaw-rate commands."""
+    from iterative_learning_nmpc_b200 import problem as P
+    from iterative_learning_nmpc_b200._lib import default_opts
+    from iterative_learning_nmpc_b200.core import NmpcSolver
+    from iterative_learning_nmpc_b200.mpc_controller.config.quadruped.utils import get_quadruped_config
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import LocomotionMPC
+    from iterative_learning_nmpc_b200.mpc_controller.utils.contact_planner import RaiberContactPlanner
+    B, N = 131, 25
+    rng = np.random.default_rng(5)
+    for gait_name in ("trot", "crawl", "jump"):       # jump: 1250 nodes per cycle, most windows plan no touch-down at all
+        busy = gait_name != "jump"
+        gait, opt, cost = get_quadruped_config(gait_name, "go2", fallback_to_trot_cost=True, fix_swapped_heights=True)
+        dev, host = NmpcSolver(B, default_opts()), NmpcSolver(B, default_opts())
+        q0 = np.zeros((1, 36)); q0[0, 6:18] = P.GO2_JOINT_HOME
+        hip = np.array(dev.kinematics(q0)[0], dtype=float).reshape(4, 3); hip[:, 2] = 0.0
+        planner = RaiberContactPlanner(FEET, 0.04, gait, hip.copy(), y_offset=0.02, x_offset=0.04, foot_size=0.0085,
+                                       cache_cnt=False)
+        gs, ps = planner.cycle_tables()
+        ms = (planner.switch_cnt == 1).astype(np.int8)
+        node = rng.integers(0, 300, B); node[:8] = np.arange(8)
+        qv = np.tile(P.nominal_state(0.3), (B, 1)) + rng.normal(0, 0.2, (B, 36))
+        qv[:, 3] = rng.uniform(-3.0, 3.0, B)
+        qv[:, 2] = rng.uniform(0.15, 0.45, B)                  # the heuristic takes sqrt(com_z / g)
+        v_des = rng.uniform(-0.4, 0.4, (B, 3)); v_des[5] = 0.0
+        w_yaw = rng.uniform(-0.5, 0.5, B)
+        t_cnt = np.array([round(j * 0.04, 3) for j in range(N + 1)])
+        loc_d = dev.plan_tick_raibert(node, gs, ps, ms, qv, v_des, w_yaw, t_cnt, planner.offset_hip_b, gait.stance_ratio,
+                                      gait.nominal_period, planner.foot_size, planner.height_offset, cost.cnt_radius,
+                                      gait.nom_height, 0.01, P.GO2_JOINT_HOME, gait.step_height,
+                                      cost.W_foot_pos_constr_stab, True, want_locations=True)
+        _, com, _ = host.kinematics(qv)
+        loc = np.zeros((B, 4, N + 1, 3)); ref = np.zeros((B, 12)); ref_e = np.zeros((B, 12))
+        cnt, peak = planner.get_contacts_batch(node, N + 1), planner.get_peaks_batch(node, N + 1)
+
+        class _Cfg:             # what compute_base_ref_cnt_restricted reads from the controller
+            config_gait, height_offset = gait, 0.01
+        for b in range(B):
+            planner.set_state(qv[b, :3], qv[b, 18:21], qv[b, 3:6][::-1], com[b], v_des[b], w_yaw[b])
+            loc[b] = planner.get_locations(int(node[b]), N + 1)
+            ref[b], ref_e[b] = LocomotionMPC.compute_base_ref_cnt_restricted(_Cfg, qv[b, :18], loc[b])
+        n_td = (np.diff((loc != 0).all(-1).astype(int), axis=2) != 0).sum(-1) + (np.diff(loc[..., 0], axis=2) != 0).sum(-1)
+        assert not busy or (n_td.max() >= 2 and (loc[:, :, 0] != 0).any()), "several touch-downs, a window starting on one"
+        assert np.abs(loc_d - loc).max() < 1e-12
+        np.testing.assert_array_equal(loc_d == 0, loc == 0)
+        host.init_tick(ref, ref_e, P.GO2_JOINT_HOME, gait.step_height, cnt, peak, loc, cost.W_foot_pos_constr_stab,
+                       cost.cnt_radius, 0.01, True)
+        d, h = dev.get_problem_data(), host.get_problem_data()
+        pd, ph = d["p"].reshape(B, N + 1, 4, 11), h["p"].reshape(B, N + 1, 4, 11)
+        assert np.abs(pd - ph).max() < 1e-12
+        for col in (P.P_ACTIVE, P.P_RESTRICT, P.P_RADIUS, P.P_PEAK, P.P_GAIN):
+            np.testing.assert_array_equal(pd[..., col], ph[..., col])
+        assert not busy or ph[..., P.P_RESTRICT].sum() > B
+        assert np.abs(d["yref"] - h["yref"]).max() < 1e-12 and np.abs(d["yref_e"] - h["yref_e"]).max() < 1e-12
+        assert not busy or np.abs(h["yref"][..., :2]).max() > 0.05
+
+
+def test_batched_mpc_raibert_device_planning_equals_host_planning(monkeypatch):
+    """BatchedLocomotionMPC(contact_planner="raibert") -- BASELINE config 4's planner -- with the planning step on the
+    device and with the host planners + the reference's `init` sequence: the same rollouts.
+
+    The two paths hand the solver parameters and references that agree to one ulp (5.6e-17, previous test).  The
+    contact-restricted OCP from a standing start is far from converged after 6 IPM iterations (stationarity residual
+    in the hundreds, status MAXITER) and each SQP iteration multiplies such a difference by 1e3..1e5 (measured with
+    tools/dbg_raibert_gpu.py: 2e-11 in x after 1 SQP iteration, 1e-7 after 4, 2e-4 after the reference's 15 of the
+    first tick) -- a property of the truncated SQP, the same in the CPU oracle, not of the planners.  The rollouts
+    are therefore compared with one SQP iteration on the first tick too."""
+    from iterative_learning_nmpc_b200 import problem as P
+    import iterative_learning_nmpc_b200.mpc_controller.mpc as M
+    from iterative_learning_nmpc_b200.mpc_controller.mpc import BatchedLocomotionMPC
+    monkeypatch.setattr(M, "N_SQP_FIRST", 1)
+    B, T = 5, 0.085
+    rng = np.random.default_rng(4)
+    q0 = np.tile(P.nominal_state(WL.STAND_HEIGHT)[:18], (B, 1)); q0[:, 6:] += rng.uniform(-0.05, 0.05, (B, 12))
+    v0 = np.zeros((B, 18))
+    cmds = rng.uniform([0.05, -0.1, 0.0], [0.3, 0.1, 0.0], (B, 3))
+    out = []
+    for on_device in (True, False):
+        bm = BatchedLocomotionMPC(B, None, FEET, "go2", gait_name="trot", joint_ref=P.GO2_JOINT_HOME,
+                                  contact_planner="raibert")
+        assert bm.restrict_cnt and bm.solver.restrict_cnt
+        bm.plan_on_device = on_device
+        bm.reset(reset_solver=False, i_node0=np.arange(B) * 3)
+        bm.set_command(cmds, 0.1)
+        out.append(bm.open_loop(q0, v0, T))
+        assert len(bm.status_log) == 3
+    assert np.isfinite(out[0][0]).all()
+    assert np.abs(out[0][0] - out[1][0]).max() < 1e-8 and np.abs(out[0][1] - out[1][1]).max() < 1e-7
+
+
 def test_batched_mpc_device_planning_equals_host_planning():
     """BatchedLocomotionMPC with the planning step on the device (default) and with the host planners + the reference's
     `init` sequence: the same rollouts."""
