@@ -57,6 +57,7 @@ extern "C" {
 #define NMPC_ENOSYS (-2)   /* option not available in this build */
 #define NMPC_ENODEV (-3)   /* no CUDA device / wrong architecture */
 #define NMPC_ENOMEM (-4)
+#define NMPC_E2BIG (-5)    /* request beyond a fixed capacity (nmpc_kinematics_static: n > NMPC_STATIC_MAX_N) */
 
 /* per-problem solver status, acados numbering */
 #define NMPC_STATUS_SUCCESS 0
@@ -267,6 +268,23 @@ int nmpc_get_qp_step(nmpc_handle* h, double* dz);
  * 101-107; pin.centerOfMass at mpc.py:339) ---------------------------------------------- */
 /* qv [n,36] -> feet [n,4,3], com [n,3], hg [n,6]; outputs may be NULL. */
 int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, double* feet, double* com, double* hg);
+
+/* Allocation-free variant of nmpc_kinematics.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  No handle: it runs on the CURRENT device, on `stream` (a cudaStream_t; NULL = the
+ * default stream), and calls no cudaMalloc / cudaFree / allocating library routine.  Its staging buffer is a file-scope
+ * device array of NMPC_STATIC_MAX_N instances x 57 doubles (1.78 MiB) that every GPU which loads the library holds
+ * until the process exits; n > NMPC_STATIC_MAX_N is rejected with NMPC_E2BIG and a message on stderr (split the batch,
+ * or use nmpc_kinematics).  The first call on a device resolves the array's device address (cudaGetSymbolAddress):
+ * make that call outside stream capture.  Same arguments and results as nmpc_kinematics: qv [n,36] -> feet [n,4,3],
+ * com [n,3], hg [n,6]; outputs may be NULL; pointers host or device.  Outputs are complete on return (the stream is
+ * synchronised) unless `stream` is being captured.
+ * SHARED STATE: every call on a device uses the same array and finds the previous call's contents in it (nothing has
+ * to start at zero: the kernel overwrites all it reads back).  Calls of one process are serialised by a lock up to
+ * their launch, but two calls whose GPU work overlaps (different streams, or captured graphs replayed concurrently)
+ * RACE on the array: order them. */
+#define NMPC_STATIC_MAX_N 4096
+int nmpc_kinematics_static(const double* qv, int32_t n, double* feet, double* com, double* hg, void* stream);
 
 /* QuadrupedDynamics.id_torques (dynamics.py:136-163): tau [n,12] = rnea(q, v, a)[joints] -
  * sum_feet J_foot(q)^T f.  qva [n,54] = (q_euler | v | a), f [n,12] world-frame contact forces. */

@@ -104,6 +104,7 @@ _SIGS = {
     "nmpc_pack_solution": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_get_qp_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 3),
+    "nmpc_kinematics_static": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 4),
     "nmpc_inverse_dynamics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "nmpc_init_tick": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int32]),
@@ -172,6 +173,7 @@ def ptr(a):
 
 def check(rc: int, what: str) -> None:
     if rc != 0:
-        kind = {-1: "EINVAL", -2: "ENOSYS (option not available in this build)", -3: "ENODEV", -4: "ENOMEM"}.get(
+        kind = {-1: "EINVAL", -2: "ENOSYS (option not available in this build)", -3: "ENODEV", -4: "ENOMEM",
+                -5: "E2BIG (beyond a fixed capacity)"}.get(
             rc, f"cudaError {rc}" if rc > 0 else str(rc))
         raise NmpcError(f"{what} failed: {kind}")

@@ -854,6 +854,56 @@ extern "C" int nmpc_kinematics(nmpc_handle* h, const double* qv, int32_t n, doub
     return (int)cudaGetLastError();
 }
 
+// ---- allocation-free variant of nmpc_kinematics (no reference counterpart)
+// The staging buffer nmpc_kinematics takes from cudaMalloc lives here in a file-scope device array, so this entry point
+// can be called where cudaMalloc cannot: under stream capture, in serving loops, in harnesses that forbid allocation.
+// Layout, in doubles: qv [n][36] | feet [n][12] | com [n][3] | hg [n][6], n <= NMPC_STATIC_MAX_N (57 doubles each).
+// Every GPU that loads this library holds the array (1.78 MiB) until the process exits.  In host code the NAME of the
+// array is a host-side stand-in, not a device address: the address a kernel can use comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+static __device__ __align__(256) double g_static_kin_scratch[(size_t)NMPC_STATIC_MAX_N * 57];
+#define NMPC_MAX_DEVICES 64
+static double* g_static_kin_ptr[NMPC_MAX_DEVICES];      // device address of the array on each device, null until set up
+static std::mutex g_static_kin_mtx;                     // guards the table and serialises the calls of this process
+
+extern "C" int nmpc_kinematics_static(const double* qv, int32_t n, double* feet, double* com, double* hg, void* stream)
+{
+    if (!qv || n <= 0) return NMPC_EINVAL;
+    if (n > NMPC_STATIC_MAX_N) {
+        fprintf(stderr, "nmpc_kinematics_static: n = %d exceeds the static scratch (NMPC_STATIC_MAX_N = %d instances); "
+                        "split the batch or use nmpc_kinematics\n", (int)n, (int)NMPC_STATIC_MAX_N);
+        return NMPC_E2BIG;
+    }
+    std::lock_guard<std::mutex> lock(g_static_kin_mtx);
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NMPC_MAX_DEVICES) return NMPC_ENODEV;
+    if (!g_static_kin_ptr[dev]) {                       // set-up, once per device, that device current
+        double* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_kin_scratch);
+        if (e != cudaSuccess || !p) {
+            fprintf(stderr, "nmpc_kinematics_static: cudaGetSymbolAddress failed on device %d: %s\n", dev, cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : NMPC_ENODEV;
+        }
+        g_static_kin_ptr[dev] = p;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    double* d_in = g_static_kin_ptr[dev];
+    double* d_feet = d_in + (size_t)n * 36;
+    double* d_com = d_feet + (size_t)n * 12;
+    double* d_hg = d_com + (size_t)n * 3;
+    // nothing has to start at zero: the kernel writes every output of instances 0..n-1 and nothing beyond is read back
+    CK(cudaMemcpyAsync(d_in, qv, (size_t)n * 36 * 8, cudaMemcpyDefault, st));
+    nmpc_kin0_kernel<<<(n + 63) / 64, 64, 0, st>>>(d_in, n, d_feet, d_com, d_hg);
+    if (feet) CK(cudaMemcpyAsync(feet, d_feet, (size_t)n * 12 * 8, cudaMemcpyDefault, st));
+    if (com) CK(cudaMemcpyAsync(com, d_com, (size_t)n * 3 * 8, cudaMemcpyDefault, st));
+    if (hg) CK(cudaMemcpyAsync(hg, d_hg, (size_t)n * 6 * 8, cudaMemcpyDefault, st));
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone)
+        CK(cudaStreamSynchronize(st));                  // outputs complete on return (not under capture: the graph owns the order)
+    return (int)cudaGetLastError();
+}
+
 extern "C" double nmpc_model_mass(void) { return NMPC_MASS; }
 
 extern "C" int nmpc_inverse_dynamics(nmpc_handle* h, const double* qva, const double* f, int32_t n, double* tau)
