@@ -65,6 +65,20 @@ ALGO_FLOP_PER_IPM_ITER = 18.0e6
 FP64_PEAK_TFLOPS = 37.0                  # B200 nominal FP64 (vector = tensor path), no measured figure on this pool
 
 
+def launch_plan(Bl: int) -> str:
+    """How run_qp_fused (csrc/nmpc_abi.cu) sends one QP of a chunk of Bl OCPs to the GPU: full waves of 4 CTAs per SM, then
+    the rest with the residency capped so that it spreads over all SMs.  `launch_ms` is the sum over these launches."""
+    if os.environ.get("NMPC_WAVE_PLAN", "1") == "0":
+        return f"1 launch of {Bl} CTAs"
+    import torch
+    n_sm = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+    full, rest = divmod(Bl, 4 * n_sm)
+    if rest == 0 and full > 0:
+        full, rest = full - 1, 4 * n_sm
+    parts = ([f"{full} x {4 * n_sm} CTAs at 4 per SM"] if full else []) + [f"{rest} CTAs at {-(-rest // n_sm)} per SM"]
+    return " + ".join(parts) + " (one launch each; launch_ms is their sum)"
+
+
 def ocps_per_launch(B: int) -> float:
     """The QP workspace is chunked (NMPC_CHUNK, default 4096 OCPs): a launch covers one chunk."""
     chunk = int(os.environ.get("NMPC_CHUNK", "4096"))
@@ -555,6 +569,7 @@ def main() -> None:
                 "algorithmic_bytes": "SURVEY.md 8(d): (11.2k read + 2 x 5.3k factor) doubles per stage per IPM iteration x 26 stages "
                                      "x 8 B = 4.53 MB per IPM iteration per OCP, x mean IPM iterations x OCPs per launch",
                 "algorithmic_bytes_per_launch": algo, "launch_ms": ms_l,
+                "launch_plan": launch_plan(int(round(Bl))),
                 "fp64_flop_frac": (flop / (ms_l * 1e-3) / (FP64_PEAK_TFLOPS * 1e12)) if flop else None,
                 "fp64_peak_tflops_nominal": FP64_PEAK_TFLOPS,
                 "whole_solve_algorithmic_bytes": n_sqp * (ALGO_BYTES_PER_LINEARISATION + n_ipm * ALGO_BYTES_PER_IPM_ITER) + ALGO_IO_BYTES_PER_SOLVE,

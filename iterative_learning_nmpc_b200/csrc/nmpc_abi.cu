@@ -29,6 +29,7 @@
 struct nmpc_handle {
     nmpc_opts o;
     int B, N, device, Bc;        // Bc: problems per chunk of QP workspace
+    int n_sm, wave_plan;         // SMs of the device; 1: the fused QP kernel is launched wave by wave (run_qp_fused)
     cudaStream_t stream;
     long long launches;      // kernels launched on `stream` (guarded by mtx)
     long long ulaunches;     // kernels launched on `ustream` (guarded by umtx)
@@ -125,6 +126,8 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
 
     nmpc_handle* h = (nmpc_handle*)calloc(1, sizeof(nmpc_handle));
     h->o = *o; h->B = batch; h->N = o->n_nodes; h->device = device;
+    h->n_sm = prop.multiProcessorCount; h->wave_plan = 1;
+    if (const char* s = getenv("NMPC_WAVE_PLAN")) h->wave_plan = atoi(s) != 0;
     h->ev = new std::vector<cudaEvent_t>(); h->ev_kind = new std::vector<int>();
     h->mtx = new std::mutex(); h->umtx = new std::mutex();
     int cap = 4096;
@@ -146,9 +149,9 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     A_(SR, Bc * (N + 1) * SR_SZ); A_(FR, Bc * (N + 1) * FR_SZ); A_(sr_flag, 1);
 #undef A_
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
+        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_CAP1);
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_BYTES);
+        e = cudaFuncSetAttribute(nmpc_qp_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FQ_SMEM_CAP1);
     if (e == cudaSuccess) {          // the node durations start at their nominal value
         std::vector<double> d(B * N, o->dt_nodes);
         e = cudaMemcpy(h->dtn, d.data(), d.size() * 8, cudaMemcpyHostToDevice);
@@ -659,10 +662,30 @@ static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply)
     f.tol = a.tol; f.dt = h->o.dt_nodes; f.c2 = 0.5 * h->o.dt_nodes * h->o.dt_nodes;
     prof_begin(h, NMPC_PROF_QP_FUSED);
     const bool topt = h->o.enable_time_opt != 0 && a.dx0_ext == nullptr;      // externally supplied QPs have nu = 30
-    if (topt) nmpc_qp_fused_kernel<true><<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
-    else nmpc_qp_fused_kernel<false><<<Bc, FQ_THREADS, FQ_SMEM_BYTES, s>>>(f);
+    // Launch plan.  A CTA's run time hardly depends on how many CTAs share its SM (the kernel is bound by the latency of
+    // one OCP's chain: 3.8 / 4.3 / 4.9 / 5.9 ms with 1 / 2 / 3 / 4 CTAs per SM on config 2), and the hardware refills an SM
+    // as soon as its CTAs retire: in one launch of 1024 CTAs the last 432 land four to an SM on 108 SMs while 40 SMs
+    // idle, and in a long launch the co-resident CTAs drift into different passes and miss the instruction cache.  So
+    // the chunk goes out wave by wave: full waves of 4 CTAs per SM, then the rest with the residency capped (through
+    // the dynamic shared memory size) at the smallest number of CTAs per SM that holds it, spread over all SMs.
+    const int full = 4 * h->n_sm;
+    int off = 0;
+    while (off < Bc) {
+        int n = Bc - off, smem = FQ_SMEM_BYTES;
+        if (h->wave_plan) {
+            if (n > full) n = full;
+            else {
+                const int per_sm = (n + h->n_sm - 1) / h->n_sm;
+                smem = per_sm >= 4 ? FQ_SMEM_BYTES : per_sm == 3 ? FQ_SMEM_CAP3 : per_sm == 2 ? FQ_SMEM_CAP2 : FQ_SMEM_CAP1;
+            }
+        }
+        f.bl0 = off;
+        if (topt) nmpc_qp_fused_kernel<true><<<n, FQ_THREADS, smem, s>>>(f);
+        else nmpc_qp_fused_kernel<false><<<n, FQ_THREADS, smem, s>>>(f);
+        h->launches++;
+        off += n;
+    }
     prof_end(h);
-    h->launches++;
     if (apply) {
         prof_begin(h, NMPC_PROF_QP_OTHER);
         nmpc_qp_apply_sr_kernel<<<Bc, 128, 0, s>>>(a, h->SR, topt ? h->dtn : nullptr, h->lamt, h->qx);

@@ -412,6 +412,7 @@ struct FqArgs {
     const double* dx0_ext; const double* x0; const double* x;
     const int32_t* sqp_done;
     int N, b0, max_iter, warm, cond_pred_corr;   // warm: HPIPM warm_start level 0 / 1 / 2 (see nmpc_b200.h)
+    int bl0;                        // first problem of this launch inside the chunk (a chunk is launched wave by wave)
     double tol, dt, c2;              // c2 = dt^2 / 2
 };
 
@@ -428,6 +429,11 @@ __shared__ __align__(8) uint64_t fq_bars[4];
 
 #define FQ_SMEM_DOUBLES 7096
 #define FQ_SMEM_BYTES (FQ_SMEM_DOUBLES * 8)
+// Dynamic shared memory that caps the number of co-resident CTAs per SM at 3 / 2 / 1 (233472 bytes per SM, 1 KB of it
+// reserved per CTA, ~150 bytes static): the last, partial wave of a launch plan is spread over all SMs with it.
+#define FQ_SMEM_CAP3 (60 * 1024)
+#define FQ_SMEM_CAP2 (80 * 1024)
+#define FQ_SMEM_CAP1 (120 * 1024)
 #define FQ_ISSUER 96                         // the thread that issues the bulk copies of the rings: first lane of warp 3, whose
                                              // lanes have the least work in every pass (thread 0 is on every critical path)
 #define FQ_RED (FQ_SMEM_DOUBLES - 16)        // 16 reduction slots, the same place in every pass
@@ -1599,7 +1605,7 @@ template <bool TOPT>
 __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
 {
     const int tid = threadIdx.x;
-    const int bl = blockIdx.x, b = a.b0 + bl, N = a.N;
+    const int bl = a.bl0 + blockIdx.x, b = a.b0 + bl, N = a.N;
     if (a.sqp_done && a.sqp_done[b]) return;             // finished problems keep their statistics
     if (tid == 0) {
         fq_ctx.SRb = a.SR + (size_t)bl * (N + 1) * SR_SZ;

@@ -280,6 +280,41 @@ def test_batch_is_independent_and_chunking_invariant(oracle_mod, monkeypatch):
     np.testing.assert_array_equal(u0[perm], u2)
 
 
+def test_wave_launch_plan_is_invisible_in_the_results(oracle_mod, monkeypatch):
+    """The fused QP kernel goes out wave by wave (full waves of 4 CTAs per SM, the rest with the residency capped through
+    the dynamic shared memory size; run_qp_fused): a batch of two full waves and a partial one, also cut by the chunking,
+    gives bit-identical results to one launch per chunk (NMPC_WAVE_PLAN=0), with and without time optimisation, and the
+    capped launches (3, 2 and 1 CTAs per SM) run."""
+    import torch
+    NmpcSolver, default_opts = _gpu()
+    n_sm = torch.cuda.get_device_properties(0).multi_processor_count
+    cases = [(8 * n_sm + 2 * n_sm + 5, dict(real_time_it=1), None),          # 2 full waves + 3 per SM
+             (4 * n_sm + n_sm + 9, dict(real_time_it=1), None),              # 1 full wave + 2 per SM
+             (4 * n_sm + 17, dict(real_time_it=0, max_iter=2, enable_time_opt=1), None),      # + 1 per SM, time-opt kernel
+             (700, dict(real_time_it=1), 333)]                               # chunks of 333 | 333 | 34
+    for B, o, chunk in cases:
+        batch = WL.make_batch(B, seed=31)
+        _, _, hg = oracle_mod.kinematics(batch["qv"])
+        out = []
+        for plan in ("1", "0"):
+            monkeypatch.setenv("NMPC_WAVE_PLAN", plan)
+            if chunk:
+                monkeypatch.setenv("NMPC_CHUNK", str(chunk))
+            else:
+                monkeypatch.delenv("NMPC_CHUNK", raising=False)
+            s = NmpcSolver(B, default_opts(**o))
+            WL.load_into(s, batch, hg)
+            st = s.solve()
+            x, u, pi, lam = s.get_solution()
+            out.append((st, x, u, pi, lam))
+            del s
+        for a, b in zip(out[0], out[1]):
+            np.testing.assert_array_equal(a, b)
+        assert np.isfinite(out[0][1]).all() and (out[0][0] != 1).all()
+    monkeypatch.delenv("NMPC_WAVE_PLAN", raising=False)
+    monkeypatch.delenv("NMPC_CHUNK", raising=False)
+
+
 def test_full_size_batch_properties(oracle_mod):
     """BASELINE config 2 at full size (1024 OCPs, SQP_RTI): every problem succeeds, the measured
     state is imposed exactly, the QP residuals the device reports are finite, and a sample of the
