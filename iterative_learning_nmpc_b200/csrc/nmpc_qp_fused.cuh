@@ -923,7 +923,8 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
                     const int ft = (ur0 - IFRC) / 3;
                     const int cofs = IFRC + 3 * ft - uc0;    // first column of the foot inside this tile
                     if (cofs >= 0 && cofs < 6) {
-                        for (int r5 = 0; r5 < 5; r5++) {
+#pragma unroll 1
+                        for (int r5 = 0; r5 < 5; r5++) {                   // rolled: a short body that stays in the instruction cache
                             const double g = Sv[V_GAM + 5 * ft + r5];
                             const double* cf = S + SR_CF + 3 * (5 * ft + r5);
 #pragma unroll
