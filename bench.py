@@ -22,7 +22,8 @@ region, so that every rank -- the dataset writer in particular -- holds the batc
 
   value    whole-job solves/s with the batch resident in HBM, CUDA events on the solver's stream, max over ranks.
   e2e      the same through the C ABI with HOST (pinned) buffers: H2D of every input of
-           `QuadrupedAcadosSolver.init`, solve, (gather,) D2H of the solution and status inside the timed region.
+           `QuadrupedAcadosSolver.init`, solve, (gather,) D2H of the solution (nmpc_set_output: wave by wave, behind the
+           solve) and of the status inside the timed region.
   roofline dominant kernel against the HBM roof with SURVEY.md 8(d)'s numerator: 21.8k doubles per stage per IPM
            iteration x 26 stages x 8 B = 4.53 MB per IPM iteration per OCP; launch time from CUDA events around each
            launch (nmpc_set_profiling); what limits the kernel (`bound`) and the ncu counters that show it.
@@ -67,7 +68,7 @@ FP64_PEAK_TFLOPS = 37.0                  # B200 nominal FP64 (vector = tensor pa
 
 def launch_plan(Bl: int) -> str:
     """How run_qp_fused (csrc/nmpc_abi.cu) sends one QP of a chunk of Bl OCPs to the GPU: full waves of 4 CTAs per SM, then
-    the rest with the residency capped so that it spreads over all SMs.  `launch_ms` is the sum over these launches."""
+    the rest with the residency capped so that it spreads over all SMs.  `launch_ms` is the mean over these launches."""
     if os.environ.get("NMPC_WAVE_PLAN", "1") == "0":
         return f"1 launch of {Bl} CTAs"
     import torch
@@ -76,7 +77,7 @@ def launch_plan(Bl: int) -> str:
     if rest == 0 and full > 0:
         full, rest = full - 1, 4 * n_sm
     parts = ([f"{full} x {4 * n_sm} CTAs at 4 per SM"] if full else []) + [f"{rest} CTAs at {-(-rest // n_sm)} per SM"]
-    return " + ".join(parts) + " (one launch each; launch_ms is their sum)"
+    return " + ".join(parts) + " (one launch each; launch_ms and algorithmic_bytes_per_launch are means over these launches)"
 
 
 def ocps_per_launch(B: int) -> float:
@@ -460,8 +461,9 @@ def main() -> None:
                 if time_gather:
                     g_ev[1].record(stream)
         if sync_out:     # QuadrupedAcadosSolver.solve + parse_sol: status and solution back on the host
+            # x / u reach the pinned host buffers through nmpc_set_output (below): every wave's rows are copied while the
+            # next wave is being solved; reading the status synchronises the solve stream, which waits for those copies
             solver.get_status_into(out_st)
-            solver.get_solution_into(x=out_x, u=out_u)
 
     def barrier():
         torch.cuda.synchronize()
@@ -510,9 +512,13 @@ def main() -> None:
     stats = solver.get_stats()
     st_dev = solver.solve_status()
     # ---- host buffers through the C ABI: e2e ---------------------------------------------------
+    solver.set_output(out_x, out_u)
     for _ in range(2):
         step(host, True)
     ms_e2e, wall_e2e = timed(host, True, args.steps)
+    solver.set_output()
+    xs_chk, us_chk, _, _ = solver.get_solution(duals=False)      # the streamed copies are the solver's final iterate
+    assert np.array_equal(out_x.numpy(), xs_chk) and np.array_equal(out_u.numpy(), us_chk), "streamed output differs"
     clk = clocks.stop()
     status_counts = {int(k): int(v) for k, v in zip(*np.unique(st_dev[:max(n_real, 1)], return_counts=True))}
     sqp_hist = np.bincount(stats["sqp_iter"][:max(n_real, 1)], minlength=2).tolist()

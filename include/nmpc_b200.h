@@ -250,6 +250,14 @@ int nmpc_synchronize(nmpc_handle* h);
 /* x [B,N+1,42], u [B,N,30], pi [B,N,42] (multiplier of x_{k+1} = phi(x_k,u_k)),
  * lam [B,N+1,84] (lower | upper multipliers of g).  Any pointer may be NULL. */
 int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* pi, double* lam);
+/* parse_sol hidden behind the solve (solver.py:397-429: `solve` = solver call + parse_sol): destinations x [B,N+1,42] and
+ * u [B,N,30] (either may be NULL; NULL, NULL switches it off) that every following nmpc_solve fills with the final
+ * iterate.  The QP kernel is launched wave by wave; as soon as a wave's last SQP step is applied its rows are copied,
+ * on a separate copy stream, while the next wave is still being solved.  The copies are complete when the solve stream
+ * is: after nmpc_solve with status != NULL, nmpc_get_status, nmpc_synchronize.  For host destinations use pinned memory
+ * (pageable memory works but the copies then block the host).  The buffers must stay valid until nmpc_set_output is
+ * called again or the handle is destroyed. */
+int nmpc_set_output(nmpc_handle* h, double* x, double* u);
 /* dt_node_sol (solver.py:423-427): dt [B,N] -- dt_nodes everywhere unless enable_time_opt -- and the multipliers of
  * dt_min <= dt <= dt_max, lam_dt [B,N,2] (lower | upper).  Either pointer may be NULL. */
 int nmpc_get_dt(nmpc_handle* h, double* dt, double* lam_dt);

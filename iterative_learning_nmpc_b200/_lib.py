@@ -101,6 +101,7 @@ _SIGS = {
     "nmpc_get_solution": (C.c_int, [C.c_void_p] + [C.c_void_p] * 4),
     "nmpc_get_stats": (C.c_int, [C.c_void_p, C.POINTER(NmpcStats)]),
     "nmpc_get_status": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nmpc_set_output": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "nmpc_pack_solution": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_get_qp_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nmpc_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 3),

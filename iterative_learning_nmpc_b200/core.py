@@ -296,6 +296,19 @@ class NmpcSolver:
     def get_solution_into(self, x=None, u=None, pi=None, lam=None):
         check(self.lib.nmpc_get_solution(self._h, ptr(x), ptr(u), ptr(pi), ptr(lam)), "nmpc_get_solution")
 
+    def set_output(self, x=None, u=None):
+        """Destinations (pinned host or CUDA fp64 tensors / arrays, x [B,N+1,42], u [B,N,30]) that every following
+        `solve` fills with the final iterate, wave by wave, while the next wave is still being solved
+        (nmpc_set_output).  Complete once the solve stream is synchronised (`get_status_into`, `synchronize`).  The
+        solver keeps a reference to the buffers; `set_output()` switches the streaming off."""
+        B, N = self.B, self.N
+        for t, n in ((x, B * (N + 1) * NX), (u, B * N * NU)):
+            if t is not None:
+                numel = t.numel() if hasattr(t, "numel") else t.size
+                assert numel == n, "output buffer of the wrong size"
+        self._out_refs = (x, u)
+        check(self.lib.nmpc_set_output(self._h, ptr(x), ptr(u)), "nmpc_set_output")
+
     def get_status_into(self, status):
         """Per-problem status of the last solve into an int32 array / tensor (host or device)."""
         check(self.lib.nmpc_get_status(self._h, ptr(status)), "nmpc_get_status")

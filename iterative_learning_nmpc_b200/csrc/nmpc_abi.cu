@@ -30,6 +30,12 @@ struct nmpc_handle {
     nmpc_opts o;
     int B, N, device, Bc;        // Bc: problems per chunk of QP workspace
     int n_sm, wave_plan;         // SMs of the device; 1: the fused QP kernel is launched wave by wave (run_qp_fused)
+    // nmpc_set_output: host (or device) destinations the final x / u of every wave are copied to, on `cstream`, while the
+    // next wave is still being solved
+    double *out_x, *out_u;
+    cudaStream_t cstream;
+    cudaEvent_t ev_wave, ev_copied;
+    int out_pending;             // copies enqueued on cstream that the solve stream has not been made to wait for yet
     cudaStream_t stream;
     long long launches;      // kernels launched on `stream` (guarded by mtx)
     long long ulaunches;     // kernels launched on `ustream` (guarded by umtx)
@@ -136,6 +142,9 @@ extern "C" nmpc_handle* nmpc_create(const nmpc_opts* o, int32_t batch, int32_t d
     const size_t B = batch, N = h->N, Bc = h->Bc;
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->ustream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->cstream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_wave, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming);
 #define A_(ptr, n) if (e == cudaSuccess) e = dalloc(&h->ptr, (n))
     A_(x, B * (N + 1) * NX); A_(u, B * N * NU); A_(pi, B * N * NX); A_(lam, B * (N + 1) * 2 * NG);
     A_(x0, B * NX); A_(p, B * (N + 1) * NPAR); A_(yref, B * N * NY); A_(yref_e, B * NYE);
@@ -178,6 +187,9 @@ extern "C" void nmpc_destroy(nmpc_handle* h)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->ustream) cudaStreamDestroy(h->ustream);
+    if (h->cstream) cudaStreamDestroy(h->cstream);
+    if (h->ev_wave) cudaEventDestroy(h->ev_wave);
+    if (h->ev_copied) cudaEventDestroy(h->ev_copied);
     delete h->mtx; delete h->umtx;
     if (h->ev) { for (cudaEvent_t e : *h->ev) cudaEventDestroy(e); delete h->ev; }
     delete h->ev_kind;
@@ -649,7 +661,7 @@ static QpArgs qp_args(nmpc_handle* h, int b0)
 }
 
 // The product path: ONE fused kernel per QP (nmpc_qp_fused.cuh) on the stage records the linearisation wrote.
-static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply)
+static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply, bool final_iterate = false)
 {
     const int N = h->N;
     cudaStream_t s = h->stream;
@@ -659,8 +671,9 @@ static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply)
     f.dx0_ext = a.dx0_ext; f.x0 = a.x0;
     f.x = a.x; f.sqp_done = a.sqp_done; f.N = N; f.b0 = a.b0; f.max_iter = a.max_iter; f.warm = a.warm;
     f.cond_pred_corr = a.cond_pred_corr;
+    f.apply = apply ? 1 : 0; f.sx = a.x; f.su = a.u; f.spi = a.pi; f.slam = a.lam; f.sqp_iter = a.sqp_iter;
+    f.dtn = h->dtn; f.lamt = h->lamt;
     f.tol = a.tol; f.dt = h->o.dt_nodes; f.c2 = 0.5 * h->o.dt_nodes * h->o.dt_nodes;
-    prof_begin(h, NMPC_PROF_QP_FUSED);
     const bool topt = h->o.enable_time_opt != 0 && a.dx0_ext == nullptr;      // externally supplied QPs have nu = 30
     // Launch plan.  A CTA's run time hardly depends on how many CTAs share its SM (the kernel is bound by the latency of
     // one OCP's chain: 3.8 / 4.3 / 4.9 / 5.9 ms with 1 / 2 / 3 / 4 CTAs per SM on config 2), and the hardware refills an SM
@@ -680,17 +693,23 @@ static void run_qp_fused(nmpc_handle* h, QpArgs a, int Bc, bool apply)
             }
         }
         f.bl0 = off;
+        prof_begin(h, NMPC_PROF_QP_FUSED);
         if (topt) nmpc_qp_fused_kernel<true><<<n, FQ_THREADS, smem, s>>>(f);
         else nmpc_qp_fused_kernel<false><<<n, FQ_THREADS, smem, s>>>(f);
-        h->launches++;
-        off += n;
-    }
-    prof_end(h);
-    if (apply) {
-        prof_begin(h, NMPC_PROF_QP_OTHER);
-        nmpc_qp_apply_sr_kernel<<<Bc, 128, 0, s>>>(a, h->SR, topt ? h->dtn : nullptr, h->lamt, h->qx);
         prof_end(h);
         h->launches++;
+        if (apply) {             // the kernel has applied the SQP step of this wave: its rows are final
+            if (final_iterate && (h->out_x || h->out_u)) {
+                // nmpc_set_output: this wave's x / u leave on the copy stream while the next wave is being solved
+                const size_t g0 = (size_t)a.b0 + off, nx = (size_t)(N + 1) * NX * 8, nu = (size_t)N * NU * 8;
+                cudaEventRecord(h->ev_wave, s);
+                cudaStreamWaitEvent(h->cstream, h->ev_wave, 0);
+                if (h->out_x) cudaMemcpyAsync((char*)h->out_x + g0 * nx, (const char*)h->x + g0 * nx, n * nx, cudaMemcpyDefault, h->cstream);
+                if (h->out_u) cudaMemcpyAsync((char*)h->out_u + g0 * nu, (const char*)h->u + g0 * nu, n * nu, cudaMemcpyDefault, h->cstream);
+                h->out_pending = 1;
+            }
+        }
+        off += n;
     }
 }
 
@@ -734,10 +753,15 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
             // acados ocp_nlp_sqp / sqp_rti: "(typically) no warm start at first iteration" -- the QP solver's
             // warm_start is forced to 0 for the first QP of a solve unless opts->warm_start_first_qp
             if (it == 0 && !h->o.warm_start_first_qp) qa.warm = 0;
-            run_qp_fused(h, qa, Bc, true);
+            run_qp_fused(h, qa, Bc, true, /*final_iterate=*/rti || it == max_iter - 1);
             nmpc_sqp_post_qp_kernel<<<(Bc + 127) / 128, 128, 0, h->stream>>>(b0, Bc, h->qp_status, h->status, h->done);
             h->launches++;
         }
+    }
+    if (h->out_pending) {        // everything that later waits for the solve stream also waits for the streamed outputs
+        CK(cudaEventRecord(h->ev_copied, h->cstream));
+        CK(cudaStreamWaitEvent(h->stream, h->ev_copied, 0));
+        h->out_pending = 0;
     }
     CK(cudaGetLastError());
     if (status) {
@@ -800,6 +824,19 @@ extern "C" int nmpc_get_solution(nmpc_handle* h, double* x, double* u, double* p
     if (pi) if (int r = d2h(h, pi, h->pi, B * N * NX * 8)) return r;
     if (lam) if (int r = d2h(h, lam, h->lam, B * (N + 1) * 2 * NG * 8)) return r;
     CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// Output streaming: destinations that every following nmpc_solve fills with the final x / u, wave by wave, on a copy
+// stream, while the next wave is still being solved (the D2H copy of parse_sol hidden behind the solve).
+extern "C" int nmpc_set_output(nmpc_handle* h, double* x, double* u)
+{
+    if (!h) return NMPC_EINVAL;
+    LOCK(h);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));            // no solve in flight still refers to the old destinations
+    CK(cudaStreamSynchronize(h->cstream));
+    h->out_x = x; h->out_u = u;
     return 0;
 }
 

@@ -402,37 +402,3 @@ __global__ void __launch_bounds__(RES_THREADS, 4) nmpc_residual_sr_kernel(ResSrA
     }
 }
 
-// ---------------------------------------------------------------------------------------------
-// end of a QP on the fused path: SQP full step (x, u) += dz, multipliers replaced by the QP's
-// (SR twin of nmpc_qp_apply_kernel: the masks come from the stage record)
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) nmpc_qp_apply_sr_kernel(QpArgs a, const double* SR, double* dtn, double* lamt,
-                                                               const double* qx)
-{
-    const int tid = threadIdx.x, bl = blockIdx.x, b = a.b0 + bl, N = a.N;
-    if (a.sqp_done && a.sqp_done[b]) return;
-    if (tid == 0 && a.sqp_iter) a.sqp_iter[b] += 1;
-    const int status = a.qp_status[b];
-    if (!(status == 0 || status == 1)) return;
-    const double* qz = a.qz + (size_t)b * (N + 1) * NZ;
-    const double* qpi = a.qpi + (size_t)b * N * NX;
-    const double* qlam = a.qlam + (size_t)b * (N + 1) * 2 * NG;
-    const double* Sb = SR + (size_t)bl * (N + 1) * SR_SZ;
-    double* x = a.x + (size_t)b * (N + 1) * NX;
-    double* u = a.u + (size_t)b * N * NU;
-    double* pi = a.pi + (size_t)b * N * NX;
-    double* lam = a.lam + (size_t)b * (N + 1) * 2 * NG;
-    for (int i = tid; i < (N + 1) * NX; i += 128) x[i] += qz[(size_t)(i / NX) * NZ + NU + i % NX];
-    for (int i = tid; i < N * NU; i += 128) u[i] += qz[(size_t)(i / NU) * NZ + i % NU];
-    for (int i = tid; i < N * NX; i += 128) pi[i] = qpi[i];
-    for (int i = tid; i < (N + 1) * 2 * NG; i += 128) {
-        const int k = i / (2 * NG), id = i % (2 * NG);
-        lam[i] = Sb[(size_t)k * SR_SZ + SR_D + 2 * NG + id] > 0.5 ? qlam[i] : 0.0;
-    }
-    if (dtn)                                       // enable_time_opt: dt += tau, bound multipliers replaced by the QP's
-        for (int k = tid; k < N; k += 128) {
-            const double* q = qx + ((size_t)b * N + k) * QX_SZ;
-            dtn[(size_t)b * N + k] += q[0];
-            lamt[((size_t)b * N + k) * 2] = q[2]; lamt[((size_t)b * N + k) * 2 + 1] = q[3];
-        }
-}

@@ -413,6 +413,8 @@ struct FqArgs {
     const int32_t* sqp_done;
     int N, b0, max_iter, warm, cond_pred_corr;   // warm: HPIPM warm_start level 0 / 1 / 2 (see nmpc_b200.h)
     int bl0;                        // first problem of this launch inside the chunk (a chunk is launched wave by wave)
+    // SQP full step at the end of the QP (apply != 0): (x, u) += dz, multipliers replaced by the QP's, dt += tau
+    int apply; double* sx; double* su; double* spi; double* slam; int32_t* sqp_iter; double* dtn; double* lamt;
     double tol, dt, c2;              // c2 = dt^2 / 2
 };
 
@@ -1724,5 +1726,34 @@ __global__ void __launch_bounds__(FQ_THREADS, 4) nmpc_qp_fused_kernel(FqArgs a)
         a.qp_iter[b] = iters;
         a.qp_status[b] = status;
         a.qp_ncond[b] = ncond;
+    }
+    // ---- end of a QP inside an SQP iteration: full step (x, u) += dz, multipliers replaced by the QP's; the masks of
+    // the inequality rows come from the stage record.  The last pass R left the iterate in global memory. ----
+    if (a.apply) {
+        __syncthreads();
+        if (tid == 0 && a.sqp_iter) a.sqp_iter[b] += 1;
+        if (status == 0 || status == 1) {
+            const double* qz = fq_ctx.qz;
+            const double* qpi = fq_ctx.qpi;
+            const double* qlam = fq_ctx.qlam;
+            const double* Sb = fq_ctx.SRb;
+            double* x = a.sx + (size_t)b * (N + 1) * NX;
+            double* u = a.su + (size_t)b * N * NU;
+            double* pi = a.spi + (size_t)b * N * NX;
+            double* lam = a.slam + (size_t)b * (N + 1) * 2 * NG;
+            for (int i = tid; i < (N + 1) * NX; i += FQ_THREADS) x[i] += qz[(size_t)(i / NX) * NZ + NU + i % NX];
+            for (int i = tid; i < N * NU; i += FQ_THREADS) u[i] += qz[(size_t)(i / NU) * NZ + i % NU];
+            for (int i = tid; i < N * NX; i += FQ_THREADS) pi[i] = qpi[i];
+            for (int i = tid; i < (N + 1) * 2 * NG; i += FQ_THREADS) {
+                const int k = i / (2 * NG), id = i % (2 * NG);
+                lam[i] = Sb[(size_t)k * SR_SZ + SR_D + 2 * NG + id] > 0.5 ? qlam[i] : 0.0;
+            }
+            if (TOPT)
+                for (int k = tid; k < N; k += FQ_THREADS) {
+                    const double* q = fq_ctx.qx + (size_t)k * QX_SZ;
+                    a.dtn[(size_t)b * N + k] += q[0];
+                    a.lamt[((size_t)b * N + k) * 2] = q[2]; a.lamt[((size_t)b * N + k) * 2 + 1] = q[3];
+                }
+        }
     }
 }

@@ -315,6 +315,44 @@ def test_wave_launch_plan_is_invisible_in_the_results(oracle_mod, monkeypatch):
     monkeypatch.delenv("NMPC_CHUNK", raising=False)
 
 
+def test_output_streaming_delivers_the_final_iterate(oracle_mod, monkeypatch):
+    """nmpc_set_output: x / u copied wave by wave on the copy stream during the solve equal what nmpc_get_solution
+    returns afterwards -- RTI and full SQP (copied in the last iteration), batches of several waves, chunked workspace,
+    pinned host and device destinations; switching it off stops the copies."""
+    import torch
+    NmpcSolver, default_opts = _gpu()
+    n_sm = torch.cuda.get_device_properties(0).multi_processor_count
+    for B, o, chunk, on_device in ((4 * n_sm + 2 * n_sm + 3, dict(real_time_it=1), None, False),
+                                   (4 * n_sm + 40, dict(real_time_it=0, max_iter=3), None, True),
+                                   (500, dict(real_time_it=1), 210, False)):
+        if chunk:
+            monkeypatch.setenv("NMPC_CHUNK", str(chunk))
+        else:
+            monkeypatch.delenv("NMPC_CHUNK", raising=False)
+        batch = WL.make_batch(B, seed=41)
+        _, _, hg = oracle_mod.kinematics(batch["qv"])
+        s = NmpcSolver(B, default_opts(**o))
+        kw = dict(dtype=torch.float64, device="cuda") if on_device else dict(dtype=torch.float64, pin_memory=True)
+        ox = torch.full((B, 26, 42), float("nan"), **kw)
+        ou = torch.full((B, 25, 30), float("nan"), **kw)
+        s.set_output(ox, ou)
+        for rep in range(2):                          # the second solve starts from the first one's iterate
+            if rep == 0:
+                WL.load_into(s, batch, hg)
+            st = s.solve()
+            x, u, _, _ = s.get_solution()
+            np.testing.assert_array_equal(ox.cpu().numpy(), x)
+            np.testing.assert_array_equal(ou.cpu().numpy(), u)
+            assert np.isfinite(x).all() and (st != 1).all()
+        s.set_output()
+        ox.fill_(7.0)
+        s.solve()
+        s.synchronize()
+        assert (ox == 7.0).all()
+        del s
+    monkeypatch.delenv("NMPC_CHUNK", raising=False)
+
+
 def test_full_size_batch_properties(oracle_mod):
     """BASELINE config 2 at full size (1024 OCPs, SQP_RTI): every problem succeeds, the measured
     state is imposed exactly, the QP residuals the device reports are finite, and a sample of the
