@@ -1,6 +1,7 @@
 #!/bin/bash
 # round-2 evidence pass: GPU tests, bench lines of every config, launch list and ncu full capture of the fused kernel
 tag=${1:-r2k}
+timeout 600 python -c "import __graft_entry__ as g; g.smoke(); print(\"smoke ok\")" > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/${tag}_smoke.log
 timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/${tag}_pytest.log
 timeout 600 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"; cut -c1-200 gpurun_out/${tag}_bench.json
 timeout 600 python bench.py --impl reference > gpurun_out/${tag}_bench_reference.json 2>> gpurun_out/${tag}_bench.err; echo "ref rc=$?"; cut -c1-300 gpurun_out/${tag}_bench_reference.json
