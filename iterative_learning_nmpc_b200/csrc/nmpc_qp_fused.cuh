@@ -491,7 +491,9 @@ static_assert(F_V + FV_END <= FQ_RED, "pass F shared memory");
 #define AV_DX 0                              // [2][42]
 #define AV_DZ (AV_DX + 2 * NX)               // 72
 #define AV_X (AV_DZ + NZ)                    // time-opt scalar: d tau
-static_assert(AV_BASE + AV_X + 2 <= FQ_RED, "pass A1 shared memory");
+#define AV_RS (AV_X + 2)                     // 32  right-hand side of the blocked back substitution
+#define AV_XQ (AV_RS + 32)                   // 32  its solution
+static_assert(AV_BASE + AV_XQ + 32 <= FQ_RED, "pass A1 shared memory");
 
 // ---- pass A2: ring of 4 slots ----
 #define B_C 0                                // constraint part of the stage record: SR_CF .. SR_X (1042)
@@ -539,7 +541,8 @@ static_assert(CV_BASE + NG <= FQ_RED, "pass C1 shared memory");
 #define EV_LU (EV_PN + 2 * NX)               // 32
 #define EV_PT (EV_LU + 32)                   // 42  time-opt: p+ after the elimination of dt
 #define EV_X (EV_PT + NX)                    // time-opt scalar s
-static_assert(EV_BASE + EV_X + 2 <= FQ_RED, "pass C2 shared memory");
+#define EV_RS (EV_X + 2)                     // 32  right-hand side of the blocked forward substitution
+static_assert(EV_BASE + EV_RS + 32 <= FQ_RED, "pass C2 shared memory");
 
 // ---- pass D2: ring of 2 slots ----
 #define D_P 0
@@ -1229,27 +1232,36 @@ __device__ __noinline__ uint32_t fq_pass_A1(uint32_t ph)
                 for (int m = 0; m < PB; m++) cf[m] = (m >= li) ? cf[m] : 0.0;
                 // L(i, ll) for i >= ll sits at colb + 6 i (panel-packed, 6 doubles per row)
                 const double* colb = sM + P_OFF(lb) - PB * PB * lb + li;
-                double xs = 0.0;
+                // The lanes exchange through shared memory (two 32-double arrays of this warp) rather than with shuffles:
+                // a block step is 12 loads + 12 multiply-adds instead of 24 shuffles and their lane arithmetic, in a
+                // rolled body that stays in the instruction cache.  Same operations in the same order as before.
+                double* rs = av + AV_RS;
+                double* xq = av + AV_XQ;
+                rs[lane] = rhs;
+                __syncwarp();
+                FMARK(25);
 #pragma unroll 1
                 for (int bk = NU / PB - 1; bk >= 0; bk--) {
-                    double a0 = 0.0, a1 = 0.0;
+                    if (lb == bk) {                          // the lanes of block bk solve it
+                        const double* r6 = rs + PB * bk;
+                        double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-                    for (int m = 0; m < PB; m += 2) {
-                        a0 = fma(cf[m], __shfl_sync(0xffffffffu, rhs, PB * bk + m), a0);
-                        a1 = fma(cf[m + 1], __shfl_sync(0xffffffffu, rhs, PB * bk + m + 1), a1);
+                        for (int m = 0; m < PB; m += 2) { a0 = fma(cf[m], r6[m], a0); a1 = fma(cf[m + 1], r6[m + 1], a1); }
+                        xq[lane] = a0 + a1;
                     }
-                    const double xb = a0 + a1;               // the solution component of the lanes of block bk
-                    xs = (lb == bk) ? xb : xs;
-                    double u0 = 0.0, u1 = 0.0;
+                    __syncwarp();
+                    if (lane < PB * bk) {                    // the lanes before it take the block out of their right-hand side
+                        const double* x6 = xq + PB * bk;
+                        const double* lc = colb + PB * PB * bk;
+                        double u0 = 0.0, u1 = 0.0;
 #pragma unroll
-                    for (int m = 0; m < PB; m += 2) {
-                        const double l0 = (lane < PB * bk) ? colb[PB * (PB * bk + m)] : 0.0;
-                        const double l1 = (lane < PB * bk) ? colb[PB * (PB * bk + m + 1)] : 0.0;
-                        u0 = fma(l0, __shfl_sync(0xffffffffu, xb, PB * bk + m), u0);
-                        u1 = fma(l1, __shfl_sync(0xffffffffu, xb, PB * bk + m + 1), u1);
+                        for (int m = 0; m < PB; m += 2) { u0 = fma(lc[PB * m], x6[m], u0); u1 = fma(lc[PB * (m + 1)], x6[m + 1], u1); }
+                        rs[lane] -= u0 + u1;
                     }
-                    rhs -= u0 + u1;
+                    __syncwarp();
                 }
+                const double xs = xq[lane < NU ? lane : NU - 1];
+                FMARK(26);
                 const double du = -xs;
                 if (lane < NU) dz[lane] = du;
             } else if (tid < 32 + NX) dz[NU + tid - 32] = dx[tid - 32];
@@ -1559,27 +1571,32 @@ __device__ __noinline__ uint32_t fq_pass_C2(uint32_t ph)
 #pragma unroll
                 for (int m = 0; m < PB; m++) cf[m] = (m <= li) ? blk[(m < li ? m : li) * PB + li] : 0.0;
             }
-            double m0 = 0.0;
+            // exchange through shared memory, as in pass A1: the solution goes straight into lus
+            double* rs = ev + EV_RS;
+            rs[tid] = r0;
+            __syncwarp();
 #pragma unroll 1
             for (int bk = 0; bk < NU / PB; bk++) {
-                double a0 = 0.0, a1 = 0.0;
+                if (lb == bk) {
+                    const double* r6 = rs + PB * bk;
+                    double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-                for (int m = 0; m < PB; m += 2) {
-                    a0 = fma(cf[m], __shfl_sync(0xffffffffu, r0, PB * bk + m), a0);
-                    a1 = fma(cf[m + 1], __shfl_sync(0xffffffffu, r0, PB * bk + m + 1), a1);
+                    for (int m = 0; m < PB; m += 2) { a0 = fma(cf[m], r6[m], a0); a1 = fma(cf[m + 1], r6[m + 1], a1); }
+                    lus[tid] = a0 + a1;                      // lanes 30, 31 duplicate lane 29 (same value, their own slot)
                 }
-                const double yb = a0 + a1;
-                m0 = (lb == bk) ? yb : m0;
-                double lv[PB];
-                load6(sM + P_OFF(bk) + (ll - PB * bk) * PB, lv);         // L(ll, 6 bk ..), used by the lanes after the block
-                double u0 = 0.0, u1 = 0.0;
+                __syncwarp();
+                if (lb > bk) {
+                    const double* y6 = lus + PB * bk;
+                    double lv[PB];
+                    load6(sM + P_OFF(bk) + (ll - PB * bk) * PB, lv);         // L(ll, 6 bk ..)
+                    double u0 = 0.0, u1 = 0.0;
 #pragma unroll
-                for (int m = 0; m < PB; m += 2) {
-                    u0 = fma(lv[m], __shfl_sync(0xffffffffu, yb, PB * bk + m), u0);
-                    u1 = fma(lv[m + 1], __shfl_sync(0xffffffffu, yb, PB * bk + m + 1), u1);
+                    for (int m = 0; m < PB; m += 2) { u0 = fma(lv[m], y6[m], u0); u1 = fma(lv[m + 1], y6[m + 1], u1); }
+                    rs[tid] -= u0 + u1;
                 }
-                r0 = (lb > bk) ? r0 - (u0 + u1) : r0;
+                __syncwarp();
             }
+            const double m0 = lus[ll];
             if (tid < NU) { lus[tid] = m0; vk[V_KFF + tid] = m0; }
         }
         __syncthreads();

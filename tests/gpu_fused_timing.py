@@ -18,7 +18,8 @@ s = NmpcSolver(B, default_opts(real_time_it=1, warm_start_qp=0))
 _, _, hg = s.kinematics(batch["qv"])
 names = ["0 iteration bookkeeping", "1 R: update+residuals", "2 F: wait stage", "3 F: pass end", "4 F: w,U,m", "5 F: tile assembly",
          "6 F: panels", "7 F: P, gains K W, store", "8 A1: affine chain", "9 A2: affine bulk", "10 C1: corrector bulk",
-         "11 C2: corrector chain", "12 D1: corrector fwd chain", "13 D2: corrector fwd bulk", "14 A2: issue", "15 A2: wait", "16 A2: Cz", "17 A2: rows", "18 R: wait", "19 R: step 1 update", "20 R: step 2 Cz rb", "21 R: step 3 rows", "22 R: step 4 rg", "23 A1/D1: wait", "24 A1/D1: du chain"]
+         "11 C2: corrector chain", "12 D1: corrector fwd chain", "13 D2: corrector fwd bulk", "14 A2: issue", "15 A2: wait", "16 A2: Cz", "17 A2: rows", "18 R: wait", "19 R: step 1 update", "20 R: step 2 Cz rb", "21 R: step 3 rows", "22 R: step 4 rg", "23 A1/D1: wait", "24 A1/D1: du chain (tail: store, barrier)",
+         "25 A1/D1: rhs = lu + Lxu' dx", "26 A1/D1: blocked back substitution"]
 out = (C.c_ulonglong * 32)()
 for rep in range(2):
     WL.load_into(s, batch, hg)
