@@ -758,6 +758,10 @@ extern "C" int nmpc_solve(nmpc_handle* h, int32_t* status)
             h->launches++;
         }
     }
+    if ((h->out_x || h->out_u) && !h->out_pending) {     // no QP ran (max_iter = 0): the iterate as it is
+        if (h->out_x) CK(cudaMemcpyAsync(h->out_x, h->x, (size_t)B * (N + 1) * NX * 8, cudaMemcpyDefault, h->stream));
+        if (h->out_u) CK(cudaMemcpyAsync(h->out_u, h->u, (size_t)B * N * NU * 8, cudaMemcpyDefault, h->stream));
+    }
     if (h->out_pending) {        // everything that later waits for the solve stream also waits for the streamed outputs
         CK(cudaEventRecord(h->ev_copied, h->cstream));
         CK(cudaStreamWaitEvent(h->stream, h->ev_copied, 0));

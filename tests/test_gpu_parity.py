@@ -351,6 +351,16 @@ def test_output_streaming_delivers_the_final_iterate(oracle_mod, monkeypatch):
         assert (ox == 7.0).all()
         del s
     monkeypatch.delenv("NMPC_CHUNK", raising=False)
+    # max_iter = 0: no QP runs, the registered buffers still receive the (unchanged) iterate
+    B = 9
+    batch = WL.make_batch(B, seed=42)
+    _, _, hg = oracle_mod.kinematics(batch["qv"])
+    s = NmpcSolver(B, default_opts(real_time_it=0, max_iter=0))
+    WL.load_into(s, batch, hg)
+    ox = torch.full((B, 26, 42), float("nan"), dtype=torch.float64, pin_memory=True)
+    s.set_output(ox, None)
+    s.solve()
+    np.testing.assert_array_equal(ox.numpy(), s.get_solution()[0])
 
 
 def test_full_size_batch_properties(oracle_mod):
