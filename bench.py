@@ -565,7 +565,10 @@ def main() -> None:
     try:      # ncu counters of the same kernel from the committed capture (profiles/fused_counters.json: round, commit, batch)
         counters = json.load(open(os.path.join(ROOT, "profiles", "fused_counters.json")))
         if dom == "qp_fused" and args.config == int(counters.get("config", 2)) and counters.get("dram_bytes_per_launch"):
-            traffic = float(counters["dram_bytes_per_launch"]) * Bl / float(counters["batch"])
+            # measured bytes per OCP-QP of the capture x the OCP-QPs one launch of this run covers on average (a chunk goes
+            # out in several launches, one per wave): per launch, like `achieved`
+            traffic = (float(counters["dram_bytes_per_launch"]) / float(counters["batch"])
+                       * B * n_sqp / max(qp_launches_per_step, 1e-9))
     except (OSError, ValueError):
         pass
     frac = achieved / peak
