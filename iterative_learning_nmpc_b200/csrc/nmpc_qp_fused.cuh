@@ -834,51 +834,55 @@ __device__ __noinline__ uint32_t fq_pass_F(uint32_t ph)
         double xa[3][3], ua[3][6];
         const double dt = TOPT ? S[SR_X + SRX_DT] : fq_ctx.dt, c2 = TOPT ? S[SR_X + SRX_C2] : fq_ctx.c2;
         if (tid == 0) bulk_store_wait_read();                // the previous factor record has left sM / sP
-        if (TOPT && !term) {
+        if (!term) {
+            // P+ rb (kept for the corrector) and w = P+ rb + p+.
             // Time-opt: the node duration is eliminated from the stage before anything else.  With b = d x+ / d dt,
             // d = h_tt + Gamma_t + b' P+ b and s = q~_t + b' p+, the rest of the stage sees the cost-to-go
             // P~ = P+ - (P+ b)(P+ b)' / d,  p~ = p+ - (P+ b) s / d, and dt follows in the forward sweeps from
-            // tau = -(s + (P+ b)' (A dx + B du + rb)) / d.
+            // tau = -(s + (P+ b)' (A dx + B du + rb)) / d.  One sweep over the rows of P+ gives P+ b and P+ rb;
+            // P~ rb = P+ rb - (P+ b) ((P+ b)' rb) / d needs no second one.
             const double* bc = S + SR_X + SRX_B;
+            double prb = 0.0, pb = 0.0;
             if (tid < NX) {
                 const double* row = sP + tid * P_LD;
-                double s0 = 0.0, s1 = 0.0;
+                double s0 = 0.0, s1 = 0.0, b0 = 0.0, b1 = 0.0;
 #pragma unroll
-                for (int j = 0; j < NX; j += 2) { s0 = fma(row[j], bc[j], s0); s1 = fma(row[j + 1], bc[j + 1], s1); }
-                const double pb = s0 + s1;
-                fv[FV_PB + tid] = pb; vk[V_X + VX_PB + tid] = pb;
-            }
-            __syncthreads();                                 // also orders wait_read before the writes to sP
-            if (tid < 32) {
-                double d0 = 0.0, s0 = 0.0;
-                for (int j = tid; j < NX; j += 32) { d0 = fma(bc[j], fv[FV_PB + j], d0); s0 = fma(bc[j], fv[FV_PN + j], s0); }
-                d0 = warp_sum(d0); s0 = warp_sum(s0);
-                if (tid == 0) {
-                    const double d = S[SR_X + SRX_H] + fq_smem[F_XV + VX_GAM] + IPM_REG_PRIM + d0;
-                    const double dinv = d > 0.0 ? 1.0 / d : 0.0;
-                    const double sx = fq_smem[F_XV + VX_QT] + s0;
-                    fv[FV_XS] = dinv; fv[FV_XS + 1] = sx;
-                    vk[V_X + VX_DINV] = dinv; vk[V_X + VX_S] = sx;
+                for (int j = 0; j < NX; j += 2) {
+                    s0 += row[j] * Sv[V_RB + j]; s1 += row[j + 1] * Sv[V_RB + j + 1];
+                    if (TOPT) { b0 = fma(row[j], bc[j], b0); b1 = fma(row[j + 1], bc[j + 1], b1); }
                 }
+                prb = s0 + s1;
+                if (TOPT) { pb = b0 + b1; fv[FV_PB + tid] = pb; vk[V_X + VX_PB + tid] = pb; }
             }
-            __syncthreads();
-            {
-                const double dinv = fv[FV_XS], sx = fv[FV_XS + 1];
+            if (TOPT) {
+                __syncthreads();                             // also orders wait_read before the writes to sP
+                if (tid < 32) {
+                    double d0 = 0.0, s0 = 0.0, t0 = 0.0;
+                    for (int j = tid; j < NX; j += 32) {
+                        d0 = fma(bc[j], fv[FV_PB + j], d0); s0 = fma(bc[j], fv[FV_PN + j], s0);
+                        t0 = fma(Sv[V_RB + j], fv[FV_PB + j], t0);
+                    }
+                    d0 = warp_sum(d0); s0 = warp_sum(s0); t0 = warp_sum(t0);
+                    if (tid == 0) {
+                        const double d = S[SR_X + SRX_H] + fq_smem[F_XV + VX_GAM] + IPM_REG_PRIM + d0;
+                        const double dinv = d > 0.0 ? 1.0 / d : 0.0;
+                        const double sx = fq_smem[F_XV + VX_QT] + s0;
+                        fv[FV_XS] = dinv; fv[FV_XS + 1] = sx; fv[FV_XS + 2] = t0;
+                        vk[V_X + VX_DINV] = dinv; vk[V_X + VX_S] = sx;
+                    }
+                }
+                __syncthreads();
+                const double dinv = fv[FV_XS], sx = fv[FV_XS + 1], t0 = fv[FV_XS + 2];
                 for (int e = tid; e < NX * NX; e += FQ_THREADS) {
-                    const int i = e / NX, j = e % NX;
-                    sP[i * P_LD + j] = fma(-fv[FV_PB + i] * dinv, fv[FV_PB + j], sP[i * P_LD + j]);
+                    const int ii = e / NX, jj = e % NX;
+                    sP[ii * P_LD + jj] = fma(-fv[FV_PB + ii] * dinv, fv[FV_PB + jj], sP[ii * P_LD + jj]);
                 }
-                if (tid < NX) fv[FV_PN + tid] = fma(-fv[FV_PB + tid], sx * dinv, fv[FV_PN + tid]);
+                if (tid < NX) {
+                    fv[FV_PN + tid] = fma(-pb, sx * dinv, fv[FV_PN + tid]);
+                    prb = fma(-pb, t0 * dinv, prb);
+                }
             }
-            __syncthreads();
-        }
-        if (!term) {
-            if (tid < NX) {                                  // P+ rb (kept for the corrector), w = P+ rb + p+
-                const double* row = sP + tid * P_LD;
-                double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-                for (int j = 0; j < NX; j += 2) { s0 += row[j] * Sv[V_RB + j]; s1 += row[j + 1] * Sv[V_RB + j + 1]; }
-                const double prb = s0 + s1;
+            if (tid < NX) {
                 vk[V_PRB + tid] = prb;
                 fv[FV_W + tid] = prb + fv[FV_PN + tid];
             }
